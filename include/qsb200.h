@@ -1,0 +1,135 @@
+/*
+ * qsb200.h - C ABI of the B200-native spin-ensemble time-evolution engine (libqsb200.so).
+ *
+ * The reference (TimHarrelson/QuantumSimulations) has no FFI: its hot path is the Python call
+ *     qt.sesolve(H, psi0, t, e_ops=[6 ops], options)        dipolar_ensemble_with_rare.py:653-666
+ * on the operator assembled by build_hamiltonian_rare()     dipolar_ensemble_with_rare.py:453-588.
+ * These entry points are what a ctypes binding of that call would bind; each one cites the reference
+ * lines it replaces.  Plain pointers and sizes only; no torch / Python types.  All arithmetic is
+ * IEEE float64 / complex128 (interleaved re,im).  Every function returns a qsb_status; on failure
+ * qsb_last_error() holds a message (thread-local).  There is NO CPU fallback: without a CUDA device
+ * every compute entry point fails with QSB_ERR_NO_DEVICE.
+ *
+ * Index convention (reference: qt.tensor ordering, dipolar_ensemble_with_rare.py:43-45): site k of
+ * the reference is BIT n-1-k of the amplitude index; bit value 0 is Iz=+1/2.  Everything in this ABI
+ * is indexed by bit.
+ */
+#ifndef QSB200_H
+#define QSB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QSB_VERSION 100
+#define QSB_MAX_QUBITS 34
+#define QSB_SMALL_MAX_QUBITS 10 /* whole trajectory on-chip (one CTA) up to here */
+#define QSB_NOBS 8
+
+typedef enum {
+  QSB_OK = 0,
+  QSB_ERR_BAD_ARG = 1,
+  QSB_ERR_NSTEPS = 2,         /* > nsteps internal steps inside one output interval (QuTiP: "Excess work") */
+  QSB_ERR_STEP_UNDERFLOW = 3, /* step size fell below 16 ulp of t                                         */
+  QSB_ERR_CUDA = 4,
+  QSB_ERR_OOM = 5,
+  QSB_ERR_NO_DEVICE = 6,
+  QSB_ERR_UNSUPPORTED = 7
+} qsb_status;
+
+/* Integrators.  Both control the local error in the zvode sense: weighted RMS over complex components,
+ * weight 1/(atol + rtol*|y_i|), accept when <= 1 (reference knobs: options["atol"/"rtol"],
+ * dipolar_ensemble_with_rare.py:644-647). */
+typedef enum {
+  QSB_METHOD_DP5 = 0,   /* Dormand-Prince 5(4), FSAL, 6 H-applies per step attempt                          */
+  QSB_METHOD_TAYLOR = 1 /* order-p Taylor pair p(p-1) for the constant-H case, p H-applies per step attempt */
+} qsb_method;
+
+/* Coupling table: H = sum_b h[a][b] I^a_b + sum_{b<c} J[a][b][c] I^a_b I^a_c, a in {x,y,z}, I = sigma/2.
+ * Replaces the 2^N x 2^N CSR operator of build_hamiltonian_rare (dipolar_ensemble_with_rare.py:504-570). */
+typedef struct {
+  int32_t n_qubits;   /* 1 .. QSB_MAX_QUBITS                                                     */
+  const double* h;    /* [3][n]      fields (rad/s)                                              */
+  const double* J;    /* [3][n][n]   symmetric pair couplings (rad/s); diagonal ignored          */
+  uint64_t sea_mask;  /* bits summed into Ix_sea, Iy_sea, Iz_sea  (dipolar_ensemble_with_rare.py:573-575) */
+  uint64_t rare_mask; /* single bit of Iz_R, Ix_R, Iy_R           (dipolar_ensemble_with_rare.py:576-578) */
+} qsb_table;
+
+/* Solver knobs = the reference's options dict (dipolar_ensemble_with_rare.py:639-651). */
+typedef struct {
+  double atol;      /* > 0                                                                          */
+  double rtol;      /* >= 0                                                                         */
+  double max_step;  /* hard cap on h; 0 = none                                                      */
+  int64_t nsteps;   /* max internal steps per output interval (zvode MXSTEP semantics); 0 = no cap  */
+  int32_t method;   /* qsb_method                                                                   */
+  int32_t order;    /* Taylor order p (4..30); ignored for DP5; 0 = default 12                      */
+  double first_step;/* 0 = automatic                                                                */
+} qsb_solver_opts;
+
+typedef struct {
+  int64_t n_accepted;
+  int64_t n_rejected;
+  int64_t n_rhs;     /* H-applies                                              */
+  double last_h;
+  double device_ms;  /* CUDA-event time of the whole evolve on its stream      */
+  int32_t path;      /* 0 = on-chip small-N kernel, 1 = tiled HBM path         */
+  int32_t status;    /* qsb_status of this trajectory (batch calls)            */
+} qsb_stats;
+
+typedef struct qsb_plan qsb_plan;
+
+/* ---- library / device ------------------------------------------------------------------------ */
+int qsb_version(void);
+const char* qsb_last_error(void);
+int qsb_device_count(int* count);
+
+/* ---- plans: one compiled table on one device --------------------------------------------------- */
+/* Replaces build_hamiltonian_rare's operator assembly (dipolar_ensemble_with_rare.py:453-588).       */
+int qsb_plan_create(const qsb_table* table, int device, qsb_plan** plan);
+int qsb_plan_destroy(qsb_plan* plan);
+/* Device bytes the tiled path needs for `method` (state, stages, transform scratch). 0 for n <= 10.  */
+int qsb_plan_workspace_bytes(const qsb_plan* plan, int method, int order, size_t* bytes);
+/* Optional: hand the plan a caller-owned device buffer (e.g. a torch allocation) instead of letting it
+ * cudaMalloc.  Must be >= qsb_plan_workspace_bytes and 256-byte aligned; caller keeps ownership.      */
+int qsb_plan_set_workspace(qsb_plan* plan, void* device_ptr, size_t bytes);
+
+/* ---- the hot path ------------------------------------------------------------------------------ */
+/* Replaces qt.sesolve(H, psi0, t, e_ops, options) + the norm loop (dipolar_ensemble_with_rare.py:653-669).
+ * psi0: computational-basis index (psi0_host == NULL; initial_state_rare, :591-606) or a full host vector
+ * of 2^n complex128.  t_out[0] is the start time.  out_obs is HOST memory, [n_out][QSB_NOBS], columns
+ * Ix_sea, Iy_sea, Iz_sea, Iz_R, Ix_R, Iy_R (all on the output-normalised ket, as QuTiP reports them),
+ * state_norm (norm after that normalisation), raw_norm (the integrator's own norm, which QuTiP drops). */
+int qsb_evolve(qsb_plan* plan, uint64_t psi0_index, const double* psi0_host, int64_t n_out,
+               const double* t_out, const qsb_solver_opts* opts, double* out_obs, qsb_stats* stats);
+
+/* Many independent small trajectories (n <= QSB_SMALL_MAX_QUBITS) in ONE launch, one CTA each: the
+ * sweep's serial loop over detunings x variants (sweep_sea_detuning.py:611, :694-702).  tables[i] may
+ * differ in every field incl. n_qubits.  t_out is [n_traj][n_out] when t_out_per_traj != 0, else
+ * [n_out] shared.  out_obs: [n_traj][n_out][QSB_NOBS] host.  opts/stats: [n_traj].                   */
+int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
+                     const double* t_out, int32_t t_out_per_traj, const qsb_solver_opts* opts,
+                     double* out_obs, qsb_stats* stats, int device);
+
+/* ---- pieces of the path, exposed for parity tests and the benchmark ---------------------------- */
+/* out = H psi on host vectors of 2^n complex128 (one H-apply through the same kernels evolve uses).  */
+int qsb_apply_h(qsb_plan* plan, const double* psi_host, double* out_host);
+/* Stepping session with the state resident in HBM (tiled path, n > QSB_SMALL_MAX_QUBITS).            */
+int qsb_session_begin(qsb_plan* plan, uint64_t psi0_index, const double* psi0_host, double t0,
+                      const qsb_solver_opts* opts);
+/* Advance exactly n_attempts step attempts (accepted or rejected) - the benchmark's unit of work.
+ * device_ms = CUDA-event time on the plan's stream; happly_ms = summed event time of the H-apply
+ * kernels only (0 when timing of sub-ranges is off).                                                 */
+int qsb_session_step(qsb_plan* plan, int64_t n_attempts, double* t_now, qsb_stats* stats, double* device_ms);
+/* Observables of the current state, [QSB_NOBS] host.                                                 */
+int qsb_session_observe(qsb_plan* plan, double* obs);
+/* Copy the current state to host (2^n complex128).                                                   */
+int qsb_session_state(qsb_plan* plan, double* psi_host);
+int qsb_session_end(qsb_plan* plan);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QSB200_H */

@@ -71,6 +71,10 @@ def case_list(ref):
     # reference-equivalent integrator (zvode-Adams) at the sweep's tolerances, short window
     cases.append(("q_n7_d050k_center_on_short", "zvode", sweep_point(ref, 6, 50e3, "center_on", 1e-4, 201)))
     cases.append(("q_n7_d050k_center_on_30ms", "zvode", sweep_point(ref, 6, 50e3, "center_on", 3.0e-2, 2000)))
+    cases.append(("x_n7_d050k_center_on_short", "exact", sweep_point(ref, 6, 50e3, "center_on", 1e-4, 201)))
+    # same integrator with tolerances tightened until it is converged (1e-8 at 0.03 s)
+    tight = dataclasses.replace(sweep_point(ref, 6, 50e3, "center_on", 3.0e-2, 2000), solver_atol=1e-14, solver_rtol=1e-13)
+    cases.append(("q_n7_d050k_center_on_30ms_tight", "zvode", tight))
     return cases
 
 

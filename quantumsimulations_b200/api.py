@@ -1,0 +1,177 @@
+"""Reference-facing call surface: ``build_hamiltonian_rare``, ``initial_state_rare``, ``simulate_rare``
+(same names, argument meaning, return shapes and error behaviour as dipolar_ensemble_with_rare.py:453-680)
+plus the additive batch entry point ``simulate_rare_batch``.
+
+QuTiP is not a dependency: instead of ``qt.Qobj`` the builder returns ``SpinOperator`` handles around
+the compiled coupling table (dense / CSR views are available for small N).
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import engine
+from .model import DipolarRareParams
+from .table import SpinTable, compile_table
+
+TRACE_KEYS = ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R")
+
+
+class SpinOperator:
+    """Matrix-free handle for H or one of the six observables (stands in for qt.Qobj, DE:570-587)."""
+
+    def __init__(self, table: SpinTable, kind: str = "H"):
+        self.table = table
+        self.kind = kind
+        self.dims = [[2] * table.n, [2] * table.n]
+        self.shape = (table.dim, table.dim)
+
+    def _as_table(self) -> SpinTable:
+        if self.kind == "H":
+            return self.table
+        t = self.table
+        n = t.n
+        z = np.zeros(n)
+        zz = np.zeros((n, n))
+        fields = {"x": z.copy(), "y": z.copy(), "z": z.copy()}
+        axis = self.kind[1]
+        sites = t.sea_sites if self.kind.endswith("_sea") else [t.rare_site]
+        fields[axis][sites] = 1.0
+        return SpinTable(n, fields["x"], fields["y"], fields["z"], zz, zz.copy(), zz.copy(), t.sea_sites, t.rare_site,
+                         t.psi0_index)
+
+    def apply(self, psi: np.ndarray, device: int = 0) -> np.ndarray:
+        """H @ psi on the GPU (one H-apply through the engine's kernels)."""
+        with engine.Plan(self._as_table(), device) as plan:
+            return plan.apply_h(psi)
+
+    def to_csr(self):
+        """scipy CSR matrix (host, small N only; for inspection and tests - not used by the solver)."""
+        import scipy.sparse as sp
+
+        t = self._as_table()
+        if t.n > 16:
+            raise MemoryError("refusing to materialise a 2^N x 2^N operator for N > 16")
+        bm = t.bit_major()
+        h, J = bm["h"], bm["J"]
+        n, dim = t.n, t.dim
+        x = np.arange(dim, dtype=np.int64)
+        s = np.stack([1.0 - 2.0 * ((x >> b) & 1) for b in range(n)])
+        diag = 0.5 * (h[2] @ s)
+        rows, cols, vals = [], [], []
+        for b in range(n):
+            for c in range(b + 1, n):
+                if J[2, b, c] != 0.0:
+                    diag = diag + 0.25 * J[2, b, c] * s[b] * s[c]
+                if J[0, b, c] != 0.0 or J[1, b, c] != 0.0:
+                    rows.append(x)
+                    cols.append(x ^ (1 << b) ^ (1 << c))
+                    vals.append((0.25 * (J[0, b, c] - s[b] * s[c] * J[1, b, c])).astype(complex))
+            if h[0, b] != 0.0 or h[1, b] != 0.0:
+                rows.append(x)
+                cols.append(x ^ (1 << b))
+                vals.append(0.5 * (h[0, b] - 1j * s[b] * h[1, b]))
+        rows.append(x)
+        cols.append(x)
+        vals.append(diag.astype(complex))
+        m = sp.coo_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(dim, dim)).tocsr()
+        m.eliminate_zeros()
+        return m
+
+    def full(self) -> np.ndarray:
+        return self.to_csr().toarray()
+
+
+def build_hamiltonian_rare(params: DipolarRareParams) -> Tuple[SpinOperator, Dict[str, SpinOperator]]:
+    """(H, {Ix_sea, Iy_sea, Iz_sea, Iz_R, Ix_R, Iy_R}) - compiled, never materialised (DE:453-588)."""
+    table = compile_table(params)
+    obs = {k: SpinOperator(table, k) for k in TRACE_KEYS}
+    return SpinOperator(table, "H"), obs
+
+
+def initial_state_rare(params: DipolarRareParams) -> np.ndarray:
+    """The product state of DE:591-606 as a dense ket (2^N complex128); the engine itself only needs its index."""
+    table = compile_table(params)
+    psi = np.zeros(table.dim, dtype=np.complex128)
+    psi[table.psi0_index] = 1.0
+    return psi
+
+
+def _options_from(params: DipolarRareParams, method: Optional[str]) -> Tuple[engine.SolverOptions, bool]:
+    """Map the reference's solver_* fields (DE:629-651); returns (options, any_override)."""
+    knobs = (params.solver_atol, params.solver_rtol, params.solver_nsteps, params.solver_max_step)
+    override = any(v is not None for v in knobs)
+    o = engine.SolverOptions()
+    if params.solver_atol is not None:
+        o.atol = params.solver_atol
+    if params.solver_rtol is not None:
+        o.rtol = params.solver_rtol
+    if params.solver_nsteps is not None:
+        o.nsteps = int(params.solver_nsteps)
+    if params.solver_max_step is not None:
+        o.max_step = params.solver_max_step
+    o.method = method or os.environ.get("QSB200_METHOD", "dp5")
+    o.order = int(os.environ.get("QSB200_TAYLOR_ORDER", "0"))
+    return o, override
+
+
+def _check_grid(params: DipolarRareParams) -> np.ndarray:
+    if params.steps < 2 or params.t_final <= 0.0:
+        raise ValueError("Bad time grid: steps >= 2 and t_final > 0.")
+    return np.linspace(0.0, params.t_final, params.steps)
+
+
+def _pack(obs: np.ndarray, override: bool, extra: bool) -> Dict[str, np.ndarray]:
+    out = {k: np.ascontiguousarray(obs[:, i]) for i, k in enumerate(TRACE_KEYS)}
+    # DE:669: norms of the stored (output-normalised) states; no states are stored when options is None
+    out["state_norm"] = np.ascontiguousarray(obs[:, 6]) if override else np.array([])
+    if extra:
+        out["raw_norm"] = np.ascontiguousarray(obs[:, 7])
+    return out
+
+
+def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optional[str] = None,
+                  return_stats: bool = False, raw_norm: bool = False):
+    """Time evolution on the B200 engine; returns ``(t, {6 traces + state_norm})`` like DE:611-680.
+
+    ``raw_norm=True`` adds the integrator's own norm under an extra key (QuTiP discards it).
+    """
+    t = _check_grid(params)
+    table = compile_table(params)
+    opts, override = _options_from(params, method)
+    with engine.Plan(table, device) as plan:
+        obs, stats = plan.evolve(t, opts)
+    out = _pack(obs, override, raw_norm)
+    if return_stats:
+        return t, out, stats
+    return t, out
+
+
+def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int = 0, method: Optional[str] = None,
+                        raw_norm: bool = False):
+    """Independent trajectories; those with N <= 10 share ONE kernel launch (one CTA each)."""
+    n = len(params_list)
+    results: List = [None] * n
+    grids = [_check_grid(p) for p in params_list]
+    tables = [compile_table(p) for p in params_list]
+    om = [_options_from(p, method) for p in params_list]
+    small = [i for i in range(n) if tables[i].n <= engine.SMALL_MAX_QUBITS]
+    groups: Dict[int, List[int]] = {}
+    for i in small:
+        groups.setdefault(len(grids[i]), []).append(i)
+    stats_out: List = [None] * n
+    for _, idxs in groups.items():
+        tgrid = np.stack([grids[i] for i in idxs])
+        obs, stats = engine.evolve_batch([tables[i] for i in idxs], tgrid, [om[i][0] for i in idxs], device)
+        for j, i in enumerate(idxs):
+            results[i] = (grids[i], _pack(obs[j], om[i][1], raw_norm))
+            stats_out[i] = stats[j]
+    for i in range(n):
+        if results[i] is None:
+            with engine.Plan(tables[i], device) as plan:
+                obs, st = plan.evolve(grids[i], om[i][0])
+            results[i] = (grids[i], _pack(obs, om[i][1], raw_norm))
+            stats_out[i] = st
+    return results, stats_out

@@ -1,0 +1,226 @@
+// Plans, the batch path and library-level entry points; included from qsb_api.cu.
+using namespace qsb;
+
+struct Session;
+
+struct qsb_plan {
+  int n = 0;        // user qubits
+  int n_eff = 0;    // qubits of the tiled path (n padded to >= 12 with decoupled spectator bits)
+  int device = 0;
+  bool small = false;
+  std::vector<double> h, J;  // [3][n], [3][n][n] as given
+  uint64_t sea_mask = 0, rare_mask = 0;
+  cudaStream_t stream = nullptr;
+  // tiled path
+  LargeGeom g = {};
+  DiagTables tab = {};
+  double* d_tables = nullptr;   // h, J, Qx, Qy, Qz in one allocation
+  void* ws = nullptr;           // workspace (vectors + partials)
+  size_t ws_bytes = 0;
+  bool ws_owned = false;
+  double* d_red = nullptr;      // [PSTRIDE] reduced sums
+  double* h_red = nullptr;      // pinned mirror
+  Session* ses = nullptr;
+};
+
+static int n_vectors(int method) { return method == QSB_METHOD_TAYLOR ? 5 : 11; }
+
+static size_t workspace_need(const qsb_plan* p, int method) {
+  if (p->small) return 0;
+  size_t vec = sizeof(cplx) << p->n_eff;
+  size_t partials = sizeof(double) * PSTRIDE * ((size_t)1 << (p->n_eff - TB));
+  return n_vectors(method) * vec + ((partials + 255) & ~size_t(255));
+}
+
+static int ensure_workspace(qsb_plan* p, int method) {
+  size_t need = workspace_need(p, method);
+  if (p->ws && p->ws_bytes >= need) return QSB_OK;
+  if (p->ws && !p->ws_owned)
+    return fail(QSB_ERR_BAD_ARG, "caller-provided workspace is too small: need " + std::to_string(need) + " bytes");
+  if (p->ws) { cudaFree(p->ws); p->ws = nullptr; }
+  cudaError_t e = cudaMalloc(&p->ws, need);
+  if (e != cudaSuccess) {
+    p->ws = nullptr; p->ws_bytes = 0;
+    cudaGetLastError();
+    return fail(QSB_ERR_OOM, "cudaMalloc of " + std::to_string(need) + " workspace bytes failed: " + cudaGetErrorString(e));
+  }
+  p->ws_bytes = need;
+  p->ws_owned = true;
+  return QSB_OK;
+}
+
+extern "C" {
+
+int qsb_version(void) { return QSB_VERSION; }
+const char* qsb_last_error(void) { return g_err.c_str(); }
+
+int qsb_device_count(int* count) {
+  if (!count) return fail(QSB_ERR_BAD_ARG, "count is null");
+  int c = 0;
+  cudaError_t e = cudaGetDeviceCount(&c);
+  if (e != cudaSuccess) { cudaGetLastError(); c = 0; }
+  *count = c;
+  return QSB_OK;
+}
+
+int qsb_plan_create(const qsb_table* table, int device, qsb_plan** out) {
+  if (!out) return fail(QSB_ERR_BAD_ARG, "plan out-pointer is null");
+  *out = nullptr;
+  int rc = check_table(table);
+  if (rc) return rc;
+  rc = pick_device(device);
+  if (rc) return rc;
+  std::unique_ptr<qsb_plan> p(new qsb_plan);
+  const int n = table->n_qubits;
+  p->n = n;
+  p->device = device;
+  p->small = n <= QSB_SMALL_MAX_QUBITS;
+  p->h.assign(table->h, table->h + 3 * (size_t)n);
+  p->J.assign(table->J, table->J + 3 * (size_t)n * n);
+  p->sea_mask = table->sea_mask;
+  p->rare_mask = table->rare_mask;
+  QSB_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+  if (!p->small) {
+    const int ne = std::max(n, TB);
+    p->n_eff = ne;
+    p->g = make_geometry(ne);
+    p->g.sea_mask = table->sea_mask;
+    p->g.rare_mask = table->rare_mask;
+    // pad the table with decoupled spectator bits (zero coefficients) up to 12 qubits
+    std::vector<double> h(3 * (size_t)ne, 0.0), J(3 * (size_t)ne * ne, 0.0);
+    for (int a = 0; a < 3; ++a)
+      for (int b = 0; b < n; ++b) {
+        h[(size_t)a * ne + b] = table->h[a * n + b];
+        for (int c = 0; c < n; ++c)
+          if (b != c) J[((size_t)a * ne + b) * ne + c] = table->J[((size_t)a * n + b) * n + c];
+      }
+    const Layout& Lc = p->g.lay[p->g.n_layouts - 1];
+    std::vector<double> qx = host_q_table(h.data(), J.data(), ne, 0, Lc, std::ldexp(1.0, -ne));
+    std::vector<double> qy = host_q_table(h.data(), J.data(), ne, 1, Lc, std::ldexp(1.0, -ne));
+    std::vector<double> qz = host_q_table(h.data(), J.data(), ne, 2, p->g.lay[0], 1.0);
+    std::vector<double> blob;
+    blob.insert(blob.end(), h.begin(), h.end());
+    blob.insert(blob.end(), J.begin(), J.end());
+    size_t off_q = blob.size();
+    blob.insert(blob.end(), qx.begin(), qx.end());
+    blob.insert(blob.end(), qy.begin(), qy.end());
+    blob.insert(blob.end(), qz.begin(), qz.end());
+    QSB_CUDA(cudaMalloc(&p->d_tables, blob.size() * sizeof(double)));
+    QSB_CUDA(cudaMemcpy(p->d_tables, blob.data(), blob.size() * sizeof(double), cudaMemcpyHostToDevice));
+    p->tab.h = p->d_tables;
+    p->tab.J = p->d_tables + h.size();
+    p->tab.Qx = p->d_tables + off_q;
+    p->tab.Qy = p->tab.Qx + TILE;
+    p->tab.Qz = p->tab.Qy + TILE;
+    QSB_CUDA(cudaMalloc(&p->d_red, PSTRIDE * sizeof(double)));
+    QSB_CUDA(cudaMallocHost(&p->h_red, PSTRIDE * sizeof(double)));
+  }
+  *out = p.release();
+  return QSB_OK;
+}
+
+int qsb_session_end(qsb_plan* plan);
+
+int qsb_plan_destroy(qsb_plan* p) {
+  if (!p) return QSB_OK;
+  cudaSetDevice(p->device);
+  qsb_session_end(p);
+  if (p->ws && p->ws_owned) cudaFree(p->ws);
+  if (p->d_tables) cudaFree(p->d_tables);
+  if (p->d_red) cudaFree(p->d_red);
+  if (p->h_red) cudaFreeHost(p->h_red);
+  if (p->stream) cudaStreamDestroy(p->stream);
+  delete p;
+  return QSB_OK;
+}
+
+int qsb_plan_workspace_bytes(const qsb_plan* p, int method, int order, size_t* bytes) {
+  (void)order;
+  if (!p || !bytes) return fail(QSB_ERR_BAD_ARG, "null argument");
+  *bytes = workspace_need(p, method);
+  return QSB_OK;
+}
+
+int qsb_plan_set_workspace(qsb_plan* p, void* device_ptr, size_t bytes) {
+  if (!p) return fail(QSB_ERR_BAD_ARG, "null plan");
+  if (p->ses) return fail(QSB_ERR_BAD_ARG, "cannot change the workspace while a session is open");
+  if (((uintptr_t)device_ptr) & 255) return fail(QSB_ERR_BAD_ARG, "workspace must be 256-byte aligned");
+  if (p->ws && p->ws_owned) cudaFree(p->ws);
+  p->ws = device_ptr;
+  p->ws_bytes = device_ptr ? bytes : 0;
+  p->ws_owned = false;
+  return QSB_OK;
+}
+
+// ---- on-chip batch path ---------------------------------------------------------------------------
+int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
+                     const double* t_out, int32_t t_out_per_traj, const qsb_solver_opts* opts, double* out_obs,
+                     qsb_stats* stats, int device) {
+  if (n_traj < 1 || !tables || !psi0_index || !opts || !out_obs)
+    return fail(QSB_ERR_BAD_ARG, "qsb_evolve_batch: null argument or n_traj < 1");
+  int max_n = 0;
+  for (int i = 0; i < n_traj; ++i) {
+    int rc = check_table(&tables[i]);
+    if (rc) return rc;
+    if (tables[i].n_qubits > QSB_SMALL_MAX_QUBITS)
+      return fail(QSB_ERR_UNSUPPORTED, "qsb_evolve_batch handles n_qubits <= " + std::to_string(QSB_SMALL_MAX_QUBITS) +
+                                           "; use one plan + qsb_evolve per larger trajectory");
+    rc = check_opts(&opts[i]);
+    if (rc) return rc;
+    if (psi0_index[i] >> tables[i].n_qubits) return fail(QSB_ERR_BAD_ARG, "psi0_index out of range");
+    rc = check_grid(n_out, t_out + (t_out_per_traj ? (size_t)i * n_out : 0));
+    if (rc) return rc;
+    max_n = std::max(max_n, tables[i].n_qubits);
+  }
+  int rc = pick_device(device);
+  if (rc) return rc;
+  std::vector<SmallDesc> descs(n_traj);
+  for (int i = 0; i < n_traj; ++i) compile_small(&tables[i], psi0_index[i], &opts[i], t_out_per_traj, &descs[i]);
+
+  SmallDesc* d_desc = nullptr;
+  double *d_t = nullptr, *d_obs = nullptr;
+  SmallStats* d_stats = nullptr;
+  const size_t nt = (size_t)n_out * (t_out_per_traj ? n_traj : 1);
+  const size_t nobs = (size_t)n_traj * n_out * QSB_NOBS;
+  cudaStream_t st;
+  cudaEvent_t e0, e1;
+  QSB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  QSB_CUDA(cudaEventCreate(&e0));
+  QSB_CUDA(cudaEventCreate(&e1));
+  QSB_CUDA(cudaMalloc(&d_desc, sizeof(SmallDesc) * n_traj));
+  QSB_CUDA(cudaMalloc(&d_t, sizeof(double) * nt));
+  QSB_CUDA(cudaMalloc(&d_obs, sizeof(double) * nobs));
+  QSB_CUDA(cudaMalloc(&d_stats, sizeof(SmallStats) * n_traj));
+  QSB_CUDA(cudaMemcpyAsync(d_desc, descs.data(), sizeof(SmallDesc) * n_traj, cudaMemcpyHostToDevice, st));
+  QSB_CUDA(cudaMemcpyAsync(d_t, t_out, sizeof(double) * nt, cudaMemcpyHostToDevice, st));
+  QSB_CUDA(cudaEventRecord(e0, st));
+  launch_small_evolve(d_desc, n_traj, max_n, d_t, n_out, d_obs, d_stats, st);
+  QSB_CUDA(cudaGetLastError());
+  QSB_CUDA(cudaEventRecord(e1, st));
+  std::vector<SmallStats> hs(n_traj);
+  QSB_CUDA(cudaMemcpyAsync(out_obs, d_obs, sizeof(double) * nobs, cudaMemcpyDeviceToHost, st));
+  QSB_CUDA(cudaMemcpyAsync(hs.data(), d_stats, sizeof(SmallStats) * n_traj, cudaMemcpyDeviceToHost, st));
+  QSB_CUDA(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaFree(d_desc); cudaFree(d_t); cudaFree(d_obs); cudaFree(d_stats);
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st);
+  int worst = QSB_OK;
+  for (int i = 0; i < n_traj; ++i) {
+    if (stats) {
+      stats[i].n_accepted = hs[i].n_accepted; stats[i].n_rejected = hs[i].n_rejected; stats[i].n_rhs = hs[i].n_rhs;
+      stats[i].last_h = hs[i].last_h; stats[i].device_ms = ms; stats[i].path = 0; stats[i].status = hs[i].status;
+    }
+    if (hs[i].status != QSB_OK && worst == QSB_OK) {
+      worst = hs[i].status;
+      g_err = "trajectory " + std::to_string(i) + (hs[i].status == QSB_ERR_NSTEPS
+                  ? ": more than nsteps internal steps inside one output interval (excess work)"
+                  : ": step size underflow");
+    }
+  }
+  return worst;
+}
+
+}  // extern "C"
+
+#include "qsb_api_session.inl"

@@ -1,0 +1,216 @@
+// Tiled-path stepping session (host-side adaptive controller around launch_happly) and qsb_evolve.
+using namespace qsb;
+
+struct Session {
+  qsb_solver_opts o;
+  int order = 5;
+  double inv_q = 0.2;
+  double t = 0.0, h = 0.0;
+  bool after_reject = false;
+  bool have_k1 = false;
+  int64_t n_acc = 0, n_rej = 0, n_rhs = 0;
+  uint64_t dim = 0;        // amplitudes of the padded vector
+  double norm_dim = 0.0;   // 2^n of the user's problem: divisor of the weighted RMS norms
+  cplx *y = nullptr, *ys = nullptr, *k[7] = {}, *tx = nullptr, *ty = nullptr;
+  double* partials = nullptr;
+  int64_t n_tiles = 0;
+  double obs_sums[PSTRIDE] = {};  // sums belonging to the current y (when valid)
+  bool obs_valid = false;
+};
+
+static void carve(qsb_plan* p, Session* s) {
+  char* base = (char*)p->ws;
+  size_t vec = sizeof(cplx) << p->n_eff;
+  int i = 0;
+  auto next = [&]() { return (cplx*)(base + vec * (i++)); };
+  s->y = next(); s->ys = next(); s->tx = next(); s->ty = next();
+  if (s->o.method == QSB_METHOD_DP5) {
+    for (int j = 0; j < 7; ++j) s->k[j] = next();
+  } else {
+    s->k[0] = next();  // running Taylor term
+  }
+  s->partials = (double*)(base + vec * i);
+}
+
+static int fetch_sums(qsb_plan* p, Session* s, double* out) {
+  launch_reduce_partials(s->partials, s->n_tiles, p->d_red, p->stream);
+  QSB_CUDA(cudaGetLastError());
+  QSB_CUDA(cudaMemcpyAsync(p->h_red, p->d_red, PSTRIDE * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
+  QSB_CUDA(cudaStreamSynchronize(p->stream));
+  memcpy(out, p->h_red, PSTRIDE * sizeof(double));
+  return QSB_OK;
+}
+
+static Epilogue blank_epilogue(const Session* s) {
+  Epilogue e = {};
+  e.alpha = 1.0;
+  e.sc_i0 = 0; e.sc_i1 = 0;
+  e.atol = s->o.atol; e.rtol = s->o.rtol;
+  return e;
+}
+
+static void obs_from_sums(const qsb_plan* p, const double* s, double* obs) {
+  const double nrm2 = s[0], sx = std::ldexp(0.5, -p->n_eff) / nrm2;
+  obs[0] = s[3] * sx;            // Ix_sea
+  obs[1] = s[5] * sx;            // Iy_sea
+  obs[2] = 0.5 * s[1] / nrm2;    // Iz_sea
+  obs[3] = 0.5 * s[2] / nrm2;    // Iz_R
+  obs[4] = s[4] * sx;            // Ix_R
+  obs[5] = s[6] * sx;            // Iy_R
+  obs[6] = 1.0;
+  obs[7] = std::sqrt(nrm2);
+}
+
+// k1 = f(y) with observables of y and the start-up step size.
+static int session_prime(qsb_plan* p, Session* s) {
+  Epilogue e = blank_epilogue(s);
+  e.o1 = s->k[0];
+  e.vin[0] = s->y; e.n_in = 1; e.c[0] = 0.0; e.e[0] = 0.0; e.ek = 1.0; e.want_err = 1;
+  if (s->o.method == QSB_METHOD_TAYLOR) e.o1 = nullptr;  // Taylor recomputes its first term with h folded in
+  launch_happly(p->g, p->tab, s->y, s->tx, s->ty, e, 1, s->partials, p->stream);
+  QSB_CUDA(cudaGetLastError());
+  ++s->n_rhs;
+  double sums[PSTRIDE];
+  int rc = fetch_sums(p, s, sums);
+  if (rc) return rc;
+  memcpy(s->obs_sums, sums, sizeof sums);
+  s->obs_valid = true;
+  s->have_k1 = (s->o.method == QSB_METHOD_DP5);
+  if (s->h == 0.0) {
+    double d1 = std::sqrt(sums[7] / s->norm_dim), d0 = std::sqrt(sums[8] / s->norm_dim);
+    s->h = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
+    if (s->o.first_step > 0.0) s->h = s->o.first_step;
+    if (s->o.max_step > 0.0 && s->h > s->o.max_step) s->h = s->o.max_step;
+  }
+  return QSB_OK;
+}
+
+// y2 = y + c k1 as its own sweep: k1 comes from the previous step's FSAL apply, whose epilogue could not know h.
+__global__ void axpy_kernel(cplx* __restrict__ out, const cplx* __restrict__ a, double c, const cplx* __restrict__ b,
+                            uint64_t n) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    cplx v = a[i];
+    axpy(v, c, b[i]);
+    out[i] = v;
+  }
+}
+
+// One step attempt of size hu.  Returns the weighted RMS error in *err; obs sums of the candidate in cand_sums.
+static int attempt_dp5(qsb_plan* p, Session* s, double hu, double* err, double* cand_sums) {
+  static const DP5 T = dp5_tableau();
+  const int blocks = (int)std::min<uint64_t>((s->dim + 255) / 256, 148 * 8);
+  axpy_kernel<<<blocks, 256, 0, p->stream>>>(s->ys, s->y, hu * T.a[0][0], s->k[0], s->dim);
+  for (int st = 1; st <= 5; ++st) {  // apply #st: src = y_{st+1}, produces k_{st+1} and y_{st+2}
+    Epilogue e = blank_epilogue(s);
+    e.o1 = s->k[st];
+    e.o2 = s->ys;
+    e.vin[0] = s->y; e.c[0] = 1.0; e.n_in = 1;
+    for (int j = 0; j < st; ++j)
+      if (T.a[st][j] != 0.0) { e.vin[e.n_in] = s->k[j]; e.c[e.n_in] = hu * T.a[st][j]; ++e.n_in; }
+    e.ck = hu * T.a[st][st];
+    launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, 0, s->partials, p->stream);
+  }
+  {  // FSAL apply on y_new: k7, the error estimate, and y_new's observable sums
+    Epilogue e = blank_epilogue(s);
+    e.o1 = s->k[6];
+    e.vin[0] = s->y; e.vin[1] = s->ys; e.n_in = 2;
+    for (int j = 0; j < 6; ++j)
+      if (T.e[j] != 0.0) { e.vin[e.n_in] = s->k[j]; e.e[e.n_in] = hu * T.e[j]; ++e.n_in; }
+    e.ek = hu * T.e[6];
+    e.want_err = 1; e.sc_i0 = 0; e.sc_i1 = 1;
+    launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, 1, s->partials, p->stream);
+  }
+  QSB_CUDA(cudaGetLastError());
+  s->n_rhs += 6;
+  int rc = fetch_sums(p, s, cand_sums);
+  if (rc) return rc;
+  *err = std::sqrt(cand_sums[7] / s->norm_dim);
+  return QSB_OK;
+}
+
+static int attempt_taylor(qsb_plan* p, Session* s, double hu, double* err, double* cand_sums) {
+  // ys accumulates y + sum of terms; k[0] holds the running term; term_{m+1} = hu/(m+1) * f(term_m)
+  QSB_CUDA(cudaMemcpyAsync(s->ys, s->y, sizeof(cplx) * s->dim, cudaMemcpyDeviceToDevice, p->stream));
+  for (int m = 0; m < s->order; ++m) {
+    Epilogue e = blank_epilogue(s);
+    e.alpha = hu / (double)(m + 1);
+    e.o1 = s->k[0];
+    e.o2 = s->ys;
+    e.vin[0] = s->ys; e.c[0] = 1.0; e.vin[1] = s->y; e.c[1] = 0.0; e.n_in = 2;
+    e.ck = e.alpha;
+    if (m == s->order - 1) { e.want_err = 1; e.ek = e.alpha; e.sc_i0 = 1; e.sc_i1 = -1; }
+    launch_happly(p->g, p->tab, m == 0 ? s->y : s->k[0], s->tx, s->ty, e, 0, s->partials, p->stream);
+  }
+  QSB_CUDA(cudaGetLastError());
+  s->n_rhs += s->order;
+  int rc = fetch_sums(p, s, cand_sums);
+  if (rc) return rc;
+  *err = std::sqrt(cand_sums[7] / s->norm_dim);
+  return QSB_OK;
+}
+
+// Advance until t_target (if finite) or for max_attempts attempts, whichever comes first.
+static int session_advance(qsb_plan* p, Session* s, double t_target, int64_t max_attempts, int64_t nsteps_cap,
+                           int64_t* attempts_done) {
+  int64_t in_interval = 0;
+  *attempts_done = 0;
+  const bool bounded = std::isfinite(t_target);
+  while ((!bounded || s->t < t_target) && *attempts_done < max_attempts) {
+    if (nsteps_cap > 0 && in_interval >= nsteps_cap)
+      return fail(QSB_ERR_NSTEPS, "more than nsteps internal steps inside one output interval (excess work)");
+    if (s->o.method == QSB_METHOD_DP5 && !s->have_k1) {
+      int rc = session_prime(p, s);
+      if (rc) return rc;
+    }
+    double hmax = s->o.max_step > 0.0 ? std::min(s->h, s->o.max_step) : s->h;
+    double hu = hmax;
+    bool hit = false;
+    if (bounded) {
+      double remaining = t_target - s->t;
+      if (hu >= remaining * (1.0 - 1e-12)) { hu = remaining; hit = true; }
+      else if (2.0 * hu > remaining) hu = 0.5 * remaining;
+    }
+    if (hu <= 16.0 * 2.220446049250313e-16 * std::fabs(s->t)) return fail(QSB_ERR_STEP_UNDERFLOW, "step size underflow");
+    double err = 0.0, cand[PSTRIDE];
+    int rc = (s->o.method == QSB_METHOD_DP5) ? attempt_dp5(p, s, hu, &err, cand) : attempt_taylor(p, s, hu, &err, cand);
+    if (rc) return rc;
+    ++in_interval;
+    ++*attempts_done;
+    if (!(err == err)) return fail(QSB_ERR_CUDA, "non-finite error estimate (state blew up)");
+    if (err <= 1.0) {
+      std::swap(s->y, s->ys);
+      if (s->o.method == QSB_METHOD_DP5) {
+        std::swap(s->k[0], s->k[6]);
+        memcpy(s->obs_sums, cand, sizeof cand);
+        s->obs_valid = true;
+      } else {
+        s->obs_valid = false;
+      }
+      s->t = hit ? t_target : s->t + hu;
+      ++s->n_acc;
+      double hn = hu * Controller::factor(err, s->inv_q, s->after_reject);
+      s->h = (hu < hmax) ? std::max(hn, s->h) : hn;
+      s->after_reject = false;
+    } else {
+      ++s->n_rej;
+      s->h = hu * Controller::factor(err, s->inv_q, true);
+      s->after_reject = true;
+    }
+  }
+  return QSB_OK;
+}
+
+static int session_observe(qsb_plan* p, Session* s, double* obs) {
+  if (!s->obs_valid) {
+    launch_observe(p->g, p->tab, s->y, s->tx, s->ty, s->partials, p->stream);
+    QSB_CUDA(cudaGetLastError());
+    int rc = fetch_sums(p, s, s->obs_sums);
+    if (rc) return rc;
+    s->obs_valid = true;
+  }
+  obs_from_sums(p, s->obs_sums, obs);
+  return QSB_OK;
+}
+
+#include "qsb_api_entry.inl"

@@ -1,0 +1,75 @@
+// Tiled HBM path (n >= 12): matrix-free H-apply as three diagonal forms in three bases,
+//     H psi = Dz psi + W Dx W psi + S W Dy W S^dagger psi,      W = Hadamard^(x n), S = diag(1,i)^(x n),
+// because every term of the table is a product of same-axis spin operators (include/qsb200.h).  The
+// Walsh-Hadamard transforms are done 12 bits at a time on 4096-amplitude tiles staged in shared memory;
+// bits above 12 are reached by further passes whose tiles gather strided 2^lk-amplitude runs.
+#pragma once
+#include <vector>
+
+#include "qsb_common.cuh"
+
+namespace qsb {
+
+constexpr int TB = 12;                 // tile bits
+constexpr int TILE = 1 << TB;          // amplitudes per tile
+constexpr int TPT = 256;               // threads per tile (16 amplitudes each)
+constexpr int TILE_PHYS = TILE + TILE / 16;  // padded length in cplx (bank-conflict-free 16-strided access)
+constexpr int MAX_LAYOUTS = 6;
+constexpr int MAX_VEC_IN = 8;
+constexpr int PSTRIDE = 10;             // doubles per tile in the partial-sum buffer
+
+// One tile layout: tile-local bits [0,lk) = global bits [0,lk); local [lk,12) = global [gs, gs+12-lk).
+struct Layout {
+  int lk, gs, ge;
+  int m8, m4, m0;        // Hadamard stage masks for local-bit windows [8,12), [4,8), [0,4)
+  uint64_t tile_mask;    // global bits covered by the tile
+};
+
+struct DiagTables {      // device pointers
+  const double* h;       // [3][n]
+  const double* J;       // [3][n][n]
+  const double* Qx;      // [4096] centre-layout, x basis (2^-n folded in)
+  const double* Qy;      // [4096] centre-layout, y basis
+  const double* Qz;      // [4096] layout 0, z basis
+};
+
+// Fused epilogue of the last pass: k = -i H v (or H v), then stage algebra on k.
+struct Epilogue {
+  const cplx* vin[MAX_VEC_IN];
+  double c[MAX_VEC_IN];  // o2 = sum c_j vin_j + ck k
+  double e[MAX_VEC_IN];  // err = sum e_j vin_j + ek k
+  double ck, ek, alpha;  // o1 = alpha k
+  cplx* o1;
+  cplx* o2;
+  int n_in;
+  int want_err;          // accumulate |err|^2 / sc^2 into partials
+  int sc_i0, sc_i1;      // sc = atol + rtol max(|vin[sc_i0]|, sc_i1 < 0 ? |o2| : |vin[sc_i1]|)
+  int raw_h;             // 1: k = H v (no -i), for qsb_apply_h
+  double atol, rtol;
+};
+
+struct LargeGeom {
+  int n;                 // qubits (>= 12)
+  int n_layouts;         // 1..MAX_LAYOUTS; layout 0 is the contiguous one, the last one is the centre
+  Layout lay[MAX_LAYOUTS];
+  uint64_t sea_mask, rare_mask;
+  int has_x, has_y;      // basis has any non-zero coefficient
+};
+
+LargeGeom make_geometry(int n);
+std::vector<double> host_q_table(const double* h, const double* J, int n, int basis, const Layout& L, double scale);
+
+// One H-apply: src -> epilogue.  tx/ty: scratch vectors of 2^n cplx.  partials: device doubles,
+// [n_tiles][PSTRIDE] = (nrm2, zsea, zrare, xsea, xrare, ysea, yrare, err, aux).  collect_obs: fill the observable slots.
+void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
+                   const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream);
+// Observables only (pass_first + mids + pass_centre), filling partial slots 0..6.
+void launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
+                    double* partials, cudaStream_t stream);
+// out[PSTRIDE] = column sums of partials[n_tiles][PSTRIDE] in a fixed order.
+void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out8, cudaStream_t stream);
+// psi <- basis state / zero
+void launch_set_basis_state(cplx* psi, uint64_t dim, uint64_t index, cudaStream_t stream);
+size_t happly_smem_bytes();
+
+}  // namespace qsb

@@ -1,0 +1,167 @@
+// Kernels of the tiled path; included at the end of qsb_large.cu.
+namespace qsb {
+namespace {
+
+struct PassArgs {
+  LargeGeom g;
+  DiagTables tab;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// pass_first: layout 0.  tX = W_g0 psi, tY = W_g0 S^dagger psi.  512 threads: threads 0-255 carry the
+// x-branch tile, 256-511 the y-branch tile.  Optionally the z-basis observable partial sums.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(2 * TPT, 1)
+pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx* __restrict__ ty,
+           int collect_obs, double* __restrict__ partials) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  __shared__ double red[3 * 32 + 3];
+  const int half = threadIdx.x >> 8, tt = threadIdx.x & (TPT - 1);
+  cplx* mine = sm + half * TILE_PHYS;
+  const uint64_t base = (uint64_t)blockIdx.x << TB;
+  cplx r[16];
+  double s[3] = {0.0, 0.0, 0.0};
+  const int n_sea = __popcll(a.g.sea_mask);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    int i = elem<8>(tt, j);
+    uint64_t idx = base | (uint64_t)i;
+    cplx v = psi[idx];
+    if (half == 0) {
+      if (collect_obs) {
+        double p = norm2(v);
+        s[0] += p;
+        s[1] = fma(p, (double)sea_weight(idx, a.g.sea_mask, n_sea), s[1]);
+        s[2] += (idx & a.g.rare_mask) ? -p : p;
+      }
+    } else {
+      v = mul_mi_pow(v, __popcll(idx));
+    }
+    r[j] = v;
+  }
+  bfly16(r, 0xF);
+  smem_store16<8>(mine, tt, r);
+  __syncthreads();
+  smem_round<0>(mine, tt, 0xF);
+  __syncthreads();
+  smem_load16<4>(mine, tt, r);
+  bfly16(r, 0xF);
+  cplx* dst = half ? ty : tx;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) dst[base | (uint64_t)elem<4>(tt, j)] = r[j];
+  if (collect_obs) {
+    block_reduce<3>(s, red);
+    if (threadIdx.x == 0) {
+      double* p = partials + (size_t)blockIdx.x * PSTRIDE;
+      p[0] = s[0]; p[1] = s[1]; p[2] = s[2];
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// pass_mid: in-place Hadamard on one group's bits (layout k, 0 < k < centre).  blockIdx.y = branch.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TPT, 2)
+pass_mid(Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  cplx* t = blockIdx.y ? ty : tx;
+  const int tt = threadIdx.x;
+  const uint64_t base = tile_base(L, blockIdx.x);
+  cplx r[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) r[j] = t[gidx(L, base, elem<8>(tt, j))];
+  bfly16(r, L.m8);
+  smem_store16<8>(sm, tt, r);
+  __syncthreads();
+  if (L.m0) {
+    smem_round<0>(sm, tt, L.m0);
+    __syncthreads();
+  }
+  smem_load16<4>(sm, tt, r);
+  bfly16(r, L.m4);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) t[gidx(L, base, elem<4>(tt, j))] = r[j];
+}
+
+// ---------------------------------------------------------------------------------------------------
+// pass_centre: t <- W_g D W_g t on the centre layout; D is the x- or y-basis diagonal form evaluated on
+// the full index.  Optionally that basis' observable partial sums (taken on the fully transformed vector).
+// ---------------------------------------------------------------------------------------------------
+template <int W>
+__device__ __forceinline__ void centre_core(cplx (&r)[16], int tt, int mask, const DiagShared& ds,
+                                            const double* __restrict__ Q, const Layout& L, uint64_t base,
+                                            const LargeGeom& g, int collect_obs, double (&s)[2]) {
+  bfly16(r, mask);
+  const int n_sea = __popcll(g.sea_mask);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    int i = elem<W>(tt, j);
+    if (collect_obs) {
+      uint64_t idx = gidx(L, base, i);
+      double p = norm2(r[j]);
+      s[0] = fma(p, (double)sea_weight(idx, g.sea_mask, n_sea), s[0]);
+      s[1] += (idx & g.rare_mask) ? -p : p;
+    }
+    r[j] = diag_at(ds, Q, i) * r[j];
+  }
+  bfly16(r, mask);
+}
+
+__global__ void __launch_bounds__(TPT, 2)
+pass_centre(PassArgs a, Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty, int collect_obs,
+            double* __restrict__ partials) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  __shared__ DiagShared ds;
+  __shared__ double red[2 * 32 + 2];
+  const int branch = blockIdx.y;  // 0: x, 1: y
+  cplx* t = branch ? ty : tx;
+  const double* Q = branch ? a.tab.Qy : a.tab.Qx;
+  const int n = a.g.n, tt = threadIdx.x;
+  const uint64_t base = tile_base(L, blockIdx.x);
+  diag_prologue(ds, a.tab.h + (size_t)branch * n, a.tab.J + (size_t)branch * n * n, n, L, base,
+                ldexp(1.0, -n), tt);
+  cplx r[16];
+  double s[2] = {0.0, 0.0};
+#pragma unroll
+  for (int j = 0; j < 16; ++j) r[j] = t[gidx(L, base, elem<8>(tt, j))];
+  if (!L.m4 && !L.m0) {
+    centre_core<8>(r, tt, L.m8, ds, Q, L, base, a.g, collect_obs, s);
+  } else {
+    bfly16(r, L.m8);
+    smem_store16<8>(sm, tt, r);
+    __syncthreads();
+    if (!L.m0) {
+      smem_load16<4>(sm, tt, r);
+      centre_core<4>(r, tt, L.m4, ds, Q, L, base, a.g, collect_obs, s);
+      smem_store16<4>(sm, tt, r);
+    } else {
+      smem_round<4>(sm, tt, L.m4);
+      __syncthreads();
+      smem_load16<0>(sm, tt, r);
+      centre_core<0>(r, tt, L.m0, ds, Q, L, base, a.g, collect_obs, s);
+      smem_store16<0>(sm, tt, r);
+      __syncthreads();
+      smem_round<4>(sm, tt, L.m4);
+    }
+    __syncthreads();
+    smem_load16<8>(sm, tt, r);
+    bfly16(r, L.m8);
+  }
+#pragma unroll
+  for (int j = 0; j < 16; ++j) t[gidx(L, base, elem<8>(tt, j))] = r[j];
+  if (collect_obs) {
+    block_reduce<2>(s, red);
+    if (threadIdx.x == 0) {
+      double* p = partials + (size_t)blockIdx.x * PSTRIDE + 3 + 2 * branch;
+      p[0] = s[0]; p[1] = s[1];
+    }
+  }
+}
+
+}  // namespace
+}  // namespace qsb
+
+#include "qsb_large_last.inl"

@@ -1,0 +1,273 @@
+"""ctypes binding of libqsb200.so (include/qsb200.h) and the Python-level hot-path calls built on it.
+
+There is no CPU fallback anywhere in this module: if the shared library is missing, or no CUDA device
+is present, the calls raise.  torch is used only as a device-buffer allocator (``use_torch_workspace``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from .table import SpinTable
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libqsb200.so")
+
+NOBS = 8
+OBS_COLUMNS = ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R", "state_norm", "raw_norm")
+SMALL_MAX_QUBITS = 10
+METHOD_DP5, METHOD_TAYLOR = 0, 1
+_METHODS = {"dp5": METHOD_DP5, "taylor": METHOD_TAYLOR}
+
+# QuTiP 5 defaults that apply when the reference passes options=None
+DEFAULT_ATOL, DEFAULT_RTOL, DEFAULT_NSTEPS = 1e-8, 1e-6, 2500
+
+
+class EngineError(RuntimeError):
+    """Any non-zero qsb_status."""
+
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"libqsb200 status {code}: {msg}")
+        self.code = code
+
+
+class IntegratorError(EngineError):
+    """nsteps exhausted inside one output interval / step underflow (QuTiP raises IntegratorException here)."""
+
+
+class _Table(C.Structure):
+    _fields_ = [("n_qubits", C.c_int32), ("h", C.POINTER(C.c_double)), ("J", C.POINTER(C.c_double)),
+                ("sea_mask", C.c_uint64), ("rare_mask", C.c_uint64)]
+
+
+class _Opts(C.Structure):
+    _fields_ = [("atol", C.c_double), ("rtol", C.c_double), ("max_step", C.c_double), ("nsteps", C.c_int64),
+                ("method", C.c_int32), ("order", C.c_int32), ("first_step", C.c_double)]
+
+
+class _Stats(C.Structure):
+    _fields_ = [("n_accepted", C.c_int64), ("n_rejected", C.c_int64), ("n_rhs", C.c_int64), ("last_h", C.c_double),
+                ("device_ms", C.c_double), ("path", C.c_int32), ("status", C.c_int32)]
+
+
+EXPORTS = (
+    "qsb_version", "qsb_last_error", "qsb_device_count", "qsb_plan_create", "qsb_plan_destroy",
+    "qsb_plan_workspace_bytes", "qsb_plan_set_workspace", "qsb_evolve", "qsb_evolve_batch", "qsb_apply_h",
+    "qsb_session_begin", "qsb_session_step", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
+)
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """dlopen libqsb200.so; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing - build it with `python -m quantumsimulations_b200.build` "
+            "(there is no CPU fallback for the time-evolution path)"
+        )
+    lib = C.CDLL(LIB_PATH)
+    dp, vp = C.POINTER(C.c_double), C.c_void_p
+    lib.qsb_version.restype = C.c_int
+    lib.qsb_last_error.restype = C.c_char_p
+    lib.qsb_device_count.argtypes = [C.POINTER(C.c_int)]
+    lib.qsb_plan_create.argtypes = [C.POINTER(_Table), C.c_int, C.POINTER(vp)]
+    lib.qsb_plan_destroy.argtypes = [vp]
+    lib.qsb_plan_workspace_bytes.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_size_t)]
+    lib.qsb_plan_set_workspace.argtypes = [vp, vp, C.c_size_t]
+    lib.qsb_evolve.argtypes = [vp, C.c_uint64, dp, C.c_int64, dp, C.POINTER(_Opts), dp, C.POINTER(_Stats)]
+    lib.qsb_evolve_batch.argtypes = [C.c_int32, C.POINTER(_Table), C.POINTER(C.c_uint64), C.c_int64, dp, C.c_int32,
+                                     C.POINTER(_Opts), dp, C.POINTER(_Stats), C.c_int]
+    lib.qsb_apply_h.argtypes = [vp, dp, dp]
+    lib.qsb_session_begin.argtypes = [vp, C.c_uint64, dp, C.c_double, C.POINTER(_Opts)]
+    lib.qsb_session_step.argtypes = [vp, C.c_int64, dp, C.POINTER(_Stats), dp]
+    lib.qsb_session_observe.argtypes = [vp, dp]
+    lib.qsb_session_state.argtypes = [vp, dp]
+    lib.qsb_session_end.argtypes = [vp]
+    _lib = lib
+    return lib
+
+
+def _check(code: int) -> None:
+    if code == 0:
+        return
+    msg = load_library().qsb_last_error().decode("utf-8", "replace")
+    if code in (2, 3):
+        raise IntegratorError(code, msg)
+    if code == 1:
+        raise ValueError(f"libqsb200: {msg}")
+    raise EngineError(code, msg)
+
+
+def device_count() -> int:
+    n = C.c_int(0)
+    _check(load_library().qsb_device_count(C.byref(n)))
+    return n.value
+
+
+def _dptr(a: np.ndarray):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+@dataclass
+class SolverOptions:
+    atol: float = DEFAULT_ATOL
+    rtol: float = DEFAULT_RTOL
+    max_step: float = 0.0
+    nsteps: int = DEFAULT_NSTEPS
+    method: str = "dp5"
+    order: int = 0
+    first_step: float = 0.0
+
+    def to_c(self) -> _Opts:
+        return _Opts(float(self.atol), float(self.rtol), float(self.max_step or 0.0), int(self.nsteps or 0),
+                     _METHODS[self.method], int(self.order), float(self.first_step or 0.0))
+
+
+@dataclass
+class Stats:
+    n_accepted: int
+    n_rejected: int
+    n_rhs: int
+    last_h: float
+    device_ms: float
+    path: int
+    status: int
+
+    @classmethod
+    def from_c(cls, s: _Stats) -> "Stats":
+        return cls(s.n_accepted, s.n_rejected, s.n_rhs, s.last_h, s.device_ms, s.path, s.status)
+
+
+class _TableHolder:
+    """Keeps the numpy arrays behind a C qsb_table alive."""
+
+    def __init__(self, table: SpinTable):
+        bm = table.bit_major()
+        self.h = np.ascontiguousarray(bm["h"], dtype=np.float64)
+        self.J = np.ascontiguousarray(bm["J"], dtype=np.float64)
+        self.c = _Table(table.n, _dptr(self.h), _dptr(self.J), table.sea_mask, table.rare_mask)
+
+
+class Plan:
+    """One compiled coupling table on one device (qsb_plan)."""
+
+    def __init__(self, table: SpinTable, device: int = 0):
+        self.lib = load_library()
+        self.table = table
+        self._holder = _TableHolder(table)
+        self._h = C.c_void_p()
+        self._ws = None
+        _check(self.lib.qsb_plan_create(C.byref(self._holder.c), int(device), C.byref(self._h)))
+
+    def close(self) -> None:
+        if self._h:
+            self.lib.qsb_plan_destroy(self._h)
+            self._h = C.c_void_p()
+            self._ws = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def workspace_bytes(self, method: str = "dp5", order: int = 0) -> int:
+        n = C.c_size_t(0)
+        _check(self.lib.qsb_plan_workspace_bytes(self._h, _METHODS[method], order, C.byref(n)))
+        return n.value
+
+    def use_torch_workspace(self, method: str = "dp5", device: Optional[int] = None) -> None:
+        """Allocate the HBM workspace through torch's caching allocator instead of cudaMalloc."""
+        import torch
+
+        need = self.workspace_bytes(method)
+        if need == 0:
+            return
+        dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+        self._ws = torch.empty(need + 256, dtype=torch.uint8, device=dev)
+        ptr = (self._ws.data_ptr() + 255) & ~255
+        _check(self.lib.qsb_plan_set_workspace(self._h, C.c_void_p(ptr), need))
+
+    # ---- the hot path ----------------------------------------------------------------------------
+    def evolve(self, t_out: np.ndarray, opts: SolverOptions, psi0: Optional[np.ndarray] = None):
+        t_out = np.ascontiguousarray(t_out, dtype=np.float64)
+        obs = np.empty((len(t_out), NOBS), dtype=np.float64)
+        st = _Stats()
+        copts = opts.to_c()
+        psi_ptr = None
+        if psi0 is not None:
+            psi0 = np.ascontiguousarray(psi0, dtype=np.complex128)
+            if psi0.shape != (self.table.dim,):
+                raise ValueError("psi0 must have 2^n amplitudes")
+            psi_ptr = psi0.view(np.float64).ctypes.data_as(C.POINTER(C.c_double))
+        _check(self.lib.qsb_evolve(self._h, self.table.psi0_index, psi_ptr, len(t_out), _dptr(t_out),
+                                   C.byref(copts), _dptr(obs), C.byref(st)))
+        return obs, Stats.from_c(st)
+
+    def apply_h(self, psi: np.ndarray) -> np.ndarray:
+        psi = np.ascontiguousarray(psi, dtype=np.complex128)
+        if psi.shape != (self.table.dim,):
+            raise ValueError("psi must have 2^n amplitudes")
+        out = np.empty_like(psi)
+        _check(self.lib.qsb_apply_h(self._h, _dptr(psi.view(np.float64)), _dptr(out.view(np.float64))))
+        return out
+
+    # ---- stepping session (tiled path) -------------------------------------------------------------
+    def session_begin(self, opts: SolverOptions, t0: float = 0.0, psi0: Optional[np.ndarray] = None) -> None:
+        copts = opts.to_c()
+        ptr = None
+        if psi0 is not None:
+            psi0 = np.ascontiguousarray(psi0, dtype=np.complex128)
+            ptr = _dptr(psi0.view(np.float64))
+        _check(self.lib.qsb_session_begin(self._h, self.table.psi0_index, ptr, float(t0), C.byref(copts)))
+
+    def session_step(self, n_attempts: int):
+        t = C.c_double(0.0)
+        ms = C.c_double(0.0)
+        st = _Stats()
+        _check(self.lib.qsb_session_step(self._h, int(n_attempts), C.byref(t), C.byref(st), C.byref(ms)))
+        return t.value, Stats.from_c(st), ms.value
+
+    def session_observe(self) -> np.ndarray:
+        obs = np.empty(NOBS, dtype=np.float64)
+        _check(self.lib.qsb_session_observe(self._h, _dptr(obs)))
+        return obs
+
+    def session_state(self) -> np.ndarray:
+        out = np.empty(self.table.dim, dtype=np.complex128)
+        _check(self.lib.qsb_session_state(self._h, _dptr(out.view(np.float64))))
+        return out
+
+    def session_end(self) -> None:
+        _check(self.lib.qsb_session_end(self._h))
+
+
+def evolve_batch(tables: Sequence[SpinTable], t_out: np.ndarray, opts: Sequence[SolverOptions], device: int = 0):
+    """Many n <= 10 trajectories in one launch (one CTA each).  t_out: (n_out,) shared or (n_traj, n_out)."""
+    lib = load_library()
+    n = len(tables)
+    if n == 0:
+        return np.empty((0, 0, NOBS)), []
+    t_out = np.ascontiguousarray(t_out, dtype=np.float64)
+    per_traj = 1 if t_out.ndim == 2 else 0
+    n_out = t_out.shape[-1]
+    holders = [_TableHolder(t) for t in tables]
+    ctabs = (_Table * n)(*[h.c for h in holders])
+    psi0 = (C.c_uint64 * n)(*[t.psi0_index for t in tables])
+    copts = (_Opts * n)(*[o.to_c() for o in opts])
+    cstats = (_Stats * n)()
+    obs = np.empty((n, n_out, NOBS), dtype=np.float64)
+    code = lib.qsb_evolve_batch(n, ctabs, psi0, n_out, _dptr(t_out), per_traj, copts, _dptr(obs), cstats, int(device))
+    stats = [Stats.from_c(s) for s in cstats]
+    _check(code)
+    return obs, stats

@@ -1,0 +1,50 @@
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+    config.addinivalue_line("markers", "reference: needs /root/reference (build container only)")
+
+
+@pytest.fixture(scope="session")
+def golden_cases():
+    with open(os.path.join(GOLDEN, "traj_cases.json")) as f:
+        meta = json.load(f)
+    arrs = np.load(os.path.join(GOLDEN, "traj_cases.npz"))
+    return meta, arrs
+
+
+@pytest.fixture(scope="session")
+def golden_hams():
+    return np.load(os.path.join(GOLDEN, "hamiltonians.npz"))
+
+
+def params_from_meta(meta_entry):
+    from quantumsimulations_b200 import DipolarRareParams
+
+    return DipolarRareParams(**meta_entry["params"])
+
+
+def random_table(n, seed, dense_pairs=True):
+    """Random XYZ table (all three axes populated) as a SpinTable, plus bit-major arrays."""
+    from quantumsimulations_b200.table import SpinTable
+
+    rng = np.random.default_rng(seed)
+    hx, hy, hz = rng.normal(size=(3, n))
+    def tri():
+        m = np.triu(rng.normal(size=(n, n)), 1)
+        if not dense_pairs:
+            m *= rng.random((n, n)) < 0.4
+        return m
+    sea = list(range(n - 1))
+    return SpinTable(n, hx, hy, hz, tri(), tri(), tri(), sea, n - 1, int(rng.integers(0, 1 << n)))
