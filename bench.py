@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""Benchmark of the hot path (see DESIGN.md "Measurement").
+
+    python bench.py --gpus N --steps K --warmup W            # B200 engine (one rank per GPU under torchrun)
+    python bench.py --impl reference --gpus N --steps K ...  # CPU reference arm (rank 0 only)
+
+Workload (config.workload = "C4"): one trajectory of the reference's Ga/Al geometry at n_sea = 27 (N = 28
+spins, 4.3 GB state vector, Fibonacci shell of dipolar_ensemble_with_rare.py:232-247), sea detuning
+50 kHz (+12.5 kHz per extra rank: independent sweep points, no collective), rare drive ON, the sweep's
+tolerances atol 1e-10 / rtol 1e-9.  A "step" is one Dormand-Prince 5(4) step attempt = 6 H-applies.
+The N = 7 detuning sweep (C2, CI-sized window) is timed as well and reported under "sweep".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+G_SEA, G_RARE, B0_T, F1A = 8.1812e7, 6.976e7, 3.0, 50_000.0
+
+
+def sweep_params(n_sea, delta_hz, variant="center_on", t_final=3.0e-2, steps=2000, f1a=F1A):
+    """DipolarRareParams as sweep_sea_detuning.py:414-668 derives them."""
+    from quantumsimulations_b200 import DipolarRareParams
+
+    f_az = G_SEA * B0_T / (2 * np.pi)
+    f1r = (f1a**2 + f1a**2) ** 0.5
+    b0 = 2 * np.pi * f_az / G_SEA
+    f_rz = G_RARE * b0 / (2 * np.pi)
+    return DipolarRareParams(
+        n_sea=n_sea, gamma_sea=G_SEA, gamma_rare=G_RARE, B0_sea=b0, B0_rare=b0,
+        B1_sea=2 * np.pi * f1a / G_SEA, B1_rare=2 * np.pi * f1r / G_RARE,
+        omega_rf_sea=2 * np.pi * (f_az - delta_hz), omega_rf_rare=2 * np.pi * f_rz,
+        phi_sea=np.pi / 2.0, phi_rare=np.pi / 2.0, dipolar_scale=1.0e-7 * 1.054571817e-34,
+        shell_scale=0.282393e-9, t_final=t_final, steps=steps, drive_sea=True,
+        drive_rare=(variant == "center_on"), is_spin_three_half=False, is_center_rare=(variant != "shell_off"),
+        solver_atol=1e-10, solver_rtol=1e-9, solver_nsteps=10_000_000, solver_max_step=1e-5,
+    )
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._pump, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc:
+            self.proc.terminate()
+            self.th.join(timeout=2)
+
+    def summary(self):
+        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = sorted({n for r in self.rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v == "Active"})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic():
+    """Per-launch DRAM bytes of the dominant kernel from the committed ncu capture, if any."""
+    path = os.path.join(ROOT, "profiles", "ncu_summary.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f)
+    return None
+
+
+# --------------------------------------------------------------------------------------------------------
+# CPU baseline (oracle port): the row-gather product a CSR matvec performs, matrix-free, OpenMP on all cores
+# --------------------------------------------------------------------------------------------------------
+def cpu_port_step_rate(n_sea, delta_hz, budget_s=15.0, samples=1):
+    from oracle.c import build as oc
+    from quantumsimulations_b200 import compile_table
+
+    table = compile_table(sweep_params(n_sea, delta_hz))
+    bm = table.bit_major()
+    n = table.n
+    psi = np.zeros(1 << n, dtype=np.complex128)
+    rng = np.random.default_rng(0)
+    psi[: 1 << 20] = rng.normal(size=1 << 20) + 1j * rng.normal(size=1 << 20)
+    psi[table.psi0_index] = 1.0
+    rows = 1 << 16
+    t0 = time.perf_counter()
+    oc.apply_h(bm["h"], bm["J"], psi, 0, rows)
+    per_row = (time.perf_counter() - t0) / rows
+    rows = int(min(1 << n, max(1 << 16, budget_s / samples / per_row)))
+    rows = 1 << (rows.bit_length() - 1)
+    rates, secs = [], []
+    for s in range(samples):
+        row0 = (s * rows) % (1 << n)
+        t0 = time.perf_counter()
+        oc.apply_h(bm["h"], bm["J"], psi, row0, row0 + rows)
+        dt = time.perf_counter() - t0
+        secs.append(dt)
+        rates.append(1.0 / (6.0 * dt * (1 << n) / rows))   # 6 H-applies per DP5 step attempt; axpys not charged
+    return {"value": float(np.mean(rates)), "unit": "ODE steps/s", "cores": oc.max_threads(), "kind": "port",
+            "sample": f"rows [0,2^{rows.bit_length()-1}) of one matrix-free H-apply at N={n} "
+                      f"({np.mean(secs):.1f} s each, x{samples}), scaled to 6 full H-applies per DP5 step; "
+                      "stage axpys not charged to the CPU",
+            "seconds_per_sample": secs}
+
+
+def cpu_zvode_rate(window=2.0e-3):
+    """Reference-equivalent integrator (SciPy zvode-Adams as QuTiP drives it) on one N=7 sweep point, 1 core."""
+    from oracle import dense, solvers
+    from quantumsimulations_b200 import compile_table
+
+    p = sweep_params(6, 50e3, t_final=window, steps=21)
+    table = compile_table(p)
+    bm = table.bit_major()
+    H = dense.csr_from_table(bm["h"], bm["J"])
+    psi0 = np.zeros(table.dim, complex)
+    psi0[table.psi0_index] = 1.0
+    t = np.linspace(0, p.t_final, p.steps)
+    t0 = time.perf_counter()
+    _, _, _, st = solvers.evolve_csr(H, psi0, t, [], backend="zvode", atol=p.solver_atol, rtol=p.solver_rtol,
+                                     nsteps=p.solver_nsteps, max_step=p.solver_max_step)
+    dt = time.perf_counter() - t0
+    return {"steps_per_s_1core": st["n_steps"] / dt, "rhs_per_s_1core": st["n_rhs"] / dt, "window_s": window,
+            "n_steps": st["n_steps"], "kind": "port (SciPy zvode-Adams, QuTiP's default integrator)"}
+
+
+# --------------------------------------------------------------------------------------------------------
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    n_sea = args.n_qubits - 1
+    base = cpu_port_step_rate(n_sea, 50e3, budget_s=max(5.0, 20.0 * args.steps), samples=max(1, args.steps))
+    ms = 1e3 / base["value"]
+    line = {
+        "impl": "reference", "metric": "ODE steps/s", "value": base["value"], "unit": "ODE steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"C4: single trajectory N={args.n_qubits} (n_sea={n_sea}), DP5 step attempts, CPU port",
+                   "n_qubits": args.n_qubits, "timing": "bounded row sample of one H-apply per step, extrapolated"},
+        "cpu_baseline": base,
+        "e2e": {"value": base["value"], "unit": "ODE steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args, rank, world, local_rank):
+    import torch
+
+    from quantumsimulations_b200 import compile_table, engine, simulate_rare_batch
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n = args.n_qubits
+    n_sea = n - 1
+    delta = 50e3 + 12.5e3 * rank
+    params = sweep_params(n_sea, delta)
+    table = compile_table(params)
+    opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, max_step=1e-5, nsteps=0, method=args.method)
+    S = 16.0 * (1 << n)
+    n_rhs = 6 if args.method == "dp5" else 12
+
+    plan = engine.Plan(table, local_rank)
+    plan.use_torch_workspace(args.method, local_rank)
+    plan.session_begin(opts)
+    plan.session_step(args.warmup)
+    barrier()
+    with ClockSampler(local_rank) as clk:
+        t_now, st, ms = plan.session_step(args.steps)
+    barrier()
+    ms_max = allmax(ms)
+    value = world * args.steps / (ms_max / 1e3)
+    obs = plan.session_observe()
+    t_end = t_now
+
+    line = None
+    if rank == 0:
+        # ---- per-kernel shares (separate, serialised pass: never part of the timed number) ----------------
+        engine.profile(True)
+        plan.session_step(2)
+        kms, kcnt = engine.profile_read()
+        engine.profile(False)
+        tot = sum(kms.values()) or 1.0
+        moved = {"pass_first": 3.0, "pass_mid": 4.0, "pass_centre": 4.0, "pass_last": None}
+        kernels = {}
+        for k in kms:
+            if kcnt[k]:
+                avg = kms[k] / kcnt[k]
+                kernels[k] = {"launches_per_step": kcnt[k] / 2.0, "avg_ms": avg, "share": kms[k] / tot}
+                if moved[k]:
+                    kernels[k]["moved_GBps"] = moved[k] * S / (avg * 1e-3) / 1e9
+        dominant = max(kernels, key=lambda k: kernels[k]["share"]) if kernels else None
+        peak, how = measured_peak()
+        alg_bytes_step = (n_rhs + 1) * 2.0 * S
+        achieved = alg_bytes_step * args.steps / (ms / 1e3) / 1e9
+        prof = ncu_traffic()
+        roofline = {
+            "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": (prof or {}).get("dram_bytes_per_step"), "peak_source": how,
+            "kernel": "one DP5 step attempt = 6 H-applies (pass_first/mid/centre/mid/last) + fused stage algebra",
+            "algorithmic_bytes_per_step": alg_bytes_step, "dominant_kernel": dominant, "kernels": kernels,
+        }
+    plan.session_end()
+    plan.close()
+
+    # ---- end to end through the public call: plan creation, table upload, evolve, observables back --------
+    barrier()
+    t_out = np.array([0.0, t_end])
+    t0 = time.perf_counter()
+    with engine.Plan(table, local_rank) as p2:
+        obs2, st2 = p2.evolve(t_out, opts)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    e2e_s = allmax(e2e_s)
+    attempts2 = st2.n_accepted + st2.n_rejected
+    bm = table.bit_major()
+    h2d = bm["h"].nbytes + bm["J"].nbytes + 3 * 4096 * 8 + t_out.nbytes
+    d2h = obs2.nbytes + 10 * 8 * attempts2
+    e2e = {"value": world * attempts2 / e2e_s, "unit": "ODE steps/s", "h2d_bytes_per_step": h2d / attempts2,
+           "d2h_bytes_per_step": d2h / attempts2, "steps": attempts2, "seconds": e2e_s,
+           "call": "engine.Plan(table).evolve(t_out, opts) [what simulate_rare() runs], host in / host out"}
+
+    # ---- C2 sweep (CI-sized window), trajectories sharded round-robin over ranks, no collective ----------
+    dets = np.linspace(0.0, 3.0 * F1A, 13)
+    plist = [sweep_params(6, d, v) for d in dets for v in ("center_off", "center_on", "shell_off")]
+    mine = plist[rank::world]
+    barrier()
+    t0 = time.perf_counter()
+    res, sst = simulate_rare_batch(mine, device=local_rank) if mine else ([], [])
+    sweep_s = allmax(time.perf_counter() - t0)
+    sweep_steps = float(sum(s.n_accepted + s.n_rejected for s in sst))
+    sweep_kernel_ms = max([s.device_ms for s in sst], default=0.0)
+    if dist is not None:
+        tt = torch.tensor([sweep_steps], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt)
+        sweep_steps = float(tt.item())
+        sweep_kernel_ms = allmax(sweep_kernel_ms)
+
+    if rank == 0:
+        launches_per_step = 1 + n_rhs * kernels_per_apply(n) + 1 if args.method == "dp5" else n_rhs * kernels_per_apply(n) + 2
+        cpu = cpu_port_step_rate(n_sea, 50e3) if world == 1 and not args.no_cpu else None
+        zv = cpu_zvode_rate() if world == 1 and not args.no_cpu else None
+        line = {
+            "metric": "ODE steps/s", "value": value, "unit": "ODE steps/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"C4: single trajectory per GPU, N={n} spins (n_sea={n_sea}, Ga/Al constants, "
+                                   f"delta=50 kHz + 12.5 kHz*rank, rare drive ON), {args.method} step attempts",
+                       "n_qubits": n, "state_bytes": S, "method": args.method, "atol": 1e-10, "rtol": 1e-9,
+                       "l2": "inputs larger than L2 (4.3 GB vectors vs 126 MB)", "parallelism": f"independent sweep points x{world}"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps),
+            "clocks": clk.summary(),
+            "accepted": st.n_accepted, "rejected": st.n_rejected, "rhs": st.n_rhs, "t_reached": t_end,
+            "raw_norm": float(obs[7]),
+            "sweep": {"workload": "C2 (CI-sized): 13 detunings x 3 variants, N=7, t_final=0.03 s, 2000 outputs, "
+                                  "atol 1e-10 / rtol 1e-9, one CTA per trajectory",
+                      "trajectories": len(plist), "wall_s": sweep_s, "kernel_ms": sweep_kernel_ms,
+                      "steps_per_s": sweep_steps / sweep_s, "total_steps": sweep_steps, "cpu_zvode": zv},
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def kernels_per_apply(n):
+    rest = n - 12
+    groups = (rest + 7) // 8 if rest > 0 else 1
+    return 2 + 1 + 2 * (groups - 1)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n-qubits", type=int, default=28)
+    ap.add_argument("--method", default="dp5", choices=["dp5", "taylor"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline legs")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_b200(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -129,6 +129,13 @@ int qsb_session_observe(qsb_plan* plan, double* obs);
 int qsb_session_state(qsb_plan* plan, double* psi_host);
 int qsb_session_end(qsb_plan* plan);
 
+
+/* Benchmark aid: when enabled, every launch of the tiled H-apply is bracketed by CUDA events on its stream
+ * (this serialises host and device; never enable it inside a timed throughput run).  ms4/count4: summed
+ * milliseconds and launch counts of pass_first, pass_mid, pass_centre, pass_last since the last enable.    */
+int qsb_profile(int enable);
+int qsb_profile_read(double* ms4, int64_t* count4);
+
 #ifdef __cplusplus
 }
 #endif

@@ -132,6 +132,19 @@ int qsb_evolve(qsb_plan* p, uint64_t psi0_index, const double* psi0_host, int64_
   return rc;
 }
 
+int qsb_profile(int enable) {
+  Profile& pr = profile();
+  pr.on = enable != 0;
+  for (int i = 0; i < 4; ++i) { pr.ms[i] = 0.0; pr.count[i] = 0; }
+  return QSB_OK;
+}
+
+int qsb_profile_read(double* ms4, int64_t* count4) {
+  if (!ms4 || !count4) return fail(QSB_ERR_BAD_ARG, "null argument");
+  for (int i = 0; i < 4; ++i) { ms4[i] = profile().ms[i]; count4[i] = profile().count[i]; }
+  return QSB_OK;
+}
+
 int qsb_apply_h(qsb_plan* p, const double* psi_host, double* out_host) {
   if (!p || !psi_host || !out_host) return fail(QSB_ERR_BAD_ARG, "null argument");
   QSB_CUDA(cudaSetDevice(p->device));

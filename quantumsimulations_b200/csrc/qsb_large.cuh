@@ -72,4 +72,12 @@ void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out
 void launch_set_basis_state(cplx* psi, uint64_t dim, uint64_t index, cudaStream_t stream);
 size_t happly_smem_bytes();
 
+// Per-kernel-class CUDA-event timing (bench.py's roofline leg).  Classes: 0 first, 1 mid, 2 centre, 3 last.
+struct Profile {
+  bool on = false;
+  double ms[4] = {0, 0, 0, 0};
+  long long count[4] = {0, 0, 0, 0};
+};
+Profile& profile();
+
 }  // namespace qsb

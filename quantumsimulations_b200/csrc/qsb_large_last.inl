@@ -103,6 +103,34 @@ __global__ void set_basis_kernel(cplx* psi, uint64_t dim, uint64_t index) {
 
 size_t happly_smem_bytes() { return 2 * (size_t)TILE_PHYS * sizeof(cplx); }
 
+Profile& profile() {
+  static Profile p;
+  return p;
+}
+
+namespace {
+// Times one launch with CUDA events on its own stream when profiling is on (serialises; bench-only).
+struct Timed {
+  int cls;
+  cudaStream_t st;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  Timed(int c, cudaStream_t s) : cls(c), st(s) {
+    if (profile().on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, st); }
+  }
+  ~Timed() {
+    if (e0) {
+      cudaEventRecord(e1, st);
+      cudaEventSynchronize(e1);
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, e0, e1);
+      profile().ms[cls] += ms;
+      profile().count[cls] += 1;
+      cudaEventDestroy(e0); cudaEventDestroy(e1);
+    }
+  }
+};
+}  // namespace
+
 void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
                    const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream) {
   static bool attr = false;
@@ -119,11 +147,11 @@ void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, c
   a.tab = tab;
   const unsigned n_tiles = 1u << (g.n - TB);
   const int centre = g.n_layouts - 1;
-  pass_first<<<n_tiles, 2 * TPT, sm2, stream>>>(a, src, tx, ty, collect_obs, partials);
-  for (int k = 1; k < centre; ++k) pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty);
-  pass_centre<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], tx, ty, collect_obs, partials);
-  for (int k = centre - 1; k >= 1; --k) pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty);
-  pass_last<<<n_tiles, 2 * TPT, sm2, stream>>>(a, src, tx, ty, ep, partials);
+  { Timed t(0, stream); pass_first<<<n_tiles, 2 * TPT, sm2, stream>>>(a, src, tx, ty, collect_obs, partials); }
+  for (int k = 1; k < centre; ++k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty); }
+  { Timed t(2, stream); pass_centre<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], tx, ty, collect_obs, partials); }
+  for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty); }
+  { Timed t(3, stream); pass_last<<<n_tiles, 2 * TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); }
 }
 
 void launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,

@@ -57,7 +57,7 @@ class _Stats(C.Structure):
 EXPORTS = (
     "qsb_version", "qsb_last_error", "qsb_device_count", "qsb_plan_create", "qsb_plan_destroy",
     "qsb_plan_workspace_bytes", "qsb_plan_set_workspace", "qsb_evolve", "qsb_evolve_batch", "qsb_apply_h",
-    "qsb_session_begin", "qsb_session_step", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
+    "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
 )
 
 _lib = None
@@ -91,6 +91,8 @@ def load_library() -> C.CDLL:
     lib.qsb_session_observe.argtypes = [vp, dp]
     lib.qsb_session_state.argtypes = [vp, dp]
     lib.qsb_session_end.argtypes = [vp]
+    lib.qsb_profile.argtypes = [C.c_int]
+    lib.qsb_profile_read.argtypes = [dp, C.POINTER(C.c_int64)]
     _lib = lib
     return lib
 
@@ -104,6 +106,19 @@ def _check(code: int) -> None:
     if code == 1:
         raise ValueError(f"libqsb200: {msg}")
     raise EngineError(code, msg)
+
+
+def profile(enable: bool) -> None:
+    _check(load_library().qsb_profile(1 if enable else 0))
+
+
+def profile_read():
+    """({class: summed ms}, {class: launches}) of the tiled H-apply kernels since profile(True)."""
+    ms = (C.c_double * 4)()
+    cnt = (C.c_int64 * 4)()
+    _check(load_library().qsb_profile_read(ms, cnt))
+    names = ("pass_first", "pass_mid", "pass_centre", "pass_last")
+    return dict(zip(names, list(ms))), dict(zip(names, list(cnt)))
 
 
 def device_count() -> int:
