@@ -160,7 +160,7 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
     small = [i for i in range(n) if tables[i].n <= engine.SMALL_MAX_QUBITS]
     groups: Dict[int, List[int]] = {}
     for i in small:
-        groups.setdefault(len(grids[i]), []).append(i)
+        groups.setdefault((tables[i].n, len(grids[i])), []).append(i)  # uniform n -> register-resident rows
     stats_out: List = [None] * n
     for _, idxs in groups.items():
         tgrid = np.stack([grids[i] for i in idxs])

@@ -87,6 +87,8 @@ static void compile_small(const qsb_table* t, uint64_t psi0, const qsb_solver_op
   int pi = 0;
   for (int b = 0; b < n; ++b) {
     d->hz_half[b] = 0.5 * hz[b];
+    d->hx_half[b] = 0.5 * hx[b];
+    d->hy_half[b] = 0.5 * hy[b];
     if (hx[b] != 0.0 || hy[b] != 0.0) {
       SmallFlip& f = d->flip[d->n_flip++];
       f.hxh = 0.5 * hx[b]; f.hyh = 0.5 * hy[b]; f.mask = 1u << b;
@@ -94,6 +96,8 @@ static void compile_small(const qsb_table* t, uint64_t psi0, const qsb_solver_op
     for (int c = b + 1; c < n; ++c, ++pi) {
       d->jzz_quarter[pi] = 0.25 * jz[b * n + c];
       double xx = jx[b * n + c], yy = jy[b * n + c];
+      d->pair_same[pi] = 0.25 * (xx - yy);
+      d->pair_diff[pi] = 0.25 * (xx + yy);
       if (xx != 0.0 || yy != 0.0) {
         SmallPair& p = d->pair[d->n_pair++];
         p.c_same = 0.25 * (xx - yy); p.c_diff = 0.25 * (xx + yy); p.mask = (1u << b) | (1u << c);

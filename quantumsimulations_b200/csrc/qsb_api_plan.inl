@@ -158,7 +158,7 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
                      qsb_stats* stats, int device) {
   if (n_traj < 1 || !tables || !psi0_index || !opts || !out_obs)
     return fail(QSB_ERR_BAD_ARG, "qsb_evolve_batch: null argument or n_traj < 1");
-  int max_n = 0;
+  int max_n = 0, min_n = QSB_MAX_QUBITS;
   for (int i = 0; i < n_traj; ++i) {
     int rc = check_table(&tables[i]);
     if (rc) return rc;
@@ -171,6 +171,7 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
     rc = check_grid(n_out, t_out + (t_out_per_traj ? (size_t)i * n_out : 0));
     if (rc) return rc;
     max_n = std::max(max_n, tables[i].n_qubits);
+    min_n = std::min(min_n, tables[i].n_qubits);
   }
   int rc = pick_device(device);
   if (rc) return rc;
@@ -194,7 +195,7 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
   QSB_CUDA(cudaMemcpyAsync(d_desc, descs.data(), sizeof(SmallDesc) * n_traj, cudaMemcpyHostToDevice, st));
   QSB_CUDA(cudaMemcpyAsync(d_t, t_out, sizeof(double) * nt, cudaMemcpyHostToDevice, st));
   QSB_CUDA(cudaEventRecord(e0, st));
-  launch_small_evolve(d_desc, n_traj, max_n, d_t, n_out, d_obs, d_stats, st);
+  launch_small_evolve(d_desc, n_traj, max_n, min_n == max_n, d_t, n_out, d_obs, d_stats, st);
   QSB_CUDA(cudaGetLastError());
   QSB_CUDA(cudaEventRecord(e1, st));
   std::vector<SmallStats> hs(n_traj);

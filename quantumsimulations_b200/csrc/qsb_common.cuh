@@ -72,7 +72,12 @@ __host__ __device__ inline DP5 dp5_tableau() {
 struct Controller {
   static constexpr double safety = 0.9, fac_min = 0.2, fac_max = 5.0;
   __host__ __device__ static double factor(double err, double inv_q, bool after_reject) {
-    double f = (err > 0.0) ? safety * pow(err, -inv_q) : fac_max;
+    // single precision is plenty for a step-size factor and ~30x cheaper than double pow on the device
+#ifdef __CUDA_ARCH__
+    double f = (err > 0.0) ? safety * (double)__powf((float)err, -(float)inv_q) : fac_max;
+#else
+    double f = (err > 0.0) ? safety * (double)powf((float)err, -(float)inv_q) : fac_max;
+#endif
     f = f < fac_min ? fac_min : f;
     double cap = after_reject ? 1.0 : fac_max;
     return f > cap ? cap : f;

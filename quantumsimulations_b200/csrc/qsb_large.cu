@@ -98,7 +98,11 @@ __device__ __forceinline__ uint64_t gidx(const Layout& L, uint64_t base, int i) 
   return (uint64_t)(i & ((1 << L.lk) - 1)) | ((uint64_t)(i >> L.lk) << L.gs) | base;
 }
 
-// 16-point Walsh-Hadamard butterflies on the stages selected by mask (unnormalised).
+// 16-point butterflies on the stages selected by mask (all unnormalised):
+//   MODE 0  Hadamard           (a,b) -> (a+b, a-b)
+//   MODE 1  M  = H S H         (a,b) -> (p+iq, p-iq),  p = a+b, q = a-b      [W^-1 S W = (M/2)^(x n)]
+//   MODE 2  M' = H S^dagger H  (a,b) -> (p-iq, p+iq)
+template <int MODE>
 __device__ __forceinline__ void bfly16(cplx (&r)[16], int mask) {
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
@@ -107,8 +111,17 @@ __device__ __forceinline__ void bfly16(cplx (&r)[16], int mask) {
       for (int j = 0; j < 16; ++j) {
         if (!(j >> s & 1)) {
           cplx a = r[j], b = r[j | (1 << s)];
-          r[j] = a + b;
-          r[j | (1 << s)] = a - b;
+          cplx p = a + b, q = a - b;
+          if (MODE == 0) {
+            r[j] = p;
+            r[j | (1 << s)] = q;
+          } else if (MODE == 1) {
+            r[j] = mk(p.x - q.y, p.y + q.x);
+            r[j | (1 << s)] = mk(p.x + q.y, p.y - q.x);
+          } else {
+            r[j] = mk(p.x + q.y, p.y - q.x);
+            r[j | (1 << s)] = mk(p.x - q.y, p.y + q.x);
+          }
         }
       }
     }
@@ -125,11 +138,11 @@ __device__ __forceinline__ void smem_store16(cplx* sm, int tt, const cplx (&r)[1
 #pragma unroll
   for (int j = 0; j < 16; ++j) sm[phys(elem<W>(tt, j))] = r[j];
 }
-template <int W>
+template <int W, int MODE>
 __device__ __forceinline__ void smem_round(cplx* sm, int tt, int mask) {
   cplx r[16];
   smem_load16<W>(sm, tt, r);
-  bfly16(r, mask);
+  bfly16<MODE>(r, mask);
   smem_store16<W>(sm, tt, r);
 }
 

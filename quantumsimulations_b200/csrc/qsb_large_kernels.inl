@@ -1,4 +1,9 @@
 // Kernels of the tiled path; included at the end of qsb_large.cu.
+//
+// Every pass is one 256-thread CTA per 4096-amplitude tile with a single padded shared-memory buffer
+// (2 CTAs per SM).  The y-branch never needs its own copy of the layout-0 transform:
+//     W0 S0^dagger = (M'/2)^(x12) W0      and      S0 W0 = W0 (M/2)^(x12),
+// so pass_first derives tY from tX in place, and pass_last folds tY into tX before ONE inverse transform.
 namespace qsb {
 namespace {
 
@@ -7,49 +12,55 @@ struct PassArgs {
   DiagTables tab;
 };
 
+constexpr double INV_TILE = 1.0 / (double)TILE;  // the 2^-12 of (M/2)^(x12)
+
 // ---------------------------------------------------------------------------------------------------
-// pass_first: layout 0.  tX = W_g0 psi, tY = W_g0 S^dagger psi.  512 threads: threads 0-255 carry the
-// x-branch tile, 256-511 the y-branch tile.  Optionally the z-basis observable partial sums.
+// pass_first: layout 0.  tX = W0 psi;  tY = W0 S^dagger psi = c^dagger(v) (M'/2)^(x12) tX.
+// Optionally the z-basis observable partial sums.
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(2 * TPT, 1)
+__global__ void __launch_bounds__(TPT, 2)
 pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx* __restrict__ ty,
            int collect_obs, double* __restrict__ partials) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
   __shared__ double red[3 * 32 + 3];
-  const int half = threadIdx.x >> 8, tt = threadIdx.x & (TPT - 1);
-  cplx* mine = sm + half * TILE_PHYS;
+  const int tt = threadIdx.x;
   const uint64_t base = (uint64_t)blockIdx.x << TB;
   cplx r[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) r[j] = psi[base | (uint64_t)elem<8>(tt, j)];
   double s[3] = {0.0, 0.0, 0.0};
-  const int n_sea = __popcll(a.g.sea_mask);
+  if (collect_obs) {
+    const int n_sea = __popcll(a.g.sea_mask);
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    int i = elem<8>(tt, j);
-    uint64_t idx = base | (uint64_t)i;
-    cplx v = psi[idx];
-    if (half == 0) {
-      if (collect_obs) {
-        double p = norm2(v);
-        s[0] += p;
-        s[1] = fma(p, (double)sea_weight(idx, a.g.sea_mask, n_sea), s[1]);
-        s[2] += (idx & a.g.rare_mask) ? -p : p;
-      }
-    } else {
-      v = mul_mi_pow(v, __popcll(idx));
+    for (int j = 0; j < 16; ++j) {
+      uint64_t idx = base | (uint64_t)elem<8>(tt, j);
+      double p = norm2(r[j]);
+      s[0] += p;
+      s[1] = fma(p, (double)sea_weight(idx, a.g.sea_mask, n_sea), s[1]);
+      s[2] += (idx & a.g.rare_mask) ? -p : p;
     }
-    r[j] = v;
   }
-  bfly16(r, 0xF);
-  smem_store16<8>(mine, tt, r);
+  bfly16<0>(r, 0xF);
+  smem_store16<8>(sm, tt, r);
   __syncthreads();
-  smem_round<0>(mine, tt, 0xF);
+  smem_round<0, 0>(sm, tt, 0xF);
   __syncthreads();
-  smem_load16<4>(mine, tt, r);
-  bfly16(r, 0xF);
-  cplx* dst = half ? ty : tx;
+  smem_load16<4>(sm, tt, r);
+  bfly16<0>(r, 0xF);
 #pragma unroll
-  for (int j = 0; j < 16; ++j) dst[base | (uint64_t)elem<4>(tt, j)] = r[j];
+  for (int j = 0; j < 16; ++j) tx[base | (uint64_t)elem<4>(tt, j)] = r[j];
+  // y branch, continuing from the registers (each thread owns its window-4 elements: no barrier needed here)
+  bfly16<2>(r, 0xF);
+  smem_store16<4>(sm, tt, r);
+  __syncthreads();
+  smem_round<0, 2>(sm, tt, 0xF);
+  __syncthreads();
+  smem_load16<8>(sm, tt, r);
+  bfly16<2>(r, 0xF);
+  const int pv = __popcll(base);  // S_rest^dagger = (-i)^popcount(outer bits)
+#pragma unroll
+  for (int j = 0; j < 16; ++j) ty[base | (uint64_t)elem<8>(tt, j)] = mul_mi_pow(INV_TILE * r[j], pv);
   if (collect_obs) {
     block_reduce<3>(s, red);
     if (threadIdx.x == 0) {
@@ -72,15 +83,15 @@ pass_mid(Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty) {
   cplx r[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) r[j] = t[gidx(L, base, elem<8>(tt, j))];
-  bfly16(r, L.m8);
+  bfly16<0>(r, L.m8);
   smem_store16<8>(sm, tt, r);
   __syncthreads();
   if (L.m0) {
-    smem_round<0>(sm, tt, L.m0);
+    smem_round<0, 0>(sm, tt, L.m0);
     __syncthreads();
   }
   smem_load16<4>(sm, tt, r);
-  bfly16(r, L.m4);
+  bfly16<0>(r, L.m4);
 #pragma unroll
   for (int j = 0; j < 16; ++j) t[gidx(L, base, elem<4>(tt, j))] = r[j];
 }
@@ -93,7 +104,7 @@ template <int W>
 __device__ __forceinline__ void centre_core(cplx (&r)[16], int tt, int mask, const DiagShared& ds,
                                             const double* __restrict__ Q, const Layout& L, uint64_t base,
                                             const LargeGeom& g, int collect_obs, double (&s)[2]) {
-  bfly16(r, mask);
+  bfly16<0>(r, mask);
   const int n_sea = __popcll(g.sea_mask);
 #pragma unroll
   for (int j = 0; j < 16; ++j) {
@@ -106,7 +117,7 @@ __device__ __forceinline__ void centre_core(cplx (&r)[16], int tt, int mask, con
     }
     r[j] = diag_at(ds, Q, i) * r[j];
   }
-  bfly16(r, mask);
+  bfly16<0>(r, mask);
 }
 
 __global__ void __launch_bounds__(TPT, 2)
@@ -121,16 +132,17 @@ pass_centre(PassArgs a, Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty, 
   const double* Q = branch ? a.tab.Qy : a.tab.Qx;
   const int n = a.g.n, tt = threadIdx.x;
   const uint64_t base = tile_base(L, blockIdx.x);
-  diag_prologue(ds, a.tab.h + (size_t)branch * n, a.tab.J + (size_t)branch * n * n, n, L, base,
-                ldexp(1.0, -n), tt);
   cplx r[16];
   double s[2] = {0.0, 0.0};
 #pragma unroll
   for (int j = 0; j < 16; ++j) r[j] = t[gidx(L, base, elem<8>(tt, j))];
+  // the per-tile diagonal pieces are computed while the tile's loads are in flight
+  diag_prologue(ds, a.tab.h + (size_t)branch * n, a.tab.J + (size_t)branch * n * n, n, L, base,
+                ldexp(1.0, -n), tt);
   if (!L.m4 && !L.m0) {
     centre_core<8>(r, tt, L.m8, ds, Q, L, base, a.g, collect_obs, s);
   } else {
-    bfly16(r, L.m8);
+    bfly16<0>(r, L.m8);
     smem_store16<8>(sm, tt, r);
     __syncthreads();
     if (!L.m0) {
@@ -138,17 +150,17 @@ pass_centre(PassArgs a, Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty, 
       centre_core<4>(r, tt, L.m4, ds, Q, L, base, a.g, collect_obs, s);
       smem_store16<4>(sm, tt, r);
     } else {
-      smem_round<4>(sm, tt, L.m4);
+      smem_round<4, 0>(sm, tt, L.m4);
       __syncthreads();
       smem_load16<0>(sm, tt, r);
       centre_core<0>(r, tt, L.m0, ds, Q, L, base, a.g, collect_obs, s);
       smem_store16<0>(sm, tt, r);
       __syncthreads();
-      smem_round<4>(sm, tt, L.m4);
+      smem_round<4, 0>(sm, tt, L.m4);
     }
     __syncthreads();
     smem_load16<8>(sm, tt, r);
-    bfly16(r, L.m8);
+    bfly16<0>(r, L.m8);
   }
 #pragma unroll
   for (int j = 0; j < 16; ++j) t[gidx(L, base, elem<8>(tt, j))] = r[j];

@@ -3,46 +3,55 @@ namespace qsb {
 namespace {
 
 // ---------------------------------------------------------------------------------------------------
-// pass_last: layout 0.  k = -i (Dz v + W_g0 tX + S W_g0 tY), then the fused stage algebra (Epilogue):
-// o1 = alpha k, o2 = sum c_j vin_j + ck k, err += |sum e_j vin_j + ek k|^2 / sc^2.
-// 512 threads; both transformed tiles end up in shared memory, the combine phase then streams the other
-// vectors with fully coalesced accesses.
+// pass_last: layout 0.  k = -i (Dz v + W0 [tX + c(v) (M/2)^(x12) tY]), then the fused stage algebra
+// (Epilogue): o1 = alpha k, o2 = sum c_j vin_j + ck k, err += |sum e_j vin_j + ek k|^2 / sc^2.
+// The last butterfly round leaves thread t with amplitudes t + 256 j, so the epilogue streams the other
+// vectors straight from registers with fully coalesced accesses.
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(2 * TPT, 1)
+__global__ void __launch_bounds__(TPT, 2)
 pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* __restrict__ ty,
           Epilogue ep, double* __restrict__ partials) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
   __shared__ DiagShared ds;
   __shared__ double red[2 * 32 + 2];
-  const int half = threadIdx.x >> 8, tt = threadIdx.x & (TPT - 1);
-  cplx* mine = sm + half * TILE_PHYS;
+  const int tt = threadIdx.x;
   const uint64_t base = (uint64_t)blockIdx.x << TB;
   const int n = a.g.n;
-  {
-    cplx r[16];
-    const cplx* t = half ? ty : tx;
+  cplx r[16];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) r[j] = t[base | (uint64_t)elem<8>(tt, j)];
-    bfly16(r, 0xF);
-    smem_store16<8>(mine, tt, r);
+  for (int j = 0; j < 16; ++j) r[j] = ty[base | (uint64_t)elem<8>(tt, j)];
+  {  // pull the tX tile (needed three rounds from now) towards L2 while the tY loads are in flight
+    const char* p = reinterpret_cast<const char*>(tx + base) + (size_t)tt * 256;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128));
   }
-  diag_prologue(ds, a.tab.h + 2 * (size_t)n, a.tab.J + 2 * (size_t)n * n, n, a.g.lay[0], base, 1.0,
-                threadIdx.x);  // two __syncthreads inside: the window-8 stores are visible afterwards
-  smem_round<0>(mine, tt, 0xF);
+  diag_prologue(ds, a.tab.h + 2 * (size_t)n, a.tab.J + 2 * (size_t)n * n, n, a.g.lay[0], base, 1.0, tt);
+  bfly16<1>(r, 0xF);
+  smem_store16<8>(sm, tt, r);
   __syncthreads();
-  smem_round<4>(mine, tt, 0xF);
+  smem_round<0, 1>(sm, tt, 0xF);
   __syncthreads();
+  smem_load16<4>(sm, tt, r);
+  bfly16<1>(r, 0xF);
+  const int pv = __popcll(base);  // S_rest = (+i)^popcount(outer bits)
+#pragma unroll
+  for (int j = 0; j < 16; ++j) r[j] = mul_pi_pow(INV_TILE * r[j], pv) + tx[base | (uint64_t)elem<4>(tt, j)];
+  bfly16<0>(r, 0xF);
+  smem_store16<4>(sm, tt, r);
+  __syncthreads();
+  smem_round<0, 0>(sm, tt, 0xF);
+  __syncthreads();
+  smem_load16<8>(sm, tt, r);
+  bfly16<0>(r, 0xF);
 
   double err_acc = 0.0, aux_acc = 0.0;
-#pragma unroll 2
-  for (int jj = 0; jj < TILE / (2 * TPT); ++jj) {
-    const int i = threadIdx.x + jj * 2 * TPT;
+#pragma unroll 4
+  for (int j = 0; j < 16; ++j) {
+    const int i = elem<8>(tt, j);
     const uint64_t idx = base | (uint64_t)i;
     cplx v = src[idx];
-    cplx acc = diag_at(ds, a.tab.Qz, i) * v;
-    acc = acc + sm[phys(i)];
-    acc = acc + mul_pi_pow(sm[TILE_PHYS + phys(i)], __popcll(idx));
+    cplx acc = diag_at(ds, a.tab.Qz, i) * v + r[j];
     cplx k = ep.raw_h ? acc : mul_mi(acc);
     if (ep.o1) ep.o1[idx] = ep.alpha * k;
     if (ep.o2 || ep.want_err) {
@@ -101,7 +110,7 @@ __global__ void set_basis_kernel(cplx* psi, uint64_t dim, uint64_t index) {
 
 }  // namespace
 
-size_t happly_smem_bytes() { return 2 * (size_t)TILE_PHYS * sizeof(cplx); }
+size_t happly_smem_bytes() { return (size_t)TILE_PHYS * sizeof(cplx); }
 
 Profile& profile() {
   static Profile p;
@@ -134,7 +143,7 @@ struct Timed {
 void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
                    const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream) {
   static bool attr = false;
-  const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx), sm2 = 2 * sm1;
+  const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx), sm2 = sm1;
   if (!attr) {
     cudaFuncSetAttribute(pass_first, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     cudaFuncSetAttribute(pass_last, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
@@ -147,11 +156,11 @@ void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, c
   a.tab = tab;
   const unsigned n_tiles = 1u << (g.n - TB);
   const int centre = g.n_layouts - 1;
-  { Timed t(0, stream); pass_first<<<n_tiles, 2 * TPT, sm2, stream>>>(a, src, tx, ty, collect_obs, partials); }
+  { Timed t(0, stream); pass_first<<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, collect_obs, partials); }
   for (int k = 1; k < centre; ++k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty); }
   { Timed t(2, stream); pass_centre<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], tx, ty, collect_obs, partials); }
   for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty); }
-  { Timed t(3, stream); pass_last<<<n_tiles, 2 * TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); }
+  { Timed t(3, stream); pass_last<<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); }
 }
 
 void launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
@@ -159,7 +168,7 @@ void launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, 
   // the transform half of an H-apply: z sums in pass_first, x/y sums in pass_centre (tx/ty are clobbered)
   Epilogue none = {};
   (void)none;
-  const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx), sm2 = 2 * sm1;
+  const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx), sm2 = sm1;
   PassArgs a;
   a.g = g;
   a.tab = tab;
@@ -168,7 +177,7 @@ void launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, 
   cudaFuncSetAttribute(pass_first, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
   cudaFuncSetAttribute(pass_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
   cudaFuncSetAttribute(pass_centre, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
-  pass_first<<<n_tiles, 2 * TPT, sm2, stream>>>(a, src, tx, ty, 1, partials);
+  pass_first<<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, 1, partials);
   for (int k = 1; k < centre; ++k) pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty);
   pass_centre<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], tx, ty, 1, partials);
 }

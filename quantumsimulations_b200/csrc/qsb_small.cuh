@@ -26,6 +26,9 @@ struct SmallDesc {
   double jzz_quarter[SMALL_MAXPAIR];  // Jzz_bc / 4, (b<c) row-major
   SmallFlip flip[SMALL_MAXQ];
   SmallPair pair[SMALL_MAXPAIR];
+  // dense per-bit / per-bit-pair copies for the register-resident kernel (row-major b<c like jzz_quarter)
+  double hx_half[SMALL_MAXQ], hy_half[SMALL_MAXQ];
+  double pair_same[SMALL_MAXPAIR], pair_diff[SMALL_MAXPAIR];
 };
 
 struct SmallStats {
@@ -34,8 +37,9 @@ struct SmallStats {
   int32_t status, pad;
 };
 
-// Launch: one CTA per trajectory, blockDim.x = max(32, 2^max_n) over the batch.
-void launch_small_evolve(const SmallDesc* d_desc, int n_traj, int max_n, const double* d_t_out,
+// Launch: one CTA per trajectory, blockDim.x = max(32, 2^max_n) over the batch.  uniform_n != 0 promises
+// that every trajectory has exactly max_n qubits, which enables the register-resident row product (n <= 8).
+void launch_small_evolve(const SmallDesc* d_desc, int n_traj, int max_n, int uniform_n, const double* d_t_out,
                          int64_t n_out, double* d_obs, SmallStats* d_stats, cudaStream_t stream);
 
 // out = H in for one n <= 10 table (test hook: same RHS routine the trajectory kernel uses).

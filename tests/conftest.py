@@ -48,3 +48,21 @@ def random_table(n, seed, dense_pairs=True):
         return m
     sea = list(range(n - 1))
     return SpinTable(n, hx, hy, hz, tri(), tri(), tri(), sea, n - 1, int(rng.integers(0, 1 << n)))
+
+
+def exact_traces(table, t):
+    """Oracle X on a compiled table: dict of the six normalised traces (numpy index arithmetic + eigh)."""
+    from oracle import dense, solvers
+
+    bm = table.bit_major()
+    H = dense.csr_from_table(bm["h"], bm["J"])
+    psi0 = np.zeros(table.dim, complex)
+    psi0[table.psi0_index] = 1.0
+    states = solvers.exact_states(H, psi0, np.asarray(t))
+    keys = ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R")
+    out = {k: np.empty(len(t)) for k in keys}
+    for i in range(len(t)):
+        o = dense.observable_sums(states[:, i], table.sea_mask, table.rare_mask)
+        for k in keys:
+            out[k][i] = o[k]
+    return out

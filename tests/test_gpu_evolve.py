@@ -124,3 +124,40 @@ def test_deterministic(golden_cases):
     b = simulate_rare(p)[1]
     for k in KEYS:
         assert np.array_equal(a[k], b[k])
+
+
+def _sweep_like(n_sea, delta, variant="center_on", t_final=2e-4, steps=21, **kw):
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+
+    import dataclasses
+    return dataclasses.replace(bench.sweep_params(n_sea, delta, variant, t_final, steps), **kw)
+
+
+@pytest.mark.parametrize("n_sea,method", [(9, "dp5"), (9, "taylor"), (10, "dp5"), (11, "taylor")])
+def test_boundary_sizes_vs_oracle(n_sea, method):
+    """N = 10 (1024-thread on-chip CTA), N = 11 (padded to the 12-bit tile), N = 12 (single-tile tiled path)."""
+    from conftest import exact_traces
+    from quantumsimulations_b200 import compile_table, simulate_rare
+
+    p = _sweep_like(n_sea, 50e3, solver_atol=1e-12, solver_rtol=1e-11)
+    t, out, st = simulate_rare(p, method=method, return_stats=True)
+    want = exact_traces(compile_table(p), t)
+    dev = max(float(np.max(np.abs(out[k] - want[k]))) for k in KEYS)
+    assert dev < TOL, f"N={n_sea+1} {method}: {dev:.2e} {st}"
+    assert st.path == (0 if n_sea + 1 <= 10 else 1)
+
+
+def test_large_batch_matches_single_runs():
+    """A batch big enough to change the lanes-per-amplitude choice must give the same traces (to rounding)."""
+    from quantumsimulations_b200 import simulate_rare, simulate_rare_batch
+
+    dets = np.linspace(0.0, 150e3, 100)
+    plist = [_sweep_like(6, d, v) for d in dets for v in ("center_off", "center_on", "shell_off")]
+    res, stats = simulate_rare_batch(plist)
+    assert len(res) == 300
+    for i in (0, 17, 151, 299):
+        t, single = simulate_rare(plist[i])
+        for k in KEYS:
+            assert np.max(np.abs(res[i][1][k] - single[k])) < 1e-9
