@@ -65,7 +65,7 @@ typedef struct {
   double max_step;  /* hard cap on h; 0 = none                                                      */
   int64_t nsteps;   /* max internal steps per output interval (zvode MXSTEP semantics); 0 = no cap  */
   int32_t method;   /* qsb_method                                                                   */
-  int32_t order;    /* Taylor order p (4..30); ignored for DP5; 0 = default 12                      */
+  int32_t order;    /* Taylor order p (4..30); ignored for DP5; 0 = default 20                      */
   double first_step;/* 0 = automatic                                                                */
 } qsb_solver_opts;
 

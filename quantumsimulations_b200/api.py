@@ -99,7 +99,18 @@ def initial_state_rare(params: DipolarRareParams) -> np.ndarray:
     return psi
 
 
-def _options_from(params: DipolarRareParams, method: Optional[str]) -> Tuple[engine.SolverOptions, bool]:
+# Default integrator of the reference-facing calls.  H is time-independent in the reference (DE:514, DE:570), so
+# the order-p Taylor pair applies; measured on the sweep's own 12 golden points (profiles/r1_methods.log) it needs
+# ~10x fewer H-applies than DP5 at equal tolerances.  Its cost grows only logarithmically with the tolerance
+# (1.4x for 1000x tighter), while the reference's own trajectories are integrator-error-limited at its tolerances
+# (SURVEY.md TL;DR 6), so the requested atol/rtol are tightened by DEFAULT_TOL_SCALE before they reach the C ABI.
+DEFAULT_METHOD = "taylor"
+DEFAULT_TAYLOR_ORDER = 20
+DEFAULT_TOL_SCALE = {"taylor": 1e-3, "dp5": 1.0}
+
+
+def _options_from(params: DipolarRareParams, method: Optional[str], tol_scale: Optional[float] = None
+                  ) -> Tuple[engine.SolverOptions, bool]:
     """Map the reference's solver_* fields (DE:629-651); returns (options, any_override)."""
     knobs = (params.solver_atol, params.solver_rtol, params.solver_nsteps, params.solver_max_step)
     override = any(v is not None for v in knobs)
@@ -112,8 +123,12 @@ def _options_from(params: DipolarRareParams, method: Optional[str]) -> Tuple[eng
         o.nsteps = int(params.solver_nsteps)
     if params.solver_max_step is not None:
         o.max_step = params.solver_max_step
-    o.method = method or os.environ.get("QSB200_METHOD", "dp5")
-    o.order = int(os.environ.get("QSB200_TAYLOR_ORDER", "0"))
+    o.method = method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)
+    o.order = int(os.environ.get("QSB200_TAYLOR_ORDER", str(DEFAULT_TAYLOR_ORDER)))
+    if tol_scale is None:
+        tol_scale = float(os.environ.get("QSB200_TOL_SCALE", DEFAULT_TOL_SCALE[o.method]))
+    o.atol = max(o.atol * tol_scale, 1e-300)
+    o.rtol = max(o.rtol * tol_scale, 1e-14) if o.rtol > 0 else 0.0
     return o, override
 
 
@@ -133,14 +148,16 @@ def _pack(obs: np.ndarray, override: bool, extra: bool) -> Dict[str, np.ndarray]
 
 
 def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optional[str] = None,
-                  return_stats: bool = False, raw_norm: bool = False):
+                  tol_scale: Optional[float] = None, return_stats: bool = False, raw_norm: bool = False):
     """Time evolution on the B200 engine; returns ``(t, {6 traces + state_norm})`` like DE:611-680.
 
+    ``method``: "taylor" (default, order 20) or "dp5".  ``tol_scale`` multiplies solver_atol/solver_rtol before
+    they reach the integrator (default 1e-3 for taylor, 1 for dp5; see DEFAULT_TOL_SCALE).
     ``raw_norm=True`` adds the integrator's own norm under an extra key (QuTiP discards it).
     """
     t = _check_grid(params)
     table = compile_table(params)
-    opts, override = _options_from(params, method)
+    opts, override = _options_from(params, method, tol_scale)
     with engine.Plan(table, device) as plan:
         obs, stats = plan.evolve(t, opts)
     out = _pack(obs, override, raw_norm)
@@ -150,13 +167,13 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
 
 
 def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int = 0, method: Optional[str] = None,
-                        raw_norm: bool = False):
+                        tol_scale: Optional[float] = None, raw_norm: bool = False):
     """Independent trajectories; those with N <= 10 share ONE kernel launch (one CTA each)."""
     n = len(params_list)
     results: List = [None] * n
     grids = [_check_grid(p) for p in params_list]
     tables = [compile_table(p) for p in params_list]
-    om = [_options_from(p, method) for p in params_list]
+    om = [_options_from(p, method, tol_scale) for p in params_list]
     small = [i for i in range(n) if tables[i].n <= engine.SMALL_MAX_QUBITS]
     groups: Dict[int, List[int]] = {}
     for i in small:

@@ -75,7 +75,7 @@ static void compile_small(const qsb_table* t, uint64_t psi0, const qsb_solver_op
   const int n = t->n_qubits;
   d->n = n;
   d->method = o->method;
-  d->order = (o->method == QSB_METHOD_TAYLOR) ? (o->order ? o->order : 12) : 5;
+  d->order = (o->method == QSB_METHOD_TAYLOR) ? (o->order ? o->order : 20) : 5;
   d->t_per_traj = t_per_traj;
   d->sea_mask = (uint32_t)t->sea_mask;
   d->rare_mask = (uint32_t)t->rare_mask;

@@ -27,7 +27,7 @@ int qsb_session_begin(qsb_plan* p, uint64_t psi0_index, const double* psi0_host,
   if (rc) return rc;
   Session* s = new Session;
   s->o = *opts;
-  s->order = (opts->method == QSB_METHOD_TAYLOR) ? (opts->order ? opts->order : 12) : 5;
+  s->order = (opts->method == QSB_METHOD_TAYLOR) ? (opts->order ? opts->order : 20) : 5;
   s->inv_q = (opts->method == QSB_METHOD_TAYLOR) ? 1.0 / s->order : 0.2;
   s->t = t0;
   s->dim = 1ull << p->n_eff;

@@ -15,6 +15,7 @@ struct qsb_plan {
   LargeGeom g = {};
   DiagTables tab = {};
   double* d_tables = nullptr;   // h, J, Qx, Qy, Qz in one allocation
+  double* d_tiles = nullptr;    // per-tile diagonal rows Tx, Ty, Tz
   void* ws = nullptr;           // workspace (vectors + partials)
   size_t ws_bytes = 0;
   bool ws_owned = false;
@@ -112,6 +113,18 @@ int qsb_plan_create(const qsb_table* table, int device, qsb_plan** out) {
     p->tab.Qx = p->d_tables + off_q;
     p->tab.Qy = p->tab.Qx + TILE;
     p->tab.Qz = p->tab.Qy + TILE;
+    const size_t td = tile_diag_doubles(ne);
+    QSB_CUDA(cudaMalloc(&p->d_tiles, 3 * td * sizeof(double)));
+    const double sxy = std::ldexp(1.0, -ne);
+    launch_build_tile_diag(p->tab.h, p->tab.J, ne, Lc, sxy, p->d_tiles, p->stream);
+    launch_build_tile_diag(p->tab.h + ne, p->tab.J + (size_t)ne * ne, ne, Lc, sxy, p->d_tiles + td, p->stream);
+    launch_build_tile_diag(p->tab.h + 2 * ne, p->tab.J + 2 * (size_t)ne * ne, ne, p->g.lay[0], 1.0, p->d_tiles + 2 * td,
+                           p->stream);
+    QSB_CUDA(cudaGetLastError());
+    QSB_CUDA(cudaStreamSynchronize(p->stream));
+    p->tab.Tx = p->d_tiles;
+    p->tab.Ty = p->d_tiles + td;
+    p->tab.Tz = p->d_tiles + 2 * td;
     QSB_CUDA(cudaMalloc(&p->d_red, PSTRIDE * sizeof(double)));
     QSB_CUDA(cudaMallocHost(&p->h_red, PSTRIDE * sizeof(double)));
   }
@@ -127,6 +140,7 @@ int qsb_plan_destroy(qsb_plan* p) {
   qsb_session_end(p);
   if (p->ws && p->ws_owned) cudaFree(p->ws);
   if (p->d_tables) cudaFree(p->d_tables);
+  if (p->d_tiles) cudaFree(p->d_tiles);
   if (p->d_red) cudaFree(p->d_red);
   if (p->h_red) cudaFreeHost(p->h_red);
   if (p->stream) cudaStreamDestroy(p->stream);

@@ -137,9 +137,12 @@ static int attempt_taylor(qsb_plan* p, Session* s, double hu, double* err, doubl
     e.alpha = hu / (double)(m + 1);
     e.o1 = s->k[0];
     e.o2 = s->ys;
-    e.vin[0] = s->ys; e.c[0] = 1.0; e.vin[1] = s->y; e.c[1] = 0.0; e.n_in = 2;
+    e.vin[0] = s->ys; e.c[0] = 1.0; e.n_in = 1;
     e.ck = e.alpha;
-    if (m == s->order - 1) { e.want_err = 1; e.ek = e.alpha; e.sc_i0 = 1; e.sc_i1 = -1; }
+    if (m == s->order - 1) {  // last term = error estimate; y is read only here, for the error weights
+      e.vin[1] = s->y; e.c[1] = 0.0; e.n_in = 2;
+      e.want_err = 1; e.ek = e.alpha; e.sc_i0 = 1; e.sc_i1 = -1;
+    }
     launch_happly(p->g, p->tab, m == 0 ? s->y : s->k[0], s->tx, s->ty, e, 0, s->partials, p->stream);
   }
   QSB_CUDA(cudaGetLastError());

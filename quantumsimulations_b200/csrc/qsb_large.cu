@@ -146,59 +146,79 @@ __device__ __forceinline__ void smem_round(cplx* sm, int tt, int mask) {
   smem_store16<W>(sm, tt, r);
 }
 
-// Per-CTA part of a diagonal form D(u; v) = Q[u] + cst + LinLo[u & 63] + LinHi[u >> 6]  (see DESIGN.md):
-// lin_b(v) = scale/4 * sum_{c outer} J[gb(b)][c] s_c(v),  cst(v) = scale * (sum_c h_c s_c/2 + sum_{c<c'} J s s'/4)
-// over outer bits only.  Needs >= 128 threads; ends with __syncthreads().
-struct DiagShared {
-  double lin[TB];
-  double lo[64], hi[64];
-  double cst;
+// Diagonal form on a tile:  D(u; v) = Q[u] + cst(v) + sum_b s_b(u) lin_b(v)   (u = tile-local index, v = tile).
+// (lin[12], cst) per tile come from a table built once per plan (build_tile_diag below), one 128-byte row per
+// tile, so a pass issues these 13 uniform loads next to its tile loads and needs no shared memory or barrier.
+constexpr int TD_STRIDE = 16;  // doubles per tile row: lin[0..11], cst, 3 pad
+
+// Everything of D that a thread can hoist out of its 16-element loop for window W: the cst + the eight
+// non-window bits (fixed by the thread index) and the sixteen window-bit sign combinations.
+template <int W>
+struct TileDiag {
+  double fixed;
+  double w[4];
+  __device__ __forceinline__ void load(const double* __restrict__ row, int tt) {
+    fixed = __ldg(row + TB);
+    const int i0 = elem<W>(tt, 0);
+#pragma unroll
+    for (int b = 0; b < TB; ++b) {
+      double l = __ldg(row + b);
+      if (b >= W && b < W + 4) w[b - W] = l;
+      else fixed += (i0 >> b & 1) ? -l : l;
+    }
+  }
+  // j must be a compile-time constant after unrolling: the sign pattern then folds into add/sub
+  __device__ __forceinline__ double at(const double* __restrict__ Q, int tt, int j) const {
+    double a = fixed;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) a += (j >> k & 1) ? -w[k] : w[k];
+    return __ldg(Q + elem<W>(tt, j)) + a;
+  }
 };
-__device__ void diag_prologue(DiagShared& ds, const double* __restrict__ h, const double* __restrict__ J, int n,
-                              const Layout& L, uint64_t base, double scale, int tt) {
-  const uint64_t outer = ~L.tile_mask & ((n >= 64) ? ~0ull : ((1ull << n) - 1));
-  const int lane = tt & 31, warp = tt >> 5;
-  if (warp == 0) {
-    if (lane < TB) {
-      int gb = lane < L.lk ? lane : L.gs + (lane - L.lk);
-      double acc = 0.0;
-      for (int c = 0; c < n; ++c)
-        if (outer >> c & 1) acc = fma((base >> c & 1) ? -0.25 : 0.25, J[(size_t)gb * n + c], acc);
-      ds.lin[lane] = acc * scale;
-    }
-  } else if (warp == 1) {
-    double part = 0.0;
-    for (int c = lane; c < n; c += 32) {
-      if (!(outer >> c & 1)) continue;
-      double sc = (base >> c & 1) ? -1.0 : 1.0;
-      double acc = 0.5 * h[c];
-      for (int c2 = c + 1; c2 < n; ++c2)
-        if (outer >> c2 & 1) acc = fma((base >> c2 & 1) ? -0.25 : 0.25, J[(size_t)c * n + c2], acc);
-      part = fma(sc, acc, part);
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) part += __shfl_xor_sync(0xffffffffu, part, off);
-    if (lane == 0) ds.cst = part * scale;
-  }
-  __syncthreads();
-  if (tt < 128) {
-    int a = tt & 63, half = tt >> 6;
-    double acc = 0.0;
-#pragma unroll
-    for (int b = 0; b < 6; ++b) acc = fma((a >> b & 1) ? -1.0 : 1.0, ds.lin[half * 6 + b], acc);
-    (half ? ds.hi : ds.lo)[a] = acc;
-  }
-  __syncthreads();
-}
-__device__ __forceinline__ double diag_at(const DiagShared& ds, const double* __restrict__ Q, int u) {
-  return __ldg(Q + u) + ds.cst + ds.lo[u & 63] + ds.hi[u >> 6];
-}
 
 __device__ __forceinline__ int sea_weight(uint64_t idx, uint64_t sea_mask, int n_sea) {
   return n_sea - 2 * __popcll(idx & sea_mask);
 }
 
+// One thread per tile: lin_b(v) = scale/4 * sum_{c outer} J[gb(b)][c] s_c(v),
+// cst(v) = scale * (sum_{c outer} h_c s_c/2 + sum_{c<c' outer} J[c][c'] s_c s_c'/4).
+__global__ void build_tile_diag_kernel(const double* __restrict__ h, const double* __restrict__ J, int n, Layout L,
+                                       double scale, double* __restrict__ out, uint64_t n_tiles) {
+  uint64_t v = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_tiles) return;
+  const uint64_t base = tile_base(L, v);
+  const uint64_t outer = ~L.tile_mask & ((1ull << n) - 1);
+  double* row = out + v * TD_STRIDE;
+  for (int b = 0; b < TB; ++b) {
+    int gb = b < L.lk ? b : L.gs + (b - L.lk);
+    double acc = 0.0;
+    for (int c = 0; c < n; ++c)
+      if (outer >> c & 1) acc = fma((base >> c & 1) ? -0.25 : 0.25, J[(size_t)gb * n + c], acc);
+    row[b] = acc * scale;
+  }
+  double cst = 0.0;
+  for (int c = 0; c < n; ++c) {
+    if (!(outer >> c & 1)) continue;
+    double acc = 0.5 * h[c];
+    for (int c2 = c + 1; c2 < n; ++c2)
+      if (outer >> c2 & 1) acc = fma((base >> c2 & 1) ? -0.25 : 0.25, J[(size_t)c * n + c2], acc);
+    cst = fma((base >> c & 1) ? -1.0 : 1.0, acc, cst);
+  }
+  row[TB] = cst * scale;
+  row[TB + 1] = row[TB + 2] = row[TB + 3] = 0.0;
+}
+
 }  // namespace
+
+size_t tile_diag_doubles(int n) { return (size_t)TD_STRIDE << (n - TB); }
+
+void launch_build_tile_diag(const double* d_h, const double* d_J, int n, const Layout& L, double scale, double* d_out,
+                            cudaStream_t stream) {
+  const uint64_t n_tiles = 1ull << (n - TB);
+  const unsigned blocks = (unsigned)((n_tiles + 127) / 128);
+  build_tile_diag_kernel<<<blocks, 128, 0, stream>>>(d_h, d_J, n, L, scale, d_out, n_tiles);
+}
+
 }  // namespace qsb
 
 #include "qsb_large_kernels.inl"

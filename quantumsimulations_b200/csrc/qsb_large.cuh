@@ -31,6 +31,9 @@ struct DiagTables {      // device pointers
   const double* Qx;      // [4096] centre-layout, x basis (2^-n folded in)
   const double* Qy;      // [4096] centre-layout, y basis
   const double* Qz;      // [4096] layout 0, z basis
+  const double* Tx;      // [n_tiles][16] per-tile (lin[12], cst) of the centre layout, x basis
+  const double* Ty;      //               ... y basis
+  const double* Tz;      //               ... layout 0, z basis
 };
 
 // Fused epilogue of the last pass: k = -i H v (or H v), then stage algebra on k.
@@ -57,6 +60,10 @@ struct LargeGeom {
 };
 
 LargeGeom make_geometry(int n);
+size_t tile_diag_doubles(int n);
+// d_h/d_J: device [n] / [n][n] of ONE basis.  Fills d_out[n_tiles][16].
+void launch_build_tile_diag(const double* d_h, const double* d_J, int n, const Layout& L, double scale, double* d_out,
+                            cudaStream_t stream);
 std::vector<double> host_q_table(const double* h, const double* J, int n, int basis, const Layout& L, double scale);
 
 // One H-apply: src -> epilogue.  tx/ty: scratch vectors of 2^n cplx.  partials: device doubles,

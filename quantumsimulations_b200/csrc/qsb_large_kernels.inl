@@ -101,21 +101,22 @@ pass_mid(Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty) {
 // the full index.  Optionally that basis' observable partial sums (taken on the fully transformed vector).
 // ---------------------------------------------------------------------------------------------------
 template <int W>
-__device__ __forceinline__ void centre_core(cplx (&r)[16], int tt, int mask, const DiagShared& ds,
+__device__ __forceinline__ void centre_core(cplx (&r)[16], int tt, int mask, const double* __restrict__ trow,
                                             const double* __restrict__ Q, const Layout& L, uint64_t base,
                                             const LargeGeom& g, int collect_obs, double (&s)[2]) {
+  TileDiag<W> td;
+  td.load(trow, tt);
   bfly16<0>(r, mask);
   const int n_sea = __popcll(g.sea_mask);
 #pragma unroll
   for (int j = 0; j < 16; ++j) {
-    int i = elem<W>(tt, j);
     if (collect_obs) {
-      uint64_t idx = gidx(L, base, i);
+      uint64_t idx = gidx(L, base, elem<W>(tt, j));
       double p = norm2(r[j]);
       s[0] = fma(p, (double)sea_weight(idx, g.sea_mask, n_sea), s[0]);
       s[1] += (idx & g.rare_mask) ? -p : p;
     }
-    r[j] = diag_at(ds, Q, i) * r[j];
+    r[j] = td.at(Q, tt, j) * r[j];
   }
   bfly16<0>(r, mask);
 }
@@ -125,35 +126,32 @@ pass_centre(PassArgs a, Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty, 
             double* __restrict__ partials) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
-  __shared__ DiagShared ds;
   __shared__ double red[2 * 32 + 2];
   const int branch = blockIdx.y;  // 0: x, 1: y
   cplx* t = branch ? ty : tx;
   const double* Q = branch ? a.tab.Qy : a.tab.Qx;
-  const int n = a.g.n, tt = threadIdx.x;
+  const double* trow = (branch ? a.tab.Ty : a.tab.Tx) + (size_t)blockIdx.x * TD_STRIDE;
+  const int tt = threadIdx.x;
   const uint64_t base = tile_base(L, blockIdx.x);
   cplx r[16];
   double s[2] = {0.0, 0.0};
 #pragma unroll
   for (int j = 0; j < 16; ++j) r[j] = t[gidx(L, base, elem<8>(tt, j))];
-  // the per-tile diagonal pieces are computed while the tile's loads are in flight
-  diag_prologue(ds, a.tab.h + (size_t)branch * n, a.tab.J + (size_t)branch * n * n, n, L, base,
-                ldexp(1.0, -n), tt);
   if (!L.m4 && !L.m0) {
-    centre_core<8>(r, tt, L.m8, ds, Q, L, base, a.g, collect_obs, s);
+    centre_core<8>(r, tt, L.m8, trow, Q, L, base, a.g, collect_obs, s);
   } else {
     bfly16<0>(r, L.m8);
     smem_store16<8>(sm, tt, r);
     __syncthreads();
     if (!L.m0) {
       smem_load16<4>(sm, tt, r);
-      centre_core<4>(r, tt, L.m4, ds, Q, L, base, a.g, collect_obs, s);
+      centre_core<4>(r, tt, L.m4, trow, Q, L, base, a.g, collect_obs, s);
       smem_store16<4>(sm, tt, r);
     } else {
       smem_round<4, 0>(sm, tt, L.m4);
       __syncthreads();
       smem_load16<0>(sm, tt, r);
-      centre_core<0>(r, tt, L.m0, ds, Q, L, base, a.g, collect_obs, s);
+      centre_core<0>(r, tt, L.m0, trow, Q, L, base, a.g, collect_obs, s);
       smem_store16<0>(sm, tt, r);
       __syncthreads();
       smem_round<4, 0>(sm, tt, L.m4);

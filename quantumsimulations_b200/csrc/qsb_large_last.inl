@@ -8,25 +8,37 @@ namespace {
 // The last butterfly round leaves thread t with amplitudes t + 256 j, so the epilogue streams the other
 // vectors straight from registers with fully coalesced accesses.
 // ---------------------------------------------------------------------------------------------------
+// EPI bit 0: o2 is produced; bit 1: the error sums are produced.  The epilogue works on batches of B amplitudes:
+// all loads of a batch are issued before anything of that batch is stored, because o1/o2 may alias inputs at
+// the SAME index (in-place stage vectors) and the compiler must therefore keep loads behind earlier stores.
+template <int EPI>
 __global__ void __launch_bounds__(TPT, 2)
 pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* __restrict__ ty,
           Epilogue ep, double* __restrict__ partials) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
-  __shared__ DiagShared ds;
   __shared__ double red[2 * 32 + 2];
   const int tt = threadIdx.x;
   const uint64_t base = (uint64_t)blockIdx.x << TB;
-  const int n = a.g.n;
   cplx r[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) r[j] = ty[base | (uint64_t)elem<8>(tt, j)];
-  {  // pull the tX tile (needed three rounds from now) towards L2 while the tY loads are in flight
-    const char* p = reinterpret_cast<const char*>(tx + base) + (size_t)tt * 256;
+  {  // pull the tiles needed later (tX in three rounds, the epilogue inputs after six) towards L2
+    const size_t off = (size_t)tt * 256;
+    const char* p = reinterpret_cast<const char*>(tx + base) + off;
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128));
+    p = reinterpret_cast<const char*>(src + base) + off;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128));
+    if (EPI) {
+      for (int q = 0; q < ep.n_in; ++q) {
+        p = reinterpret_cast<const char*>(ep.vin[q] + base) + off;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128));
+      }
+    }
   }
-  diag_prologue(ds, a.tab.h + 2 * (size_t)n, a.tab.J + 2 * (size_t)n * n, n, a.g.lay[0], base, 1.0, tt);
   bfly16<1>(r, 0xF);
   smem_store16<8>(sm, tt, r);
   __syncthreads();
@@ -45,38 +57,69 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
   smem_load16<8>(sm, tt, r);
   bfly16<0>(r, 0xF);
 
+  TileDiag<8> td;
+  td.load(a.tab.Tz + (size_t)blockIdx.x * TD_STRIDE, tt);
+  const uint64_t idx0 = base | (uint64_t)tt;  // element j of this thread is idx0 + 256 j
   double err_acc = 0.0, aux_acc = 0.0;
-#pragma unroll 4
-  for (int j = 0; j < 16; ++j) {
-    const int i = elem<8>(tt, j);
-    const uint64_t idx = base | (uint64_t)i;
-    cplx v = src[idx];
-    cplx acc = diag_at(ds, a.tab.Qz, i) * v + r[j];
-    cplx k = ep.raw_h ? acc : mul_mi(acc);
-    if (ep.o1) ep.o1[idx] = ep.alpha * k;
-    if (ep.o2 || ep.want_err) {
-      cplx o2 = ep.ck * k, er = ep.ek * k;
-      double m0 = 0.0, m1 = 0.0;
+  constexpr int B = (EPI & 2) ? 4 : 8;
 #pragma unroll
-      for (int q = 0; q < MAX_VEC_IN; ++q) {
-        if (q < ep.n_in) {
-          cplx w = ep.vin[q][idx];
-          axpy(o2, ep.c[q], w);
-          axpy(er, ep.e[q], w);
-          if (q == ep.sc_i0) m0 = norm2(w);
-          if (q == ep.sc_i1) m1 = norm2(w);
+  for (int j0 = 0; j0 < 16; j0 += B) {
+    {  // k = -i (Dz v + r)   (kept in r)
+      cplx v[B];
+#pragma unroll
+      for (int jj = 0; jj < B; ++jj) v[jj] = src[idx0 + 256u * (j0 + jj)];
+#pragma unroll
+      for (int jj = 0; jj < B; ++jj) {
+        cplx acc = td.at(a.tab.Qz, tt, j0 + jj) * v[jj] + r[j0 + jj];
+        r[j0 + jj] = ep.raw_h ? acc : mul_mi(acc);
+      }
+    }
+    if (EPI == 0) {
+      if (ep.o1) {
+#pragma unroll
+        for (int jj = 0; jj < B; ++jj) ep.o1[idx0 + 256u * (j0 + jj)] = ep.alpha * r[j0 + jj];
+      }
+    } else {
+      cplx o2[(EPI & 1) ? B : 1], er[(EPI & 2) ? B : 1];
+      double m0[(EPI & 2) ? B : 1], m1[(EPI & 2) ? B : 1];
+#pragma unroll
+      for (int jj = 0; jj < B; ++jj) {
+        if (EPI & 1) o2[jj] = ep.ck * r[j0 + jj];
+        if (EPI & 2) { er[jj] = ep.ek * r[j0 + jj]; m0[jj] = 0.0; m1[jj] = 0.0; }
+      }
+      for (int q = 0; q < ep.n_in; ++q) {
+        const cplx* vq = ep.vin[q];
+        const double cq = ep.c[q], eq = ep.e[q];
+        cplx w[B];
+#pragma unroll
+        for (int jj = 0; jj < B; ++jj) w[jj] = vq[idx0 + 256u * (j0 + jj)];
+#pragma unroll
+        for (int jj = 0; jj < B; ++jj) {
+          if (EPI & 1) axpy(o2[jj], cq, w[jj]);
+          if (EPI & 2) {
+            axpy(er[jj], eq, w[jj]);
+            if (q == ep.sc_i0) m0[jj] = norm2(w[jj]);
+            if (q == ep.sc_i1) m1[jj] = norm2(w[jj]);
+          }
         }
       }
-      if (ep.o2) ep.o2[idx] = o2;
-      if (ep.want_err) {
-        if (ep.sc_i1 < 0) m1 = norm2(o2);
-        double sc = ep.atol + ep.rtol * sqrt(fmax(m0, m1));
-        err_acc += norm2(er) / (sc * sc);
-        aux_acc += m0 / (sc * sc);
+      if (ep.o1) {
+#pragma unroll
+        for (int jj = 0; jj < B; ++jj) ep.o1[idx0 + 256u * (j0 + jj)] = ep.alpha * r[j0 + jj];
+      }
+#pragma unroll
+      for (int jj = 0; jj < B; ++jj) {
+        if (EPI & 1) ep.o2[idx0 + 256u * (j0 + jj)] = o2[jj];
+        if (EPI & 2) {
+          if (ep.sc_i1 < 0) m1[jj] = (EPI & 1) ? norm2(o2[jj]) : 0.0;
+          double sc = ep.atol + ep.rtol * sqrt(fmax(m0[jj], m1[jj]));
+          err_acc += norm2(er[jj]) / (sc * sc);
+          aux_acc += m0[jj] / (sc * sc);
+        }
       }
     }
   }
-  if (ep.want_err) {
+  if (EPI & 2) {
     double s[2] = {err_acc, aux_acc};
     block_reduce<2>(s, red);
     if (threadIdx.x == 0) {
@@ -146,7 +189,10 @@ void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, c
   const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx), sm2 = sm1;
   if (!attr) {
     cudaFuncSetAttribute(pass_first, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
-    cudaFuncSetAttribute(pass_last, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+    cudaFuncSetAttribute(pass_last<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+    cudaFuncSetAttribute(pass_last<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+    cudaFuncSetAttribute(pass_last<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+    cudaFuncSetAttribute(pass_last<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     cudaFuncSetAttribute(pass_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
     cudaFuncSetAttribute(pass_centre, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
     attr = true;
@@ -160,7 +206,16 @@ void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, c
   for (int k = 1; k < centre; ++k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty); }
   { Timed t(2, stream); pass_centre<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], tx, ty, collect_obs, partials); }
   for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty); }
-  { Timed t(3, stream); pass_last<<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); }
+  {
+    Timed t(3, stream);
+    const int epi = (ep.o2 ? 1 : 0) | (ep.want_err ? 2 : 0);
+    switch (epi) {
+      case 0: pass_last<0><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
+      case 1: pass_last<1><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
+      case 2: pass_last<2><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
+      default: pass_last<3><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
+    }
+  }
 }
 
 void launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,

@@ -1,0 +1,284 @@
+"""CPU tests of the host layer: model mirror, table compiler, metrics, sweep driver file contract, the C ABI's
+exported symbols and loud failure without a GPU, and the N>1 sharding logic over gloo.  No compute kernels."""
+import dataclasses
+import json
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT, exact_traces, params_from_meta
+
+KEYS = ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R")
+
+
+# ---- model mirror ------------------------------------------------------------------------------------------
+def test_params_fields_and_defaults_match_golden_serialisation(golden_cases):
+    from quantumsimulations_b200 import DipolarRareParams
+
+    meta, _ = golden_cases
+    ref_keys = list(meta["n7_d050k_center_on"]["params"].keys())       # asdict() of the REFERENCE dataclass
+    assert [f.name for f in dataclasses.fields(DipolarRareParams)] == ref_keys
+    d = meta["n13_dataclass_default"]["params"]                          # reference defaults (+2 overrides)
+    mine = dataclasses.asdict(DipolarRareParams(is_spin_three_half=False, steps=201))
+    assert mine == d
+
+
+def test_derived_frequencies_bit_exact(golden_cases):
+    from quantumsimulations_b200 import get_derived_frequencies
+
+    meta, _ = golden_cases
+    for name, entry in meta.items():
+        got = get_derived_frequencies(params_from_meta(entry))
+        assert list(got.keys()) == list(entry["freqs"].keys())
+        for k, v in entry["freqs"].items():
+            assert got[k] == v, (name, k)
+
+
+def test_error_behaviour_matches_reference():
+    import quantumsimulations_b200 as q
+
+    with pytest.raises(ValueError, match="n_sea must be at least 1"):
+        q.shell_positions_with_rare_center(0)
+    with pytest.raises(ValueError, match="identical positions"):
+        q.dipolar_couplings_from_positions(np.zeros((3, 3)), 1.0, 1.0, 1.0)
+    with pytest.raises(ValueError, match="Bad time grid"):
+        q.simulate_rare(q.DipolarRareParams(n_sea=6, is_spin_three_half=False, steps=1))
+    with pytest.raises(ValueError, match="Bad time grid"):
+        q.simulate_rare(q.DipolarRareParams(n_sea=6, is_spin_three_half=False, t_final=0.0))
+    with pytest.raises(NotImplementedError):
+        q.compile_table(q.DipolarRareParams())          # spin-3/2 default cannot run in the reference either
+
+
+def test_geometry_shapes_and_symmetry():
+    import quantumsimulations_b200 as q
+
+    for n in (1, 4, 5, 6, 8, 12, 20, 27, 32):
+        pos = q.shell_positions_with_rare_center(n, 2.0)
+        assert pos.shape == (n + 1, 3)
+        assert np.allclose(np.linalg.norm(pos[:-1], axis=1), 2.0)
+        assert np.all(pos[-1] == 0.0)
+        b = q.dipolar_couplings_from_positions(pos, 1.0, 2.0, 3.0)
+        assert np.array_equal(b, b.T) and np.all(np.diag(b) == 0.0)
+
+
+# ---- table compiler --------------------------------------------------------------------------------------------
+def test_spin_operator_views(golden_cases, golden_hams):
+    import scipy.sparse as sp
+    from quantumsimulations_b200 import build_hamiltonian_rare, initial_state_rare
+
+    meta, _ = golden_cases
+    name = "n5_tetra"
+    p = params_from_meta(meta[name])
+    H, obs = build_hamiltonian_rare(p)
+    dim = 32
+    G = sp.csr_matrix((golden_hams[f"{name}/data"], golden_hams[f"{name}/indices"], golden_hams[f"{name}/indptr"]),
+                      shape=(dim, dim))
+    assert abs(H.to_csr() - G).max() / np.abs(G.data).max() < 1e-14
+    assert set(obs) == set(KEYS) and H.shape == (dim, dim)
+    iz = obs["Iz_sea"].full()
+    assert np.allclose(iz, np.diag(np.diag(iz))) and np.isclose(np.trace(iz), 0.0)
+    psi0 = initial_state_rare(p)
+    assert psi0[int(golden_hams[f"{name}/psi0_index"])] == 1.0 and np.count_nonzero(psi0) == 1
+    assert np.allclose(obs["Ix_R"].full(), obs["Ix_R"].full().conj().T)
+
+
+def test_bit_major_layout_is_site_reversed():
+    from quantumsimulations_b200 import DipolarRareParams, compile_table
+
+    t = compile_table(DipolarRareParams(n_sea=4, is_spin_three_half=False, drive_sea=True, B1_sea=0.3, omega_rf_sea=0.5))
+    bm = t.bit_major()
+    n = t.n
+    assert np.array_equal(bm["h"][0], t.hx[::-1])
+    assert bm["J"][2][0, n - 1] == t.jzz[0, n - 1]        # bit 0 = rare site, bit n-1 = site 0
+    assert np.array_equal(bm["J"], bm["J"].transpose(0, 2, 1))
+    assert t.rare_mask == 1 and t.sea_mask == (1 << n) - 2
+
+
+# ---- product metrics vs oracle metrics ---------------------------------------------------------------------------
+def test_product_metrics_agree_with_oracle():
+    from oracle import metrics as om
+    from quantumsimulations_b200 import metrics as pm
+
+    rng = np.random.default_rng(3)
+    t = np.linspace(0.0, 30.0, 20000)
+    y = -3.0 + 1e-3 * t + 0.02 * rng.normal(size=t.size)
+    for w in (1, 25, 100, 30000):
+        a, b = pm.coarse_grain(t, y, w), om.block_mean(t, y, w)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    tc, yc = pm.coarse_grain(t, y, 100)
+    assert pm.iz_slope_from_coarse(tc, yc) == om.central_fit(tc, yc)
+    assert all(np.isnan(v) for v in pm.iz_slope_from_coarse(tc[:3], yc[:3]).values())
+    for args in ((1.0, 2.0, 3.0, 0.5), (1.0, -2.0, 0.2, 0.3), (2.0, 1.0, 5.0, 5.0), (0.0, 0.0, 2.0, 2.0)):
+        assert pm.contrast_michelson_with_t_gate(*args) == om.gated_contrast(*args)
+    assert np.isnan(pm.contrast_michelson_with_t_gate(np.nan, 1.0, 2.0, 2.0))
+    assert pm.detuning_label(50000.0) == "delta_p50000.0Hz" and pm.detuning_label(-12.34) == "delta_m12.3Hz"
+    assert pm.f1R_for_resonance(50e3, 50e3) == (50e3**2 + 50e3**2) ** 0.5
+
+
+# ---- sweep driver: file contract and numbers against the reference's own sweep output ---------------------------
+def _oracle_batch(plist):
+    from quantumsimulations_b200 import compile_table
+
+    out = []
+    for p in plist:
+        t = np.linspace(0.0, p.t_final, p.steps)
+        obs = exact_traces(compile_table(p), t)
+        obs["state_norm"] = np.ones_like(t)
+        out.append((t, obs))
+    return out
+
+
+def test_sweep_driver_reproduces_reference_sweep_files(tmp_path):
+    """The engine's batched sweep driver, fed by the exact oracle instead of the GPU, must write the same file
+    set and the same numbers as the reference's unchanged run_sweep_sea_detuning did (tests/golden/sweep_small.json)."""
+    from quantumsimulations_b200.sweep import run_sweep_sea_detuning
+
+    with open(os.path.join(GOLDEN, "sweep_small.json")) as f:
+        gold = json.load(f)
+    gp = gold["summary"]["global_params"]
+    dets = gp["sea_detunings_Hz"][:3]
+    base = run_sweep_sea_detuning(
+        f_Az=gp["f_Az_Hz"], f1A=gp["f1A_Hz"], target_sea_detuning=gp["target_sea_detuning"],
+        gamma_sea=gp["gamma_sea"], gamma_rare=gp["gamma_rare"], sea_detunings_Hz=dets, n_sea=gp["n_sea"],
+        t_final=gp["t_final_s"], steps=gp["steps"], phi_sea=gp["phi_sea_rad"], phi_rare=gp["phi_rare_rad"],
+        out_root=str(tmp_path), is_spin_three_half=False, solver_atol=gp["solver_atol"], solver_rtol=gp["solver_rtol"],
+        solver_nsteps=gp["solver_nsteps"], solver_max_step=gp["solver_max_step"], coarse_window=gp["coarse_window"],
+        simulate_batch=_oracle_batch, timestamp="test", verbose=False)
+    with open(os.path.join(base, "summary.json")) as f:
+        mine = json.load(f)
+    assert list(mine["global_params"].keys()) == list(gp.keys())
+    for k, v in gp.items():
+        if k != "sea_detunings_Hz":
+            assert mine["global_params"][k] == v, k
+    for got, want in zip(mine["sweep_results"], gold["summary"]["sweep_results"]):
+        assert list(got.keys()) == list(want.keys())
+        for k in want:
+            if k.startswith("t_") or k.startswith("R_"):
+                assert got[k] == pytest.approx(want[k], rel=1e-6), k
+            else:
+                assert got[k] == pytest.approx(want[k], rel=1e-7, abs=1e-12), k
+    written = sorted(os.path.relpath(os.path.join(d, fn), base) for d, _, fns in os.walk(base) for fn in fns)
+    expected = [f for f in gold["files"] if not f.endswith((".png", ".pdf"))
+                and (os.sep not in f or f.split(os.sep)[0] in {"delta_p0.0Hz", "delta_p12500.0Hz", "delta_p25000.0Hz"})]
+    assert written == sorted(expected)
+    z = np.load(os.path.join(base, "delta_p12500.0Hz", "time_and_obs_center_on.npz"))
+    assert set(z.files) == {"t", "Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R", "state_norm"}
+
+
+def test_replay_shim_batches_an_unchanged_script(tmp_path):
+    """record -> batch -> replay around a stand-in 'reference script' module that calls simulate_rare serially."""
+    import types
+    from quantumsimulations_b200 import DipolarRareParams
+    from quantumsimulations_b200.sweep import replay_reference_script
+
+    calls = []
+    mod = types.ModuleType("fake_script")
+    mod.simulate_rare = lambda p: (_ for _ in ()).throw(AssertionError("serial path must not be used"))
+
+    def script(out_root, n):
+        tot = 0.0
+        for k in range(n):
+            t, obs = mod.simulate_rare(DipolarRareParams(n_sea=3, is_spin_three_half=False, t_final=1e-3 * (k + 1), steps=5))
+            tot += float(obs["Iz_sea"][-1])
+        with open(os.path.join(out_root, "out.txt"), "w") as f:
+            f.write(repr(tot))
+        return out_root
+
+    mod.script = script
+
+    def batch(plist):
+        calls.append(len(plist))
+        return [(np.linspace(0, p.t_final, p.steps), {k: np.full(p.steps, p.t_final) for k in KEYS + ("state_norm",)})
+                for p in plist]
+
+    out = replay_reference_script(mod, "script", simulate_batch=batch, out_root=str(tmp_path), n=4)
+    assert calls == [4]                                   # one batched solve for the four serial calls
+    assert float(open(os.path.join(out, "out.txt")).read()) == pytest.approx(1e-3 * 10)
+
+
+# ---- C ABI -------------------------------------------------------------------------------------------------------
+def test_library_exports_every_declared_symbol():
+    from quantumsimulations_b200 import engine
+
+    header = open(os.path.join(ROOT, "include", "qsb200.h")).read()
+    declared = set(re.findall(r"^(?:int|const char\*)\s+(qsb_\w+)\s*\(", header, flags=re.M))
+    assert len(declared) >= 15
+    lib = engine.load_library()
+    for sym in declared:
+        assert hasattr(lib, sym), sym
+    assert declared == set(engine.EXPORTS)
+    assert lib.qsb_version() == 100
+
+
+def test_no_silent_cpu_fallback():
+    """Without a CUDA device every compute entry point must fail loudly (never route through the oracle)."""
+    from quantumsimulations_b200 import DipolarRareParams, engine, simulate_rare
+
+    if engine.device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(engine.EngineError, match="no CUDA device"):
+        simulate_rare(DipolarRareParams(n_sea=6, is_spin_three_half=False))
+    src = ""
+    pkg = os.path.join(ROOT, "quantumsimulations_b200")
+    for d, _, fns in os.walk(pkg):
+        for fn in fns:
+            if fn.endswith((".py", ".cu", ".cuh", ".inl", ".h")):
+                src += open(os.path.join(d, fn)).read()
+    assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M)
+
+
+# ---- N > 1: sharding + gathering over gloo --------------------------------------------------------------------------
+def test_partition_is_balanced_and_complete():
+    from quantumsimulations_b200.dist import partition
+
+    costs = [1.0, 4.0, 2.0, 8.0, 3.0, 3.0, 1.0, 6.0]
+    bins = partition(costs, 3)
+    assert sorted(i for b in bins for i in b) == list(range(len(costs)))
+    loads = [sum(costs[i] for i in b) for b in bins]
+    assert max(loads) - min(loads) <= max(costs)
+    assert partition(costs, 1) == [list(range(len(costs)))]
+    assert sum(len(b) for b in partition(costs[:2], 4)) == 2
+
+
+_GLOO_WORKER = r"""
+import os, sys
+import numpy as np
+import torch.distributed as dist
+sys.path.insert(0, {root!r})
+from quantumsimulations_b200 import DipolarRareParams
+from quantumsimulations_b200.dist import simulate_distributed
+
+dist.init_process_group("gloo")
+rank = dist.get_rank()
+plist = [DipolarRareParams(n_sea=3, is_spin_three_half=False, t_final=1e-3 * (k + 1), steps=4, drive_sea=True,
+                           B1_sea=0.1 * k) for k in range(7)]
+seen = []
+def compute(sub, device):
+    seen.extend(p.t_final for p in sub)
+    return [(np.linspace(0, p.t_final, p.steps), {{"Iz_sea": np.full(p.steps, p.t_final)}}) for p in sub]
+out = simulate_distributed(plist, device=0, compute=compute)
+assert len(out) == 7 and all(o is not None for o in out)
+for p, (t, obs) in zip(plist, out):
+    assert t[-1] == p.t_final and obs["Iz_sea"][0] == p.t_final
+assert 0 < len(seen) < 7                 # each rank integrated only its share
+counts = [None, None]
+dist.all_gather_object(counts, len(seen))
+assert sum(counts) == 7
+dist.destroy_process_group()
+print("rank", rank, "ok")
+"""
+
+
+def test_distributed_sweep_sharding_world_size_2(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER.format(root=ROOT))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29531", str(script)]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert res.stdout.count("ok") == 2

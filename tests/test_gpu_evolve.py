@@ -161,3 +161,38 @@ def test_large_batch_matches_single_runs():
         t, single = simulate_rare(plist[i])
         for k in KEYS:
             assert np.max(np.abs(res[i][1][k] - single[k])) < 1e-9
+
+
+def test_full_sweep_matches_reference_sweep_metrics(tmp_path):
+    """C2 (CI-sized window): the engine's batched sweep vs the metrics the reference's unchanged sweep driver
+    produced on exact propagation (tests/golden/sweep_small.json).  Gate 3 of SURVEY 7.3."""
+    import json, os
+    from conftest import GOLDEN
+    from quantumsimulations_b200.sweep import run_sweep_sea_detuning
+
+    with open(os.path.join(GOLDEN, "sweep_small.json")) as f:
+        gold = json.load(f)
+    gp = gold["summary"]["global_params"]
+    base = run_sweep_sea_detuning(
+        f_Az=gp["f_Az_Hz"], f1A=gp["f1A_Hz"], target_sea_detuning=gp["target_sea_detuning"],
+        gamma_sea=gp["gamma_sea"], gamma_rare=gp["gamma_rare"], sea_detunings_Hz=gp["sea_detunings_Hz"],
+        n_sea=gp["n_sea"], t_final=gp["t_final_s"], steps=gp["steps"], phi_sea=gp["phi_sea_rad"],
+        phi_rare=gp["phi_rare_rad"], out_root=str(tmp_path), is_spin_three_half=False,
+        solver_atol=gp["solver_atol"], solver_rtol=gp["solver_rtol"], solver_nsteps=gp["solver_nsteps"],
+        solver_max_step=gp["solver_max_step"], coarse_window=gp["coarse_window"], timestamp="gpu", verbose=False)
+    with open(os.path.join(base, "summary.json")) as f:
+        mine = json.load(f)
+    assert len(mine["sweep_results"]) == 13
+    for got, want in zip(mine["sweep_results"], gold["summary"]["sweep_results"]):
+        for k in want:
+            if k.startswith("I_z_slope"):
+                assert abs(got[k] - want[k]) < 2e-6, (k, got[k], want[k])       # traces agree to 1e-6
+            elif k.startswith("t_") or k.startswith("R_"):
+                assert got[k] == pytest.approx(want[k], rel=2e-3, abs=2e-4), k
+            elif k.startswith("contrast"):
+                # discontinuous at |t| = 1 (SW:308-309): only compare when neither t is near the gate
+                ts = [want[x] for x in ("t_on_center", "t_off_center", "t_off_sea_center")]
+                if all(abs(abs(t) - 1.0) > 0.01 for t in ts):
+                    assert got[k] == pytest.approx(want[k], abs=2e-3), k
+            else:
+                assert got[k] == pytest.approx(want[k], rel=1e-9, abs=1e-12), k
