@@ -281,8 +281,12 @@ def run_b200(args, rank, world, local_rank):
     mine = plist[rank::world]
     barrier()
     t0 = time.perf_counter()
-    res, sst = simulate_rare_batch(mine, device=local_rank) if mine else ([], [])
+    res, sst = simulate_rare_batch(mine, device=local_rank, method="dp5") if mine else ([], [])
     sweep_s = allmax(time.perf_counter() - t0)
+    barrier()
+    t0 = time.perf_counter()
+    _, tst = simulate_rare_batch(mine, device=local_rank) if mine else ([], [])   # API default: Taylor(20), tol x1e-3
+    sweep_default_s = allmax(time.perf_counter() - t0)
     sweep_steps = float(sum(s.n_accepted + s.n_rejected for s in sst))
     sweep_kernel_ms = max([s.device_ms for s in sst], default=0.0)
     if dist is not None:
@@ -309,8 +313,11 @@ def run_b200(args, rank, world, local_rank):
             "raw_norm": float(obs[7]),
             "sweep": {"workload": "C2 (CI-sized): 13 detunings x 3 variants, N=7, t_final=0.03 s, 2000 outputs, "
                                   "atol 1e-10 / rtol 1e-9, one CTA per trajectory",
-                      "trajectories": len(plist), "wall_s": sweep_s, "kernel_ms": sweep_kernel_ms,
-                      "steps_per_s": sweep_steps / sweep_s, "total_steps": sweep_steps, "cpu_zvode": zv},
+                      "trajectories": len(plist), "wall_s": sweep_s, "kernel_ms": sweep_kernel_ms, "method": "dp5",
+                      "steps_per_s": sweep_steps / sweep_s, "total_steps": sweep_steps,
+                      "wall_s_default_integrator": sweep_default_s,
+                      "default_integrator": "taylor order 20, atol/rtol x 1e-3 (what simulate_rare runs)",
+                      "cpu_zvode": zv},
         }
         print(json.dumps(line), flush=True)
     if dist is not None:
