@@ -14,6 +14,19 @@ struct PassArgs {
 
 constexpr double INV_TILE = 1.0 / (double)TILE;  // the 2^-12 of (M/2)^(x12)
 
+// Which tiles a launch of a strided-layout pass covers.  Tile v of a layout is numbered by its outer bits in
+// ascending order, so for layouts sharing lk the low (12 - lk) bits of v are index bits [lk, 12): a "chunk".
+// A launch covers 2^lb consecutive chunks starting at cbase: v = cbase + (bx mod 2^lb) + (bx >> lb) << cbits.
+// All tiles of every strided layout inside one chunk touch the same 2^(n - cbits) amplitudes, which is what lets
+// consecutive passes over a chunk batch find their data in L2.  {0, cbits, cbits} is the identity map.
+struct TileMap {
+  unsigned cbase;
+  int lb, cbits;
+  __device__ __forceinline__ uint64_t tile(unsigned bx) const {
+    return (uint64_t)cbase + (bx & ((1u << lb) - 1)) + ((uint64_t)(bx >> lb) << cbits);
+  }
+};
+
 // ---------------------------------------------------------------------------------------------------
 // pass_first: layout 0.  tX = W0 psi;  tY = W0 S^dagger psi = c^dagger(v) (M'/2)^(x12) tX.
 // Optionally the z-basis observable partial sums.
@@ -74,12 +87,12 @@ pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx
 // pass_mid: in-place Hadamard on one group's bits (layout k, 0 < k < centre).  blockIdx.y = branch.
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TPT, 2)
-pass_mid(Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty) {
+pass_mid(Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
   cplx* t = blockIdx.y ? ty : tx;
   const int tt = threadIdx.x;
-  const uint64_t base = tile_base(L, blockIdx.x);
+  const uint64_t base = tile_base(L, tm.tile(blockIdx.x));
   cplx r[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) r[j] = t[gidx(L, base, elem<8>(tt, j))];
@@ -122,7 +135,7 @@ __device__ __forceinline__ void centre_core(cplx (&r)[16], int tt, int mask, con
 }
 
 __global__ void __launch_bounds__(TPT, 2)
-pass_centre(PassArgs a, Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty, int collect_obs,
+pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty, int collect_obs,
             double* __restrict__ partials) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
@@ -130,9 +143,10 @@ pass_centre(PassArgs a, Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty, 
   const int branch = blockIdx.y;  // 0: x, 1: y
   cplx* t = branch ? ty : tx;
   const double* Q = branch ? a.tab.Qy : a.tab.Qx;
-  const double* trow = (branch ? a.tab.Ty : a.tab.Tx) + (size_t)blockIdx.x * TD_STRIDE;
+  const uint64_t v = tm.tile(blockIdx.x);
+  const double* trow = (branch ? a.tab.Ty : a.tab.Tx) + (size_t)v * TD_STRIDE;
   const int tt = threadIdx.x;
-  const uint64_t base = tile_base(L, blockIdx.x);
+  const uint64_t base = tile_base(L, v);
   cplx r[16];
   double s[2] = {0.0, 0.0};
 #pragma unroll
@@ -165,7 +179,7 @@ pass_centre(PassArgs a, Layout L, cplx* __restrict__ tx, cplx* __restrict__ ty, 
   if (collect_obs) {
     block_reduce<2>(s, red);
     if (threadIdx.x == 0) {
-      double* p = partials + (size_t)blockIdx.x * PSTRIDE + 3 + 2 * branch;
+      double* p = partials + (size_t)v * PSTRIDE + 3 + 2 * branch;
       p[0] = s[0]; p[1] = s[1];
     }
   }

@@ -183,6 +183,21 @@ struct Timed {
 };
 }  // namespace
 
+
+// The strided-layout passes of one H-apply (mids forward, centre, mids back).
+// (Issuing mid -> centre -> mid chunk batch by chunk batch through TileMap so that the 2nd and 3rd pass of a
+// batch would hit L2 was measured and is slower than three full-grid launches: profiles/r1g_l2_chunk_experiment.log.)
+static void launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx, cplx* ty, int collect_obs,
+                                  double* partials, cudaStream_t stream) {
+  const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx);
+  const unsigned n_tiles = 1u << (g.n - TB);
+  const int centre = g.n_layouts - 1;
+  const TileMap all = {0u, 0, 0};
+  for (int k = 1; k < centre; ++k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+  { Timed t(2, stream); pass_centre<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], all, tx, ty, collect_obs, partials); }
+  for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+}
+
 void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
                    const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream) {
   static bool attr = false;
@@ -203,9 +218,7 @@ void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, c
   const unsigned n_tiles = 1u << (g.n - TB);
   const int centre = g.n_layouts - 1;
   { Timed t(0, stream); pass_first<<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, collect_obs, partials); }
-  for (int k = 1; k < centre; ++k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty); }
-  { Timed t(2, stream); pass_centre<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], tx, ty, collect_obs, partials); }
-  for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty); }
+  launch_strided_passes(g, a, tx, ty, collect_obs, partials, stream);
   {
     Timed t(3, stream);
     const int epi = (ep.o2 ? 1 : 0) | (ep.want_err ? 2 : 0);
@@ -233,8 +246,7 @@ void launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, 
   cudaFuncSetAttribute(pass_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
   cudaFuncSetAttribute(pass_centre, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
   pass_first<<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, 1, partials);
-  for (int k = 1; k < centre; ++k) pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], tx, ty);
-  pass_centre<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], tx, ty, 1, partials);
+  launch_strided_passes(g, a, tx, ty, 1, partials, stream);
 }
 
 void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out8, cudaStream_t stream) {
