@@ -130,6 +130,42 @@ int qsb_session_state(qsb_plan* plan, double* psi_host);
 int qsb_session_end(qsb_plan* plan);
 
 
+/* ---- sharded state: one trajectory whose 2^n amplitudes do not fit one GPU ------------------------ */
+/* (BASELINE config C5; no counterpart in the reference, whose sesolve call - dipolar_ensemble_with_rare.py:653 -
+ * holds the whole ket in one process.)  The amplitude index's top log2(world) bits are the rank: rank r holds
+ * amplitudes [r * 2^(n-log2 world), (r+1) * 2^(n-log2 world)).  One qsb_plan per rank (normally one process per
+ * GPU); all ranks then make the SAME sequence of calls (qsb_session_*, qsb_evolve, qsb_apply_h) collectively, with
+ * psi0_host / psi_host / out_host holding only the rank's own slice.  Every pass of the H-apply is local except the
+ * centre pass, which reads and writes the peers' transform scratch directly over NVLink (CUDA IPC / peer access);
+ * scalars (error norm, observable sums) are combined through the caller's all-gather hook in rank order, so every
+ * rank takes bit-identical step decisions.                                                                        */
+
+/* Gather `count` doubles from every rank: recv[r*count .. (r+1)*count) = rank r's send.  count may be 0 (a pure
+ * barrier).  Return 0 on success.  In one process per GPU this is a torch.distributed / NCCL / MPI all-gather; for
+ * ranks living in one process (threads) use qsb_local_group_*.                                                  */
+typedef int (*qsb_allgather_fn)(void* ctx, const double* send, int32_t count, double* recv);
+
+#define QSB_SHARD_BLOB_BYTES 96
+int qsb_shard_plan_create(const qsb_table* table, int device, int32_t rank, int32_t world, qsb_plan** plan);
+/* Describe this rank's exchange scratch (pid, device, address, CUDA IPC handle) in QSB_SHARD_BLOB_BYTES bytes. */
+int qsb_shard_export(qsb_plan* plan, void* blob);
+/* blobs: [world][QSB_SHARD_BLOB_BYTES], rank-ordered, as gathered from every rank's qsb_shard_export.          */
+int qsb_shard_connect(qsb_plan* plan, const void* blobs, qsb_allgather_fn allgather, void* ctx);
+/* Host-only (no device needed): the tile layouts the tiled path uses for n index bits split over `world` ranks.
+ * out[k] = {lk, gs, ge} for k < *n_layouts (<= 6): tile-local bits [0,lk) are index bits [0,lk), tile-local bits
+ * [lk,12) are index bits [gs,ge).  Layout 0 is the contiguous one; the last one is the centre and must contain all
+ * rank bits [n - log2 world, n).                                                                               */
+int qsb_debug_layouts(int32_t n_qubits, int32_t world, int32_t* n_layouts, int32_t* out /* [6][3] */);
+/* Amplitudes held by this plan (2^n for an ordinary plan).                                                     */
+int qsb_plan_local_dim(const qsb_plan* plan, uint64_t* dim);
+
+/* All-gather for `world` ranks that are threads of this process (tests; one process driving several GPUs).      */
+typedef struct qsb_local_group qsb_local_group;
+int qsb_local_group_create(int32_t world, qsb_local_group** group);
+int qsb_local_group_destroy(qsb_local_group* group);
+void* qsb_local_group_member(qsb_local_group* group, int32_t rank); /* the ctx to pass with qsb_local_allgather */
+int qsb_local_allgather(void* member_ctx, const double* send, int32_t count, double* recv);
+
 /* Benchmark aid: when enabled, every launch of the tiled H-apply is bracketed by CUDA events on its stream
  * (this serialises host and device; never enable it inside a timed throughput run).  ms4/count4: summed
  * milliseconds and launch counts of pass_first, pass_mid, pass_centre, pass_last since the last enable.    */

@@ -1,10 +1,13 @@
 // extern "C" entry points of the tiled path + qsb_evolve + qsb_apply_h; included from qsb_api_session.inl.
 
 static int upload_state(qsb_plan* p, cplx* dst, uint64_t psi0_index, const double* psi0_host) {
-  const uint64_t dim = 1ull << p->n_eff, udim = 1ull << p->n;
+  const uint64_t dim = 1ull << p->n_loc, udim = p->world > 1 ? dim : (1ull << p->n);
   if (!psi0_host) {
-    if (psi0_index >= udim) return fail(QSB_ERR_BAD_ARG, "psi0_index out of range");
-    launch_set_basis_state(dst, dim, psi0_index, p->stream);
+    if (psi0_index >> p->n) return fail(QSB_ERR_BAD_ARG, "psi0_index out of range");
+    // sharded: only the owner of the index sets a 1 (local index); everybody else zero-fills
+    uint64_t local = psi0_index;
+    if (p->world > 1) local = (psi0_index >> p->n_loc) == (uint64_t)p->rank ? (psi0_index & (dim - 1)) : ~0ull;
+    launch_set_basis_state(dst, dim, local, p->stream);
     QSB_CUDA(cudaGetLastError());
   } else {
     if (dim != udim) QSB_CUDA(cudaMemsetAsync(dst, 0, sizeof(cplx) * dim, p->stream));
@@ -19,6 +22,7 @@ int qsb_session_begin(qsb_plan* p, uint64_t psi0_index, const double* psi0_host,
                       const qsb_solver_opts* opts) {
   if (!p) return fail(QSB_ERR_BAD_ARG, "null plan");
   if (p->small) return fail(QSB_ERR_UNSUPPORTED, "sessions are for the tiled path (n_qubits > 10)");
+  if (p->world > 1 && !p->connected) return fail(QSB_ERR_BAD_ARG, "sharded plan is not connected to its peers (qsb_shard_connect)");
   int rc = check_opts(opts);
   if (rc) return rc;
   QSB_CUDA(cudaSetDevice(p->device));
@@ -30,9 +34,9 @@ int qsb_session_begin(qsb_plan* p, uint64_t psi0_index, const double* psi0_host,
   s->order = (opts->method == QSB_METHOD_TAYLOR) ? (opts->order ? opts->order : 20) : 5;
   s->inv_q = (opts->method == QSB_METHOD_TAYLOR) ? 1.0 / s->order : 0.2;
   s->t = t0;
-  s->dim = 1ull << p->n_eff;
+  s->dim = 1ull << p->n_loc;
   s->norm_dim = std::ldexp(1.0, p->n);
-  s->n_tiles = 1ll << (p->n_eff - TB);
+  s->n_tiles = 1ll << (p->n_loc - TB);
   carve(p, s);
   p->ses = s;
   rc = upload_state(p, s->y, psi0_index, psi0_host);
@@ -75,7 +79,8 @@ int qsb_session_observe(qsb_plan* p, double* obs) {
 int qsb_session_state(qsb_plan* p, double* psi_host) {
   if (!p || !p->ses || !psi_host) return fail(QSB_ERR_BAD_ARG, "no open session or null buffer");
   QSB_CUDA(cudaSetDevice(p->device));
-  QSB_CUDA(cudaMemcpyAsync(psi_host, p->ses->y, sizeof(cplx) << p->n, cudaMemcpyDeviceToHost, p->stream));
+  QSB_CUDA(cudaMemcpyAsync(psi_host, p->ses->y, sizeof(cplx) << (p->world > 1 ? p->n_loc : p->n), cudaMemcpyDeviceToHost,
+                           p->stream));
   QSB_CUDA(cudaStreamSynchronize(p->stream));
   return QSB_OK;
 }
@@ -148,7 +153,7 @@ int qsb_profile_read(double* ms4, int64_t* count4) {
 int qsb_apply_h(qsb_plan* p, const double* psi_host, double* out_host) {
   if (!p || !psi_host || !out_host) return fail(QSB_ERR_BAD_ARG, "null argument");
   QSB_CUDA(cudaSetDevice(p->device));
-  const size_t ubytes = sizeof(cplx) << p->n;
+  const size_t ubytes = sizeof(cplx) << (p->world > 1 ? p->n_loc : p->n);
   if (p->small) {
     qsb_table t;
     t.n_qubits = p->n; t.h = p->h.data(); t.J = p->J.data(); t.sea_mask = p->sea_mask; t.rare_mask = p->rare_mask;
@@ -170,6 +175,7 @@ int qsb_apply_h(qsb_plan* p, const double* psi_host, double* out_host) {
     return QSB_OK;
   }
   if (p->ses) return fail(QSB_ERR_BAD_ARG, "qsb_apply_h cannot run while a session is open (shared workspace)");
+  if (p->world > 1 && !p->connected) return fail(QSB_ERR_BAD_ARG, "sharded plan is not connected to its peers (qsb_shard_connect)");
   int rc = ensure_workspace(p, QSB_METHOD_TAYLOR);
   if (rc) return rc;
   Session s;
@@ -180,7 +186,8 @@ int qsb_apply_h(qsb_plan* p, const double* psi_host, double* out_host) {
   Epilogue e = blank_epilogue(&s);
   e.raw_h = 1;
   e.o1 = s.ys;
-  launch_happly(p->g, p->tab, s.y, s.tx, s.ty, e, 0, s.partials, p->stream);
+  rc = launch_happly(p->g, p->tab, s.y, s.tx, s.ty, e, 0, s.partials, p->stream, link_of(p));
+  if (rc) return rc;
   QSB_CUDA(cudaGetLastError());
   QSB_CUDA(cudaMemcpyAsync(out_host, s.ys, ubytes, cudaMemcpyDeviceToHost, p->stream));
   QSB_CUDA(cudaStreamSynchronize(p->stream));

@@ -6,6 +6,8 @@ struct Session;
 struct qsb_plan {
   int n = 0;        // user qubits
   int n_eff = 0;    // qubits of the tiled path (n padded to >= 12 with decoupled spectator bits)
+  int n_loc = 0;    // index bits of the local shard (n_eff when unsharded)
+  int rank = 0, world = 1;
   int device = 0;
   bool small = false;
   std::vector<double> h, J;  // [3][n], [3][n][n] as given
@@ -22,15 +24,23 @@ struct qsb_plan {
   double* d_red = nullptr;      // [PSTRIDE] reduced sums
   double* h_red = nullptr;      // pinned mirror
   Session* ses = nullptr;
+  // sharded state (world > 1): exchange scratch (tx, ty) the peers map, and the peers' mappings
+  void* xbuf = nullptr;
+  ShardLink link = {};
+  bool connected = false;
+  void* ipc_opened[MAX_WORLD] = {};
+  qsb_allgather_fn allgather = nullptr;
+  void* allgather_ctx = nullptr;
 };
 
 static int n_vectors(int method) { return method == QSB_METHOD_TAYLOR ? 5 : 11; }
 
 static size_t workspace_need(const qsb_plan* p, int method) {
   if (p->small) return 0;
-  size_t vec = sizeof(cplx) << p->n_eff;
-  size_t partials = sizeof(double) * PSTRIDE * ((size_t)1 << (p->n_eff - TB));
-  return n_vectors(method) * vec + ((partials + 255) & ~size_t(255));
+  size_t vec = sizeof(cplx) << p->n_loc;
+  size_t partials = sizeof(double) * PSTRIDE * ((size_t)1 << (p->n_loc - TB));
+  // a sharded plan keeps tx/ty in its own exchange allocation (the peers map it), not in the workspace
+  return (n_vectors(method) - (p->world > 1 ? 2 : 0)) * vec + ((partials + 255) & ~size_t(255));
 }
 
 static int ensure_workspace(qsb_plan* p, int method) {
@@ -64,18 +74,28 @@ int qsb_device_count(int* count) {
   return QSB_OK;
 }
 
-int qsb_plan_create(const qsb_table* table, int device, qsb_plan** out) {
+}  // extern "C"
+
+static int plan_create(const qsb_table* table, int device, int rank, int world, qsb_plan** out) {
   if (!out) return fail(QSB_ERR_BAD_ARG, "plan out-pointer is null");
   *out = nullptr;
   int rc = check_table(table);
   if (rc) return rc;
+  int wl = 0;
+  while ((1 << wl) < world) ++wl;
+  if (world < 1 || world > MAX_WORLD || (1 << wl) != world || rank < 0 || rank >= world)
+    return fail(QSB_ERR_BAD_ARG, "world must be 1, 2, 4 or 8 and 0 <= rank < world");
+  const int n = table->n_qubits;
+  if (world > 1 && n - wl < TB)
+    return fail(QSB_ERR_UNSUPPORTED, "a sharded plan needs n_qubits - log2(world) >= 12 (one tile per rank)");
   rc = pick_device(device);
   if (rc) return rc;
   std::unique_ptr<qsb_plan> p(new qsb_plan);
-  const int n = table->n_qubits;
   p->n = n;
   p->device = device;
-  p->small = n <= QSB_SMALL_MAX_QUBITS;
+  p->rank = rank;
+  p->world = world;
+  p->small = world == 1 && n <= QSB_SMALL_MAX_QUBITS;
   p->h.assign(table->h, table->h + 3 * (size_t)n);
   p->J.assign(table->J, table->J + 3 * (size_t)n * n);
   p->sea_mask = table->sea_mask;
@@ -84,7 +104,9 @@ int qsb_plan_create(const qsb_table* table, int device, qsb_plan** out) {
   if (!p->small) {
     const int ne = std::max(n, TB);
     p->n_eff = ne;
-    p->g = make_geometry(ne);
+    p->n_loc = ne - wl;
+    prepare_device();
+    p->g = make_geometry(ne, rank, world);
     p->g.sea_mask = table->sea_mask;
     p->g.rare_mask = table->rare_mask;
     // pad the table with decoupled spectator bits (zero coefficients) up to 12 qubits
@@ -113,13 +135,15 @@ int qsb_plan_create(const qsb_table* table, int device, qsb_plan** out) {
     p->tab.Qx = p->d_tables + off_q;
     p->tab.Qy = p->tab.Qx + TILE;
     p->tab.Qz = p->tab.Qy + TILE;
-    const size_t td = tile_diag_doubles(ne);
+    const size_t td = tile_diag_doubles(p->n_loc);
     QSB_CUDA(cudaMalloc(&p->d_tiles, 3 * td * sizeof(double)));
     const double sxy = std::ldexp(1.0, -ne);
-    launch_build_tile_diag(p->tab.h, p->tab.J, ne, Lc, sxy, p->d_tiles, p->stream);
-    launch_build_tile_diag(p->tab.h + ne, p->tab.J + (size_t)ne * ne, ne, Lc, sxy, p->d_tiles + td, p->stream);
+    // this rank's slice of the centre tiles (the rank bits are inside those tiles); its own layout-0 tiles
+    const uint64_t ntl = 1ull << (p->n_loc - TB), v0 = (uint64_t)rank * ntl;
+    launch_build_tile_diag(p->tab.h, p->tab.J, ne, Lc, sxy, p->d_tiles, ntl, v0, 0, p->stream);
+    launch_build_tile_diag(p->tab.h + ne, p->tab.J + (size_t)ne * ne, ne, Lc, sxy, p->d_tiles + td, ntl, v0, 0, p->stream);
     launch_build_tile_diag(p->tab.h + 2 * ne, p->tab.J + 2 * (size_t)ne * ne, ne, p->g.lay[0], 1.0, p->d_tiles + 2 * td,
-                           p->stream);
+                           ntl, 0, p->g.rank_bits, p->stream);
     QSB_CUDA(cudaGetLastError());
     QSB_CUDA(cudaStreamSynchronize(p->stream));
     p->tab.Tx = p->d_tiles;
@@ -127,10 +151,24 @@ int qsb_plan_create(const qsb_table* table, int device, qsb_plan** out) {
     p->tab.Tz = p->d_tiles + 2 * td;
     QSB_CUDA(cudaMalloc(&p->d_red, PSTRIDE * sizeof(double)));
     QSB_CUDA(cudaMallocHost(&p->h_red, PSTRIDE * sizeof(double)));
+    if (world > 1) {
+      cudaError_t e = cudaMalloc(&p->xbuf, 2 * (sizeof(cplx) << p->n_loc));
+      if (e != cudaSuccess) {
+        cudaGetLastError();
+        p->xbuf = nullptr;
+        qsb_plan* raw = p.release();
+        qsb_plan_destroy(raw);
+        return fail(QSB_ERR_OOM, std::string("cudaMalloc of the shard exchange scratch failed: ") + cudaGetErrorString(e));
+      }
+    }
   }
   *out = p.release();
   return QSB_OK;
 }
+
+extern "C" {
+
+int qsb_plan_create(const qsb_table* table, int device, qsb_plan** out) { return plan_create(table, device, 0, 1, out); }
 
 int qsb_session_end(qsb_plan* plan);
 
@@ -138,6 +176,10 @@ int qsb_plan_destroy(qsb_plan* p) {
   if (!p) return QSB_OK;
   cudaSetDevice(p->device);
   qsb_session_end(p);
+  if (p->stream) cudaStreamSynchronize(p->stream);
+  for (int r = 0; r < MAX_WORLD; ++r)
+    if (p->ipc_opened[r]) cudaIpcCloseMemHandle(p->ipc_opened[r]);
+  if (p->xbuf) cudaFree(p->xbuf);
   if (p->ws && p->ws_owned) cudaFree(p->ws);
   if (p->d_tables) cudaFree(p->d_tables);
   if (p->d_tiles) cudaFree(p->d_tiles);

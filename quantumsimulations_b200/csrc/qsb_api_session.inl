@@ -1,6 +1,8 @@
 // Tiled-path stepping session (host-side adaptive controller around launch_happly) and qsb_evolve.
 using namespace qsb;
 
+#include "qsb_api_shard.inl"
+
 struct Session {
   qsb_solver_opts o;
   int order = 5;
@@ -20,10 +22,12 @@ struct Session {
 
 static void carve(qsb_plan* p, Session* s) {
   char* base = (char*)p->ws;
-  size_t vec = sizeof(cplx) << p->n_eff;
+  size_t vec = sizeof(cplx) << p->n_loc;
   int i = 0;
   auto next = [&]() { return (cplx*)(base + vec * (i++)); };
-  s->y = next(); s->ys = next(); s->tx = next(); s->ty = next();
+  s->y = next(); s->ys = next();
+  if (p->world > 1) { s->tx = (cplx*)p->xbuf; s->ty = (cplx*)((char*)p->xbuf + vec); }
+  else { s->tx = next(); s->ty = next(); }
   if (s->o.method == QSB_METHOD_DP5) {
     for (int j = 0; j < 7; ++j) s->k[j] = next();
   } else {
@@ -34,12 +38,27 @@ static void carve(qsb_plan* p, Session* s) {
 
 static int fetch_sums(qsb_plan* p, Session* s, double* out) {
   launch_reduce_partials(s->partials, s->n_tiles, p->d_red, p->stream);
-  QSB_CUDA(cudaGetLastError());
-  QSB_CUDA(cudaMemcpyAsync(p->h_red, p->d_red, PSTRIDE * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
-  QSB_CUDA(cudaStreamSynchronize(p->stream));
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(p->h_red, p->d_red, PSTRIDE * sizeof(double), cudaMemcpyDeviceToHost, p->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+  if (p->world == 1) {
+    if (e != cudaSuccess) return cuda_fail(e, "fetch_sums", __FILE__, __LINE__);
+    memcpy(out, p->h_red, PSTRIDE * sizeof(double));
+    return QSB_OK;
+  }
+  // sharded: the last slot (unused by the kernels) carries this rank's failure flag through the rank sum, so a
+  // failing rank takes its peers down with it instead of leaving them at the all-gather
   memcpy(out, p->h_red, PSTRIDE * sizeof(double));
+  if (e != cudaSuccess) for (int k = 0; k < PSTRIDE; ++k) out[k] = 0.0;
+  out[PSTRIDE - 1] = (e == cudaSuccess) ? 0.0 : 1.0;
+  int rc = shard_sum(p, out, PSTRIDE);
+  if (e != cudaSuccess) return cuda_fail(e, "fetch_sums", __FILE__, __LINE__);
+  if (rc) return rc;
+  if (out[PSTRIDE - 1] != 0.0) return fail(QSB_ERR_CUDA, "a peer rank reported a CUDA failure");
   return QSB_OK;
 }
+
+static const ShardLink* link_of(const qsb_plan* p) { return p->world > 1 && p->connected ? &p->link : nullptr; }
 
 static Epilogue blank_epilogue(const Session* s) {
   Epilogue e = {};
@@ -67,11 +86,12 @@ static int session_prime(qsb_plan* p, Session* s) {
   e.o1 = s->k[0];
   e.vin[0] = s->y; e.n_in = 1; e.c[0] = 0.0; e.e[0] = 0.0; e.ek = 1.0; e.want_err = 1;
   if (s->o.method == QSB_METHOD_TAYLOR) e.o1 = nullptr;  // Taylor recomputes its first term with h folded in
-  launch_happly(p->g, p->tab, s->y, s->tx, s->ty, e, 1, s->partials, p->stream);
+  int rc = launch_happly(p->g, p->tab, s->y, s->tx, s->ty, e, 1, s->partials, p->stream, link_of(p));
+  if (rc) return rc;
   QSB_CUDA(cudaGetLastError());
   ++s->n_rhs;
   double sums[PSTRIDE];
-  int rc = fetch_sums(p, s, sums);
+  rc = fetch_sums(p, s, sums);
   if (rc) return rc;
   memcpy(s->obs_sums, sums, sizeof sums);
   s->obs_valid = true;
@@ -109,7 +129,8 @@ static int attempt_dp5(qsb_plan* p, Session* s, double hu, double* err, double* 
     for (int j = 0; j < st; ++j)
       if (T.a[st][j] != 0.0) { e.vin[e.n_in] = s->k[j]; e.c[e.n_in] = hu * T.a[st][j]; ++e.n_in; }
     e.ck = hu * T.a[st][st];
-    launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, 0, s->partials, p->stream);
+    int rc = launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, 0, s->partials, p->stream, link_of(p));
+    if (rc) return rc;
   }
   {  // FSAL apply on y_new: k7, the error estimate, and y_new's observable sums
     Epilogue e = blank_epilogue(s);
@@ -119,7 +140,8 @@ static int attempt_dp5(qsb_plan* p, Session* s, double hu, double* err, double* 
       if (T.e[j] != 0.0) { e.vin[e.n_in] = s->k[j]; e.e[e.n_in] = hu * T.e[j]; ++e.n_in; }
     e.ek = hu * T.e[6];
     e.want_err = 1; e.sc_i0 = 0; e.sc_i1 = 1;
-    launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, 1, s->partials, p->stream);
+    int rc = launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, 1, s->partials, p->stream, link_of(p));
+    if (rc) return rc;
   }
   QSB_CUDA(cudaGetLastError());
   s->n_rhs += 6;
@@ -143,7 +165,8 @@ static int attempt_taylor(qsb_plan* p, Session* s, double hu, double* err, doubl
       e.vin[1] = s->y; e.c[1] = 0.0; e.n_in = 2;
       e.want_err = 1; e.ek = e.alpha; e.sc_i0 = 1; e.sc_i1 = -1;
     }
-    launch_happly(p->g, p->tab, m == 0 ? s->y : s->k[0], s->tx, s->ty, e, 0, s->partials, p->stream);
+    int rc = launch_happly(p->g, p->tab, m == 0 ? s->y : s->k[0], s->tx, s->ty, e, 0, s->partials, p->stream, link_of(p));
+    if (rc) return rc;
   }
   QSB_CUDA(cudaGetLastError());
   s->n_rhs += s->order;
@@ -206,9 +229,10 @@ static int session_advance(qsb_plan* p, Session* s, double t_target, int64_t max
 
 static int session_observe(qsb_plan* p, Session* s, double* obs) {
   if (!s->obs_valid) {
-    launch_observe(p->g, p->tab, s->y, s->tx, s->ty, s->partials, p->stream);
+    int rc = launch_observe(p->g, p->tab, s->y, s->tx, s->ty, s->partials, p->stream, link_of(p));
+    if (rc) return rc;
     QSB_CUDA(cudaGetLastError());
-    int rc = fetch_sums(p, s, s->obs_sums);
+    rc = fetch_sums(p, s, s->obs_sums);
     if (rc) return rc;
     s->obs_valid = true;
   }

@@ -22,9 +22,15 @@ static void set_masks(Layout& L) {
   }
 }
 
-LargeGeom make_geometry(int n) {
+LargeGeom make_geometry(int n, int rank, int world) {
   LargeGeom g = {};
+  int wl = 0;
+  while ((1 << wl) < world) ++wl;
   g.n = n;
+  g.n_loc = n - wl;
+  g.rank = rank;
+  g.world = world;
+  g.rank_bits = (uint64_t)rank << g.n_loc;
   Layout& L0 = g.lay[0];
   L0.lk = TB; L0.gs = TB; L0.ge = TB;
   L0.tile_mask = (1ull << TB) - 1;
@@ -33,12 +39,22 @@ LargeGeom make_geometry(int n) {
   int rest = n - TB;
   if (rest > 0) {
     int gmax = 8;  // test knob: smaller groups exercise the multi-group passes at small n
-    if (const char* e = std::getenv("QSB200_MAX_GROUP")) gmax = std::max(1, std::min(8, atoi(e)));
+    if (const char* e = std::getenv("QSB200_MAX_GROUP")) gmax = std::max(std::max(1, wl), std::min(8, atoi(e)));
+    // group sizes, ascending bit order; the LAST group must contain all wl rank bits (it becomes the centre, the
+    // only pass that reaches the peers), so it is sized first and the other bits are balanced over the rest
+    int sizes[MAX_LAYOUTS] = {0};
     int ng = (rest + gmax - 1) / gmax;
     if (ng > MAX_LAYOUTS - 1) ng = MAX_LAYOUTS - 1;
+    int last = std::max(wl, (rest + ng - 1) / ng);
+    if (last > rest) last = rest;
+    int others = rest - last;
+    ng = 1 + (others + gmax - 1) / gmax;
+    if (ng > MAX_LAYOUTS - 1) ng = MAX_LAYOUTS - 1;
+    for (int k = 0; k + 1 < ng; ++k) sizes[k] = others / (ng - 1) + (k < others % (ng - 1) ? 1 : 0);
+    sizes[ng - 1] = last;
     int start = TB;
     for (int k = 0; k < ng; ++k) {
-      int sz = rest / ng + (k < rest % ng ? 1 : 0);
+      int sz = sizes[k];
       Layout& L = g.lay[g.n_layouts++];
       L.lk = TB - sz; L.gs = start; L.ge = start + sz;
       L.tile_mask = ((1ull << L.lk) - 1) | (((1ull << sz) - 1) << start);
@@ -183,10 +199,11 @@ __device__ __forceinline__ int sea_weight(uint64_t idx, uint64_t sea_mask, int n
 // One thread per tile: lin_b(v) = scale/4 * sum_{c outer} J[gb(b)][c] s_c(v),
 // cst(v) = scale * (sum_{c outer} h_c s_c/2 + sum_{c<c' outer} J[c][c'] s_c s_c'/4).
 __global__ void build_tile_diag_kernel(const double* __restrict__ h, const double* __restrict__ J, int n, Layout L,
-                                       double scale, double* __restrict__ out, uint64_t n_tiles) {
+                                       double scale, double* __restrict__ out, uint64_t n_tiles, uint64_t v0,
+                                       uint64_t extra_bits) {
   uint64_t v = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= n_tiles) return;
-  const uint64_t base = tile_base(L, v);
+  const uint64_t base = tile_base(L, v + v0) | extra_bits;
   const uint64_t outer = ~L.tile_mask & ((1ull << n) - 1);
   double* row = out + v * TD_STRIDE;
   for (int b = 0; b < TB; ++b) {
@@ -210,13 +227,12 @@ __global__ void build_tile_diag_kernel(const double* __restrict__ h, const doubl
 
 }  // namespace
 
-size_t tile_diag_doubles(int n) { return (size_t)TD_STRIDE << (n - TB); }
+size_t tile_diag_doubles(int n_loc) { return (size_t)TD_STRIDE << (n_loc - TB); }
 
 void launch_build_tile_diag(const double* d_h, const double* d_J, int n, const Layout& L, double scale, double* d_out,
-                            cudaStream_t stream) {
-  const uint64_t n_tiles = 1ull << (n - TB);
+                            uint64_t n_tiles, uint64_t v0, uint64_t extra_bits, cudaStream_t stream) {
   const unsigned blocks = (unsigned)((n_tiles + 127) / 128);
-  build_tile_diag_kernel<<<blocks, 128, 0, stream>>>(d_h, d_J, n, L, scale, d_out, n_tiles);
+  build_tile_diag_kernel<<<blocks, 128, 0, stream>>>(d_h, d_J, n, L, scale, d_out, n_tiles, v0, extra_bits);
 }
 
 }  // namespace qsb

@@ -51,31 +51,53 @@ struct Epilogue {
   double atol, rtol;
 };
 
+constexpr int MAX_WORLD = 8;
+
 struct LargeGeom {
-  int n;                 // qubits (>= 12)
+  int n;                 // index bits of the whole state (>= 12)
+  int n_loc;             // index bits held by this rank: n - log2(world); the top n - n_loc bits are the rank
+  int rank, world;       // world = 1: unsharded
+  uint64_t rank_bits;    // rank << n_loc
   int n_layouts;         // 1..MAX_LAYOUTS; layout 0 is the contiguous one, the last one is the centre
   Layout lay[MAX_LAYOUTS];
   uint64_t sea_mask, rare_mask;
   int has_x, has_y;      // basis has any non-zero coefficient
 };
 
-LargeGeom make_geometry(int n);
-size_t tile_diag_doubles(int n);
-// d_h/d_J: device [n] / [n][n] of ONE basis.  Fills d_out[n_tiles][16].
+// Sharded state: how a rank reaches its peers.  The centre layout's group ends with the rank bits, so the centre
+// pass is the ONLY pass that touches other ranks' memory: it loads its tiles straight from the peers' transform
+// scratch (P2P loads over NVLink), applies W_g D W_g, and stores them back in place (P2P stores).  `sync` orders
+// that pass against the peers' neighbouring passes (drain own stream + a rank barrier); see DESIGN.md.
+struct ShardLink {
+  cplx* tx[MAX_WORLD];
+  cplx* ty[MAX_WORLD];
+  int (*sync)(void* ctx);
+  void* ctx;
+};
+
+// Layouts over n index bits of which the top log2(world) are rank bits (they end up inside the centre group).
+LargeGeom make_geometry(int n, int rank = 0, int world = 1);
+size_t tile_diag_doubles(int n_loc);
+// d_h/d_J: device [n] / [n][n] of ONE basis.  Fills d_out[n_tiles_loc][16] for tiles v0 .. v0 + n_tiles_loc - 1 of
+// layout L; extra_bits are index bits outside the address space of this rank that belong to every such tile.
 void launch_build_tile_diag(const double* d_h, const double* d_J, int n, const Layout& L, double scale, double* d_out,
-                            cudaStream_t stream);
+                            uint64_t n_tiles_loc, uint64_t v0, uint64_t extra_bits, cudaStream_t stream);
+// Per-device kernel attributes (dynamic shared memory opt-in); call once per device before launching.
+void prepare_device();
 std::vector<double> host_q_table(const double* h, const double* J, int n, int basis, const Layout& L, double scale);
 
 // One H-apply: src -> epilogue.  tx/ty: scratch vectors of 2^n cplx.  partials: device doubles,
 // [n_tiles][PSTRIDE] = (nrm2, zsea, zrare, xsea, xrare, ysea, yrare, err, aux).  collect_obs: fill the observable slots.
-void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
-                   const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream);
+// link: null when unsharded.  Returns a qsb_status (only the rank barrier can fail).
+int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
+                  const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream,
+                  const ShardLink* link = nullptr);
 // Observables only (pass_first + mids + pass_centre), filling partial slots 0..6.
-void launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
-                    double* partials, cudaStream_t stream);
+int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
+                   double* partials, cudaStream_t stream, const ShardLink* link = nullptr);
 // out[PSTRIDE] = column sums of partials[n_tiles][PSTRIDE] in a fixed order.
 void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out8, cudaStream_t stream);
-// psi <- basis state / zero
+// psi <- basis state (index < dim) or zero (index >= dim)
 void launch_set_basis_state(cplx* psi, uint64_t dim, uint64_t index, cudaStream_t stream);
 size_t happly_smem_bytes();
 

@@ -47,7 +47,7 @@ pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx
     const int n_sea = __popcll(a.g.sea_mask);
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-      uint64_t idx = base | (uint64_t)elem<8>(tt, j);
+      uint64_t idx = base | a.g.rank_bits | (uint64_t)elem<8>(tt, j);
       double p = norm2(r[j]);
       s[0] += p;
       s[1] = fma(p, (double)sea_weight(idx, a.g.sea_mask, n_sea), s[1]);
@@ -71,7 +71,7 @@ pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx
   __syncthreads();
   smem_load16<8>(sm, tt, r);
   bfly16<2>(r, 0xF);
-  const int pv = __popcll(base);  // S_rest^dagger = (-i)^popcount(outer bits)
+  const int pv = __popcll(base | a.g.rank_bits);  // S_rest^dagger = (-i)^popcount(outer bits)
 #pragma unroll
   for (int j = 0; j < 16; ++j) ty[base | (uint64_t)elem<8>(tt, j)] = mul_mi_pow(INV_TILE * r[j], pv);
   if (collect_obs) {
@@ -134,9 +134,18 @@ __device__ __forceinline__ void centre_core(cplx (&r)[16], int tt, int mask, con
   bfly16<0>(r, mask);
 }
 
+// Peer bases of both branches for the sharded centre pass: element idx lives on rank idx >> n_loc.
+struct PeerPtrs {
+  cplx* t[2][MAX_WORLD];
+};
+
+// SHARDED: the group's top bits are the rank, so tile rows come from (and go back to) the peers' scratch vectors
+// through P2P loads/stores; this rank owns tiles tm.cbase .. of the centre layout and the diagonal rows / partial
+// sums are numbered locally (blockIdx.x).
+template <bool SHARDED>
 __global__ void __launch_bounds__(TPT, 2)
-pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty, int collect_obs,
-            double* __restrict__ partials) {
+pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty, PeerPtrs peers,
+            int collect_obs, double* __restrict__ partials) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
   __shared__ double red[2 * 32 + 2];
@@ -144,13 +153,17 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
   cplx* t = branch ? ty : tx;
   const double* Q = branch ? a.tab.Qy : a.tab.Qx;
   const uint64_t v = tm.tile(blockIdx.x);
-  const double* trow = (branch ? a.tab.Ty : a.tab.Tx) + (size_t)v * TD_STRIDE;
+  const double* trow = (branch ? a.tab.Ty : a.tab.Tx) + (size_t)blockIdx.x * TD_STRIDE;
   const int tt = threadIdx.x;
   const uint64_t base = tile_base(L, v);
+  const uint64_t lmask = (1ull << a.g.n_loc) - 1;
   cplx r[16];
   double s[2] = {0.0, 0.0};
 #pragma unroll
-  for (int j = 0; j < 16; ++j) r[j] = t[gidx(L, base, elem<8>(tt, j))];
+  for (int j = 0; j < 16; ++j) {
+    const uint64_t idx = gidx(L, base, elem<8>(tt, j));
+    r[j] = SHARDED ? peers.t[branch][idx >> a.g.n_loc][idx & lmask] : t[idx];
+  }
   if (!L.m4 && !L.m0) {
     centre_core<8>(r, tt, L.m8, trow, Q, L, base, a.g, collect_obs, s);
   } else {
@@ -175,11 +188,15 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
     bfly16<0>(r, L.m8);
   }
 #pragma unroll
-  for (int j = 0; j < 16; ++j) t[gidx(L, base, elem<8>(tt, j))] = r[j];
+  for (int j = 0; j < 16; ++j) {
+    const uint64_t idx = gidx(L, base, elem<8>(tt, j));
+    if (SHARDED) peers.t[branch][idx >> a.g.n_loc][idx & lmask] = r[j];
+    else t[idx] = r[j];
+  }
   if (collect_obs) {
     block_reduce<2>(s, red);
     if (threadIdx.x == 0) {
-      double* p = partials + (size_t)v * PSTRIDE + 3 + 2 * branch;
+      double* p = partials + (size_t)blockIdx.x * PSTRIDE + 3 + 2 * branch;
       p[0] = s[0]; p[1] = s[1];
     }
   }

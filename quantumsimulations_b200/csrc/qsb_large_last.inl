@@ -46,7 +46,7 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
   __syncthreads();
   smem_load16<4>(sm, tt, r);
   bfly16<1>(r, 0xF);
-  const int pv = __popcll(base);  // S_rest = (+i)^popcount(outer bits)
+  const int pv = __popcll(base | a.g.rank_bits);  // S_rest = (+i)^popcount(outer bits)
 #pragma unroll
   for (int j = 0; j < 16; ++j) r[j] = mul_pi_pow(INV_TILE * r[j], pv) + tx[base | (uint64_t)elem<4>(tt, j)];
   bfly16<0>(r, 0xF);
@@ -148,7 +148,7 @@ __global__ void reduce_partials_kernel(const double* __restrict__ partials, int6
 __global__ void set_basis_kernel(cplx* psi, uint64_t dim, uint64_t index) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  for (; i < dim; i += stride) psi[i] = mk(i == index ? 1.0 : 0.0, 0.0);
+  for (; i < dim; i += stride) psi[i] = mk(i == index ? 1.0 : 0.0, 0.0);  // index >= dim: all zero
 }
 
 }  // namespace
@@ -184,41 +184,63 @@ struct Timed {
 }  // namespace
 
 
+void prepare_device() {
+  const int sm = (int)((size_t)TILE_PHYS * sizeof(cplx));
+  cudaFuncSetAttribute(pass_first, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_last<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_last<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_last<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_last<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_centre<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_centre<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+}
+
 // The strided-layout passes of one H-apply (mids forward, centre, mids back).
 // (Issuing mid -> centre -> mid chunk batch by chunk batch through TileMap so that the 2nd and 3rd pass of a
 // batch would hit L2 was measured and is slower than three full-grid launches: profiles/r1g_l2_chunk_experiment.log.)
-static void launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx, cplx* ty, int collect_obs,
-                                  double* partials, cudaStream_t stream) {
+// Sharded: every rank runs the centre pass on its 1/world slice of the centre tiles, reading and writing the
+// peers' tx/ty in place; the rank barrier before it makes the peers' forward passes visible, the one after it
+// keeps the peers' backward passes from starting on rows that are still being written.
+static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx, cplx* ty, int collect_obs,
+                                 double* partials, cudaStream_t stream, const ShardLink* link) {
   const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx);
-  const unsigned n_tiles = 1u << (g.n - TB);
+  const unsigned n_tiles = 1u << (g.n_loc - TB);
   const int centre = g.n_layouts - 1;
   const TileMap all = {0u, 0, 0};
   for (int k = 1; k < centre; ++k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
-  { Timed t(2, stream); pass_centre<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], all, tx, ty, collect_obs, partials); }
+  if (g.world == 1) {
+    Timed t(2, stream);
+    PeerPtrs none = {};
+    pass_centre<false><<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], all, tx, ty, none, collect_obs, partials);
+  } else {
+    if (!link) { set_error("sharded plan is not connected to its peers (qsb_shard_connect)"); return QSB_ERR_BAD_ARG; }
+    int rc = link->sync(link->ctx);
+    if (rc) return rc;
+    {
+      Timed t(2, stream);
+      PeerPtrs pp = {};
+      for (int r = 0; r < g.world; ++r) { pp.t[0][r] = link->tx[r]; pp.t[1][r] = link->ty[r]; }
+      const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0};
+      pass_centre<true><<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials);
+    }
+    rc = link->sync(link->ctx);
+    if (rc) return rc;
+  }
   for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+  return QSB_OK;
 }
 
-void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
-                   const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream) {
-  static bool attr = false;
-  const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx), sm2 = sm1;
-  if (!attr) {
-    cudaFuncSetAttribute(pass_first, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
-    cudaFuncSetAttribute(pass_last<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
-    cudaFuncSetAttribute(pass_last<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
-    cudaFuncSetAttribute(pass_last<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
-    cudaFuncSetAttribute(pass_last<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
-    cudaFuncSetAttribute(pass_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
-    cudaFuncSetAttribute(pass_centre, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
-    attr = true;
-  }
+int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
+                  const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream, const ShardLink* link) {
+  const size_t sm2 = (size_t)TILE_PHYS * sizeof(cplx);
   PassArgs a;
   a.g = g;
   a.tab = tab;
-  const unsigned n_tiles = 1u << (g.n - TB);
-  const int centre = g.n_layouts - 1;
+  const unsigned n_tiles = 1u << (g.n_loc - TB);
   { Timed t(0, stream); pass_first<<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, collect_obs, partials); }
-  launch_strided_passes(g, a, tx, ty, collect_obs, partials, stream);
+  int rc = launch_strided_passes(g, a, tx, ty, collect_obs, partials, stream, link);
+  if (rc) return rc;
   {
     Timed t(3, stream);
     const int epi = (ep.o2 ? 1 : 0) | (ep.want_err ? 2 : 0);
@@ -229,24 +251,19 @@ void launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, c
       default: pass_last<3><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
     }
   }
+  return QSB_OK;
 }
 
-void launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
-                    double* partials, cudaStream_t stream) {
+int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
+                   double* partials, cudaStream_t stream, const ShardLink* link) {
   // the transform half of an H-apply: z sums in pass_first, x/y sums in pass_centre (tx/ty are clobbered)
-  Epilogue none = {};
-  (void)none;
-  const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx), sm2 = sm1;
+  const size_t sm2 = (size_t)TILE_PHYS * sizeof(cplx);
   PassArgs a;
   a.g = g;
   a.tab = tab;
-  const unsigned n_tiles = 1u << (g.n - TB);
-  const int centre = g.n_layouts - 1;
-  cudaFuncSetAttribute(pass_first, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
-  cudaFuncSetAttribute(pass_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
-  cudaFuncSetAttribute(pass_centre, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
+  const unsigned n_tiles = 1u << (g.n_loc - TB);
   pass_first<<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, 1, partials);
-  launch_strided_passes(g, a, tx, ty, 1, partials, stream);
+  return launch_strided_passes(g, a, tx, ty, 1, partials, stream, link);
 }
 
 void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out8, cudaStream_t stream) {

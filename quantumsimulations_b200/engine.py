@@ -58,7 +58,13 @@ EXPORTS = (
     "qsb_version", "qsb_last_error", "qsb_device_count", "qsb_plan_create", "qsb_plan_destroy",
     "qsb_plan_workspace_bytes", "qsb_plan_set_workspace", "qsb_evolve", "qsb_evolve_batch", "qsb_apply_h",
     "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
+    "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_plan_local_dim", "qsb_debug_layouts",
+    "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather",
 )
+
+SHARD_BLOB_BYTES = 96
+# int (*qsb_allgather_fn)(void* ctx, const double* send, int32_t count, double* recv)
+ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_double), C.c_int32, C.POINTER(C.c_double))
 
 _lib = None
 
@@ -91,6 +97,16 @@ def load_library() -> C.CDLL:
     lib.qsb_session_observe.argtypes = [vp, dp]
     lib.qsb_session_state.argtypes = [vp, dp]
     lib.qsb_session_end.argtypes = [vp]
+    lib.qsb_shard_plan_create.argtypes = [C.POINTER(_Table), C.c_int, C.c_int32, C.c_int32, C.POINTER(vp)]
+    lib.qsb_shard_export.argtypes = [vp, vp]
+    lib.qsb_shard_connect.argtypes = [vp, vp, vp, vp]
+    lib.qsb_plan_local_dim.argtypes = [vp, C.POINTER(C.c_uint64)]
+    lib.qsb_debug_layouts.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.qsb_local_group_create.argtypes = [C.c_int32, C.POINTER(vp)]
+    lib.qsb_local_group_destroy.argtypes = [vp]
+    lib.qsb_local_group_member.argtypes = [vp, C.c_int32]
+    lib.qsb_local_group_member.restype = vp
+    lib.qsb_local_allgather.argtypes = [vp, dp, C.c_int32, dp]
     lib.qsb_profile.argtypes = [C.c_int]
     lib.qsb_profile_read.argtypes = [dp, C.POINTER(C.c_int64)]
     _lib = lib
@@ -119,6 +135,14 @@ def profile_read():
     _check(load_library().qsb_profile_read(ms, cnt))
     names = ("pass_first", "pass_mid", "pass_centre", "pass_last")
     return dict(zip(names, list(ms))), dict(zip(names, list(cnt)))
+
+
+def tile_layouts(n_qubits: int, world: int = 1):
+    """[(lk, gs, ge)] of the tiled path's layouts (host-only query; see qsb_debug_layouts)."""
+    n = C.c_int32(0)
+    out = (C.c_int32 * 18)()
+    _check(load_library().qsb_debug_layouts(int(n_qubits), int(world), C.byref(n), out))
+    return [(out[3 * k], out[3 * k + 1], out[3 * k + 2]) for k in range(n.value)]
 
 
 def device_count() -> int:
@@ -180,7 +204,11 @@ class Plan:
         self._holder = _TableHolder(table)
         self._h = C.c_void_p()
         self._ws = None
-        _check(self.lib.qsb_plan_create(C.byref(self._holder.c), int(device), C.byref(self._h)))
+        self.local_dim = table.dim
+        self._create(int(device))
+
+    def _create(self, device: int) -> None:
+        _check(self.lib.qsb_plan_create(C.byref(self._holder.c), device, C.byref(self._h)))
 
     def close(self) -> None:
         if self._h:
@@ -222,8 +250,8 @@ class Plan:
         psi_ptr = None
         if psi0 is not None:
             psi0 = np.ascontiguousarray(psi0, dtype=np.complex128)
-            if psi0.shape != (self.table.dim,):
-                raise ValueError("psi0 must have 2^n amplitudes")
+            if psi0.shape != (self.local_dim,):
+                raise ValueError("psi0 must have 2^n amplitudes (the rank's own slice for a sharded plan)")
             psi_ptr = psi0.view(np.float64).ctypes.data_as(C.POINTER(C.c_double))
         _check(self.lib.qsb_evolve(self._h, self.table.psi0_index, psi_ptr, len(t_out), _dptr(t_out),
                                    C.byref(copts), _dptr(obs), C.byref(st)))
@@ -231,8 +259,8 @@ class Plan:
 
     def apply_h(self, psi: np.ndarray) -> np.ndarray:
         psi = np.ascontiguousarray(psi, dtype=np.complex128)
-        if psi.shape != (self.table.dim,):
-            raise ValueError("psi must have 2^n amplitudes")
+        if psi.shape != (self.local_dim,):
+            raise ValueError("psi must have 2^n amplitudes (the rank's own slice for a sharded plan)")
         out = np.empty_like(psi)
         _check(self.lib.qsb_apply_h(self._h, _dptr(psi.view(np.float64)), _dptr(out.view(np.float64))))
         return out
@@ -243,6 +271,8 @@ class Plan:
         ptr = None
         if psi0 is not None:
             psi0 = np.ascontiguousarray(psi0, dtype=np.complex128)
+            if psi0.shape != (self.local_dim,):
+                raise ValueError("psi0 must have 2^n amplitudes (the rank's own slice for a sharded plan)")
             ptr = _dptr(psi0.view(np.float64))
         _check(self.lib.qsb_session_begin(self._h, self.table.psi0_index, ptr, float(t0), C.byref(copts)))
 
@@ -259,12 +289,50 @@ class Plan:
         return obs
 
     def session_state(self) -> np.ndarray:
-        out = np.empty(self.table.dim, dtype=np.complex128)
+        out = np.empty(self.local_dim, dtype=np.complex128)
         _check(self.lib.qsb_session_state(self._h, _dptr(out.view(np.float64))))
         return out
 
     def session_end(self) -> None:
         _check(self.lib.qsb_session_end(self._h))
+
+
+class ShardedPlan(Plan):
+    """One rank's share of a state vector sharded on its top log2(world) index bits (qsb_shard_plan_create).
+
+    Every rank builds one from the SAME table, then ``export_blob()`` -> gather the blobs of all ranks ->
+    ``connect(blobs, allgather, ctx)``; afterwards the ordinary Plan calls are collective: every rank makes the same
+    calls, with state vectors holding only amplitudes [rank * local_dim, (rank + 1) * local_dim).
+    See ``quantumsimulations_b200.shard`` for the torch.distributed and in-process (thread) connectors.
+    """
+
+    def __init__(self, table: SpinTable, rank: int, world: int, device: int = 0):
+        self.rank, self.world = int(rank), int(world)
+        self._hook = None
+        super().__init__(table, device)
+        d = C.c_uint64(0)
+        _check(self.lib.qsb_plan_local_dim(self._h, C.byref(d)))
+        self.local_dim = int(d.value)
+
+    def _create(self, device: int) -> None:
+        _check(self.lib.qsb_shard_plan_create(C.byref(self._holder.c), device, self.rank, self.world, C.byref(self._h)))
+
+    def export_blob(self) -> bytes:
+        buf = C.create_string_buffer(SHARD_BLOB_BYTES)
+        _check(self.lib.qsb_shard_export(self._h, buf))
+        return buf.raw
+
+    def connect(self, blobs: Sequence[bytes], allgather, ctx=None) -> None:
+        """``allgather``: an ALLGATHER_FN instance or a raw function address (e.g. qsb_local_allgather)."""
+        if len(blobs) != self.world or any(len(b) != SHARD_BLOB_BYTES for b in blobs):
+            raise ValueError("need one blob of SHARD_BLOB_BYTES bytes per rank")
+        joined = C.create_string_buffer(b"".join(blobs), SHARD_BLOB_BYTES * self.world)
+        self._hook = allgather  # keep the ctypes callback alive as long as the plan
+        fn = C.cast(allgather, C.c_void_p)
+        _check(self.lib.qsb_shard_connect(self._h, joined, fn, C.c_void_p(ctx) if ctx is not None else None))
+
+    def local_slice(self) -> slice:
+        return slice(self.rank * self.local_dim, (self.rank + 1) * self.local_dim)
 
 
 def evolve_batch(tables: Sequence[SpinTable], t_out: np.ndarray, opts: Sequence[SolverOptions], device: int = 0):

@@ -1,0 +1,127 @@
+"""GPU parity of the sharded-state path (BASELINE config C5).
+
+The ranks are threads of one process (LocalShardGroup), each with its own plan, stream and exchange scratch; with
+one GPU on the box they all sit on cuda:0 and the "peer" loads/stores of the centre pass are plain device accesses
+into the other ranks' buffers.  The rank barrier is host-side (stream drain + thread barrier), so nothing spins on
+the device.  Checked: one H-apply against the numpy oracle of the table semantics, and whole trajectories against
+the unsharded engine on the same table (same kernels, different partition: agreement to rounding).
+"""
+import numpy as np
+import pytest
+
+from conftest import exact_traces, params_from_meta, random_table
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand_state(n, seed):
+    rng = np.random.default_rng(seed)
+    v = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
+    return v / np.linalg.norm(v)
+
+
+@pytest.mark.parametrize("n,world", [(13, 2), (14, 2), (14, 4), (15, 8), (16, 4), (18, 8)])
+def test_sharded_happly_random_table(n, world):
+    from oracle import dense
+    from quantumsimulations_b200 import shard
+
+    table = random_table(n, 500 + n + world)
+    bm = table.bit_major()
+    psi = _rand_state(n, n * world)
+    want = dense.apply_h(bm["h"], bm["J"], psi)
+    with shard.LocalShardGroup(table, world) as grp:
+        got = grp.apply_h(psi)
+    err = np.max(np.abs(got - want)) / np.max(np.abs(want))
+    assert err < 2e-13, f"n={n} world={world}: rel err {err:.3e}"
+
+
+@pytest.mark.parametrize("n,world,gmax", [(17, 2, 3), (18, 4, 2), (19, 2, 4), (19, 8, 3)])
+def test_sharded_happly_multi_group(n, world, gmax, monkeypatch):
+    """Mid passes on local groups plus a centre group that mixes local and rank bits."""
+    from oracle import dense
+    from quantumsimulations_b200 import shard
+
+    monkeypatch.setenv("QSB200_MAX_GROUP", str(gmax))
+    table = random_table(n, 600 + n + world, dense_pairs=False)
+    bm = table.bit_major()
+    psi = _rand_state(n, 3 * n + world)
+    want = dense.apply_h(bm["h"], bm["J"], psi)
+    with shard.LocalShardGroup(table, world) as grp:
+        got = grp.apply_h(psi)
+    err = np.max(np.abs(got - want)) / np.max(np.abs(want))
+    assert err < 2e-13, f"n={n} world={world} gmax={gmax}: rel err {err:.3e}"
+
+
+@pytest.mark.parametrize("method,world", [("dp5", 2), ("taylor", 4), ("taylor", 8)])
+def test_sharded_trajectory_matches_unsharded_and_exact(method, world, golden_cases):
+    """N = 13 reference geometry (dataclass default, icosahedron) padded by nothing: 13 - 3 < 12, so use N = 15."""
+    from bench import sweep_params
+    from quantumsimulations_b200 import compile_table, engine, shard
+
+    table = compile_table(sweep_params(14, 50e3, t_final=2e-5, steps=9))  # N = 15, Fibonacci shell, rare ON
+    t = np.linspace(0.0, 2e-5, 9)
+    opts = engine.SolverOptions(atol=1e-12, rtol=1e-11, max_step=1e-5, nsteps=100000, method=method,
+                                order=16 if method == "taylor" else 0)
+    with engine.Plan(table) as plan:
+        ref, st_ref = plan.evolve(t, opts)
+    with shard.LocalShardGroup(table, world) as grp:
+        got, st = grp.evolve(t, opts)
+    assert st.n_accepted == st_ref.n_accepted and st.n_rejected == st_ref.n_rejected
+    assert np.max(np.abs(got - ref)) < 1e-11
+    want = exact_traces(table, t) if table.n <= 13 else None
+    if want is not None:
+        for i, k in enumerate(("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R")):
+            assert np.max(np.abs(got[:, i] - want[k])) < 1e-6
+
+
+def test_sharded_exact_n13_world2(golden_cases):
+    """The reference's dataclass-default geometry (N = 13, DE:332-384) split over 2 ranks vs exact diagonalisation."""
+    from quantumsimulations_b200 import compile_table, engine, shard
+
+    meta, _ = golden_cases
+    table = compile_table(params_from_meta(meta["n13_dataclass_default"]))
+    t = np.linspace(0.0, 2e-3, 6)
+    opts = engine.SolverOptions(atol=1e-11, rtol=1e-10, nsteps=100000, method="taylor", order=20)
+    with shard.LocalShardGroup(table, 2) as grp:
+        got, _ = grp.evolve(t, opts)
+    want = exact_traces(table, t)
+    for i, k in enumerate(("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R")):
+        assert np.max(np.abs(got[:, i] - want[k])) < 1e-6, k
+
+
+def test_sharded_state_roundtrip_and_host_psi0():
+    from quantumsimulations_b200 import engine, shard
+
+    n, world = 14, 4
+    table = random_table(n, 77)
+    psi0 = _rand_state(n, 5)
+    opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, method="dp5")
+    with engine.Plan(table) as plan:
+        plan.session_begin(opts, psi0=psi0)
+        plan.session_step(3)
+        want = plan.session_state()
+        wobs = plan.session_observe()
+        plan.session_end()
+    with shard.LocalShardGroup(table, world) as grp:
+        def work(plan, r):
+            plan.session_begin(opts, psi0=psi0[plan.local_slice()])
+            plan.session_step(3)
+            out = plan.session_state(), plan.session_observe()
+            plan.session_end()
+            return out
+        res = grp.run(work)
+    got = np.concatenate([r[0] for r in res])
+    assert np.max(np.abs(got - want)) < 1e-13
+    for r in res:
+        assert np.max(np.abs(r[1] - wobs)) < 1e-12
+
+
+def test_unconnected_sharded_plan_refuses():
+    from quantumsimulations_b200 import engine
+
+    table = random_table(13, 9)
+    with engine.ShardedPlan(table, 0, 2) as plan:
+        with pytest.raises(ValueError):
+            plan.session_begin(engine.SolverOptions())
+    with pytest.raises((ValueError, engine.EngineError)):
+        engine.ShardedPlan(random_table(12, 9), 0, 2)
