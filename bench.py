@@ -191,6 +191,8 @@ def run_b200(args, rank, world, local_rank):
     if world > 1:
         import torch.distributed as dist
 
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
@@ -295,6 +297,12 @@ def run_b200(args, rank, world, local_rank):
         sweep_steps = float(tt.item())
         sweep_kernel_ms = allmax(sweep_kernel_ms)
 
+    sharded = None
+    if not args.no_sharded:
+        barrier()
+        torch.cuda.empty_cache()
+        sharded = sharded_leg(args, rank, world, local_rank, barrier, allmax)
+
     if rank == 0:
         launches_per_step = 1 + n_rhs * kernels_per_apply(n) + 1 if args.method == "dp5" else n_rhs * kernels_per_apply(n) + 2
         cpu = cpu_port_step_rate(n_sea, 50e3) if world == 1 and not args.no_cpu else None
@@ -318,11 +326,69 @@ def run_b200(args, rank, world, local_rank):
                       "wall_s_default_integrator": sweep_default_s,
                       "default_integrator": "taylor order 20, atol/rtol x 1e-3 (what simulate_rare runs)",
                       "cpu_zvode": zv},
+            "sharded": sharded,
         }
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def sharded_leg(args, rank, world, local_rank, barrier, allmax):
+    """C5: ONE trajectory whose state vector is sharded over all ranks (top log2(world) index bits = rank), Taylor
+    step attempts.  world == 1 gives the single-GPU anchor at the same per-GPU shard size.  Returns a dict on rank 0."""
+    from quantumsimulations_b200 import compile_table, engine, shard
+
+    wl = world.bit_length() - 1
+    n = args.shard_local_bits + wl
+    table = compile_table(sweep_params(n - 1, 50e3))
+    order = 8
+    opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, max_step=1e-5, nsteps=0, method="taylor", order=order)
+    if world > 1:
+        plan = shard.sharded_plan_from_env(table, local_rank)
+    else:
+        plan = engine.Plan(table, local_rank)
+    s_loc = 16.0 * plan.local_dim
+    plan.session_begin(opts)
+    plan.session_step(1)
+    barrier()
+    attempts = 2
+    _, st0, _ = plan.session_step(0)
+    t_now, st, ms = plan.session_step(attempts)
+    barrier()
+    ms = allmax(ms)
+    n_rhs = st.n_rhs - st0.n_rhs
+    obs = plan.session_observe()
+    engine.profile(True)
+    plan.session_step(1)
+    kms, kcnt = engine.profile_read()
+    engine.profile(False)
+    centre_ms = allmax(kms["pass_centre"] / max(kcnt["pass_centre"], 1))
+    plan.session_end()
+    plan.close()
+    barrier()
+    if rank != 0:
+        return None
+    peak, how = measured_peak()
+    out = {
+        "workload": f"C5: one trajectory, N={n} spins sharded over {world} GPU(s) ({args.shard_local_bits} local index bits, "
+                    f"{s_loc / 1e9:.1f} GB per vector per GPU), Taylor({order}) step attempts",
+        "n_qubits": n, "world": world, "method": f"taylor{order}", "attempts": attempts, "n_rhs": n_rhs,
+        "steps_per_s": attempts / (ms / 1e3), "ms_per_happly": ms / n_rhs,
+        "layouts": engine.tile_layouts(n, world),
+        "hbm": {"algorithmic_GBps_per_gpu": (n_rhs + attempts) * 2.0 * s_loc / (ms / 1e3) / 1e9, "peak": peak, "peak_source": how},
+        "kernel_ms": {k: (kms[k] / kcnt[k] if kcnt[k] else None) for k in kms},
+        "raw_norm": float(obs[7]), "Iz_sea": float(obs[2]), "t_reached": t_now,
+    }
+    out["hbm"]["frac"] = out["hbm"]["algorithmic_GBps_per_gpu"] / peak
+    if world > 1:
+        per_dir = 4.0 * (world - 1) / world * s_loc   # x and y branch, loads by me + stores by the peers (and vice versa)
+        out["nvlink"] = {"bytes_per_happly_per_gpu_per_direction": per_dir, "centre_ms": centre_ms,
+                         "achieved_GBps_per_direction": per_dir / (centre_ms / 1e3) / 1e9, "peak": 770.0,
+                         "peak_source": "B200_PROFILING.md measured peer copy, per direction",
+                         "frac": per_dir / (centre_ms / 1e3) / 1e9 / 770.0,
+                         "kernel": "pass_centre<sharded>: W_g D W_g on tiles gathered from / scattered to the peers' scratch (P2P ld/st)"}
+    return out
 
 
 def kernels_per_apply(n):
@@ -340,6 +406,8 @@ def main():
     ap.add_argument("--n-qubits", type=int, default=28)
     ap.add_argument("--method", default="dp5", choices=["dp5", "taylor"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline legs")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the sharded-state (C5) leg")
+    ap.add_argument("--shard-local-bits", type=int, default=30, help="index bits per GPU in the sharded leg (30: 17 GB vectors)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

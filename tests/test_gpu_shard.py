@@ -125,3 +125,21 @@ def test_unconnected_sharded_plan_refuses():
             plan.session_begin(engine.SolverOptions())
     with pytest.raises((ValueError, engine.EngineError)):
         engine.ShardedPlan(random_table(12, 9), 0, 2)
+
+
+def test_multi_process_parity_two_gpus():
+    """One process per GPU over CUDA IPC + NCCL (needs >= 2 GPUs on the box; skipped otherwise)."""
+    import os
+    import subprocess
+    import sys
+
+    from quantumsimulations_b200 import engine
+
+    if engine.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29733", os.path.join(root, "scripts", "shard_parity.py"), "--qubits", "18"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert '"ok": true' in res.stdout
