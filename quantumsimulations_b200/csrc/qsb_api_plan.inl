@@ -16,7 +16,7 @@ struct qsb_plan {
   // tiled path
   LargeGeom g = {};
   DiagTables tab = {};
-  double* d_tables = nullptr;   // h, J, Qx, Qy, Qz in one allocation
+  double* d_tables = nullptr;   // h, J and the factored in-tile diagonal tables in one allocation
   double* d_tiles = nullptr;    // per-tile diagonal rows Tx, Ty, Tz
   void* ws = nullptr;           // workspace (vectors + partials)
   size_t ws_bytes = 0;
@@ -118,31 +118,35 @@ static int plan_create(const qsb_table* table, int device, int rank, int world, 
           if (b != c) J[((size_t)a * ne + b) * ne + c] = table->J[((size_t)a * n + b) * n + c];
       }
     const Layout& Lc = p->g.lay[p->g.n_layouts - 1];
-    std::vector<double> qx = host_q_table(h.data(), J.data(), ne, 0, Lc, std::ldexp(1.0, -ne));
-    std::vector<double> qy = host_q_table(h.data(), J.data(), ne, 1, Lc, std::ldexp(1.0, -ne));
-    std::vector<double> qz = host_q_table(h.data(), J.data(), ne, 2, p->g.lay[0], 1.0);
+    const int wc = centre_window(Lc);
+    const InTileDiag qx = host_in_tile_diag(h.data(), J.data(), ne, 0, Lc, wc, std::ldexp(1.0, -ne));
+    const InTileDiag qy = host_in_tile_diag(h.data(), J.data(), ne, 1, Lc, wc, std::ldexp(1.0, -ne));
+    const InTileDiag qz = host_in_tile_diag(h.data(), J.data(), ne, 2, p->g.lay[0], 8, 1.0);
     std::vector<double> blob;
     blob.insert(blob.end(), h.begin(), h.end());
     blob.insert(blob.end(), J.begin(), J.end());
     size_t off_q = blob.size();
-    blob.insert(blob.end(), qx.begin(), qx.end());
-    blob.insert(blob.end(), qy.begin(), qy.end());
-    blob.insert(blob.end(), qz.begin(), qz.end());
+    blob.insert(blob.end(), qx.tab, qx.tab + 5 * 256);
+    blob.insert(blob.end(), qy.tab, qy.tab + 5 * 256);
+    blob.insert(blob.end(), qz.tab, qz.tab + 5 * 256);
+    memcpy(p->tab.Wx, qx.ww, sizeof qx.ww);
+    memcpy(p->tab.Wy, qy.ww, sizeof qy.ww);
+    memcpy(p->tab.Wz, qz.ww, sizeof qz.ww);
     QSB_CUDA(cudaMalloc(&p->d_tables, blob.size() * sizeof(double)));
     QSB_CUDA(cudaMemcpy(p->d_tables, blob.data(), blob.size() * sizeof(double), cudaMemcpyHostToDevice));
     p->tab.h = p->d_tables;
     p->tab.J = p->d_tables + h.size();
-    p->tab.Qx = p->d_tables + off_q;
-    p->tab.Qy = p->tab.Qx + TILE;
-    p->tab.Qz = p->tab.Qy + TILE;
+    p->tab.Ix = p->d_tables + off_q;
+    p->tab.Iy = p->tab.Ix + 5 * 256;
+    p->tab.Iz = p->tab.Iy + 5 * 256;
     const size_t td = tile_diag_doubles(p->n_loc);
     QSB_CUDA(cudaMalloc(&p->d_tiles, 3 * td * sizeof(double)));
     const double sxy = std::ldexp(1.0, -ne);
     // this rank's slice of the centre tiles (the rank bits are inside those tiles); its own layout-0 tiles
     const uint64_t ntl = 1ull << (p->n_loc - TB), v0 = (uint64_t)rank * ntl;
-    launch_build_tile_diag(p->tab.h, p->tab.J, ne, Lc, sxy, p->d_tiles, ntl, v0, 0, p->stream);
-    launch_build_tile_diag(p->tab.h + ne, p->tab.J + (size_t)ne * ne, ne, Lc, sxy, p->d_tiles + td, ntl, v0, 0, p->stream);
-    launch_build_tile_diag(p->tab.h + 2 * ne, p->tab.J + 2 * (size_t)ne * ne, ne, p->g.lay[0], 1.0, p->d_tiles + 2 * td,
+    launch_build_tile_diag(p->tab.h, p->tab.J, ne, Lc, wc, sxy, p->d_tiles, ntl, v0, 0, p->stream);
+    launch_build_tile_diag(p->tab.h + ne, p->tab.J + (size_t)ne * ne, ne, Lc, wc, sxy, p->d_tiles + td, ntl, v0, 0, p->stream);
+    launch_build_tile_diag(p->tab.h + 2 * ne, p->tab.J + 2 * (size_t)ne * ne, ne, p->g.lay[0], 8, 1.0, p->d_tiles + 2 * td,
                            ntl, 0, p->g.rank_bits, p->stream);
     QSB_CUDA(cudaGetLastError());
     QSB_CUDA(cudaStreamSynchronize(p->stream));

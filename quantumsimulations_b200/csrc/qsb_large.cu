@@ -72,25 +72,42 @@ LargeGeom make_geometry(int n, int rank, int world) {
 
 static inline int global_bit(const Layout& L, int b) { return b < L.lk ? b : L.gs + (b - L.lk); }
 
-std::vector<double> host_q_table(const double* h, const double* J, int n, int basis, const Layout& L, double scale) {
-  std::vector<double> q(TILE);
+int centre_window(const Layout& L) { return (!L.m4 && !L.m0) ? 8 : (!L.m0 ? 4 : 0); }
+
+InTileDiag host_in_tile_diag(const double* h, const double* J, int n, int basis, const Layout& L, int W, double scale) {
+  InTileDiag d;
   const double* hb = h + (size_t)basis * n;
   const double* Jb = J + (size_t)basis * n * n;
-  for (int u = 0; u < TILE; ++u) {
-    double acc = 0.0;
+  auto Jg = [&](int b, int c) { return Jb[(size_t)global_bit(L, b) * n + global_bit(L, c)]; };
+  for (int tt = 0; tt < 256; ++tt) {
+    // elem<W>(tt, 0): tt's low W bits are tile bits [0, W), the rest tile bits [W + 4, 12)
+    const int i0 = (tt & ((1 << W) - 1)) | ((tt >> W) << (W + 4));
+    auto sgn = [&](int b) { return (i0 >> b & 1) ? -1.0 : 1.0; };
+    auto in_window = [&](int b) { return b >= W && b < W + 4; };
+    double A = 0.0;
     for (int b = 0; b < TB; ++b) {
-      int gb = global_bit(L, b);
-      double sb = (u >> b & 1) ? -1.0 : 1.0;
-      acc += 0.5 * hb[gb] * sb;
-      for (int c = b + 1; c < TB; ++c) {
-        int gc = global_bit(L, c);
-        double sc = (u >> c & 1) ? -sb : sb;
-        acc += 0.25 * Jb[(size_t)gb * n + gc] * sc;
-      }
+      if (in_window(b)) continue;
+      A += 0.5 * hb[global_bit(L, b)] * sgn(b);
+      for (int c = b + 1; c < TB; ++c)
+        if (!in_window(c)) A += 0.25 * Jg(b, c) * sgn(b) * sgn(c);
     }
-    q[u] = acc * scale;
+    d.tab[tt] = A * scale;
+    for (int k = 0; k < 4; ++k) {
+      const int wb = W + k;
+      double l = 0.5 * hb[global_bit(L, wb)];
+      for (int c = 0; c < TB; ++c)
+        if (!in_window(c)) l += 0.25 * Jg(wb, c) * sgn(c);
+      d.tab[(1 + k) * 256 + tt] = l * scale;
+    }
   }
-  return q;
+  for (int j = 0; j < 16; ++j) {
+    double acc = 0.0;
+    for (int k = 0; k < 4; ++k)
+      for (int k2 = k + 1; k2 < 4; ++k2)
+        acc += 0.25 * Jg(W + k, W + k2) * ((j >> k & 1) ? -1.0 : 1.0) * ((j >> k2 & 1) ? -1.0 : 1.0);
+    d.ww[j] = acc * scale;
+  }
+  return d;
 }
 
 namespace {
@@ -110,6 +127,32 @@ __device__ __forceinline__ uint64_t tile_base(const Layout& L, uint64_t v) {
   uint64_t mid = v & ((1ull << midbits) - 1), hi = v >> midbits;
   return (mid << L.lk) | (hi << L.ge);
 }
+// Hides a value's provenance from the optimiser.  The store addresses of a pass equal its load addresses; without
+// this the compiler keeps all sixteen 64-bit addresses live across the whole kernel (32 registers -> spills).
+// Index offsets of the four window bits [W, W+4) of a tile in layout L: the 16 amplitudes a thread holds for window
+// W sit at idx0 + (sum of off[k] over the set bits of j), which costs 8 registers instead of 16 addresses.
+struct WinOff {
+  uint64_t off[4];
+  // late0: 0, optionally a "late zero" (see pass_mid / pass_centre) that keeps the offsets for a pass's stores from
+  // being shared with (and kept alive since) the ones for its loads
+  template <int W>
+  __device__ __forceinline__ void init(const Layout& L, unsigned late0) {
+    const int lk = L.lk + (int)late0, gs = L.gs;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int b = W + k;
+      off[k] = 1ull << (b < lk ? b : gs + (b - lk));
+    }
+  }
+  __device__ __forceinline__ uint64_t at(int j) const {  // j: compile-time constant after unrolling
+    uint64_t o = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (j >> k & 1) o += off[k];
+    return o;
+  }
+};
+
 __device__ __forceinline__ uint64_t gidx(const Layout& L, uint64_t base, int i) {
   return (uint64_t)(i & ((1 << L.lk) - 1)) | ((uint64_t)(i >> L.lk) << L.gs) | base;
 }
@@ -144,15 +187,25 @@ __device__ __forceinline__ void bfly16(cplx (&r)[16], int mask) {
   }
 }
 
+// Padded shared-memory position of elem<W>(tt, j): phys(elem) is linear in j because the pad (one slot per 16)
+// never splits a window, so a thread addresses its 16 slots as ONE base + compile-time offsets j * PS<W>
+// (no per-element address registers).
+template <int W>
+struct PhysStride { static constexpr int value = (W == 8) ? 256 + 16 : (W == 4) ? 16 + 1 : 1; };
+template <int W>
+__device__ __forceinline__ int phys_base(int tt) { return phys(elem<W>(tt, 0)); }
+
 template <int W>
 __device__ __forceinline__ void smem_load16(const cplx* sm, int tt, cplx (&r)[16]) {
+  const cplx* p = sm + phys_base<W>(tt);
 #pragma unroll
-  for (int j = 0; j < 16; ++j) r[j] = sm[phys(elem<W>(tt, j))];
+  for (int j = 0; j < 16; ++j) r[j] = p[j * PhysStride<W>::value];
 }
 template <int W>
 __device__ __forceinline__ void smem_store16(cplx* sm, int tt, const cplx (&r)[16]) {
+  cplx* p = sm + phys_base<W>(tt);
 #pragma unroll
-  for (int j = 0; j < 16; ++j) sm[phys(elem<W>(tt, j))] = r[j];
+  for (int j = 0; j < 16; ++j) p[j * PhysStride<W>::value] = r[j];
 }
 template <int W, int MODE>
 __device__ __forceinline__ void smem_round(cplx* sm, int tt, int mask) {
@@ -162,33 +215,34 @@ __device__ __forceinline__ void smem_round(cplx* sm, int tt, int mask) {
   smem_store16<W>(sm, tt, r);
 }
 
-// Diagonal form on a tile:  D(u; v) = Q[u] + cst(v) + sum_b s_b(u) lin_b(v)   (u = tile-local index, v = tile).
-// (lin[12], cst) per tile come from a table built once per plan (build_tile_diag below), one 128-byte row per
-// tile, so a pass issues these 13 uniform loads next to its tile loads and needs no shared memory or barrier.
-constexpr int TD_STRIDE = 16;  // doubles per tile row: lin[0..11], cst, 3 pad
+// Diagonal form on a tile:  D(u; v) = D_in(u) + cst(v) + sum_b s_b(u) lin_b(v)   (u = tile-local index, v = tile).
+// The tile-dependent part is stored per tile, already folded for the register window W the consuming pass uses
+// (one 320-byte row per tile, built once per plan by build_tile_diag below):
+//   row[0..15]  F_lo[tt & 15]  = cst + sum over the tile bits fed by tt's low nibble  of +-lin_b
+//   row[16..31] F_hi[tt >> 4]  =       sum over the tile bits fed by tt's high nibble of +-lin_b
+//   row[32..35] lin of the four window bits
+// so a thread needs 2 + 4 row values and its 5 in-tile table values: 11 loads, ~22 transient registers.
+constexpr int TD_STRIDE = 40;
 
-// Everything of D that a thread can hoist out of its 16-element loop for window W: the cst + the eight
-// non-window bits (fixed by the thread index) and the sixteen window-bit sign combinations.
+// Everything of D that a thread can hoist out of its 16-element loop for window W: the per-tile cst, the eight
+// non-window bits (fixed by the thread index) and this thread's row of the factored in-tile table; what is left per
+// element is four sign-folded adds and one constant-bank operand.
 template <int W>
 struct TileDiag {
   double fixed;
   double w[4];
-  __device__ __forceinline__ void load(const double* __restrict__ row, int tt) {
-    fixed = __ldg(row + TB);
-    const int i0 = elem<W>(tt, 0);
+  __device__ __forceinline__ void load(const double* __restrict__ row, const double* __restrict__ intile, int tt) {
+    fixed = (__ldg(row + (tt & 15)) + __ldg(row + 16 + (tt >> 4))) + __ldg(intile + tt);
 #pragma unroll
-    for (int b = 0; b < TB; ++b) {
-      double l = __ldg(row + b);
-      if (b >= W && b < W + 4) w[b - W] = l;
-      else fixed += (i0 >> b & 1) ? -l : l;
-    }
+    for (int k = 0; k < 4; ++k) w[k] = __ldg(row + 32 + k) + __ldg(intile + (1 + k) * 256 + tt);
   }
-  // j must be a compile-time constant after unrolling: the sign pattern then folds into add/sub
-  __device__ __forceinline__ double at(const double* __restrict__ Q, int tt, int j) const {
-    double a = fixed;
+  // j must be a compile-time constant after unrolling: the sign pattern folds into add/sub and ww[j] is read
+  // straight from the kernel-parameter bank
+  __device__ __forceinline__ double at(const double (&ww)[16], int j) const {
+    double a = fixed + ww[j];
 #pragma unroll
     for (int k = 0; k < 4; ++k) a += (j >> k & 1) ? -w[k] : w[k];
-    return __ldg(Q + elem<W>(tt, j)) + a;
+    return a;
   }
 };
 
@@ -197,8 +251,8 @@ __device__ __forceinline__ int sea_weight(uint64_t idx, uint64_t sea_mask, int n
 }
 
 // One thread per tile: lin_b(v) = scale/4 * sum_{c outer} J[gb(b)][c] s_c(v),
-// cst(v) = scale * (sum_{c outer} h_c s_c/2 + sum_{c<c' outer} J[c][c'] s_c s_c'/4).
-__global__ void build_tile_diag_kernel(const double* __restrict__ h, const double* __restrict__ J, int n, Layout L,
+// cst(v) = scale * (sum_{c outer} h_c s_c/2 + sum_{c<c' outer} J[c][c'] s_c s_c'/4), folded for window W.
+__global__ void build_tile_diag_kernel(const double* __restrict__ h, const double* __restrict__ J, int n, Layout L, int W,
                                        double scale, double* __restrict__ out, uint64_t n_tiles, uint64_t v0,
                                        uint64_t extra_bits) {
   uint64_t v = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -206,12 +260,13 @@ __global__ void build_tile_diag_kernel(const double* __restrict__ h, const doubl
   const uint64_t base = tile_base(L, v + v0) | extra_bits;
   const uint64_t outer = ~L.tile_mask & ((1ull << n) - 1);
   double* row = out + v * TD_STRIDE;
+  double lin[TB];
   for (int b = 0; b < TB; ++b) {
     int gb = b < L.lk ? b : L.gs + (b - L.lk);
     double acc = 0.0;
     for (int c = 0; c < n; ++c)
       if (outer >> c & 1) acc = fma((base >> c & 1) ? -0.25 : 0.25, J[(size_t)gb * n + c], acc);
-    row[b] = acc * scale;
+    lin[b] = acc * scale;
   }
   double cst = 0.0;
   for (int c = 0; c < n; ++c) {
@@ -221,18 +276,29 @@ __global__ void build_tile_diag_kernel(const double* __restrict__ h, const doubl
       if (outer >> c2 & 1) acc = fma((base >> c2 & 1) ? -0.25 : 0.25, J[(size_t)c * n + c2], acc);
     cst = fma((base >> c & 1) ? -1.0 : 1.0, acc, cst);
   }
-  row[TB] = cst * scale;
-  row[TB + 1] = row[TB + 2] = row[TB + 3] = 0.0;
+  cst *= scale;
+  // thread bits in ascending order: tt bit q feeds tile bit (q < W ? q : q + 4)
+  for (int half = 0; half < 2; ++half)
+    for (int m = 0; m < 16; ++m) {
+      double acc = half ? 0.0 : cst;
+      for (int q = 0; q < 4; ++q) {
+        const int tq = 4 * half + q, b = tq < W ? tq : tq + 4;
+        acc += (m >> q & 1) ? -lin[b] : lin[b];
+      }
+      row[16 * half + m] = acc;
+    }
+  for (int k = 0; k < 4; ++k) row[32 + k] = lin[W + k];
+  row[36] = row[37] = row[38] = row[39] = 0.0;
 }
 
 }  // namespace
 
 size_t tile_diag_doubles(int n_loc) { return (size_t)TD_STRIDE << (n_loc - TB); }
 
-void launch_build_tile_diag(const double* d_h, const double* d_J, int n, const Layout& L, double scale, double* d_out,
-                            uint64_t n_tiles, uint64_t v0, uint64_t extra_bits, cudaStream_t stream) {
+void launch_build_tile_diag(const double* d_h, const double* d_J, int n, const Layout& L, int W, double scale,
+                            double* d_out, uint64_t n_tiles, uint64_t v0, uint64_t extra_bits, cudaStream_t stream) {
   const unsigned blocks = (unsigned)((n_tiles + 127) / 128);
-  build_tile_diag_kernel<<<blocks, 128, 0, stream>>>(d_h, d_J, n, L, scale, d_out, n_tiles, v0, extra_bits);
+  build_tile_diag_kernel<<<blocks, 128, 0, stream>>>(d_h, d_J, n, L, W, scale, d_out, n_tiles, v0, extra_bits);
 }
 
 }  // namespace qsb

@@ -28,10 +28,12 @@ struct Layout {
 struct DiagTables {      // device pointers
   const double* h;       // [3][n]
   const double* J;       // [3][n][n]
-  const double* Qx;      // [4096] centre-layout, x basis (2^-n folded in)
-  const double* Qy;      // [4096] centre-layout, y basis
-  const double* Qz;      // [4096] layout 0, z basis
-  const double* Tx;      // [n_tiles][16] per-tile (lin[12], cst) of the centre layout, x basis
+  // In-tile part of a diagonal form, factored for the register window the pass evaluates it in (InTileDiag):
+  const double* Ix;      // [5][256] centre layout, x basis (2^-n folded in)
+  const double* Iy;      // [5][256] centre layout, y basis
+  const double* Iz;      // [5][256] layout 0, z basis, window 8
+  double Wx[16], Wy[16], Wz[16];  // window-window pair sums; live in the kernel parameter (constant) bank
+  const double* Tx;      // [n_tiles][40] per-tile rows (window-folded lin/cst) of the centre layout, x basis
   const double* Ty;      //               ... y basis
   const double* Tz;      //               ... layout 0, z basis
 };
@@ -78,13 +80,24 @@ struct ShardLink {
 // Layouts over n index bits of which the top log2(world) are rank bits (they end up inside the centre group).
 LargeGeom make_geometry(int n, int rank = 0, int world = 1);
 size_t tile_diag_doubles(int n_loc);
-// d_h/d_J: device [n] / [n][n] of ONE basis.  Fills d_out[n_tiles_loc][16] for tiles v0 .. v0 + n_tiles_loc - 1 of
+// d_h/d_J: device [n] / [n][n] of ONE basis.  Fills d_out[n_tiles_loc][40] for tiles v0 .. v0 + n_tiles_loc - 1 of
 // layout L; extra_bits are index bits outside the address space of this rank that belong to every such tile.
-void launch_build_tile_diag(const double* d_h, const double* d_J, int n, const Layout& L, double scale, double* d_out,
-                            uint64_t n_tiles_loc, uint64_t v0, uint64_t extra_bits, cudaStream_t stream);
+// W: the register window of the pass that will consume the rows (centre_window(L) for the centre, 8 for layout 0).
+void launch_build_tile_diag(const double* d_h, const double* d_J, int n, const Layout& L, int W, double scale,
+                            double* d_out, uint64_t n_tiles_loc, uint64_t v0, uint64_t extra_bits, cudaStream_t stream);
 // Per-device kernel attributes (dynamic shared memory opt-in); call once per device before launching.
 void prepare_device();
-std::vector<double> host_q_table(const double* h, const double* J, int n, int basis, const Layout& L, double scale);
+// In-tile diagonal D_in(u) = sum_b h_b s_b/2 + sum_{b<c} J_bc s_b s_c/4 over the 12 tile bits, factored for a thread
+// that holds the 16 amplitudes u = i0(tt) | j << W (window bits [W, W+4), the other 8 bits fixed by tt):
+//   D_in = A[tt] + sum_k s_k(j) Lk[tt] + Ww[j],   tab = {A[256], L0[256], L1[256], L2[256], L3[256]}, Ww[16].
+// 5 coalesced loads per thread instead of 16 gathers from a 4096-entry table, and far fewer live registers.
+struct InTileDiag {
+  double tab[5 * 256];
+  double ww[16];
+};
+InTileDiag host_in_tile_diag(const double* h, const double* J, int n, int basis, const Layout& L, int W, double scale);
+// Register window in which pass_centre evaluates the diagonal for layout L (8, 4 or 0).
+int centre_window(const Layout& L);
 
 // One H-apply: src -> epilogue.  tx/ty: scratch vectors of 2^n cplx.  partials: device doubles,
 // [n_tiles][PSTRIDE] = (nrm2, zsea, zrare, xsea, xrare, ysea, yrare, err, aux).  collect_obs: fill the observable slots.

@@ -22,6 +22,7 @@ constexpr double INV_TILE = 1.0 / (double)TILE;  // the 2^-12 of (M/2)^(x12)
 struct TileMap {
   unsigned cbase;
   int lb, cbits;
+  unsigned zero;  // always 0; see opaque()
   __device__ __forceinline__ uint64_t tile(unsigned bx) const {
     return (uint64_t)cbase + (bx & ((1u << lb) - 1)) + ((uint64_t)(bx >> lb) << cbits);
   }
@@ -94,8 +95,13 @@ pass_mid(Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty) {
   const int tt = threadIdx.x;
   const uint64_t base = tile_base(L, tm.tile(blockIdx.x));
   cplx r[16];
+  {
+    WinOff wo;
+    wo.init<8>(L, 0);
+    const cplx* p = t + gidx(L, base, elem<8>(tt, 0));
 #pragma unroll
-  for (int j = 0; j < 16; ++j) r[j] = t[gidx(L, base, elem<8>(tt, j))];
+    for (int j = 0; j < 16; ++j) r[j] = p[wo.at(j)];
+  }
   bfly16<0>(r, L.m8);
   smem_store16<8>(sm, tt, r);
   __syncthreads();
@@ -105,32 +111,36 @@ pass_mid(Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty) {
   }
   smem_load16<4>(sm, tt, r);
   bfly16<0>(r, L.m4);
+  {
+    const unsigned late0 = tm.zero & (unsigned)__double2loint(r[0].x);  // 0, but only known once the data is final
+    WinOff wo;
+    wo.init<4>(L, late0);
+    cplx* p = t + gidx(L, base | late0, elem<4>(tt, 0));
 #pragma unroll
-  for (int j = 0; j < 16; ++j) t[gidx(L, base, elem<4>(tt, j))] = r[j];
+    for (int j = 0; j < 16; ++j) p[wo.at(j)] = r[j];
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------
 // pass_centre: t <- W_g D W_g t on the centre layout; D is the x- or y-basis diagonal form evaluated on
 // the full index.  Optionally that basis' observable partial sums (taken on the fully transformed vector).
 // ---------------------------------------------------------------------------------------------------
-template <int W>
-__device__ __forceinline__ void centre_core(cplx (&r)[16], int tt, int mask, const double* __restrict__ trow,
-                                            const double* __restrict__ Q, const Layout& L, uint64_t base,
-                                            const LargeGeom& g, int collect_obs, double (&s)[2]) {
-  TileDiag<W> td;
-  td.load(trow, tt);
+template <int W, bool COLLECT>
+__device__ __forceinline__ void centre_core(cplx (&r)[16], int tt, int mask, const TileDiag<W>& td, const double (&ww)[16],
+                                            const Layout& L, uint64_t base, const LargeGeom& g, double (&s)[2]) {
   bfly16<0>(r, mask);
-  const int n_sea = __popcll(g.sea_mask);
+  if (COLLECT) {
+    const int n_sea = __popcll(g.sea_mask);
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    if (collect_obs) {
+    for (int j = 0; j < 16; ++j) {
       uint64_t idx = gidx(L, base, elem<W>(tt, j));
       double p = norm2(r[j]);
       s[0] = fma(p, (double)sea_weight(idx, g.sea_mask, n_sea), s[0]);
       s[1] += (idx & g.rare_mask) ? -p : p;
     }
-    r[j] = td.at(Q, tt, j) * r[j];
   }
+#pragma unroll
+  for (int j = 0; j < 16; ++j) r[j] = td.at(ww, j) * r[j];
   bfly16<0>(r, mask);
 }
 
@@ -139,46 +149,56 @@ struct PeerPtrs {
   cplx* t[2][MAX_WORLD];
 };
 
+// W = centre_window(L): the register window the diagonal is evaluated in (8: the group fits window [8,12) and never
+// touches shared memory; 4: N = 28; 0: groups wider than 8 bits do not exist, but layout 0 as centre (n = 12) and
+// short groups with lk > 8 land here).  The diagonal coefficients (10 registers) are fetched FIRST so that their
+// latency hides behind the tile loads and nothing but the data is live across the butterflies.
 // SHARDED: the group's top bits are the rank, so tile rows come from (and go back to) the peers' scratch vectors
 // through P2P loads/stores; this rank owns tiles tm.cbase .. of the centre layout and the diagonal rows / partial
 // sums are numbered locally (blockIdx.x).
-template <bool SHARDED>
+template <bool SHARDED, bool COLLECT, int W>
 __global__ void __launch_bounds__(TPT, 2)
 pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty, PeerPtrs peers,
-            int collect_obs, double* __restrict__ partials) {
+            double* __restrict__ partials) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
   __shared__ double red[2 * 32 + 2];
   const int branch = blockIdx.y;  // 0: x, 1: y
   cplx* t = branch ? ty : tx;
-  const double* Q = branch ? a.tab.Qy : a.tab.Qx;
+  const double (&ww)[16] = branch ? a.tab.Wy : a.tab.Wx;
   const uint64_t v = tm.tile(blockIdx.x);
-  const double* trow = (branch ? a.tab.Ty : a.tab.Tx) + (size_t)blockIdx.x * TD_STRIDE;
   const int tt = threadIdx.x;
+  TileDiag<W> td;
+  td.load((branch ? a.tab.Ty : a.tab.Tx) + (size_t)blockIdx.x * TD_STRIDE, branch ? a.tab.Iy : a.tab.Ix, tt);
   const uint64_t base = tile_base(L, v);
   const uint64_t lmask = (1ull << a.g.n_loc) - 1;
   cplx r[16];
   double s[2] = {0.0, 0.0};
+  {
+    WinOff wo;
+    wo.init<8>(L, 0);
+    const uint64_t idx0 = gidx(L, base, elem<8>(tt, 0));
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const uint64_t idx = gidx(L, base, elem<8>(tt, j));
-    r[j] = SHARDED ? peers.t[branch][idx >> a.g.n_loc][idx & lmask] : t[idx];
+    for (int j = 0; j < 16; ++j) {
+      const uint64_t idx = idx0 + wo.at(j);
+      r[j] = SHARDED ? peers.t[branch][idx >> a.g.n_loc][idx & lmask] : t[idx];
+    }
   }
-  if (!L.m4 && !L.m0) {
-    centre_core<8>(r, tt, L.m8, trow, Q, L, base, a.g, collect_obs, s);
+  if constexpr (W == 8) {
+    centre_core<8, COLLECT>(r, tt, L.m8, td, ww, L, base, a.g, s);
   } else {
     bfly16<0>(r, L.m8);
     smem_store16<8>(sm, tt, r);
     __syncthreads();
-    if (!L.m0) {
+    if constexpr (W == 4) {
       smem_load16<4>(sm, tt, r);
-      centre_core<4>(r, tt, L.m4, trow, Q, L, base, a.g, collect_obs, s);
+      centre_core<4, COLLECT>(r, tt, L.m4, td, ww, L, base, a.g, s);
       smem_store16<4>(sm, tt, r);
     } else {
       smem_round<4, 0>(sm, tt, L.m4);
       __syncthreads();
       smem_load16<0>(sm, tt, r);
-      centre_core<0>(r, tt, L.m0, trow, Q, L, base, a.g, collect_obs, s);
+      centre_core<0, COLLECT>(r, tt, L.m0, td, ww, L, base, a.g, s);
       smem_store16<0>(sm, tt, r);
       __syncthreads();
       smem_round<4, 0>(sm, tt, L.m4);
@@ -187,13 +207,19 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
     smem_load16<8>(sm, tt, r);
     bfly16<0>(r, L.m8);
   }
+  {
+    const unsigned late0 = tm.zero & (unsigned)__double2loint(r[0].x);  // 0, but only known once the data is final
+    WinOff wo;
+    wo.init<8>(L, late0);
+    const uint64_t idx0 = gidx(L, base | late0, elem<8>(tt, 0));
 #pragma unroll
-  for (int j = 0; j < 16; ++j) {
-    const uint64_t idx = gidx(L, base, elem<8>(tt, j));
-    if (SHARDED) peers.t[branch][idx >> a.g.n_loc][idx & lmask] = r[j];
-    else t[idx] = r[j];
+    for (int j = 0; j < 16; ++j) {
+      const uint64_t idx = idx0 + wo.at(j);
+      if (SHARDED) peers.t[branch][idx >> a.g.n_loc][idx & lmask] = r[j];
+      else t[idx] = r[j];
+    }
   }
-  if (collect_obs) {
+  if (COLLECT) {
     block_reduce<2>(s, red);
     if (threadIdx.x == 0) {
       double* p = partials + (size_t)blockIdx.x * PSTRIDE + 3 + 2 * branch;

@@ -58,7 +58,7 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
   bfly16<0>(r, 0xF);
 
   TileDiag<8> td;
-  td.load(a.tab.Tz + (size_t)blockIdx.x * TD_STRIDE, tt);
+  td.load(a.tab.Tz + (size_t)blockIdx.x * TD_STRIDE, a.tab.Iz, tt);
   const uint64_t idx0 = base | (uint64_t)tt;  // element j of this thread is idx0 + 256 j
   double err_acc = 0.0, aux_acc = 0.0;
   constexpr int B = (EPI & 2) ? 4 : 8;
@@ -70,7 +70,7 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
       for (int jj = 0; jj < B; ++jj) v[jj] = src[idx0 + 256u * (j0 + jj)];
 #pragma unroll
       for (int jj = 0; jj < B; ++jj) {
-        cplx acc = td.at(a.tab.Qz, tt, j0 + jj) * v[jj] + r[j0 + jj];
+        cplx acc = td.at(a.tab.Wz, j0 + jj) * v[jj] + r[j0 + jj];
         r[j0 + jj] = ep.raw_h ? acc : mul_mi(acc);
       }
     }
@@ -184,6 +184,30 @@ struct Timed {
 }  // namespace
 
 
+template <int W>
+static void set_centre_attrs(int sm) {
+  cudaFuncSetAttribute(pass_centre<false, false, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_centre<false, true, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_centre<true, false, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_centre<true, true, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+}
+
+template <bool SHARDED, int W>
+static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, const PeerPtrs& pp,
+                          int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream) {
+  if (collect_obs) pass_centre<SHARDED, true, W><<<dim3(n_tiles, 2), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
+  else pass_centre<SHARDED, false, W><<<dim3(n_tiles, 2), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
+}
+template <bool SHARDED>
+static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, const PeerPtrs& pp,
+                          int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream) {
+  switch (centre_window(L)) {
+    case 8: launch_centre<SHARDED, 8>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream); break;
+    case 4: launch_centre<SHARDED, 4>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream); break;
+    default: launch_centre<SHARDED, 0>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream); break;
+  }
+}
+
 void prepare_device() {
   const int sm = (int)((size_t)TILE_PHYS * sizeof(cplx));
   cudaFuncSetAttribute(pass_first, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
@@ -192,8 +216,9 @@ void prepare_device() {
   cudaFuncSetAttribute(pass_last<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
   cudaFuncSetAttribute(pass_last<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
   cudaFuncSetAttribute(pass_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_centre<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_centre<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  set_centre_attrs<8>(sm);
+  set_centre_attrs<4>(sm);
+  set_centre_attrs<0>(sm);
 }
 
 // The strided-layout passes of one H-apply (mids forward, centre, mids back).
@@ -207,12 +232,12 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
   const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx);
   const unsigned n_tiles = 1u << (g.n_loc - TB);
   const int centre = g.n_layouts - 1;
-  const TileMap all = {0u, 0, 0};
+  const TileMap all = {0u, 0, 0, 0u};
   for (int k = 1; k < centre; ++k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
   if (g.world == 1) {
     Timed t(2, stream);
     PeerPtrs none = {};
-    pass_centre<false><<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], all, tx, ty, none, collect_obs, partials);
+    launch_centre<false>(a, g.lay[centre], all, tx, ty, none, collect_obs, partials, n_tiles, sm1, stream);
   } else {
     if (!link) { set_error("sharded plan is not connected to its peers (qsb_shard_connect)"); return QSB_ERR_BAD_ARG; }
     int rc = link->sync(link->ctx);
@@ -221,8 +246,8 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
       Timed t(2, stream);
       PeerPtrs pp = {};
       for (int r = 0; r < g.world; ++r) { pp.t[0][r] = link->tx[r]; pp.t[1][r] = link->ty[r]; }
-      const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0};
-      pass_centre<true><<<dim3(n_tiles, 2), TPT, sm1, stream>>>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials);
+      const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u};
+      launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, stream);
     }
     rc = link->sync(link->ctx);
     if (rc) return rc;
