@@ -105,43 +105,32 @@ static int session_prime(qsb_plan* p, Session* s) {
   return QSB_OK;
 }
 
-// y2 = y + c k1 as its own sweep: k1 comes from the previous step's FSAL apply, whose epilogue could not know h.
-__global__ void axpy_kernel(cplx* __restrict__ out, const cplx* __restrict__ a, double c, const cplx* __restrict__ b,
-                            uint64_t n) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (uint64_t)gridDim.x * blockDim.x;
-  for (; i < n; i += stride) {
-    cplx v = a[i];
-    axpy(v, c, b[i]);
-    out[i] = v;
-  }
-}
-
 // One step attempt of size hu.  Returns the weighted RMS error in *err; obs sums of the candidate in cand_sums.
+// Every stage input y + hu sum_j a_sj k_j is formed inside pass_first of the apply that consumes it (Combine), the
+// applies end in the plain k-producing pass_last, and the embedded error estimate is one streaming sweep at the end:
+// no stage vector is read by a latency-bound epilogue.
 static int attempt_dp5(qsb_plan* p, Session* s, double hu, double* err, double* cand_sums) {
   static const DP5 T = dp5_tableau();
-  const int blocks = (int)std::min<uint64_t>((s->dim + 255) / 256, 148 * 8);
-  axpy_kernel<<<blocks, 256, 0, p->stream>>>(s->ys, s->y, hu * T.a[0][0], s->k[0], s->dim);
-  for (int st = 1; st <= 5; ++st) {  // apply #st: src = y_{st+1}, produces k_{st+1} and y_{st+2}
+  for (int st = 0; st <= 5; ++st) {  // apply #st: src = ys = y + hu sum_j a[st][j] k_j, produces k_{st+1} (0-based k[st+1])
+    Combine cb = {};
+    cb.vin[0] = s->y; cb.c[0] = 1.0; cb.n_in = 1;
+    for (int j = 0; j <= st; ++j)
+      if (T.a[st][j] != 0.0) { cb.vin[cb.n_in] = s->k[j]; cb.c[cb.n_in] = hu * T.a[st][j]; ++cb.n_in; }
+    cb.out = s->ys;
     Epilogue e = blank_epilogue(s);
-    e.o1 = s->k[st];
-    e.o2 = s->ys;
-    e.vin[0] = s->y; e.c[0] = 1.0; e.n_in = 1;
-    for (int j = 0; j < st; ++j)
-      if (T.a[st][j] != 0.0) { e.vin[e.n_in] = s->k[j]; e.c[e.n_in] = hu * T.a[st][j]; ++e.n_in; }
-    e.ck = hu * T.a[st][st];
-    int rc = launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, 0, s->partials, p->stream, link_of(p));
+    e.o1 = s->k[st + 1];
+    // the last apply acts on y_new (FSAL): its pass_first / pass_centre also collect y_new's observable sums
+    int rc = launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, st == 5 ? 1 : 0, s->partials, p->stream, link_of(p), &cb);
     if (rc) return rc;
   }
-  {  // FSAL apply on y_new: k7, the error estimate, and y_new's observable sums
-    Epilogue e = blank_epilogue(s);
-    e.o1 = s->k[6];
-    e.vin[0] = s->y; e.vin[1] = s->ys; e.n_in = 2;
-    for (int j = 0; j < 6; ++j)
-      if (T.e[j] != 0.0) { e.vin[e.n_in] = s->k[j]; e.e[e.n_in] = hu * T.e[j]; ++e.n_in; }
-    e.ek = hu * T.e[6];
-    e.want_err = 1; e.sc_i0 = 0; e.sc_i1 = 1;
-    int rc = launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, 1, s->partials, p->stream, link_of(p));
-    if (rc) return rc;
+  {
+    ErrSpec es = {};
+    es.vin[0] = s->y; es.vin[1] = s->ys; es.n_in = 2;
+    for (int j = 0; j < 7; ++j)
+      if (T.e[j] != 0.0) { es.vin[es.n_in] = s->k[j]; es.e[es.n_in] = hu * T.e[j]; ++es.n_in; }
+    es.sc_i0 = 0; es.sc_i1 = 1;
+    es.atol = s->o.atol; es.rtol = s->o.rtol;
+    launch_error_sums(p->g, es, s->partials, p->stream);
   }
   QSB_CUDA(cudaGetLastError());
   s->n_rhs += 6;

@@ -55,6 +55,26 @@ struct Epilogue {
 
 constexpr int MAX_WORLD = 8;
 
+// Stage combination fused into the load phase of pass_first: the vector the H-apply acts on is FORMED there,
+//     v = sum_q c_q vin_q      (e.g. the DP5 stage input y + h sum_j a_sj k_j),
+// written once to `out` (pass_last needs it for the Dz term) and transformed in the same pass.  n_in = 0: no
+// combination, pass_first just reads its src.
+struct Combine {
+  const cplx* vin[MAX_VEC_IN];
+  double c[MAX_VEC_IN];
+  cplx* out;
+  int n_in;
+};
+
+// Weighted error sums of an embedded pair, as its own streaming sweep (one CTA per 4096 amplitudes):
+//     partials[tile][7] = sum |sum_q e_q vin_q|^2 / sc^2,  sc = atol + rtol max(|vin[sc_i0]|, |vin[sc_i1]|)
+struct ErrSpec {
+  const cplx* vin[MAX_VEC_IN];
+  double e[MAX_VEC_IN];
+  int n_in, sc_i0, sc_i1;
+  double atol, rtol;
+};
+
 struct LargeGeom {
   int n;                 // index bits of the whole state (>= 12)
   int n_loc;             // index bits held by this rank: n - log2(world); the top n - n_loc bits are the rank
@@ -102,9 +122,12 @@ int centre_window(const Layout& L);
 // One H-apply: src -> epilogue.  tx/ty: scratch vectors of 2^n cplx.  partials: device doubles,
 // [n_tiles][PSTRIDE] = (nrm2, zsea, zrare, xsea, xrare, ysea, yrare, err, aux).  collect_obs: fill the observable slots.
 // link: null when unsharded.  Returns a qsb_status (only the rank barrier can fail).
+// comb: optional stage combination; when comb->n_in > 0 the apply acts on sum_q c_q vin_q, which is also written
+// to comb->out, and `src` must equal comb->out.  Epilogues take at most 2 input vectors.
 int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
                   const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream,
-                  const ShardLink* link = nullptr);
+                  const ShardLink* link = nullptr, const Combine* comb = nullptr);
+void launch_error_sums(const LargeGeom& g, const ErrSpec& es, double* partials, cudaStream_t stream);
 // Observables only (pass_first + mids + pass_centre), filling partial slots 0..6.
 int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
                    double* partials, cudaStream_t stream, const ShardLink* link = nullptr);

@@ -32,8 +32,11 @@ struct TileMap {
 // pass_first: layout 0.  tX = W0 psi;  tY = W0 S^dagger psi = c^dagger(v) (M'/2)^(x12) tX.
 // Optionally the z-basis observable partial sums.
 // ---------------------------------------------------------------------------------------------------
+// COMB: psi is formed here as sum_q c_q vin_q (Combine) and written to cb.out on the way; the loads go in two
+// half-bursts of 8 per input vector so that accumulators + in-flight values fit the register file.
+template <bool COMB>
 __global__ void __launch_bounds__(TPT, 2)
-pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx* __restrict__ ty,
+pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx* __restrict__ ty, Combine cb,
            int collect_obs, double* __restrict__ partials) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
@@ -41,8 +44,32 @@ pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx
   const int tt = threadIdx.x;
   const uint64_t base = (uint64_t)blockIdx.x << TB;
   cplx r[16];
+  if (!COMB) {
 #pragma unroll
-  for (int j = 0; j < 16; ++j) r[j] = psi[base | (uint64_t)elem<8>(tt, j)];
+    for (int j = 0; j < 16; ++j) r[j] = psi[base | (uint64_t)elem<8>(tt, j)];
+  } else {
+    const uint64_t i0 = base | (uint64_t)tt;  // elem<8>(tt, j) = tt + 256 j
+#pragma unroll
+    for (int half = 0; half < 16; half += 8) {
+      {
+        const cplx* v0 = cb.vin[0];
+        const double c0 = cb.c[0];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) r[half + j] = c0 * v0[i0 + 256u * (half + j)];
+      }
+      for (int q = 1; q < cb.n_in; ++q) {
+        const cplx* vq = cb.vin[q];
+        const double cq = cb.c[q];
+        cplx w[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) w[j] = vq[i0 + 256u * (half + j)];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) axpy(r[half + j], cq, w[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) cb.out[i0 + 256u * (half + j)] = r[half + j];
+    }
+  }
   double s[3] = {0.0, 0.0, 0.0};
   if (collect_obs) {
     const int n_sea = __popcll(a.g.sea_mask);
@@ -225,6 +252,49 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
       double* p = partials + (size_t)blockIdx.x * PSTRIDE + 3 + 2 * branch;
       p[0] = s[0]; p[1] = s[1];
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// error_sums: the embedded-pair error norm as one streaming sweep; CTA b covers amplitudes [4096 b, 4096 (b+1)),
+// so its partial sums land in the same per-tile slots (7: error, 8: |vin[sc_i0]|^2 / sc^2) the fused epilogues use.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TPT, 4)
+error_sums_kernel(ErrSpec es, double* __restrict__ partials) {
+  __shared__ double red[2 * 32 + 2];
+  const uint64_t i0 = ((uint64_t)blockIdx.x << TB) | threadIdx.x;
+  double err_acc = 0.0, aux_acc = 0.0;
+#pragma unroll 1
+  for (int j0 = 0; j0 < 16; j0 += 4) {
+    cplx er[4];
+    double m0[4], m1[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { er[j] = mk(0.0, 0.0); m0[j] = 0.0; m1[j] = 0.0; }
+    for (int q = 0; q < es.n_in; ++q) {
+      const cplx* vq = es.vin[q];
+      const double eq = es.e[q];
+      cplx w[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) w[j] = vq[i0 + 256u * (j0 + j)];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        axpy(er[j], eq, w[j]);
+        if (q == es.sc_i0) m0[j] = norm2(w[j]);
+        if (q == es.sc_i1) m1[j] = norm2(w[j]);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const double sc = es.atol + es.rtol * sqrt(fmax(m0[j], m1[j]));
+      err_acc += norm2(er[j]) / (sc * sc);
+      aux_acc += m0[j] / (sc * sc);
+    }
+  }
+  double s[2] = {err_acc, aux_acc};
+  block_reduce<2>(s, red);
+  if (threadIdx.x == 0) {
+    partials[(size_t)blockIdx.x * PSTRIDE + 7] = s[0];
+    partials[(size_t)blockIdx.x * PSTRIDE + 8] = s[1];
   }
 }
 

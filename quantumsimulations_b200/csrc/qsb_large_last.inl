@@ -11,7 +11,9 @@ namespace {
 // EPI bit 0: o2 is produced; bit 1: the error sums are produced.  The epilogue works on batches of B amplitudes:
 // all loads of a batch are issued before anything of that batch is stored, because o1/o2 may alias inputs at
 // the SAME index (in-place stage vectors) and the compiler must therefore keep loads behind earlier stores.
-template <int EPI>
+// B x NQ: elements per batch x input vectors the batch can take (n_in <= NQ): <4, 2> for short epilogues (Taylor
+// terms, first DP5 stage), <2, 8> for the long DP5 stage combinations; EPI == 0 has no inputs (<8, 0>).
+template <int EPI, int B, int NQ>
 __global__ void __launch_bounds__(TPT, 2)
 pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* __restrict__ ty,
           Epilogue ep, double* __restrict__ partials) {
@@ -57,55 +59,75 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
   smem_load16<8>(sm, tt, r);
   bfly16<0>(r, 0xF);
 
+  // ---- epilogue ----------------------------------------------------------------------------------------------
+  // The transformed tile is parked in this thread's own (now free) shared-memory slots, so the registers can hold a
+  // whole batch of outstanding loads: B elements x (src + up to NQ input vectors), all issued before the first use.
+  // The groups of two input vectors sit behind uniform branches on n_in, which resolve at once and therefore do not
+  // break up the load burst.
+  {
+    cplx* park = sm + phys_base<8>(tt);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) park[j * PhysStride<8>::value] = r[j];
+  }
+  const cplx* park = sm + phys_base<8>(tt);
   TileDiag<8> td;
   td.load(a.tab.Tz + (size_t)blockIdx.x * TD_STRIDE, a.tab.Iz, tt);
   const uint64_t idx0 = base | (uint64_t)tt;  // element j of this thread is idx0 + 256 j
   double err_acc = 0.0, aux_acc = 0.0;
-  constexpr int B = (EPI & 2) ? 4 : 8;
+  const int n_in = EPI ? ep.n_in : 0;
 #pragma unroll
   for (int j0 = 0; j0 < 16; j0 += B) {
-    {  // k = -i (Dz v + r)   (kept in r)
-      cplx v[B];
+    cplx v[B], w[NQ > 0 ? NQ : 1][B];
 #pragma unroll
-      for (int jj = 0; jj < B; ++jj) v[jj] = src[idx0 + 256u * (j0 + jj)];
+    for (int jj = 0; jj < B; ++jj) v[jj] = src[idx0 + 256u * (j0 + jj)];
 #pragma unroll
-      for (int jj = 0; jj < B; ++jj) {
-        cplx acc = td.at(a.tab.Wz, j0 + jj) * v[jj] + r[j0 + jj];
-        r[j0 + jj] = ep.raw_h ? acc : mul_mi(acc);
+    for (int q0 = 0; q0 < NQ; q0 += 2) {
+      if (q0 < n_in) {
+#pragma unroll
+        for (int jj = 0; jj < B; ++jj) w[q0][jj] = ep.vin[q0][idx0 + 256u * (j0 + jj)];
       }
+      if (q0 + 1 < n_in) {
+#pragma unroll
+        for (int jj = 0; jj < B; ++jj) w[q0 + 1][jj] = ep.vin[q0 + 1][idx0 + 256u * (j0 + jj)];
+      }
+    }
+    cplx k[B];
+#pragma unroll
+    for (int jj = 0; jj < B; ++jj) {  // k = -i (Dz v + r)
+      cplx acc = td.at(a.tab.Wz, j0 + jj) * v[jj] + park[(j0 + jj) * PhysStride<8>::value];
+      k[jj] = ep.raw_h ? acc : mul_mi(acc);
     }
     if (EPI == 0) {
       if (ep.o1) {
 #pragma unroll
-        for (int jj = 0; jj < B; ++jj) ep.o1[idx0 + 256u * (j0 + jj)] = ep.alpha * r[j0 + jj];
+        for (int jj = 0; jj < B; ++jj) ep.o1[idx0 + 256u * (j0 + jj)] = ep.alpha * k[jj];
       }
     } else {
       cplx o2[(EPI & 1) ? B : 1], er[(EPI & 2) ? B : 1];
       double m0[(EPI & 2) ? B : 1], m1[(EPI & 2) ? B : 1];
 #pragma unroll
       for (int jj = 0; jj < B; ++jj) {
-        if (EPI & 1) o2[jj] = ep.ck * r[j0 + jj];
-        if (EPI & 2) { er[jj] = ep.ek * r[j0 + jj]; m0[jj] = 0.0; m1[jj] = 0.0; }
+        if (EPI & 1) o2[jj] = ep.ck * k[jj];
+        if (EPI & 2) { er[jj] = ep.ek * k[jj]; m0[jj] = 0.0; m1[jj] = 0.0; }
       }
-      for (int q = 0; q < ep.n_in; ++q) {
-        const cplx* vq = ep.vin[q];
-        const double cq = ep.c[q], eq = ep.e[q];
-        cplx w[B];
 #pragma unroll
-        for (int jj = 0; jj < B; ++jj) w[jj] = vq[idx0 + 256u * (j0 + jj)];
+      for (int q = 0; q < NQ; ++q) {
+        if (q < n_in) {
+          const double cq = ep.c[q], eq = ep.e[q];
 #pragma unroll
-        for (int jj = 0; jj < B; ++jj) {
-          if (EPI & 1) axpy(o2[jj], cq, w[jj]);
-          if (EPI & 2) {
-            axpy(er[jj], eq, w[jj]);
-            if (q == ep.sc_i0) m0[jj] = norm2(w[jj]);
-            if (q == ep.sc_i1) m1[jj] = norm2(w[jj]);
+          for (int jj = 0; jj < B; ++jj) {
+            if (EPI & 1) axpy(o2[jj], cq, w[q][jj]);
+            if (EPI & 2) {
+              axpy(er[jj], eq, w[q][jj]);
+              if (q == ep.sc_i0) m0[jj] = norm2(w[q][jj]);
+              if (q == ep.sc_i1) m1[jj] = norm2(w[q][jj]);
+            }
           }
         }
       }
       if (ep.o1) {
 #pragma unroll
-        for (int jj = 0; jj < B; ++jj) ep.o1[idx0 + 256u * (j0 + jj)] = ep.alpha * r[j0 + jj];
+        for (int jj = 0; jj < B; ++jj) ep.o1[idx0 + 256u * (j0 + jj)] = ep.alpha * k[jj];
       }
 #pragma unroll
       for (int jj = 0; jj < B; ++jj) {
@@ -210,11 +232,12 @@ static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm,
 
 void prepare_device() {
   const int sm = (int)((size_t)TILE_PHYS * sizeof(cplx));
-  cudaFuncSetAttribute(pass_first, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_last<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_last<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_last<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_last<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_first<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_first<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_last<0, 8, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_last<1, 4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_last<2, 4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  cudaFuncSetAttribute(pass_last<3, 4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
   cudaFuncSetAttribute(pass_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
   set_centre_attrs<8>(sm);
   set_centre_attrs<4>(sm);
@@ -257,23 +280,34 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
 }
 
 int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
-                  const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream, const ShardLink* link) {
+                  const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream, const ShardLink* link,
+                  const Combine* comb) {
   const size_t sm2 = (size_t)TILE_PHYS * sizeof(cplx);
   PassArgs a;
   a.g = g;
   a.tab = tab;
   const unsigned n_tiles = 1u << (g.n_loc - TB);
-  { Timed t(0, stream); pass_first<<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, collect_obs, partials); }
+  if (ep.n_in > 2) { set_error("internal: fused epilogues take at most 2 input vectors"); return QSB_ERR_BAD_ARG; }
+  {
+    Timed t(0, stream);
+    if (comb && comb->n_in > 0) {
+      if (comb->out != src) { set_error("internal: Combine::out must be the vector the apply acts on"); return QSB_ERR_BAD_ARG; }
+      pass_first<true><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, *comb, collect_obs, partials);
+    } else {
+      Combine none = {};
+      pass_first<false><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, none, collect_obs, partials);
+    }
+  }
   int rc = launch_strided_passes(g, a, tx, ty, collect_obs, partials, stream, link);
   if (rc) return rc;
   {
     Timed t(3, stream);
     const int epi = (ep.o2 ? 1 : 0) | (ep.want_err ? 2 : 0);
     switch (epi) {
-      case 0: pass_last<0><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
-      case 1: pass_last<1><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
-      case 2: pass_last<2><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
-      default: pass_last<3><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
+      case 0: pass_last<0, 8, 0><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
+      case 1: pass_last<1, 4, 2><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
+      case 2: pass_last<2, 4, 2><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
+      default: pass_last<3, 4, 2><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
     }
   }
   return QSB_OK;
@@ -287,8 +321,14 @@ int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, c
   a.g = g;
   a.tab = tab;
   const unsigned n_tiles = 1u << (g.n_loc - TB);
-  pass_first<<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, 1, partials);
+  Combine none = {};
+  pass_first<false><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, none, 1, partials);
   return launch_strided_passes(g, a, tx, ty, 1, partials, stream, link);
+}
+
+void launch_error_sums(const LargeGeom& g, const ErrSpec& es, double* partials, cudaStream_t stream) {
+  Timed t(3, stream);
+  error_sums_kernel<<<1u << (g.n_loc - TB), TPT, 0, stream>>>(es, partials);
 }
 
 void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out8, cudaStream_t stream) {
