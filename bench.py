@@ -235,17 +235,17 @@ def run_b200(args, rank, world, local_rank):
         # ---- per-kernel shares (separate, serialised pass: never part of the timed number) ----------------
         engine.profile(True)
         plan.session_step(2)
-        kms, kcnt = engine.profile_read()
+        kms, kcnt, kbytes = engine.profile_read(with_bytes=True)
         engine.profile(False)
         tot = sum(kms.values()) or 1.0
-        moved = {"pass_first": 3.0, "pass_mid": 4.0, "pass_centre": 4.0, "pass_last": None}
         kernels = {}
         for k in kms:
             if kcnt[k]:
                 avg = kms[k] / kcnt[k]
-                kernels[k] = {"launches_per_step": kcnt[k] / 2.0, "avg_ms": avg, "share": kms[k] / tot}
-                if moved[k]:
-                    kernels[k]["moved_GBps"] = moved[k] * S / (avg * 1e-3) / 1e9
+                kernels[k] = {"launches_per_step": kcnt[k] / 2.0, "avg_ms": avg, "share": kms[k] / tot,
+                              "moved_bytes_per_launch": kbytes[k] / kcnt[k],
+                              "moved_GBps": kbytes[k] / (kms[k] * 1e-3) / 1e9}
+        moved_per_step = sum(kbytes.values()) / 2.0
         dominant = max(kernels, key=lambda k: kernels[k]["share"]) if kernels else None
         peak, how = measured_peak()
         alg_bytes_step = (n_rhs + 1) * 2.0 * S
@@ -254,8 +254,11 @@ def run_b200(args, rank, world, local_rank):
         roofline = {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
             "traffic": (prof or {}).get("dram_bytes_per_step"), "peak_source": how,
-            "kernel": "one DP5 step attempt = 6 H-applies (pass_first/mid/centre/mid/last) + fused stage algebra",
-            "algorithmic_bytes_per_step": alg_bytes_step, "dominant_kernel": dominant, "kernels": kernels,
+            "kernel": "one DP5 step attempt = 6 H-applies (pass_first[+stage combination]/mid/centre/mid/last) + error sweep",
+            "algorithmic_bytes_per_step": alg_bytes_step, "moved_bytes_per_step": moved_per_step,
+            "moved_GBps": moved_per_step * args.steps / (ms / 1e3) / 1e9,
+            "moved_frac_of_peak": moved_per_step * args.steps / (ms / 1e3) / 1e9 / peak,
+            "dominant_kernel": dominant, "kernels": kernels,
         }
     plan.session_end()
     plan.close()

@@ -166,11 +166,13 @@ int qsb_local_group_destroy(qsb_local_group* group);
 void* qsb_local_group_member(qsb_local_group* group, int32_t rank); /* the ctx to pass with qsb_local_allgather */
 int qsb_local_allgather(void* member_ctx, const double* send, int32_t count, double* recv);
 
-/* Benchmark aid: when enabled, every launch of the tiled H-apply is bracketed by CUDA events on its stream
- * (this serialises host and device; never enable it inside a timed throughput run).  ms4/count4: summed
- * milliseconds and launch counts of pass_first, pass_mid, pass_centre, pass_last since the last enable.    */
+/* Benchmark aid: when enabled, every launch of the tiled path is bracketed by CUDA events on its stream (this
+ * serialises host and device; never enable it inside a timed throughput run).  Classes: 0 pass_first, 1 pass_mid,
+ * 2 pass_centre, 3 pass_last, 4 pass_first with a fused stage combination, 5 error_sums.  ms / count / bytes: summed
+ * milliseconds, launches and bytes moved by design (vectors read + written) per class since the last enable.        */
+#define QSB_N_PROFILE 6
 int qsb_profile(int enable);
-int qsb_profile_read(double* ms4, int64_t* count4);
+int qsb_profile_read(double* ms, int64_t* count, double* bytes, int32_t n);
 
 #ifdef __cplusplus
 }

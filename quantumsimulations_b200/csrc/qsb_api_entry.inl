@@ -140,13 +140,18 @@ int qsb_evolve(qsb_plan* p, uint64_t psi0_index, const double* psi0_host, int64_
 int qsb_profile(int enable) {
   Profile& pr = profile();
   pr.on = enable != 0;
-  for (int i = 0; i < 4; ++i) { pr.ms[i] = 0.0; pr.count[i] = 0; }
+  for (int i = 0; i < N_PROFILE; ++i) { pr.ms[i] = 0.0; pr.count[i] = 0; pr.bytes[i] = 0.0; }
   return QSB_OK;
 }
 
-int qsb_profile_read(double* ms4, int64_t* count4) {
-  if (!ms4 || !count4) return fail(QSB_ERR_BAD_ARG, "null argument");
-  for (int i = 0; i < 4; ++i) { ms4[i] = profile().ms[i]; count4[i] = profile().count[i]; }
+int qsb_profile_read(double* ms, int64_t* count, double* bytes, int32_t n) {
+  if (!ms || !count || !bytes || n < 0) return fail(QSB_ERR_BAD_ARG, "null argument");
+  for (int i = 0; i < n; ++i) {
+    const bool have = i < N_PROFILE;
+    ms[i] = have ? profile().ms[i] : 0.0;
+    count[i] = have ? profile().count[i] : 0;
+    bytes[i] = have ? profile().bytes[i] : 0.0;
+  }
   return QSB_OK;
 }
 

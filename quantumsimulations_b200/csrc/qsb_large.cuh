@@ -137,11 +137,15 @@ void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out
 void launch_set_basis_state(cplx* psi, uint64_t dim, uint64_t index, cudaStream_t stream);
 size_t happly_smem_bytes();
 
-// Per-kernel-class CUDA-event timing (bench.py's roofline leg).  Classes: 0 first, 1 mid, 2 centre, 3 last.
+// Per-kernel-class CUDA-event timing (bench.py's roofline leg).  Classes: 0 pass_first, 1 pass_mid, 2 pass_centre,
+// 3 pass_last, 4 pass_first with a fused stage combination, 5 error_sums.  bytes = what the launch moves by design
+// (vectors read + written, in bytes), so ms and bytes of a class give its achieved GB/s.
+constexpr int N_PROFILE = 6;
 struct Profile {
   bool on = false;
-  double ms[4] = {0, 0, 0, 0};
-  long long count[4] = {0, 0, 0, 0};
+  double ms[N_PROFILE] = {};
+  long long count[N_PROFILE] = {};
+  double bytes[N_PROFILE] = {};
 };
 Profile& profile();
 

@@ -187,8 +187,9 @@ namespace {
 struct Timed {
   int cls;
   cudaStream_t st;
+  double bytes;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
-  Timed(int c, cudaStream_t s) : cls(c), st(s) {
+  Timed(int c, cudaStream_t s, double b = 0.0) : cls(c), st(s), bytes(b) {
     if (profile().on) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, st); }
   }
   ~Timed() {
@@ -199,6 +200,7 @@ struct Timed {
       cudaEventElapsedTime(&ms, e0, e1);
       profile().ms[cls] += ms;
       profile().count[cls] += 1;
+      profile().bytes[cls] += bytes;
       cudaEventDestroy(e0); cudaEventDestroy(e1);
     }
   }
@@ -256,9 +258,10 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
   const unsigned n_tiles = 1u << (g.n_loc - TB);
   const int centre = g.n_layouts - 1;
   const TileMap all = {0u, 0, 0, 0u};
-  for (int k = 1; k < centre; ++k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+  const double S = (double)(sizeof(cplx) << g.n_loc);  // bytes of one local vector
+  for (int k = 1; k < centre; ++k) { Timed t(1, stream, 4 * S); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
   if (g.world == 1) {
-    Timed t(2, stream);
+    Timed t(2, stream, 4 * S);
     PeerPtrs none = {};
     launch_centre<false>(a, g.lay[centre], all, tx, ty, none, collect_obs, partials, n_tiles, sm1, stream);
   } else {
@@ -266,7 +269,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
     int rc = link->sync(link->ctx);
     if (rc) return rc;
     {
-      Timed t(2, stream);
+      Timed t(2, stream, 4 * S);
       PeerPtrs pp = {};
       for (int r = 0; r < g.world; ++r) { pp.t[0][r] = link->tx[r]; pp.t[1][r] = link->ty[r]; }
       const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u};
@@ -275,7 +278,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
     rc = link->sync(link->ctx);
     if (rc) return rc;
   }
-  for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+  for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream, 4 * S); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
   return QSB_OK;
 }
 
@@ -288,8 +291,10 @@ int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cp
   a.tab = tab;
   const unsigned n_tiles = 1u << (g.n_loc - TB);
   if (ep.n_in > 2) { set_error("internal: fused epilogues take at most 2 input vectors"); return QSB_ERR_BAD_ARG; }
+  const double S = (double)(sizeof(cplx) << g.n_loc);
   {
-    Timed t(0, stream);
+    const bool cmb = comb && comb->n_in > 0;
+    Timed t(cmb ? 4 : 0, stream, cmb ? (comb->n_in + 3) * S : 3 * S);
     if (comb && comb->n_in > 0) {
       if (comb->out != src) { set_error("internal: Combine::out must be the vector the apply acts on"); return QSB_ERR_BAD_ARG; }
       pass_first<true><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, *comb, collect_obs, partials);
@@ -301,8 +306,8 @@ int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cp
   int rc = launch_strided_passes(g, a, tx, ty, collect_obs, partials, stream, link);
   if (rc) return rc;
   {
-    Timed t(3, stream);
     const int epi = (ep.o2 ? 1 : 0) | (ep.want_err ? 2 : 0);
+    Timed t(3, stream, (3 + ep.n_in + (ep.o1 ? 1 : 0) + (ep.o2 ? 1 : 0)) * S);
     switch (epi) {
       case 0: pass_last<0, 8, 0><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
       case 1: pass_last<1, 4, 2><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, ep, partials); break;
@@ -327,7 +332,7 @@ int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, c
 }
 
 void launch_error_sums(const LargeGeom& g, const ErrSpec& es, double* partials, cudaStream_t stream) {
-  Timed t(3, stream);
+  Timed t(5, stream, es.n_in * (double)(sizeof(cplx) << g.n_loc));
   error_sums_kernel<<<1u << (g.n_loc - TB), TPT, 0, stream>>>(es, partials);
 }
 

@@ -108,7 +108,7 @@ def load_library() -> C.CDLL:
     lib.qsb_local_group_member.restype = vp
     lib.qsb_local_allgather.argtypes = [vp, dp, C.c_int32, dp]
     lib.qsb_profile.argtypes = [C.c_int]
-    lib.qsb_profile_read.argtypes = [dp, C.POINTER(C.c_int64)]
+    lib.qsb_profile_read.argtypes = [dp, C.POINTER(C.c_int64), dp, C.c_int32]
     _lib = lib
     return lib
 
@@ -128,13 +128,19 @@ def profile(enable: bool) -> None:
     _check(load_library().qsb_profile(1 if enable else 0))
 
 
-def profile_read():
-    """({class: summed ms}, {class: launches}) of the tiled H-apply kernels since profile(True)."""
-    ms = (C.c_double * 4)()
-    cnt = (C.c_int64 * 4)()
-    _check(load_library().qsb_profile_read(ms, cnt))
-    names = ("pass_first", "pass_mid", "pass_centre", "pass_last")
-    return dict(zip(names, list(ms))), dict(zip(names, list(cnt)))
+PROFILE_CLASSES = ("pass_first", "pass_mid", "pass_centre", "pass_last", "pass_first_comb", "error_sums")
+
+
+def profile_read(with_bytes: bool = False):
+    """({class: summed ms}, {class: launches}[, {class: bytes moved by design}]) of the tiled-path kernels since
+    profile(True)."""
+    n = len(PROFILE_CLASSES)
+    ms = (C.c_double * n)()
+    cnt = (C.c_int64 * n)()
+    byt = (C.c_double * n)()
+    _check(load_library().qsb_profile_read(ms, cnt, byt, n))
+    out = dict(zip(PROFILE_CLASSES, list(ms))), dict(zip(PROFILE_CLASSES, list(cnt)))
+    return out + (dict(zip(PROFILE_CLASSES, list(byt))),) if with_bytes else out
 
 
 def tile_layouts(n_qubits: int, world: int = 1):

@@ -37,9 +37,10 @@ with engine.Plan(table) as plan:
     if a.profile:
         engine.profile(True)
         plan.session_step(1)
-        pms, cnt = engine.profile_read()
+        pms, cnt, byt = engine.profile_read(with_bytes=True)
         engine.profile(False)
-        out["profile_ms_per_launch"] = {k: (pms[k] / cnt[k] if cnt[k] else None) for k in pms}
-        out["profile_launches"] = cnt
+        out["profile_ms_per_launch"] = {k: round(pms[k] / cnt[k], 3) for k in pms if cnt[k]}
+        out["profile_GBps"] = {k: round(byt[k] / pms[k] / 1e6) for k in pms if cnt[k]}
+        out["profile_launches"] = {k: cnt[k] for k in pms if cnt[k]}
     plan.session_end()
 print(json.dumps(out))

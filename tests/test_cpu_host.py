@@ -205,7 +205,7 @@ def test_library_exports_every_declared_symbol():
     from quantumsimulations_b200 import engine
 
     header = open(os.path.join(ROOT, "include", "qsb200.h")).read()
-    declared = set(re.findall(r"^(?:int|const char\*)\s+(qsb_\w+)\s*\(", header, flags=re.M))
+    declared = set(re.findall(r"^(?:int|const char\*|void\*)\s+(qsb_\w+)\s*\(", header, flags=re.M))
     assert len(declared) >= 15
     lib = engine.load_library()
     for sym in declared:
