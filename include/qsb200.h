@@ -156,6 +156,12 @@ int qsb_shard_connect(qsb_plan* plan, const void* blobs, qsb_allgather_fn allgat
  * [lk,12) are index bits [gs,ge).  Layout 0 is the contiguous one; the last one is the centre and must contain all
  * rank bits [n - log2 world, n).                                                                               */
 int qsb_debug_layouts(int32_t n_qubits, int32_t world, int32_t* n_layouts, int32_t* out /* [6][3] */);
+/* Host-only: how the strided passes (mid .. centre .. mid) of an unsharded n-qubit plan are fused into one L2-resident
+ * persistent launch on a device with n_sms SMs.  out = {on, f, m, fbits, tiles_lb, lag, vmask, fixed_vmask[6]}:
+ * layouts f .. f+m (the centre) are fused, a unit fixes fbits index bits and has 2^tiles_lb tiles per phase, phases of
+ * one unit are `lag` units apart in the ticket order, and tile v of fused layout k belongs to the unit whose id is the
+ * bits of v selected by fixed_vmask[k].  on = 0: every pass is its own launch.                                  */
+int qsb_debug_fusion(int32_t n_qubits, int32_t n_sms, int64_t* out /* [13] */);
 /* Amplitudes held by this plan (2^n for an ordinary plan).                                                     */
 int qsb_plan_local_dim(const qsb_plan* plan, uint64_t* dim);
 
@@ -168,9 +174,10 @@ int qsb_local_allgather(void* member_ctx, const double* send, int32_t count, dou
 
 /* Benchmark aid: when enabled, every launch of the tiled path is bracketed by CUDA events on its stream (this
  * serialises host and device; never enable it inside a timed throughput run).  Classes: 0 pass_first, 1 pass_mid,
- * 2 pass_centre, 3 pass_last, 4 pass_first with a fused stage combination, 5 error_sums.  ms / count / bytes: summed
+ * 2 pass_centre, 3 pass_last, 4 pass_first with a fused stage combination, 5 error_sums, 6 strided_fused (mid .. centre
+ * .. mid as one L2-resident persistent launch).  ms / count / bytes: summed
  * milliseconds, launches and bytes moved by design (vectors read + written) per class since the last enable.        */
-#define QSB_N_PROFILE 6
+#define QSB_N_PROFILE 7
 int qsb_profile(int enable);
 int qsb_profile_read(double* ms, int64_t* count, double* bytes, int32_t n);
 

@@ -191,7 +191,7 @@ int qsb_apply_h(qsb_plan* p, const double* psi_host, double* out_host) {
   Epilogue e = blank_epilogue(&s);
   e.raw_h = 1;
   e.o1 = s.ys;
-  rc = launch_happly(p->g, p->tab, s.y, s.tx, s.ty, e, 0, s.partials, p->stream, link_of(p));
+  rc = launch_happly(p->g, p->tab, s.y, s.tx, s.ty, e, 0, s.partials, p->stream, link_of(p), nullptr, &p->fu);
   if (rc) return rc;
   QSB_CUDA(cudaGetLastError());
   QSB_CUDA(cudaMemcpyAsync(out_host, s.ys, ubytes, cudaMemcpyDeviceToHost, p->stream));

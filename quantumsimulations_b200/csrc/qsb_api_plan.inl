@@ -24,6 +24,7 @@ struct qsb_plan {
   double* d_red = nullptr;      // [PSTRIDE] reduced sums
   double* h_red = nullptr;      // pinned mirror
   Session* ses = nullptr;
+  StridedFusion fu;             // L2-resident fusion of the strided passes (unsharded plans); fu.ctrl is owned here
   // sharded state (world > 1): exchange scratch (tx, ty) the peers map, and the peers' mappings
   void* xbuf = nullptr;
   ShardLink link = {};
@@ -155,6 +156,12 @@ static int plan_create(const qsb_table* table, int device, int rank, int world, 
     p->tab.Tz = p->d_tiles + 2 * td;
     QSB_CUDA(cudaMalloc(&p->d_red, PSTRIDE * sizeof(double)));
     QSB_CUDA(cudaMallocHost(&p->h_red, PSTRIDE * sizeof(double)));
+    {
+      int n_sms = 0;
+      QSB_CUDA(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, device));
+      p->fu = plan_fusion(p->g, n_sms);
+      if (p->fu.on) QSB_CUDA(cudaMalloc(&p->fu.ctrl, p->fu.ctrl_bytes));
+    }
     if (world > 1) {
       cudaError_t e = cudaMalloc(&p->xbuf, 2 * (sizeof(cplx) << p->n_loc));
       if (e != cudaSuccess) {
@@ -188,6 +195,7 @@ int qsb_plan_destroy(qsb_plan* p) {
   if (p->d_tables) cudaFree(p->d_tables);
   if (p->d_tiles) cudaFree(p->d_tiles);
   if (p->d_red) cudaFree(p->d_red);
+  if (p->fu.ctrl) cudaFree(p->fu.ctrl);
   if (p->h_red) cudaFreeHost(p->h_red);
   if (p->stream) cudaStreamDestroy(p->stream);
   delete p;

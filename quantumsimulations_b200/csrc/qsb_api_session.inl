@@ -86,7 +86,7 @@ static int session_prime(qsb_plan* p, Session* s) {
   e.o1 = s->k[0];
   e.vin[0] = s->y; e.n_in = 1; e.c[0] = 0.0; e.e[0] = 0.0; e.ek = 1.0; e.want_err = 1;
   if (s->o.method == QSB_METHOD_TAYLOR) e.o1 = nullptr;  // Taylor recomputes its first term with h folded in
-  int rc = launch_happly(p->g, p->tab, s->y, s->tx, s->ty, e, 1, s->partials, p->stream, link_of(p));
+  int rc = launch_happly(p->g, p->tab, s->y, s->tx, s->ty, e, 1, s->partials, p->stream, link_of(p), nullptr, &p->fu);
   if (rc) return rc;
   QSB_CUDA(cudaGetLastError());
   ++s->n_rhs;
@@ -120,7 +120,7 @@ static int attempt_dp5(qsb_plan* p, Session* s, double hu, double* err, double* 
     Epilogue e = blank_epilogue(s);
     e.o1 = s->k[st + 1];
     // the last apply acts on y_new (FSAL): its pass_first / pass_centre also collect y_new's observable sums
-    int rc = launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, st == 5 ? 1 : 0, s->partials, p->stream, link_of(p), &cb);
+    int rc = launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, st == 5 ? 1 : 0, s->partials, p->stream, link_of(p), &cb, &p->fu);
     if (rc) return rc;
   }
   {
@@ -154,7 +154,7 @@ static int attempt_taylor(qsb_plan* p, Session* s, double hu, double* err, doubl
       e.vin[1] = s->y; e.c[1] = 0.0; e.n_in = 2;
       e.want_err = 1; e.ek = e.alpha; e.sc_i0 = 1; e.sc_i1 = -1;
     }
-    int rc = launch_happly(p->g, p->tab, m == 0 ? s->y : s->k[0], s->tx, s->ty, e, 0, s->partials, p->stream, link_of(p));
+    int rc = launch_happly(p->g, p->tab, m == 0 ? s->y : s->k[0], s->tx, s->ty, e, 0, s->partials, p->stream, link_of(p), nullptr, &p->fu);
     if (rc) return rc;
   }
   QSB_CUDA(cudaGetLastError());
@@ -218,7 +218,7 @@ static int session_advance(qsb_plan* p, Session* s, double t_target, int64_t max
 
 static int session_observe(qsb_plan* p, Session* s, double* obs) {
   if (!s->obs_valid) {
-    int rc = launch_observe(p->g, p->tab, s->y, s->tx, s->ty, s->partials, p->stream, link_of(p));
+    int rc = launch_observe(p->g, p->tab, s->y, s->tx, s->ty, s->partials, p->stream, link_of(p), &p->fu);
     if (rc) return rc;
     QSB_CUDA(cudaGetLastError());
     rc = fetch_sums(p, s, s->obs_sums);

@@ -116,6 +116,18 @@ int qsb_debug_layouts(int32_t n_qubits, int32_t world, int32_t* n_layouts, int32
   return QSB_OK;
 }
 
+int qsb_debug_fusion(int32_t n_qubits, int32_t n_sms, int64_t* out) {
+  if (!out) return fail(QSB_ERR_BAD_ARG, "null argument");
+  if (n_qubits < TB || n_qubits > QSB_MAX_QUBITS) return fail(QSB_ERR_BAD_ARG, "unsupported n_qubits");
+  const LargeGeom g = make_geometry(n_qubits, 0, 1);
+  const StridedFusion fu = plan_fusion(g, n_sms);
+  const FusedSpec& s = fu.spec;
+  const int64_t head[7] = {fu.on ? 1 : 0, s.f, s.m, s.fbits, s.tiles_lb, s.lag, (int64_t)s.vmask};
+  for (int i = 0; i < 7; ++i) out[i] = head[i];
+  for (int k = 0; k < MAX_LAYOUTS; ++k) out[7 + k] = s.fixed_vmask[k];
+  return QSB_OK;
+}
+
 int qsb_plan_local_dim(const qsb_plan* p, uint64_t* dim) {
   if (!p || !dim) return fail(QSB_ERR_BAD_ARG, "null argument");
   *dim = p->small ? (1ull << p->n) : (p->world > 1 ? (1ull << p->n_loc) : (1ull << p->n));

@@ -236,6 +236,12 @@ struct TileDiag {
 #pragma unroll
     for (int k = 0; k < 4; ++k) w[k] = __ldg(row + 32 + k) + __ldg(intile + (1 + k) * 256 + tt);
   }
+  // the same sums from shared-memory copies of the row and the table (the TMA-fed fused pass)
+  __device__ __forceinline__ void load_shared(const double* row, const double* intile, int tt) {
+    fixed = (row[tt & 15] + row[16 + (tt >> 4)]) + intile[tt];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) w[k] = row[32 + k] + intile[(1 + k) * 256 + tt];
+  }
   // j must be a compile-time constant after unrolling: the sign pattern folds into add/sub and ww[j] is read
   // straight from the kernel-parameter bank
   __device__ __forceinline__ double at(const double (&ww)[16], int j) const {

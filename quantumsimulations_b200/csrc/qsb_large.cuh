@@ -4,6 +4,8 @@
 // Walsh-Hadamard transforms are done 12 bits at a time on 4096-amplitude tiles staged in shared memory;
 // bits above 12 are reached by further passes whose tiles gather strided 2^lk-amplitude runs.
 #pragma once
+#include <cuda.h>
+
 #include <vector>
 
 #include "qsb_common.cuh"
@@ -97,6 +99,32 @@ struct ShardLink {
   void* ctx;
 };
 
+// L2-resident fusion of the strided passes f .. centre .. f into one persistent launch (qsb_large_fused.inl).
+constexpr int MAX_PHASES = 2 * (MAX_LAYOUTS - 2) + 1;
+struct FusedSpec {
+  int f, m;                 // first fused layout, centre - f; phases P = 2 m + 1
+  int fbits;                // number of index bits a unit fixes
+  int tiles_lb;             // log2 T, tiles of one phase of one unit
+  int lag;                  // pipeline lag in units between consecutive phases
+  unsigned fixed_vmask[MAX_LAYOUTS];  // per layout: the bits of a tile number v that carry the unit id
+  unsigned vmask;           // n_tiles - 1
+};
+struct StridedFusion {
+  bool on = false;
+  FusedSpec spec = {};
+  int grid = 0;             // persistent CTAs (1 per SM)
+  int* ctrl = nullptr;      // device: ticket + per (unit, phase) counters; owned by the plan
+  size_t ctrl_bytes = 0;
+  // TMA descriptors of the scratch vectors, [branch][layout], rebuilt when the vectors change (host cache)
+  CUtensorMap maps[2][MAX_LAYOUTS];
+  const void* maps_tx = nullptr;
+  const void* maps_ty = nullptr;
+};
+// Decides whether (and from which layout on) the strided passes of geometry g are fused: the smallest f whose unit
+// is at most 2^unit_lb amplitudes.  Unsharded plans with >= 3 layouts only.  Off unless QSB200_FUSE_LB sets unit_lb
+// (20 = 16 MB units); QSB200_FUSE_LAG overrides the pipeline lag.  Does not allocate: the caller provides ctrl.
+StridedFusion plan_fusion(const LargeGeom& g, int n_sms);
+
 // Layouts over n index bits of which the top log2(world) are rank bits (they end up inside the centre group).
 LargeGeom make_geometry(int n, int rank = 0, int world = 1);
 size_t tile_diag_doubles(int n_loc);
@@ -126,11 +154,12 @@ int centre_window(const Layout& L);
 // to comb->out, and `src` must equal comb->out.  Epilogues take at most 2 input vectors.
 int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
                   const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream,
-                  const ShardLink* link = nullptr, const Combine* comb = nullptr);
+                  const ShardLink* link = nullptr, const Combine* comb = nullptr, StridedFusion* fu = nullptr);
 void launch_error_sums(const LargeGeom& g, const ErrSpec& es, double* partials, cudaStream_t stream);
 // Observables only (pass_first + mids + pass_centre), filling partial slots 0..6.
 int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
-                   double* partials, cudaStream_t stream, const ShardLink* link = nullptr);
+                   double* partials, cudaStream_t stream, const ShardLink* link = nullptr,
+                   StridedFusion* fu = nullptr);
 // out[PSTRIDE] = column sums of partials[n_tiles][PSTRIDE] in a fixed order.
 void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out8, cudaStream_t stream);
 // psi <- basis state (index < dim) or zero (index >= dim)
@@ -138,9 +167,9 @@ void launch_set_basis_state(cplx* psi, uint64_t dim, uint64_t index, cudaStream_
 size_t happly_smem_bytes();
 
 // Per-kernel-class CUDA-event timing (bench.py's roofline leg).  Classes: 0 pass_first, 1 pass_mid, 2 pass_centre,
-// 3 pass_last, 4 pass_first with a fused stage combination, 5 error_sums.  bytes = what the launch moves by design
+// 3 pass_last, 4 pass_first with a fused stage combination, 5 error_sums, 6 the fused strided passes.  bytes = what the launch moves by design
 // (vectors read + written, in bytes), so ms and bytes of a class give its achieved GB/s.
-constexpr int N_PROFILE = 6;
+constexpr int N_PROFILE = 7;
 struct Profile {
   bool on = false;
   double ms[N_PROFILE] = {};

@@ -301,4 +301,5 @@ error_sums_kernel(ErrSpec es, double* __restrict__ partials) {
 }  // namespace
 }  // namespace qsb
 
+#include "qsb_large_fused.inl"
 #include "qsb_large_last.inl"

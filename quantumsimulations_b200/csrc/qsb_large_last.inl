@@ -232,6 +232,56 @@ static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm,
   }
 }
 
+StridedFusion plan_fusion(const LargeGeom& g, int n_sms) {
+  StridedFusion fu;
+  // Opt-in (QSB200_FUSE_LB=20: units of 2^20 amplitudes = 16 MB): measured on B200 the fused launch does cut the
+  // DRAM traffic of the strided passes to 2.0 S read + 2.35 S written, but it is bound by tile turnaround inside the
+  // SM (shared-memory bandwidth and a three-buffer pipeline), 9.05 ms against 8.76 ms for the three separate
+  // HBM-bound launches at N = 28 (profiles/r1m_fused_strided_experiment.md).
+  int unit_lb = 0;
+  if (const char* e = std::getenv("QSB200_FUSE_LB")) unit_lb = atoi(e);
+  const int centre = g.n_layouts - 1;
+  if (unit_lb <= 0 || g.world != 1 || centre < 2 || n_sms <= 0) return fu;
+  for (int f = 1; f < centre; ++f) {
+    int lkmax = 0;
+    for (int k = f; k <= centre; ++k) lkmax = std::max(lkmax, g.lay[k].lk);
+    // bits a unit fixes: tile pad bits no fused layout transforms or reads across, and the groups of layouts < f
+    uint64_t fixed = ((1ull << TB) - 1) & ~((1ull << lkmax) - 1);
+    for (int k = 1; k < f; ++k) fixed |= ((1ull << (g.lay[k].ge - g.lay[k].gs)) - 1) << g.lay[k].gs;
+    const int fbits = __builtin_popcountll(fixed);
+    if (g.n_loc - fbits > unit_lb) continue;
+    FusedSpec& s = fu.spec;
+    s.f = f;
+    s.m = centre - f;
+    s.fbits = fbits;
+    s.tiles_lb = g.n_loc - TB - fbits;
+    s.vmask = (1u << (g.n_loc - TB)) - 1;
+    for (int k = f; k <= centre; ++k) {
+      unsigned vm = 0;
+      int pos = 0;
+      for (int b = 0; b < g.n_loc; ++b) {
+        if (g.lay[k].tile_mask >> b & 1) continue;  // outer bits of the layout, ascending = bits of v
+        if (fixed >> b & 1) vm |= 1u << pos;
+        ++pos;
+      }
+      s.fixed_vmask[k] = vm;
+    }
+    // A dependant is drawn lag P T - 2 T tickets after the last tile of its dependency: make that at least one wave
+    // of CTAs where the units in flight ((P - 1) lag + 1 of them) still fit comfortably in L2.
+    const int P = 2 * s.m + 1, grid = n_sms;
+    const long long PT = (long long)P << s.tiles_lb, T = 1ll << s.tiles_lb;
+    const double unit_mb = (double)(sizeof(cplx) << (g.n_loc - fbits)) / (1 << 20);
+    s.lag = 1;
+    while (s.lag * PT - 2 * T < NBUF * grid && ((P - 1) * (s.lag + 1) + 1) * unit_mb <= 64.0) ++s.lag;
+    if (const char* e = std::getenv("QSB200_FUSE_LAG")) s.lag = std::max(1, atoi(e));
+    fu.grid = grid;
+    fu.ctrl_bytes = sizeof(int) * (1 + ((size_t)2 << fbits) * P);
+    fu.on = true;
+    return fu;
+  }
+  return fu;
+}
+
 void prepare_device() {
   const int sm = (int)((size_t)TILE_PHYS * sizeof(cplx));
   cudaFuncSetAttribute(pass_first<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
@@ -244,6 +294,11 @@ void prepare_device() {
   set_centre_attrs<8>(sm);
   set_centre_attrs<4>(sm);
   set_centre_attrs<0>(sm);
+  const int fsm = (int)sizeof(FusedSmem);
+  cudaFuncSetAttribute(pass_strided_fused<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
+  cudaFuncSetAttribute(pass_strided_fused<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
+  cudaFuncSetAttribute(pass_strided_fused<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
+  cudaFuncSetAttribute(pass_strided_fused<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
 }
 
 // The strided-layout passes of one H-apply (mids forward, centre, mids back).
@@ -252,13 +307,77 @@ void prepare_device() {
 // Sharded: every rank runs the centre pass on its 1/world slice of the centre tiles, reading and writing the
 // peers' tx/ty in place; the rank barrier before it makes the peers' forward passes visible, the one after it
 // keeps the peers' backward passes from starting on rows that are still being written.
+// cuTensorMapEncodeTiled through the runtime's driver entry point query (libqsb200 does not link libcuda).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess ||
+        qr != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    cudaGetLastError();
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+// The vector `base` (2^n_loc cplx) as a 5-d tensor of doubles whose box {2^(a+1), 2^(lk-a), 1, 2^(ge-gs), 1} is one
+// tile of layout L in tile-local order: dims = pad bits [0,a) x 2 doubles, pad bits [a,lk), bits [lk,gs), the group
+// [gs,ge), bits [ge,n_loc).  a = min(lk, 7) keeps the innermost box extent within TMA's 256 elements.
+static bool encode_tile_map(CUtensorMap* map, const Layout& L, int n_loc, void* base) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) return false;
+  const int a = std::min(L.lk, 7);
+  const cuuint64_t dims[5] = {2ull << a, 1ull << (L.lk - a), 1ull << (L.gs - L.lk), 1ull << (L.ge - L.gs), 1ull << (n_loc - L.ge)};
+  const cuuint64_t strides[4] = {sizeof(cplx) << a, sizeof(cplx) << L.lk, sizeof(cplx) << L.gs, sizeof(cplx) << L.ge};
+  const cuuint32_t box[5] = {2u << a, 1u << (L.lk - a), 1u, 1u << (L.ge - L.gs), 1u};
+  const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 5, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+static bool ensure_tile_maps(const LargeGeom& g, StridedFusion& fu, cplx* tx, cplx* ty) {
+  if (fu.maps_tx == tx && fu.maps_ty == ty) return true;
+  for (int k = fu.spec.f; k < g.n_layouts; ++k)
+    if (!encode_tile_map(&fu.maps[0][k], g.lay[k], g.n_loc, tx) || !encode_tile_map(&fu.maps[1][k], g.lay[k], g.n_loc, ty))
+      return false;
+  fu.maps_tx = tx;
+  fu.maps_ty = ty;
+  return true;
+}
+
+template <int W>
+static void launch_fused(const PassArgs& a, const StridedFusion& fu, int collect_obs, double* partials, cudaStream_t stream) {
+  TmaMaps maps;
+  memcpy(maps.m, fu.maps, sizeof maps.m);
+  const int threads = FUSED_NG * TPT + 64;
+  if (collect_obs) pass_strided_fused<W, true><<<fu.grid, threads, sizeof(FusedSmem), stream>>>(a, fu.spec, maps, partials, fu.ctrl);
+  else pass_strided_fused<W, false><<<fu.grid, threads, sizeof(FusedSmem), stream>>>(a, fu.spec, maps, partials, fu.ctrl);
+}
+
 static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx, cplx* ty, int collect_obs,
-                                 double* partials, cudaStream_t stream, const ShardLink* link) {
+                                 double* partials, cudaStream_t stream, const ShardLink* link, StridedFusion* fu) {
   const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx);
   const unsigned n_tiles = 1u << (g.n_loc - TB);
   const int centre = g.n_layouts - 1;
   const TileMap all = {0u, 0, 0, 0u};
   const double S = (double)(sizeof(cplx) << g.n_loc);  // bytes of one local vector
+  if (fu && fu->on && g.world == 1 && centre_window(g.lay[centre]) != 0 && ensure_tile_maps(g, *fu, tx, ty)) {
+    // layouts before f stay full-grid launches; f .. centre .. f is one persistent launch
+    const int f = fu->spec.f;
+    for (int k = 1; k < f; ++k) { Timed t(1, stream, 4 * S); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+    {
+      Timed t(6, stream, 4 * S);
+      cudaMemsetAsync(fu->ctrl, 0, fu->ctrl_bytes, stream);
+      if (centre_window(g.lay[centre]) == 8) launch_fused<8>(a, *fu, collect_obs, partials, stream);
+      else launch_fused<4>(a, *fu, collect_obs, partials, stream);
+    }
+    for (int k = f - 1; k >= 1; --k) { Timed t(1, stream, 4 * S); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+    return QSB_OK;
+  }
   for (int k = 1; k < centre; ++k) { Timed t(1, stream, 4 * S); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
   if (g.world == 1) {
     Timed t(2, stream, 4 * S);
@@ -284,7 +403,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
 
 int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
                   const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream, const ShardLink* link,
-                  const Combine* comb) {
+                  const Combine* comb, StridedFusion* fu) {
   const size_t sm2 = (size_t)TILE_PHYS * sizeof(cplx);
   PassArgs a;
   a.g = g;
@@ -303,7 +422,7 @@ int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cp
       pass_first<false><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, none, collect_obs, partials);
     }
   }
-  int rc = launch_strided_passes(g, a, tx, ty, collect_obs, partials, stream, link);
+  int rc = launch_strided_passes(g, a, tx, ty, collect_obs, partials, stream, link, fu);
   if (rc) return rc;
   {
     const int epi = (ep.o2 ? 1 : 0) | (ep.want_err ? 2 : 0);
@@ -319,7 +438,7 @@ int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cp
 }
 
 int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
-                   double* partials, cudaStream_t stream, const ShardLink* link) {
+                   double* partials, cudaStream_t stream, const ShardLink* link, StridedFusion* fu) {
   // the transform half of an H-apply: z sums in pass_first, x/y sums in pass_centre (tx/ty are clobbered)
   const size_t sm2 = (size_t)TILE_PHYS * sizeof(cplx);
   PassArgs a;
@@ -328,7 +447,7 @@ int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, c
   const unsigned n_tiles = 1u << (g.n_loc - TB);
   Combine none = {};
   pass_first<false><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, none, 1, partials);
-  return launch_strided_passes(g, a, tx, ty, 1, partials, stream, link);
+  return launch_strided_passes(g, a, tx, ty, 1, partials, stream, link, fu);
 }
 
 void launch_error_sums(const LargeGeom& g, const ErrSpec& es, double* partials, cudaStream_t stream) {

@@ -58,7 +58,7 @@ EXPORTS = (
     "qsb_version", "qsb_last_error", "qsb_device_count", "qsb_plan_create", "qsb_plan_destroy",
     "qsb_plan_workspace_bytes", "qsb_plan_set_workspace", "qsb_evolve", "qsb_evolve_batch", "qsb_apply_h",
     "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
-    "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_plan_local_dim", "qsb_debug_layouts",
+    "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather",
 )
 
@@ -128,7 +128,8 @@ def profile(enable: bool) -> None:
     _check(load_library().qsb_profile(1 if enable else 0))
 
 
-PROFILE_CLASSES = ("pass_first", "pass_mid", "pass_centre", "pass_last", "pass_first_comb", "error_sums")
+PROFILE_CLASSES = ("pass_first", "pass_mid", "pass_centre", "pass_last", "pass_first_comb", "error_sums",
+                   "strided_fused")
 
 
 def profile_read(with_bytes: bool = False):
@@ -149,6 +150,19 @@ def tile_layouts(n_qubits: int, world: int = 1):
     out = (C.c_int32 * 18)()
     _check(load_library().qsb_debug_layouts(int(n_qubits), int(world), C.byref(n), out))
     return [(out[3 * k], out[3 * k + 1], out[3 * k + 2]) for k in range(n.value)]
+
+
+def strided_fusion(n_qubits: int, n_sms: int = 148):
+    """How the strided passes of an unsharded n-qubit plan are fused (host-only query; see qsb_debug_fusion).
+    None when every pass is its own launch."""
+    out = (C.c_int64 * 13)()
+    lib = load_library()
+    lib.qsb_debug_fusion.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_int64)]
+    _check(lib.qsb_debug_fusion(int(n_qubits), int(n_sms), out))
+    if not out[0]:
+        return None
+    return {"f": out[1], "m": out[2], "fbits": out[3], "tiles_lb": out[4], "lag": out[5], "vmask": out[6],
+            "fixed_vmask": [out[7 + k] for k in range(6)]}
 
 
 def device_count() -> int:

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Time the tiled H-apply at N spins through a Taylor session (order p => p H-applies per attempt).
 
-    QSB200_CHUNK_LB=1 python scripts/time_happly.py --n 28 --attempts 3 [--profile]
+    QSB200_FUSE_LB=0 python scripts/time_happly.py --n 28 --attempts 3 [--profile]
 
 Prints ms per H-apply (CUDA events on the plan's stream) and, with --profile, the per-kernel-class times.
 """
@@ -32,7 +32,7 @@ with engine.Plan(table) as plan:
     t, st0, _ = plan.session_step(0)
     t, st, ms = plan.session_step(a.attempts)
     n_rhs = st.n_rhs - st0.n_rhs
-    out = {"n": a.n, "chunk_lb": os.environ.get("QSB200_CHUNK_LB"), "method": a.method, "ms_per_attempt": ms / a.attempts,
+    out = {"n": a.n, "fuse_lb": os.environ.get("QSB200_FUSE_LB"), "fuse_lag": os.environ.get("QSB200_FUSE_LAG"), "method": a.method, "ms_per_attempt": ms / a.attempts,
            "ms_per_happly": ms / n_rhs, "n_rhs": n_rhs, "obs": [float(x) for x in plan.session_observe()[:4]]}
     if a.profile:
         engine.profile(True)

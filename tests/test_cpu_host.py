@@ -282,3 +282,82 @@ def test_distributed_sweep_sharding_world_size_2(tmp_path):
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert res.stdout.count("ok") == 2
+
+
+# ---- L2-resident fusion of the strided passes: the ticket schedule, checked on the host ------------------------
+def _deposit(x, mask):
+    out, pos = 0, 0
+    while mask:
+        low = mask & -mask
+        if x & 1:
+            out |= low
+        x >>= 1
+        mask ^= low
+    return out
+
+
+def _tile_indices(lay, v, n):
+    """Index set of tile v of layout (lk, gs, ge): outer bits ascending = bits of v."""
+    lk, gs, ge = lay
+    tile_bits = list(range(lk)) + list(range(gs, ge))
+    outer = [b for b in range(n) if b not in tile_bits]
+    base = sum(((v >> i) & 1) << b for i, b in enumerate(outer))
+    idx = np.zeros(1, dtype=np.int64) + base
+    for b in tile_bits:
+        idx = np.concatenate([idx, idx | (1 << b)])
+    return idx
+
+
+@pytest.mark.parametrize("n,gmax", [(16, 2), (18, 2), (17, 3), (19, 4), (21, 8)])
+def test_fused_strided_schedule_covers_tiles_and_respects_dependencies(n, gmax, monkeypatch):
+    """Replays pass_strided_fused's ticket decoding: every tile of every fused layout is visited once per phase,
+    the phases of a unit touch one and the same index set, and a phase's dependency always has smaller tickets."""
+    from quantumsimulations_b200 import engine
+
+    monkeypatch.setenv("QSB200_MAX_GROUP", str(gmax))
+    monkeypatch.setenv("QSB200_FUSE_LB", "20")
+    lays = engine.tile_layouts(n)
+    fu = engine.strided_fusion(n, 148)
+    assert fu is not None and fu["f"] + fu["m"] == len(lays) - 1
+    f, m, lag, T = fu["f"], fu["m"], fu["lag"], 1 << fu["tiles_lb"]
+    P, U = 2 * m + 1, 1 << fu["fbits"]  # one branch is enough: the branch is the low bit of the unit number
+    n_tiles = 1 << (n - 12)
+    assert U * T == n_tiles and fu["vmask"] == n_tiles - 1
+    first_ticket, last_ticket, seen, sets = {}, {}, {}, {}
+    ticket = 0
+    for slot in range(U + (P - 1) * lag):
+        for p in range(P - 1, -1, -1):
+            u = slot - p * lag
+            for q in range(T):
+                if 0 <= u < U:
+                    li = f + (p if p <= m else 2 * m - p)
+                    fm = fu["fixed_vmask"][li]
+                    v = _deposit(u, fm) | _deposit(q, fu["vmask"] & ~fm)
+                    seen.setdefault(p, []).append(v)
+                    first_ticket.setdefault((u, p), ticket)
+                    last_ticket[(u, p)] = ticket
+                    if u in (0, U - 1, U // 2):
+                        sets.setdefault((u, p), []).append(_tile_indices(lays[li], v, n))
+                ticket += 1
+    for p in range(P):
+        assert sorted(seen[p]) == list(range(n_tiles))
+    for u in range(U):
+        for p in range(1, P):
+            assert last_ticket[(u, p - 1)] < first_ticket[(u, p)]
+    for u in (0, U - 1, U // 2):
+        ref = np.sort(np.concatenate(sets[(u, 0)]))
+        assert len(np.unique(ref)) == len(ref) == (1 << n) // U
+        for p in range(1, P):
+            assert np.array_equal(np.sort(np.concatenate(sets[(u, p)])), ref)
+
+
+def test_fusion_plan_at_bench_sizes(monkeypatch):
+    from quantumsimulations_b200 import engine
+
+    assert engine.strided_fusion(28, 148) is None  # opt-in: off by default
+    monkeypatch.setenv("QSB200_FUSE_LB", "20")
+    fu = engine.strided_fusion(28, 148)
+    assert fu and (fu["f"], fu["m"], fu["fbits"], fu["tiles_lb"]) == (1, 1, 8, 8)  # 16 MB units
+    assert engine.strided_fusion(20, 148) is None  # two layouts: nothing to fuse
+    fu30 = engine.strided_fusion(30, 148)
+    assert fu30 and fu30["f"] == 2  # the first mid layout stays a full-grid launch

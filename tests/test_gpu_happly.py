@@ -46,6 +46,25 @@ def test_tiled_path_multi_group(n, gmax, monkeypatch):
     _check(random_table(n, 300 + n + gmax, dense_pairs=False), n)
 
 
+@pytest.mark.parametrize("n,gmax", [(16, 2), (18, 2), (19, 4), (21, 8), (22, 5)])
+def test_fused_strided_passes_are_bitwise_the_unfused_ones(n, gmax, monkeypatch):
+    """The L2-resident persistent launch (mid .. centre .. mid) does the per-tile arithmetic of the separate passes."""
+    from quantumsimulations_b200 import engine
+
+    monkeypatch.setenv("QSB200_MAX_GROUP", str(gmax))
+    monkeypatch.setenv("QSB200_FUSE_LB", "20")
+    assert engine.strided_fusion(n) is not None
+    table = random_table(n, 700 + n, dense_pairs=False)
+    psi = _rand_state(n, n)
+    with engine.Plan(table) as plan:
+        fused = plan.apply_h(psi)
+    monkeypatch.setenv("QSB200_FUSE_LB", "0")
+    assert engine.strided_fusion(n) is None
+    with engine.Plan(table) as plan:
+        plain = plan.apply_h(psi)
+    assert np.array_equal(fused, plain)
+
+
 def test_reference_tables(golden_cases):
     from quantumsimulations_b200 import compile_table
 
