@@ -56,7 +56,11 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.marks = index, [], None, []
+
+    def mark(self):
+        """Rows between the first and the second mark are the timed region."""
+        self.marks.append(len(self.rows))
 
     def __enter__(self):
         try:
@@ -79,10 +83,15 @@ class ClockSampler:
             self.th.join(timeout=2)
 
     def summary(self):
-        sm = [float(r[1]) for r in self.rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
+        rows = self.rows
+        if len(self.marks) == 2 and self.marks[1] > self.marks[0]:
+            rows = rows[self.marks[0]:self.marks[1]]
+        elif len(self.marks) == 2 and self.rows:          # region shorter than one sample: the nearest sample
+            rows = rows[max(0, self.marks[0] - 1):self.marks[0] + 1]
+        sm = [float(r[1]) for r in rows if len(r) >= 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
-        reasons = sorted({n for r in self.rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v == "Active"})
+        reasons = sorted({n for r in rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v == "Active"})
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": reasons, "samples": len(sm)}
 
@@ -220,10 +229,12 @@ def run_b200(args, rank, world, local_rank):
     plan = engine.Plan(table, local_rank)
     plan.use_torch_workspace(args.method, local_rank)
     plan.session_begin(opts)
-    plan.session_step(args.warmup)
-    barrier()
-    with ClockSampler(local_rank) as clk:
+    with ClockSampler(local_rank) as clk:   # started before the warm-up: nvidia-smi needs ~1 s to begin streaming
+        plan.session_step(args.warmup)
+        barrier()
+        clk.mark()
         t_now, st, ms = plan.session_step(args.steps)
+        clk.mark()
     barrier()
     ms_max = allmax(ms)
     value = world * args.steps / (ms_max / 1e3)
@@ -300,6 +311,31 @@ def run_b200(args, rank, world, local_rank):
         sweep_steps = float(tt.item())
         sweep_kernel_ms = allmax(sweep_kernel_ms)
 
+    # ---- C3 grid (CI-sized window): 19 f1A x 13 detunings x 3 variants, cost-balanced over ranks, no collective ----
+    grid = None
+    if not args.no_grid:
+        from quantumsimulations_b200.dist import estimate_cost, partition
+
+        f1as = np.arange(5.0e3, 50.0e3 + 1.0, 2.5e3)   # the 5..50 kHz step 2.5 kHz grid 2D_sweep_report.py is drawn on
+        glist = [sweep_params(6, d, v, f1a=f) for f in f1as for d in np.linspace(0.0, 3.0 * f, 13)
+                 for v in ("center_off", "center_on", "shell_off")]
+        gmine = [glist[i] for i in partition([estimate_cost(p) for p in glist], world)[rank]]
+        barrier()
+        t0 = time.perf_counter()
+        _, gst = simulate_rare_batch(gmine, device=local_rank) if gmine else ([], [])
+        grid_s = allmax(time.perf_counter() - t0)
+        gsteps = float(sum(s.n_accepted + s.n_rejected for s in gst))
+        grhs = float(sum(s.n_rhs for s in gst))
+        if dist is not None:
+            tt = torch.tensor([gsteps, grhs], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt)
+            gsteps, grhs = float(tt[0].item()), float(tt[1].item())
+        grid = {"workload": "C3 (CI-sized): 19 f1A (5..50 kHz) x 13 detunings (0..3 f1A) x 3 variants, N=7, t_final=0.03 s, "
+                            "2000 outputs, one CTA per trajectory, API default integrator (Taylor 20)",
+                "trajectories": len(glist), "wall_s": grid_s, "trajectories_per_s": len(glist) / grid_s,
+                "step_attempts": gsteps, "h_applies_per_s": grhs / grid_s,
+                "parallelism": f"longest-first partition over {world} GPU(s), no collective"}
+
     sharded = None
     if not args.no_sharded:
         barrier()
@@ -329,6 +365,7 @@ def run_b200(args, rank, world, local_rank):
                       "wall_s_default_integrator": sweep_default_s,
                       "default_integrator": "taylor order 20, atol/rtol x 1e-3 (what simulate_rare runs)",
                       "cpu_zvode": zv},
+            "grid": grid,
             "sharded": sharded,
         }
         print(json.dumps(line), flush=True)
@@ -410,6 +447,7 @@ def main():
     ap.add_argument("--method", default="dp5", choices=["dp5", "taylor"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline legs")
     ap.add_argument("--no-sharded", action="store_true", help="skip the sharded-state (C5) leg")
+    ap.add_argument("--no-grid", action="store_true", help="skip the 2D-grid (C3) leg")
     ap.add_argument("--shard-local-bits", type=int, default=30, help="index bits per GPU in the sharded leg (30: 17 GB vectors)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -123,6 +123,11 @@ int qsb_session_begin(qsb_plan* plan, uint64_t psi0_index, const double* psi0_ho
  * device_ms = CUDA-event time on the plan's stream; happly_ms = summed event time of the H-apply
  * kernels only (0 when timing of sub-ranges is off).                                                 */
 int qsb_session_step(qsb_plan* plan, int64_t n_attempts, double* t_now, qsb_stats* stats, double* device_ms);
+/* Advance the open session to exactly t_target (steps land on it; zvode's nsteps cap applies to this interval).
+ * With qsb_session_state / qsb_session_begin(psi0_host, t0, opts.first_step = stats.last_h) this is what trajectory
+ * checkpoint / resume is made of: the reference restarts a 10^9-step trajectory from zero
+ * (sweep_sea_detuning.py:483-485 names a fresh directory per run and keeps no solver state).                     */
+int qsb_session_advance(qsb_plan* plan, double t_target, double* t_now, qsb_stats* stats);
 /* Observables of the current state, [QSB_NOBS] host.                                                 */
 int qsb_session_observe(qsb_plan* plan, double* obs);
 /* Copy the current state to host (2^n complex128).                                                   */

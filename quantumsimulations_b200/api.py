@@ -148,18 +148,27 @@ def _pack(obs: np.ndarray, override: bool, extra: bool) -> Dict[str, np.ndarray]
 
 
 def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optional[str] = None,
-                  tol_scale: Optional[float] = None, return_stats: bool = False, raw_norm: bool = False):
+                  tol_scale: Optional[float] = None, return_stats: bool = False, raw_norm: bool = False,
+                  checkpoint: Optional[str] = None, checkpoint_every: int = 16):
     """Time evolution on the B200 engine; returns ``(t, {6 traces + state_norm})`` like DE:611-680.
 
     ``method``: "taylor" (default, order 20) or "dp5".  ``tol_scale`` multiplies solver_atol/solver_rtol before
     they reach the integrator (default 1e-3 for taylor, 1 for dp5; see DEFAULT_TOL_SCALE).
     ``raw_norm=True`` adds the integrator's own norm under an extra key (QuTiP discards it).
+    ``checkpoint``: file the tiled path (N >= 11) writes its state to every ``checkpoint_every`` output times and
+    resumes from if it exists (``checkpoint.evolve_checkpointed``); the on-chip path is one launch per trajectory
+    and is cached whole instead (``checkpoint.TrajectoryCache``, ``run_sweep_sea_detuning(cache_dir=...)``).
     """
     t = _check_grid(params)
     table = compile_table(params)
     opts, override = _options_from(params, method, tol_scale)
     with engine.Plan(table, device) as plan:
-        obs, stats = plan.evolve(t, opts)
+        if checkpoint is not None and table.n > engine.SMALL_MAX_QUBITS:
+            from .checkpoint import evolve_checkpointed
+
+            obs, stats, _ = evolve_checkpointed(plan, t, opts, checkpoint, every=checkpoint_every)
+        else:
+            obs, stats = plan.evolve(t, opts)
     out = _pack(obs, override, raw_norm)
     if return_stats:
         return t, out, stats

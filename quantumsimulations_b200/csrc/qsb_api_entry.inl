@@ -70,6 +70,21 @@ int qsb_session_step(qsb_plan* p, int64_t n_attempts, double* t_now, qsb_stats* 
   return rc;
 }
 
+int qsb_session_advance(qsb_plan* p, double t_target, double* t_now, qsb_stats* stats) {
+  if (!p || !p->ses) return fail(QSB_ERR_BAD_ARG, "no open session");
+  Session* s = p->ses;
+  if (!(t_target >= s->t)) return fail(QSB_ERR_BAD_ARG, "t_target lies before the session's current time");
+  QSB_CUDA(cudaSetDevice(p->device));
+  int64_t done = 0;
+  int rc = session_advance(p, s, t_target, INT64_MAX, s->o.nsteps, &done);
+  if (t_now) *t_now = s->t;
+  if (stats) {
+    stats->n_accepted = s->n_acc; stats->n_rejected = s->n_rej; stats->n_rhs = s->n_rhs;
+    stats->last_h = s->h; stats->device_ms = 0.0; stats->path = 1; stats->status = rc;
+  }
+  return rc;
+}
+
 int qsb_session_observe(qsb_plan* p, double* obs) {
   if (!p || !p->ses || !obs) return fail(QSB_ERR_BAD_ARG, "no open session or null obs");
   QSB_CUDA(cudaSetDevice(p->device));

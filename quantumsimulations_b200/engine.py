@@ -57,7 +57,7 @@ class _Stats(C.Structure):
 EXPORTS = (
     "qsb_version", "qsb_last_error", "qsb_device_count", "qsb_plan_create", "qsb_plan_destroy",
     "qsb_plan_workspace_bytes", "qsb_plan_set_workspace", "qsb_evolve", "qsb_evolve_batch", "qsb_apply_h",
-    "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
+    "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather",
 )
@@ -302,6 +302,14 @@ class Plan:
         st = _Stats()
         _check(self.lib.qsb_session_step(self._h, int(n_attempts), C.byref(t), C.byref(st), C.byref(ms)))
         return t.value, Stats.from_c(st), ms.value
+
+    def session_advance(self, t_target: float):
+        """Integrate the open session to exactly ``t_target``; returns (t, Stats) with Stats.last_h = the controller's
+        step size (what a resumed session passes as ``first_step``)."""
+        t = C.c_double(0.0)
+        st = _Stats()
+        _check(self.lib.qsb_session_advance(self._h, float(t_target), C.byref(t), C.byref(st)))
+        return t.value, Stats.from_c(st)
 
     def session_observe(self) -> np.ndarray:
         obs = np.empty(NOBS, dtype=np.float64)

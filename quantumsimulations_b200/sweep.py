@@ -58,6 +58,14 @@ def sweep_point_params(*, n_sea, gamma_sea, gamma_rare, B0_common, B1_sea, B1_ra
     }
 
 
+def _with_cache(batch: BatchFn, cache_dir: Optional[str]) -> BatchFn:
+    if not cache_dir:
+        return batch
+    from .checkpoint import TrajectoryCache, cached_batch
+
+    return cached_batch(batch, TrajectoryCache(cache_dir))
+
+
 def _default_batch(devices: Optional[Sequence[int]]) -> BatchFn:
     from .dist import simulate_on_devices
 
@@ -88,9 +96,15 @@ def run_sweep_sea_detuning(
     simulate_batch: Optional[BatchFn] = None,
     timestamp: Optional[str] = None,
     verbose: bool = True,
-) -> str:
+    cache_dir: Optional[str] = None,
+    _defer: bool = False,
+):
     """Reference keyword arguments (SW:356-376) + ``devices`` (GPUs to spread trajectories over),
-    ``simulate_batch`` (override of the batch solver: list[params] -> list[(t, obs)]) and ``timestamp``."""
+    ``simulate_batch`` (override of the batch solver: list[params] -> list[(t, obs)]), ``timestamp`` and
+    ``cache_dir`` (finished trajectories are kept there, keyed by their parameters, and an interrupted or repeated
+    sweep integrates only what is missing; the reference starts every run from zero, SW:483-485).
+    Returns the sweep directory.  (``_defer``: return ``(plist, finish)`` instead of integrating, so that
+    ``run_multi_sweep`` can put the trajectories of many sweeps into one batch.)"""
     say = print if verbose else (lambda *a, **k: None)
     f1R = M.f1R_for_resonance(f1A, target_sea_detuning, 0.0)
     dets = np.asarray(sea_detunings_Hz, dtype=float)
@@ -153,11 +167,21 @@ def run_sweep_sea_detuning(
         plist.extend(variants[tag] for tag in VARIANTS)
     say(f"Sea detuning sweep: {len(dets)} detunings x {len(VARIANTS)} variants = {len(plist)} trajectories "
         f"(N = {n_sea + 1} spins) -> {base_dir}", flush=True)
-    t0 = time.perf_counter()
-    results = (simulate_batch or _default_batch(devices))(plist)
-    say(f"  integrated in {time.perf_counter() - t0:.2f} s", flush=True)
 
-    # ---- per-detuning files and metrics (SW:671-792) -------------------------------------------------------
+    def finish(results) -> str:
+        return _write_sweep(results, base_dir=base_dir, dets=dets, per_det=per_det, summary=summary, f_Az=f_Az, f1A=f1A,
+                            f1R=f1R, sea_rare_rms_Hz=sea_rare_rms_Hz, coarse_window=coarse_window, say=say)
+
+    if _defer:
+        return plist, finish
+    t0 = time.perf_counter()
+    results = _with_cache(simulate_batch or _default_batch(devices), cache_dir)(plist)
+    say(f"  integrated in {time.perf_counter() - t0:.2f} s", flush=True)
+    return finish(results)
+
+
+def _write_sweep(results, *, base_dir, dets, per_det, summary, f_Az, f1A, f1R, sea_rare_rms_Hz, coarse_window, say) -> str:
+    """Per-detuning files and metrics (SW:671-792), global_params.json and summary.json (SW:1153-1157)."""
     for i, delta_Hz in enumerate(dets):
         det_dir = os.path.join(base_dir, M.detuning_label(delta_Hz))
         os.makedirs(det_dir, exist_ok=True)
@@ -198,6 +222,46 @@ def run_sweep_sea_detuning(
     _dump(os.path.join(base_dir, "summary.json"), summary)
     say(f"Sweep complete: {base_dir}", flush=True)
     return base_dir
+
+
+def run_multi_sweep(
+    *,
+    f1A_values: Sequence[float],
+    detunings_for: Optional[Callable[[float], Sequence[float]]] = None,
+    out_root: str = "results",
+    devices: Optional[Sequence[int]] = None,
+    simulate_batch: Optional[BatchFn] = None,
+    timestamp: Optional[str] = None,
+    verbose: bool = True,
+    cache_dir: Optional[str] = None,
+    **sweep_kwargs,
+) -> List[str]:
+    """The 2D grid that ``2D_sweep_report.py`` consumes: one detuning sweep per sea drive amplitude f1A, each
+    with ``target_sea_detuning = f1A`` and detunings ``linspace(0, 3 f1A, 13)`` (the rule of SW:1231, override with
+    ``detunings_for``), written as one ``sea_detuning_sweep_*`` directory per f1A under ``out_root``.
+
+    The reference would run the sweeps (and every trajectory inside them) one after the other; here ALL
+    trajectories of ALL sweeps go through one batch call, so the grid fills the GPU(s): 19 x 13 x 3 = 741
+    one-CTA trajectories are five waves on one B200 and less than one on eight.
+    ``sweep_kwargs`` are the remaining keyword arguments of ``run_sweep_sea_detuning`` (f_Az, gamma_sea, ...).
+    """
+    say = print if verbose else (lambda *a, **k: None)
+    rule = detunings_for or (lambda f1a: np.linspace(0.0, 3.0 * f1a, 13))
+    t_base = _dt.datetime.strptime(timestamp, "%Y%m%d_%H%M%S") if timestamp else _dt.datetime.now()
+    plist: List[DipolarRareParams] = []
+    parts = []
+    for k, f1a in enumerate(f1A_values):
+        stamp = (t_base + _dt.timedelta(seconds=k)).strftime("%Y%m%d_%H%M%S")  # one directory per sweep
+        sub, finish = run_sweep_sea_detuning(
+            f1A=float(f1a), target_sea_detuning=float(f1a), sea_detunings_Hz=rule(float(f1a)), out_root=out_root,
+            timestamp=stamp, verbose=False, _defer=True, **sweep_kwargs)
+        parts.append((len(plist), len(sub), finish))
+        plist.extend(sub)
+    say(f"2D grid: {len(parts)} sweeps, {len(plist)} trajectories in one batch", flush=True)
+    t0 = time.perf_counter()
+    results = _with_cache(simulate_batch or _default_batch(devices), cache_dir)(plist)
+    say(f"  integrated in {time.perf_counter() - t0:.2f} s", flush=True)
+    return [finish(results[a:a + n]) for a, n, finish in parts]
 
 
 def replay_reference_script(module, func_name: str = "run_sweep_sea_detuning", *, devices=None,

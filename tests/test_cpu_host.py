@@ -361,3 +361,76 @@ def test_fusion_plan_at_bench_sizes(monkeypatch):
     assert engine.strided_fusion(20, 148) is None  # two layouts: nothing to fuse
     fu30 = engine.strided_fusion(30, 148)
     assert fu30 and fu30["f"] == 2  # the first mid layout stays a full-grid launch
+
+
+def test_multi_sweep_grid_is_one_batch_and_one_directory_per_f1a(tmp_path):
+    """C3: the 2D (f1A x detuning) grid goes through ONE batch call and lands as one reference-layout sweep
+    directory per f1A (what 2D_sweep_report.py walks for summary.json); each sweep equals the stand-alone one."""
+    from quantumsimulations_b200.sweep import run_multi_sweep, run_sweep_sea_detuning
+
+    with open(os.path.join(GOLDEN, "sweep_small.json")) as f:
+        gp = json.load(f)["summary"]["global_params"]
+    calls = []
+
+    def batch(plist):
+        calls.append(len(plist))
+        return _oracle_batch(plist)
+
+    common = dict(f_Az=gp["f_Az_Hz"], gamma_sea=gp["gamma_sea"], gamma_rare=gp["gamma_rare"], n_sea=gp["n_sea"],
+                  t_final=2.0e-3, steps=101, phi_sea=gp["phi_sea_rad"], phi_rare=gp["phi_rare_rad"],
+                  is_spin_three_half=False, solver_atol=gp["solver_atol"], solver_rtol=gp["solver_rtol"],
+                  solver_nsteps=gp["solver_nsteps"], solver_max_step=gp["solver_max_step"], coarse_window=5)
+    f1as = [20e3, 35e3]
+    rule = lambda f1a: np.linspace(0.0, 3.0 * f1a, 3)
+    dirs = run_multi_sweep(f1A_values=f1as, detunings_for=rule, out_root=str(tmp_path / "grid"), simulate_batch=batch,
+                           timestamp="20250101_000000", verbose=False, **common)
+    assert calls == [2 * 3 * 3]
+    assert [os.path.basename(d) for d in dirs] == ["sea_detuning_sweep_20250101_000000", "sea_detuning_sweep_20250101_000001"]
+    for f1a, d in zip(f1as, dirs):
+        with open(os.path.join(d, "summary.json")) as f:
+            got = json.load(f)
+        assert got["global_params"]["f1A_Hz"] == f1a and got["global_params"]["target_sea_detuning"] == f1a
+        assert [r["delta_Hz"] for r in got["sweep_results"]] == list(rule(f1a))
+        alone = run_sweep_sea_detuning(f1A=f1a, target_sea_detuning=f1a, sea_detunings_Hz=rule(f1a),
+                                       out_root=str(tmp_path / "alone"), simulate_batch=_oracle_batch,
+                                       timestamp=f"{int(f1a)}", verbose=False, **common)
+        with open(os.path.join(alone, "summary.json")) as f:
+            want = json.load(f)
+        assert json.dumps(got, sort_keys=True) == json.dumps(want, sort_keys=True)
+
+
+def test_trajectory_cache_serves_repeated_and_interrupted_sweeps(tmp_path):
+    """8(f) rank 3 for the on-chip path: finished trajectories are cached by their parameters, so the second sweep
+    integrates nothing and a sweep that shares points with an earlier one integrates only the new ones."""
+    from quantumsimulations_b200.checkpoint import trajectory_key
+    from quantumsimulations_b200.sweep import run_sweep_sea_detuning
+
+    with open(os.path.join(GOLDEN, "sweep_small.json")) as f:
+        gp = json.load(f)["summary"]["global_params"]
+    calls = []
+
+    def batch(plist):
+        calls.append(len(plist))
+        return _oracle_batch(plist)
+
+    kw = dict(f_Az=gp["f_Az_Hz"], f1A=gp["f1A_Hz"], target_sea_detuning=gp["target_sea_detuning"], gamma_sea=gp["gamma_sea"],
+              gamma_rare=gp["gamma_rare"], n_sea=gp["n_sea"], t_final=2.0e-3, steps=101, phi_sea=gp["phi_sea_rad"],
+              phi_rare=gp["phi_rare_rad"], solver_atol=1e-10, solver_rtol=1e-9, solver_nsteps=10**7, solver_max_step=1e-5,
+              coarse_window=5, simulate_batch=batch, cache_dir=str(tmp_path / "cache"), verbose=False)
+    a = run_sweep_sea_detuning(sea_detunings_Hz=[0.0, 25e3], out_root=str(tmp_path / "a"), timestamp="a", **kw)
+    b = run_sweep_sea_detuning(sea_detunings_Hz=[0.0, 25e3, 50e3], out_root=str(tmp_path / "b"), timestamp="b", **kw)
+    c = run_sweep_sea_detuning(sea_detunings_Hz=[0.0, 25e3, 50e3], out_root=str(tmp_path / "c"), timestamp="c", **kw)
+    assert calls == [6, 3]          # b integrates only delta = 50 kHz, c nothing
+    sb, sc = (json.load(open(os.path.join(d, "summary.json")))["sweep_results"] for d in (b, c))
+    assert sb == sc
+    sa = json.load(open(os.path.join(a, "summary.json")))["sweep_results"]
+    assert sa == sb[:2]
+    za = np.load(os.path.join(a, "delta_p25000.0Hz", "time_and_obs_center_on.npz"))
+    zc = np.load(os.path.join(c, "delta_p25000.0Hz", "time_and_obs_center_on.npz"))
+    assert all(np.array_equal(za[k], zc[k]) for k in za.files)
+    # the key sees every field of the record and the solver choice
+    from conftest import params_from_meta  # noqa: F401
+    from quantumsimulations_b200 import DipolarRareParams
+    p = DipolarRareParams(n_sea=6, is_spin_three_half=False)
+    assert trajectory_key(p) != trajectory_key(dataclasses.replace(p, gamma_sea=np.nextafter(p.gamma_sea, np.inf)))
+    assert trajectory_key(p, method="dp5") != trajectory_key(p, method="taylor")

@@ -196,3 +196,35 @@ def test_full_sweep_matches_reference_sweep_metrics(tmp_path):
                     assert got[k] == pytest.approx(want[k], abs=2e-3), k
             else:
                 assert got[k] == pytest.approx(want[k], rel=1e-9, abs=1e-12), k
+
+
+@pytest.mark.parametrize("method", ["dp5", "taylor"])
+def test_checkpointed_trajectory_resumes_bitwise(tmp_path, method):
+    """8(f) rank 3: a tiled-path trajectory interrupted after some output times and resumed from its checkpoint file
+    (state, time, controller step size) produces exactly the traces and step counts of the uninterrupted run."""
+    from bench import sweep_params
+    from quantumsimulations_b200 import compile_table, engine
+    from quantumsimulations_b200.checkpoint import evolve_checkpointed
+
+    table = compile_table(sweep_params(13, 50e3))      # N = 14: tiled path
+    t_out = np.linspace(0.0, 4.0e-5, 9)
+    opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, max_step=1e-5, nsteps=100000, method=method, order=12)
+    with engine.Plan(table) as plan:
+        want, wst = plan.evolve(t_out, opts)
+    path = str(tmp_path / "traj.npz")
+    with engine.Plan(table) as plan:
+        part, _, done = evolve_checkpointed(plan, t_out, opts, path, every=2, stop_after=3)
+    assert not done and np.array_equal(part[:4], want[:4]) and np.all(np.isnan(part[4:]))
+    with engine.Plan(table) as plan:               # a fresh plan, as after a crash
+        part, _, done = evolve_checkpointed(plan, t_out, opts, path, every=2, stop_after=2)
+    assert not done and np.array_equal(part[:6], want[:6])
+    with engine.Plan(table) as plan:
+        got, gst, done = evolve_checkpointed(plan, t_out, opts, path, every=100)
+    assert done and np.array_equal(got, want)
+    assert (gst.n_accepted, gst.n_rejected) == (wst.n_accepted, wst.n_rejected)
+    with engine.Plan(table) as plan:               # finished checkpoint: nothing left to integrate
+        again, _, done = evolve_checkpointed(plan, t_out, opts, path)
+    assert done and np.array_equal(again, want)
+    with pytest.raises(ValueError):
+        with engine.Plan(table) as plan:
+            evolve_checkpointed(plan, t_out[:5], opts, path)
