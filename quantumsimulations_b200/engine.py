@@ -94,6 +94,7 @@ def load_library() -> C.CDLL:
     lib.qsb_apply_h.argtypes = [vp, dp, dp]
     lib.qsb_session_begin.argtypes = [vp, C.c_uint64, dp, C.c_double, C.POINTER(_Opts)]
     lib.qsb_session_step.argtypes = [vp, C.c_int64, dp, C.POINTER(_Stats), dp]
+    lib.qsb_session_advance.argtypes = [vp, C.c_double, dp, C.POINTER(_Stats)]
     lib.qsb_session_observe.argtypes = [vp, dp]
     lib.qsb_session_state.argtypes = [vp, dp]
     lib.qsb_session_end.argtypes = [vp]
