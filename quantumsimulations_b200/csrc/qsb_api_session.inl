@@ -141,18 +141,26 @@ static int attempt_dp5(qsb_plan* p, Session* s, double hu, double* err, double* 
 }
 
 static int attempt_taylor(qsb_plan* p, Session* s, double hu, double* err, double* cand_sums) {
-  // ys accumulates y + sum of terms; k[0] holds the running term; term_{m+1} = hu/(m+1) * f(term_m)
-  QSB_CUDA(cudaMemcpyAsync(s->ys, s->y, sizeof(cplx) * s->dim, cudaMemcpyDeviceToDevice, p->stream));
+  // k[0] holds the running term, term_{m+1} = hu/(m+1) * f(term_m), term_0 = y; ys becomes y + sum of terms.
+  // The vector an apply acts on (term_m) is in pass_last's registers anyway, so ys is only touched by every second
+  // apply, which adds BOTH term_m and term_{m+1}:  m = 1: ys = y + term_1 + term_2;  m = 3, 5, ..: ys += term_m +
+  // term_{m+1};  an odd order's last apply adds its single term.  The other applies end in the plain term-producing
+  // pass_last (4 S instead of 6 S), and no initial copy of y is needed.
   for (int m = 0; m < s->order; ++m) {
+    const bool last = m == s->order - 1;
     Epilogue e = blank_epilogue(s);
     e.alpha = hu / (double)(m + 1);
     e.o1 = s->k[0];
-    e.o2 = s->ys;
-    e.vin[0] = s->ys; e.c[0] = 1.0; e.n_in = 1;
-    e.ck = e.alpha;
-    if (m == s->order - 1) {  // last term = error estimate; y is read only here, for the error weights
-      e.vin[1] = s->y; e.c[1] = 0.0; e.n_in = 2;
-      e.want_err = 1; e.ek = e.alpha; e.sc_i0 = 1; e.sc_i1 = -1;
+    if ((m & 1) || last) {
+      e.o2 = s->ys;
+      e.vin[0] = m <= 1 ? s->y : s->ys; e.c[0] = 1.0; e.n_in = 1;
+      e.ck = e.alpha;
+      e.cs = (m & 1) ? 1.0 : 0.0;
+    }
+    if (last) {  // last term = error estimate; y is read here for the error weights
+      e.vin[e.n_in] = s->y; e.c[e.n_in] = 0.0;
+      e.want_err = 1; e.ek = e.alpha; e.sc_i0 = e.n_in; e.sc_i1 = -1;
+      ++e.n_in;
     }
     int rc = launch_happly(p->g, p->tab, m == 0 ? s->y : s->k[0], s->tx, s->ty, e, 0, s->partials, p->stream, link_of(p), nullptr, &p->fu);
     if (rc) return rc;

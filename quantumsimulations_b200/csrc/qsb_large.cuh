@@ -43,9 +43,10 @@ struct DiagTables {      // device pointers
 // Fused epilogue of the last pass: k = -i H v (or H v), then stage algebra on k.
 struct Epilogue {
   const cplx* vin[MAX_VEC_IN];
-  double c[MAX_VEC_IN];  // o2 = sum c_j vin_j + ck k
+  double c[MAX_VEC_IN];  // o2 = sum c_j vin_j + ck k + cs v     (v = the vector the apply acted on)
   double e[MAX_VEC_IN];  // err = sum e_j vin_j + ek k
   double ck, ek, alpha;  // o1 = alpha k
+  double cs;             // weight of v in o2: v is in registers anyway (the Dz term), so adding it costs no traffic
   cplx* o1;
   cplx* o2;
   int n_in;

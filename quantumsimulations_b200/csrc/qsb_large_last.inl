@@ -107,7 +107,7 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
       double m0[(EPI & 2) ? B : 1], m1[(EPI & 2) ? B : 1];
 #pragma unroll
       for (int jj = 0; jj < B; ++jj) {
-        if (EPI & 1) o2[jj] = ep.ck * k[jj];
+        if (EPI & 1) { o2[jj] = ep.ck * k[jj]; axpy(o2[jj], ep.cs, v[jj]); }
         if (EPI & 2) { er[jj] = ep.ek * k[jj]; m0[jj] = 0.0; m1[jj] = 0.0; }
       }
 #pragma unroll
