@@ -64,7 +64,8 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
   // whole batch of outstanding loads: B elements x (src + up to NQ input vectors), all issued before the first use.
   // The groups of two input vectors sit behind uniform branches on n_in, which resolve at once and therefore do not
   // break up the load burst.
-  {
+  // (EPI == 0 has no input vectors: src alone fits next to the tile, which then stays in registers.)
+  if (EPI != 0) {
     cplx* park = sm + phys_base<8>(tt);
 #pragma unroll
     for (int j = 0; j < 16; ++j) park[j * PhysStride<8>::value] = r[j];
@@ -94,7 +95,7 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
     cplx k[B];
 #pragma unroll
     for (int jj = 0; jj < B; ++jj) {  // k = -i (Dz v + r)
-      cplx acc = td.at(a.tab.Wz, j0 + jj) * v[jj] + park[(j0 + jj) * PhysStride<8>::value];
+      cplx acc = td.at(a.tab.Wz, j0 + jj) * v[jj] + (EPI != 0 ? park[(j0 + jj) * PhysStride<8>::value] : r[j0 + jj]);
       k[jj] = ep.raw_h ? acc : mul_mi(acc);
     }
     if (EPI == 0) {
