@@ -158,9 +158,12 @@ __device__ __forceinline__ uint64_t gidx(const Layout& L, uint64_t base, int i) 
 }
 
 // 16-point butterflies on the stages selected by mask (all unnormalised):
-//   MODE 0  Hadamard           (a,b) -> (a+b, a-b)
-//   MODE 1  M  = H S H         (a,b) -> (p+iq, p-iq),  p = a+b, q = a-b      [W^-1 S W = (M/2)^(x n)]
-//   MODE 2  M' = H S^dagger H  (a,b) -> (p-iq, p+iq)
+//   MODE 0  Hadamard            (a,b) -> (a+b, a-b)
+//   MODE 1  K  = M  / (1+i)     (a,b) -> (a - i b, b - i a)      M  = H S H         [W^-1 S W = (M/2)^(x n)]
+//   MODE 2  K' = M' / (1-i)     (a,b) -> (a + i b, b + i a)      M' = H S^dagger H
+// M = [[1+i, 1-i], [1-i, 1+i]] = (1+i) [[1, -i], [-i, 1]], so the scalar is pulled out of every stage: a K stage costs
+// the four additions of a Hadamard stage (M done literally costs eight), and over the twelve bits of a tile the
+// scalars multiply to the REAL number (1+i)^12 = (1-i)^12 = -64, which the callers fold into their 2^-12 (M_SCALE).
 template <int MODE>
 __device__ __forceinline__ void bfly16(cplx (&r)[16], int mask) {
 #pragma unroll
@@ -170,16 +173,15 @@ __device__ __forceinline__ void bfly16(cplx (&r)[16], int mask) {
       for (int j = 0; j < 16; ++j) {
         if (!(j >> s & 1)) {
           cplx a = r[j], b = r[j | (1 << s)];
-          cplx p = a + b, q = a - b;
           if (MODE == 0) {
-            r[j] = p;
-            r[j | (1 << s)] = q;
+            r[j] = a + b;
+            r[j | (1 << s)] = a - b;
           } else if (MODE == 1) {
-            r[j] = mk(p.x - q.y, p.y + q.x);
-            r[j | (1 << s)] = mk(p.x + q.y, p.y - q.x);
+            r[j] = mk(a.x + b.y, a.y - b.x);
+            r[j | (1 << s)] = mk(b.x + a.y, b.y - a.x);
           } else {
-            r[j] = mk(p.x + q.y, p.y - q.x);
-            r[j | (1 << s)] = mk(p.x - q.y, p.y + q.x);
+            r[j] = mk(a.x - b.y, a.y + b.x);
+            r[j | (1 << s)] = mk(b.x - a.y, b.y + a.x);
           }
         }
       }

@@ -12,7 +12,8 @@ struct PassArgs {
   DiagTables tab;
 };
 
-constexpr double INV_TILE = 1.0 / (double)TILE;  // the 2^-12 of (M/2)^(x12)
+// (M/2)^(x12) = M_SCALE K^(x12): the 2^-12 of the twelve halvings times (1 +- i)^12 = -64 (see bfly16)
+constexpr double M_SCALE = -64.0 / (double)TILE;
 
 // Which tiles a launch of a strided-layout pass covers.  Tile v of a layout is numbered by its outer bits in
 // ascending order, so for layouts sharing lk the low (12 - lk) bits of v are index bits [lk, 12): a "chunk".
@@ -101,7 +102,7 @@ pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx
   bfly16<2>(r, 0xF);
   const int pv = __popcll(base | a.g.rank_bits);  // S_rest^dagger = (-i)^popcount(outer bits)
 #pragma unroll
-  for (int j = 0; j < 16; ++j) ty[base | (uint64_t)elem<8>(tt, j)] = mul_mi_pow(INV_TILE * r[j], pv);
+  for (int j = 0; j < 16; ++j) ty[base | (uint64_t)elem<8>(tt, j)] = mul_mi_pow(M_SCALE * r[j], pv);
   if (collect_obs) {
     block_reduce<3>(s, red);
     if (threadIdx.x == 0) {

@@ -50,7 +50,7 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
   bfly16<1>(r, 0xF);
   const int pv = __popcll(base | a.g.rank_bits);  // S_rest = (+i)^popcount(outer bits)
 #pragma unroll
-  for (int j = 0; j < 16; ++j) r[j] = mul_pi_pow(INV_TILE * r[j], pv) + tx[base | (uint64_t)elem<4>(tt, j)];
+  for (int j = 0; j < 16; ++j) r[j] = mul_pi_pow(M_SCALE * r[j], pv) + tx[base | (uint64_t)elem<4>(tt, j)];
   bfly16<0>(r, 0xF);
   smem_store16<4>(sm, tt, r);
   __syncthreads();
