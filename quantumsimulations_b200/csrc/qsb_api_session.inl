@@ -58,7 +58,7 @@ static int fetch_sums(qsb_plan* p, Session* s, double* out) {
   return QSB_OK;
 }
 
-static const ShardLink* link_of(const qsb_plan* p) { return p->world > 1 && p->connected ? &p->link : nullptr; }
+static ShardLink* link_of(qsb_plan* p) { return p->world > 1 && p->connected ? &p->link : nullptr; }
 
 static Epilogue blank_epilogue(const Session* s) {
   Epilogue e = {};

@@ -187,6 +187,7 @@ int qsb_shard_connect(qsb_plan* p, const void* blobs, qsb_allgather_fn allgather
   }
   p->allgather = allgather;
   p->allgather_ctx = ctx;
+  p->link.ring_ready = false;  // the peers' pointers changed: the TMA descriptors are rebuilt on first use
   p->link.sync = shard_sync;
   p->link.ctx = p;
   p->connected = true;

@@ -98,6 +98,10 @@ struct ShardLink {
   cplx* ty[MAX_WORLD];
   int (*sync)(void* ctx);
   void* ctx;
+  // TMA descriptors of the peers' scratch vectors for the ring version of the centre pass, [branch][peer]; built on
+  // first use after the link is connected (host cache)
+  CUtensorMap ring_maps[2][MAX_WORLD];
+  bool ring_ready;
 };
 
 // L2-resident fusion of the strided passes f .. centre .. f into one persistent launch (qsb_large_fused.inl).
@@ -155,11 +159,11 @@ int centre_window(const Layout& L);
 // to comb->out, and `src` must equal comb->out.  Epilogues take at most 2 input vectors.
 int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
                   const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream,
-                  const ShardLink* link = nullptr, const Combine* comb = nullptr, StridedFusion* fu = nullptr);
+                  ShardLink* link = nullptr, const Combine* comb = nullptr, StridedFusion* fu = nullptr);
 void launch_error_sums(const LargeGeom& g, const ErrSpec& es, double* partials, cudaStream_t stream);
 // Observables only (pass_first + mids + pass_centre), filling partial slots 0..6.
 int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
-                   double* partials, cudaStream_t stream, const ShardLink* link = nullptr,
+                   double* partials, cudaStream_t stream, ShardLink* link = nullptr,
                    StridedFusion* fu = nullptr);
 // out[PSTRIDE] = column sums of partials[n_tiles][PSTRIDE] in a fixed order.
 void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out8, cudaStream_t stream);

@@ -32,17 +32,22 @@ constexpr int FUSED_NG = QSB_FUSED_NG;  // compute groups of TPT threads (2: 17 
 constexpr int TILE_BYTES = TILE * (int)sizeof(cplx);
 constexpr int ROW_BYTES = TD_STRIDE * (int)sizeof(double);
 
+constexpr int MAX_MAPS = MAX_WORLD > MAX_LAYOUTS ? MAX_WORLD : MAX_LAYOUTS;
 struct alignas(64) TmaMaps {
-  CUtensorMap m[2][MAX_LAYOUTS];  // [branch][layout]: the branch's scratch vector as a 5-d tensor of doubles
+  // fused strided pass: [branch][layout], the branch's scratch vector as a 5-d tensor of doubles whose box is a tile;
+  // sharded centre ring: [branch][peer], the PEER's scratch vector, box = the slab of a centre tile that peer holds
+  CUtensorMap m[2][MAX_MAPS];
 };
 
 struct TaskDesc {
   int kind;      // 0 mid, 1 centre, 2 exit
   int li;        // layout
   int branch;
-  unsigned v;    // tile number
+  unsigned v;    // tile number (index arithmetic)
+  unsigned slot; // this rank's number for the tile (diagonal rows, partial sums); = v when unsharded
   int c2, c4;    // its TMA box coordinates (dims 2 and 4; the others are 0)
-  int ctr;       // counter to bump when the tile's store has completed (-1: last phase, nobody waits)
+  int ctr;       // counter to bump when the tile's store has completed (-1: nobody waits)
+  int map0, n_parts;  // the tile is moved as n_parts boxes through maps m[branch][map0 .. map0 + n_parts)
 };
 
 struct FusedSmem {
@@ -191,9 +196,9 @@ __device__ __forceinline__ void smem_mid_tile(const Layout& L, cplx* sm, int tt,
 
 // t <- W_g D W_g t on one centre tile in shared memory (W: the register window the diagonal is evaluated in)
 template <int W, bool COLLECT>
-__device__ __forceinline__ void smem_centre_tile(const PassArgs& a, const Layout& L, uint64_t v, int branch, cplx* sm,
-                                                 const double* row, const double* intile, double* red, int tt, int g,
-                                                 double* __restrict__ partials) {
+__device__ __forceinline__ void smem_centre_tile(const PassArgs& a, const Layout& L, uint64_t v, unsigned slot, int branch,
+                                                 cplx* sm, const double* row, const double* intile, double* red, int tt,
+                                                 int g, double* __restrict__ partials) {
   const double (&ww)[16] = branch ? a.tab.Wy : a.tab.Wx;
   TileDiag<W> td;
   td.load_shared(row, intile, tt);
@@ -218,26 +223,21 @@ __device__ __forceinline__ void smem_centre_tile(const PassArgs& a, const Layout
   if (COLLECT) {
     group_reduce2(s, red, tt, g);
     if (tt == 0) {
-      double* p = partials + (size_t)v * PSTRIDE + 3 + 2 * branch;
+      double* p = partials + (size_t)slot * PSTRIDE + 3 + 2 * branch;
       p[0] = s[0]; p[1] = s[1];
     }
   }
 }
 
-// ctrl[0]: ticket counter; ctrl[1 + unit * P + phase]: published tiles.  Zeroed by the launcher before every launch.
-// Block: FUSED_NG * TPT compute threads + a loader warp + a storer warp (lane 0 of each works).
-//   loader : ticket -> dependency (acquire) -> buffer free (empty[b]) -> descriptor, TMA load (full[b])
+// ---------------------------------------------------------------------------------------------------
+// The three roles of a ring CTA.  Block: FUSED_NG * TPT compute threads + a loader warp + a storer warp (lane 0 of
+// each works).
+//   loader : (next task) -> buffer free (empty[b]) -> descriptor, TMA load(s) (full[b])
 //   compute: full[b] -> transform in place -> computed[b]
-//   storer : computed[b] -> TMA store -> empty[b] once the store has read the buffer -> publishes the PREVIOUS tile
-//            once its store has completed (so a completion wait never sits between two stores)
-template <int W, bool COLLECT>
-__global__ void __launch_bounds__(FUSED_NG * TPT + 64, 1)
-pass_strided_fused(PassArgs a, FusedSpec fs, const __grid_constant__ TmaMaps maps, double* __restrict__ partials,
-                   int* ctrl) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  FusedSmem& S = *reinterpret_cast<FusedSmem*>(smem_raw);
-  const int tid = threadIdx.x;
-  const int centre = fs.f + fs.m;
+//   storer : computed[b] -> TMA store(s) -> empty[b] once the store has read the buffer -> publishes the PREVIOUS
+//            tile once its store has completed (so a completion wait never sits between two stores)
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ring_init(FusedSmem& S, const PassArgs& a, int tid) {
   for (int i = tid; i < 5 * 256; i += blockDim.x) {
     S.intile[0][i] = a.tab.Ix[i];
     S.intile[1][i] = a.tab.Iy[i];
@@ -249,9 +249,110 @@ pass_strided_fused(PassArgs a, FusedSpec fs, const __grid_constant__ TmaMaps map
     asm volatile("fence.proxy.async;" ::: "memory");
   }
   __syncthreads();
+}
 
+// Loader side of one task: wait for the buffer, publish the descriptor, issue the loads.
+__device__ __forceinline__ void ring_issue(FusedSmem& S, const PassArgs& a, const TmaMaps& maps, int seq, const TaskDesc& task) {
+  const int b = seq % NBUF, round = seq / NBUF;
+  if (round > 0) mbar_wait(&S.empty[b], (round - 1) & 1);
+  S.desc[b] = task;
+  const bool is_centre = task.kind == 1;
+  mbar_arrive_expect_tx(&S.full[b], TILE_BYTES + (is_centre ? ROW_BYTES : 0));
+  const int part = TILE / task.n_parts;
+  for (int r = 0; r < task.n_parts; ++r)
+    tma_load_5d(S.buf[b] + r * part, &maps.m[task.branch][task.map0 + r], &S.full[b], task.c2, task.c4);
+  if (is_centre)
+    bulk_load(S.row[b], (task.branch ? a.tab.Ty : a.tab.Tx) + (size_t)task.slot * TD_STRIDE, ROW_BYTES, &S.full[b]);
+}
+
+__device__ __forceinline__ void ring_finish_loads(FusedSmem& S, int seq) {
+  *(volatile int*)&S.final_count = seq;
+  for (int g = 0; g < FUSED_NG; ++g) {  // one exit marker per compute group
+    const int b = seq % NBUF, round = seq / NBUF;
+    if (round > 0) mbar_wait(&S.empty[b], (round - 1) & 1);
+    S.desc[b].kind = 2;
+    mbar_arrive(&S.full[b]);
+    ++seq;
+  }
+}
+
+// ctrl == nullptr: nothing is published (no other CTA depends on this one's tiles).
+__device__ __forceinline__ void ring_storer(FusedSmem& S, const TmaMaps& maps, int* ctrl) {
+  // prev_ctr: the counter of the last stored tile, still to be bumped once that store has completed.  While stores
+  // follow each other the completion wait rides behind the next store; when the storer idles it publishes at once
+  // (the tile some loader is waiting for may depend on exactly this publication).
+  int prev_ctr = -1;
+  Watchdog wd;
+  for (int seq = 0;; ++seq) {
+    const int b = seq % NBUF, par = (seq / NBUF) & 1;
+    bool done = false;
+    while (!mbar_test(&S.computed[b], par)) {
+      if (prev_ctr >= 0) {
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        asm volatile("fence.proxy.async;" ::: "memory");
+        __threadfence();
+        atomicAdd(ctrl + prev_ctr, 1);
+        prev_ctr = -1;
+      }
+      const int fc = *(volatile int*)&S.final_count;
+      if (fc >= 0 && seq >= fc) { done = true; break; }
+      wd.tick();
+    }
+    if (done) break;
+    const TaskDesc d = S.desc[b];
+    const int part = TILE / d.n_parts;
+    for (int r = 0; r < d.n_parts; ++r) tma_store_5d(&maps.m[d.branch][d.map0 + r], S.buf[b] + r * part, d.c2, d.c4);
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    mbar_arrive(&S.empty[b]);
+    if (seq > 0 && prev_ctr >= 0) {
+      asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
+      asm volatile("fence.proxy.async;" ::: "memory");
+      __threadfence();
+      atomicAdd(ctrl + prev_ctr, 1);
+    }
+    prev_ctr = ctrl ? d.ctr : -1;
+  }
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // the kernel must not end with stores in flight
+  if (prev_ctr >= 0) {
+    asm volatile("fence.proxy.async;" ::: "memory");
+    __threadfence();
+    atomicAdd(ctrl + prev_ctr, 1);
+  }
+}
+
+template <int W, bool COLLECT>
+__device__ __forceinline__ void ring_compute(FusedSmem& S, const PassArgs& a, int tid, double* __restrict__ partials) {
+  const int g = tid / TPT, tt = tid - g * TPT;
+  for (int seq = g;; seq += FUSED_NG) {
+    const int b = seq % NBUF;
+    mbar_wait(&S.full[b], (seq / NBUF) & 1);
+    const TaskDesc d = S.desc[b];
+    if (d.kind == 2) break;
+    if (d.kind == 1)
+      smem_centre_tile<W, COLLECT>(a, a.g.lay[d.li], d.v, d.slot, d.branch, S.buf[b], S.row[b], S.intile[d.branch], S.red[g],
+                                   tt, g, partials);
+    else
+      smem_mid_tile(a.g.lay[d.li], S.buf[b], tt, g);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the tile is about to be read by the TMA store
+    mbar_arrive(&S.computed[b]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// pass_strided_fused: the L2-resident mid .. centre .. mid pipeline of an unsharded plan.
+// ctrl[0]: ticket counter; ctrl[1 + unit * P + phase]: published tiles.  Zeroed by the launcher before every launch.
+// ---------------------------------------------------------------------------------------------------
+template <int W, bool COLLECT>
+__global__ void __launch_bounds__(FUSED_NG * TPT + 64, 1)
+pass_strided_fused(PassArgs a, FusedSpec fs, const __grid_constant__ TmaMaps maps, double* __restrict__ partials,
+                   int* ctrl) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  FusedSmem& S = *reinterpret_cast<FusedSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  ring_init(S, a, tid);
   if (tid == FUSED_NG * TPT) {
-    // -------------------------------------------------------------------------------------------- loader
+    const int centre = fs.f + fs.m;
     const int P = 2 * fs.m + 1;
     const int T = 1 << fs.tiles_lb;
     const int U = 2 << fs.fbits;  // unit = (fixed bits, branch); branch is the lowest bit of the unit number
@@ -273,106 +374,76 @@ pass_strided_fused(PassArgs a, FusedSpec fs, const __grid_constant__ TmaMaps map
         if (u >= 0 && u < U) { valid = true; break; }
       }
       if (!valid) break;
-      const int branch = u & 1;
-      const int li = fs.f + (p <= fs.m ? p : 2 * fs.m - p);
-      const unsigned fm = fs.fixed_vmask[li];
-      const unsigned v = deposit_bits((unsigned)(u >> 1), fm) | deposit_bits((unsigned)q, fs.vmask & ~fm);
-      const int b = seq % NBUF, round = seq / NBUF;
-      if (round > 0) mbar_wait(&S.empty[b], (round - 1) & 1);
-      if (p > 0) {
+      TaskDesc d;
+      d.branch = u & 1;
+      d.li = fs.f + (p <= fs.m ? p : 2 * fs.m - p);
+      const unsigned fm = fs.fixed_vmask[d.li];
+      d.v = deposit_bits((unsigned)(u >> 1), fm) | deposit_bits((unsigned)q, fs.vmask & ~fm);
+      d.slot = d.v;
+      if (p > 0) {  // every tile of the unit's previous phase must have been stored and published
         const int* flag = ctrl + 1 + u * P + (p - 1);
         Watchdog wd;
         while (ld_acquire(flag) < T) { __nanosleep(32); wd.tick(); }
         asm volatile("fence.proxy.async;" ::: "memory");
       }
-      const Layout& L = a.g.lay[li];
+      const Layout& L = a.g.lay[d.li];
       const int midbits = L.gs - L.lk;
-      const bool is_centre = li == centre;
-      TaskDesc& d = S.desc[b];
-      d.kind = is_centre ? 1 : 0;
-      d.li = li;
-      d.branch = branch;
-      d.v = v;
-      d.c2 = (int)(v & ((1u << midbits) - 1));
-      d.c4 = (int)(v >> midbits);
+      d.kind = d.li == centre ? 1 : 0;
+      d.c2 = (int)(d.v & ((1u << midbits) - 1));
+      d.c4 = (int)(d.v >> midbits);
       d.ctr = p < P - 1 ? 1 + u * P + p : -1;
-      mbar_arrive_expect_tx(&S.full[b], TILE_BYTES + (is_centre ? ROW_BYTES : 0));
-      tma_load_5d(S.buf[b], &maps.m[branch][li], &S.full[b], d.c2, d.c4);
-      if (is_centre) bulk_load(S.row[b], (branch ? a.tab.Ty : a.tab.Tx) + (size_t)v * TD_STRIDE, ROW_BYTES, &S.full[b]);
+      d.map0 = d.li;
+      d.n_parts = 1;
+      ring_issue(S, a, maps, seq, d);
       ++seq;
     }
-    *(volatile int*)&S.final_count = seq;
-    for (int g = 0; g < FUSED_NG; ++g) {  // one exit marker per compute group
-      const int b = seq % NBUF, round = seq / NBUF;
-      if (round > 0) mbar_wait(&S.empty[b], (round - 1) & 1);
-      S.desc[b].kind = 2;
-      mbar_arrive(&S.full[b]);
-      ++seq;
-    }
-    return;
+    ring_finish_loads(S, seq);
+  } else if (tid == FUSED_NG * TPT + 32) {
+    ring_storer(S, maps, ctrl);
+  } else if (tid < FUSED_NG * TPT) {
+    ring_compute<W, COLLECT>(S, a, tid, partials);
   }
-  if (tid == FUSED_NG * TPT + 32) {
-    // -------------------------------------------------------------------------------------------- storer
-    // prev_ctr: the counter of the last stored tile, still to be bumped once that store has completed.  While stores
-    // follow each other the completion wait rides behind the next store; when the storer idles it publishes at once
-    // (the tile the loader is waiting for may depend on exactly this publication).
-    int prev_ctr = -1;
-    Watchdog wd;
-    for (int seq = 0;; ++seq) {
-      const int b = seq % NBUF, par = (seq / NBUF) & 1;
-      bool done = false;
-      while (!mbar_test(&S.computed[b], par)) {
-        if (prev_ctr >= 0) {
-          asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-          asm volatile("fence.proxy.async;" ::: "memory");
-          __threadfence();
-          atomicAdd(ctrl + prev_ctr, 1);
-          prev_ctr = -1;
-        }
-        const int fc = *(volatile int*)&S.final_count;
-        if (fc >= 0 && seq >= fc) { done = true; break; }
-        wd.tick();
-      }
-      if (done) break;
-      const TaskDesc d = S.desc[b];
-      tma_store_5d(&maps.m[d.branch][d.li], S.buf[b], d.c2, d.c4);
-      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-      asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-      mbar_arrive(&S.empty[b]);
-      if (seq > 0) {
-        asm volatile("cp.async.bulk.wait_group 1;" ::: "memory");
-        if (prev_ctr >= 0) {
-          asm volatile("fence.proxy.async;" ::: "memory");
-          __threadfence();
-          atomicAdd(ctrl + prev_ctr, 1);
-        }
-      }
-      prev_ctr = d.ctr;
-    }
-    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-    if (prev_ctr >= 0) {
-      asm volatile("fence.proxy.async;" ::: "memory");
-      __threadfence();
-      atomicAdd(ctrl + prev_ctr, 1);
-    }
-    return;
-  }
-  if (tid >= FUSED_NG * TPT) return;
+}
 
-  // ---------------------------------------------------------------------------------------------- compute groups
-  const int g = tid / TPT, tt = tid - g * TPT;
-  for (int seq = g;; seq += FUSED_NG) {
-    const int b = seq % NBUF;
-    mbar_wait(&S.full[b], (seq / NBUF) & 1);
-    const TaskDesc d = S.desc[b];
-    if (d.kind == 2) break;
-    if (d.kind == 1)
-      smem_centre_tile<W, COLLECT>(a, a.g.lay[d.li], d.v, d.branch, S.buf[b], S.row[b], S.intile[d.branch], S.red[g], tt, g,
-                                   partials);
-    else
-      smem_mid_tile(a.g.lay[d.li], S.buf[b], tt, g);
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the tile is about to be read by the TMA store
-    mbar_arrive(&S.computed[b]);
+// ---------------------------------------------------------------------------------------------------
+// pass_centre_ring: the sharded centre pass (the one exchange step of a sharded H-apply) on the same ring.
+// A centre tile has one slab of TILE / world amplitudes on every rank (the rank bits are the top bits of the tile);
+// rank r owns tiles v0 .. v0 + n_tiles_loc of the centre layout and both branches.  The loader pulls the world slabs
+// of a tile straight out of the peers' scratch vectors with one TMA tensor load each (NVLink reads issued by the copy
+// engine, never waited for by arithmetic), the compute groups apply W_g D W_g in shared memory, and the storer
+// pushes the slabs back in place with one TMA store each: exchange and compute are one kernel, and up to three tiles
+// per SM are in flight on the links at any time.  Tiles are dealt round-robin to the CTAs; nothing is published
+// (the rank barriers around the pass order it against the peers' neighbouring passes).
+// ---------------------------------------------------------------------------------------------------
+template <int W, bool COLLECT>
+__global__ void __launch_bounds__(FUSED_NG * TPT + 64, 1)
+pass_centre_ring(PassArgs a, int li, unsigned v0, unsigned n_tiles_loc, int world, const __grid_constant__ TmaMaps maps,
+                 double* __restrict__ partials) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  FusedSmem& S = *reinterpret_cast<FusedSmem*>(smem_raw);
+  const int tid = threadIdx.x;
+  ring_init(S, a, tid);
+  if (tid == FUSED_NG * TPT) {
+    int seq = 0;
+    for (unsigned i = blockIdx.x; i < 2u * n_tiles_loc; i += gridDim.x, ++seq) {
+      TaskDesc d;
+      d.kind = 1;
+      d.li = li;
+      d.branch = (int)(i & 1u);   // x and y tiles alternate: both branches' slabs share the peers' pages
+      d.slot = i >> 1;
+      d.v = v0 + d.slot;
+      d.c2 = (int)d.v;            // the centre group reaches the top index bit: every outer bit of the tile is a "mid" bit
+      d.c4 = 0;
+      d.ctr = -1;
+      d.map0 = 0;
+      d.n_parts = world;
+      ring_issue(S, a, maps, seq, d);
+    }
+    ring_finish_loads(S, seq);
+  } else if (tid == FUSED_NG * TPT + 32) {
+    ring_storer(S, maps, nullptr);
+  } else if (tid < FUSED_NG * TPT) {
+    ring_compute<W, COLLECT>(S, a, tid, partials);
   }
 }
 

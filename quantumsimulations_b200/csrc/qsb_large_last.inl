@@ -300,6 +300,10 @@ void prepare_device() {
   cudaFuncSetAttribute(pass_strided_fused<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
   cudaFuncSetAttribute(pass_strided_fused<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
   cudaFuncSetAttribute(pass_strided_fused<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
+  cudaFuncSetAttribute(pass_centre_ring<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
+  cudaFuncSetAttribute(pass_centre_ring<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
+  cudaFuncSetAttribute(pass_centre_ring<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
+  cudaFuncSetAttribute(pass_centre_ring<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm);
 }
 
 // The strided-layout passes of one H-apply (mids forward, centre, mids back).
@@ -328,13 +332,16 @@ static EncodeTiledFn encode_tiled_fn() {
 // The vector `base` (2^n_loc cplx) as a 5-d tensor of doubles whose box {2^(a+1), 2^(lk-a), 1, 2^(ge-gs), 1} is one
 // tile of layout L in tile-local order: dims = pad bits [0,a) x 2 doubles, pad bits [a,lk), bits [lk,gs), the group
 // [gs,ge), bits [ge,n_loc).  a = min(lk, 7) keeps the innermost box extent within TMA's 256 elements.
+// A sharded centre group ends above n_loc (its top bits are the rank): the box then covers the LOCAL group bits only,
+// i.e. the slab of the tile that this vector's owner holds.
 static bool encode_tile_map(CUtensorMap* map, const Layout& L, int n_loc, void* base) {
   EncodeTiledFn enc = encode_tiled_fn();
   if (!enc) return false;
   const int a = std::min(L.lk, 7);
-  const cuuint64_t dims[5] = {2ull << a, 1ull << (L.lk - a), 1ull << (L.gs - L.lk), 1ull << (L.ge - L.gs), 1ull << (n_loc - L.ge)};
-  const cuuint64_t strides[4] = {sizeof(cplx) << a, sizeof(cplx) << L.lk, sizeof(cplx) << L.gs, sizeof(cplx) << L.ge};
-  const cuuint32_t box[5] = {2u << a, 1u << (L.lk - a), 1u, 1u << (L.ge - L.gs), 1u};
+  const int ge = std::min(L.ge, n_loc);
+  const cuuint64_t dims[5] = {2ull << a, 1ull << (L.lk - a), 1ull << (L.gs - L.lk), 1ull << (ge - L.gs), 1ull << (n_loc - ge)};
+  const cuuint64_t strides[4] = {sizeof(cplx) << a, sizeof(cplx) << L.lk, sizeof(cplx) << L.gs, sizeof(cplx) << ge};
+  const cuuint32_t box[5] = {2u << a, 1u << (L.lk - a), 1u, 1u << (ge - L.gs), 1u};
   const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   return enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 5, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -350,17 +357,52 @@ static bool ensure_tile_maps(const LargeGeom& g, StridedFusion& fu, cplx* tx, cp
   return true;
 }
 
+static bool ensure_ring_maps(const LargeGeom& g, ShardLink& link) {
+  if (link.ring_ready) return true;
+  const Layout& L = g.lay[g.n_layouts - 1];
+  for (int r = 0; r < g.world; ++r)
+    if (!encode_tile_map(&link.ring_maps[0][r], L, g.n_loc, link.tx[r]) || !encode_tile_map(&link.ring_maps[1][r], L, g.n_loc, link.ty[r]))
+      return false;
+  link.ring_ready = true;
+  return true;
+}
+
+// Opt-in (QSB200_SHARD_RING=1).  Measured on 2 x B200 at N = 28 the ring and the register-staged P2P centre pass are
+// both NVLink-bound (691 vs 703 GB/s per direction, 91 % of the peer-copy peak), so the ring buys nothing there; with
+// one process per GPU (CUDA-IPC mappings) and >= 8 GB vectors its TMA loads from the peers did not complete within
+// the watchdog, while ranks that are threads of one process work at every size (profiles/r1s_shard_ring_experiment.md).
+static bool shard_ring_enabled() {
+  static int on = -1;
+  if (on < 0) { const char* e = std::getenv("QSB200_SHARD_RING"); on = (e && *e == '1') ? 1 : 0; }
+  return on == 1;
+}
+
+template <int W>
+static void launch_centre_ring(const PassArgs& a, const LargeGeom& g, const ShardLink& link, int collect_obs, double* partials,
+                               unsigned n_tiles, cudaStream_t stream) {
+  TmaMaps maps;
+  for (int br = 0; br < 2; ++br) memcpy(maps.m[br], link.ring_maps[br], sizeof(CUtensorMap) * MAX_WORLD);
+  int dev = 0, n_sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+  const int grid = (int)std::min<unsigned>(2u * n_tiles, (unsigned)std::max(1, n_sms));
+  const int threads = FUSED_NG * TPT + 64, centre = g.n_layouts - 1;
+  const unsigned v0 = (unsigned)g.rank * n_tiles;
+  if (collect_obs) pass_centre_ring<W, true><<<grid, threads, sizeof(FusedSmem), stream>>>(a, centre, v0, n_tiles, g.world, maps, partials);
+  else pass_centre_ring<W, false><<<grid, threads, sizeof(FusedSmem), stream>>>(a, centre, v0, n_tiles, g.world, maps, partials);
+}
+
 template <int W>
 static void launch_fused(const PassArgs& a, const StridedFusion& fu, int collect_obs, double* partials, cudaStream_t stream) {
   TmaMaps maps;
-  memcpy(maps.m, fu.maps, sizeof maps.m);
+  for (int br = 0; br < 2; ++br) memcpy(maps.m[br], fu.maps[br], sizeof(CUtensorMap) * MAX_LAYOUTS);
   const int threads = FUSED_NG * TPT + 64;
   if (collect_obs) pass_strided_fused<W, true><<<fu.grid, threads, sizeof(FusedSmem), stream>>>(a, fu.spec, maps, partials, fu.ctrl);
   else pass_strided_fused<W, false><<<fu.grid, threads, sizeof(FusedSmem), stream>>>(a, fu.spec, maps, partials, fu.ctrl);
 }
 
 static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx, cplx* ty, int collect_obs,
-                                 double* partials, cudaStream_t stream, const ShardLink* link, StridedFusion* fu) {
+                                 double* partials, cudaStream_t stream, ShardLink* link, StridedFusion* fu) {
   const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx);
   const unsigned n_tiles = 1u << (g.n_loc - TB);
   const int centre = g.n_layouts - 1;
@@ -390,10 +432,16 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
     if (rc) return rc;
     {
       Timed t(2, stream, 4 * S);
-      PeerPtrs pp = {};
-      for (int r = 0; r < g.world; ++r) { pp.t[0][r] = link->tx[r]; pp.t[1][r] = link->ty[r]; }
-      const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u};
-      launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, stream);
+      const int w = centre_window(g.lay[centre]);
+      if (shard_ring_enabled() && w != 0 && ensure_ring_maps(g, *link)) {
+        if (w == 8) launch_centre_ring<8>(a, g, *link, collect_obs, partials, n_tiles, stream);
+        else launch_centre_ring<4>(a, g, *link, collect_obs, partials, n_tiles, stream);
+      } else {
+        PeerPtrs pp = {};
+        for (int r = 0; r < g.world; ++r) { pp.t[0][r] = link->tx[r]; pp.t[1][r] = link->ty[r]; }
+        const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u};
+        launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, stream);
+      }
     }
     rc = link->sync(link->ctx);
     if (rc) return rc;
@@ -403,7 +451,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
 }
 
 int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
-                  const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream, const ShardLink* link,
+                  const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream, ShardLink* link,
                   const Combine* comb, StridedFusion* fu) {
   const size_t sm2 = (size_t)TILE_PHYS * sizeof(cplx);
   PassArgs a;
@@ -439,7 +487,7 @@ int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cp
 }
 
 int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
-                   double* partials, cudaStream_t stream, const ShardLink* link, StridedFusion* fu) {
+                   double* partials, cudaStream_t stream, ShardLink* link, StridedFusion* fu) {
   // the transform half of an H-apply: z sums in pass_first, x/y sums in pass_centre (tx/ty are clobbered)
   const size_t sm2 = (size_t)TILE_PHYS * sizeof(cplx);
   PassArgs a;

@@ -143,3 +143,24 @@ def test_multi_process_parity_two_gpus():
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert '"ok": true' in res.stdout
+
+
+@pytest.mark.parametrize("n,world", [(16, 2), (19, 4), (21, 8)])
+def test_ring_centre_pass_is_bitwise_the_register_staged_one(n, world):
+    """The TMA-ring version of the sharded centre pass (QSB200_SHARD_RING=1, read once per process) gives the same
+    observables, bit for bit, as the default P2P load/store kernel (ranks = threads on one GPU)."""
+    import json
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for ring in ("0", "1"):
+        env = dict(os.environ, QSB200_SHARD_RING=ring)
+        res = subprocess.run([sys.executable, os.path.join(root, "scripts", "shard_ring_check.py"), "--n", str(n), "--world", str(world)],
+                             capture_output=True, text=True, timeout=300, env=env)
+        assert res.returncode == 0, res.stdout[-1500:] + res.stderr[-1500:]
+        outs.append(json.loads(res.stdout.strip().splitlines()[-1]))
+    assert outs[0]["ring"] == "0" and outs[1]["ring"] == "1"
+    assert outs[0]["obs"] == outs[1]["obs"] and outs[0]["rhs"] == outs[1]["rhs"]
