@@ -209,6 +209,33 @@ __device__ __forceinline__ void smem_store16(cplx* sm, int tt, const cplx (&r)[1
 #pragma unroll
   for (int j = 0; j < 16; ++j) p[j * PhysStride<W>::value] = r[j];
 }
+// The same accesses on an UNPADDED tile (element i at slot i).  Windows [8,12) and [4,8) are conflict-free without
+// the pad (a quarter-warp reads 8 consecutive 16-byte slots); only window [0,4) needs it.  Passes that never touch
+// window [0,4) - every strided pass, whose low >= 4 tile bits are pad bits - use these and 64 KB of shared memory
+// instead of 69.6 KB: two CTAs then fit the 132 KB carve-out step instead of 164 KB, which leaves 32 KB more L1 for
+// loads in flight.
+template <int W>
+__device__ __forceinline__ void tile_load16(const cplx* sm, int tt, cplx (&r)[16]) {
+  const cplx* p = sm + elem<W>(tt, 0);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) r[j] = p[j << W];
+}
+template <int W>
+__device__ __forceinline__ void tile_store16(cplx* sm, int tt, const cplx (&r)[16]) {
+  cplx* p = sm + elem<W>(tt, 0);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) p[j << W] = r[j];
+}
+// PAD selects between the two at compile time
+template <int W, bool PAD>
+__device__ __forceinline__ void any_load16(const cplx* sm, int tt, cplx (&r)[16]) {
+  if constexpr (PAD) smem_load16<W>(sm, tt, r); else tile_load16<W>(sm, tt, r);
+}
+template <int W, bool PAD>
+__device__ __forceinline__ void any_store16(cplx* sm, int tt, const cplx (&r)[16]) {
+  if constexpr (PAD) smem_store16<W>(sm, tt, r); else tile_store16<W>(sm, tt, r);
+}
+
 template <int W, int MODE>
 __device__ __forceinline__ void smem_round(cplx* sm, int tt, int mask) {
   cplx r[16];

@@ -145,19 +145,6 @@ __device__ __forceinline__ void bulk_load(void* dst, const void* src, int bytes,
 }
 __device__ __forceinline__ void group_bar(int g) { asm volatile("bar.sync %0, %1;" ::"r"(1 + g), "r"(TPT) : "memory"); }
 
-template <int W>
-__device__ __forceinline__ void tile_load16(const cplx* sm, int tt, cplx (&r)[16]) {
-  const cplx* p = sm + elem<W>(tt, 0);
-#pragma unroll
-  for (int j = 0; j < 16; ++j) r[j] = p[j << W];
-}
-template <int W>
-__device__ __forceinline__ void tile_store16(cplx* sm, int tt, const cplx (&r)[16]) {
-  cplx* p = sm + elem<W>(tt, 0);
-#pragma unroll
-  for (int j = 0; j < 16; ++j) p[j << W] = r[j];
-}
-
 // block_reduce<2> for one compute group: the same shuffle trees, so the sums are bitwise those of pass_centre
 __device__ __forceinline__ void group_reduce2(double (&v)[2], double* scratch, int tt, int g) {
   const int lane = tt & 31, warp = tt >> 5;

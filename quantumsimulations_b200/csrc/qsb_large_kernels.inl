@@ -115,6 +115,9 @@ pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx
 // ---------------------------------------------------------------------------------------------------
 // pass_mid: in-place Hadamard on one group's bits (layout k, 0 < k < centre).  blockIdx.y = branch.
 // ---------------------------------------------------------------------------------------------------
+// PAD: the tile buffer has the bank-conflict pad (needed only if the layout transforms window [0,4), which no layout
+// built by make_geometry does: groups have at most 8 bits)
+template <bool PAD>
 __global__ void __launch_bounds__(TPT, 2)
 pass_mid(Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -131,13 +134,15 @@ pass_mid(Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty) {
     for (int j = 0; j < 16; ++j) r[j] = p[wo.at(j)];
   }
   bfly16<0>(r, L.m8);
-  smem_store16<8>(sm, tt, r);
+  any_store16<8, PAD>(sm, tt, r);
   __syncthreads();
-  if (L.m0) {
-    smem_round<0, 0>(sm, tt, L.m0);
-    __syncthreads();
+  if constexpr (PAD) {
+    if (L.m0) {
+      smem_round<0, 0>(sm, tt, L.m0);
+      __syncthreads();
+    }
   }
-  smem_load16<4>(sm, tt, r);
+  any_load16<4, PAD>(sm, tt, r);
   bfly16<0>(r, L.m4);
   {
     const unsigned late0 = tm.zero & (unsigned)__double2loint(r[0].x);  // 0, but only known once the data is final
@@ -215,13 +220,14 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
   if constexpr (W == 8) {
     centre_core<8, COLLECT>(r, tt, L.m8, td, ww, L, base, a.g, s);
   } else {
+    constexpr bool PAD = W == 0;  // only window [0,4) needs the padded buffer
     bfly16<0>(r, L.m8);
-    smem_store16<8>(sm, tt, r);
+    any_store16<8, PAD>(sm, tt, r);
     __syncthreads();
     if constexpr (W == 4) {
-      smem_load16<4>(sm, tt, r);
+      tile_load16<4>(sm, tt, r);
       centre_core<4, COLLECT>(r, tt, L.m4, td, ww, L, base, a.g, s);
-      smem_store16<4>(sm, tt, r);
+      tile_store16<4>(sm, tt, r);
     } else {
       smem_round<4, 0>(sm, tt, L.m4);
       __syncthreads();
@@ -232,7 +238,7 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
       smem_round<4, 0>(sm, tt, L.m4);
     }
     __syncthreads();
-    smem_load16<8>(sm, tt, r);
+    any_load16<8, PAD>(sm, tt, r);
     bfly16<0>(r, L.m8);
   }
   {

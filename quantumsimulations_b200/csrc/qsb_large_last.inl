@@ -211,15 +211,24 @@ struct Timed {
 
 template <int W>
 static void set_centre_attrs(int sm) {
-  cudaFuncSetAttribute(pass_centre<false, false, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_centre<false, true, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_centre<true, false, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_centre<true, true, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  tile_kernel_attrs(pass_centre<false, false, W>, sm);
+  tile_kernel_attrs(pass_centre<false, true, W>, sm);
+  tile_kernel_attrs(pass_centre<true, false, W>, sm);
+  tile_kernel_attrs(pass_centre<true, true, W>, sm);
+}
+
+// Shared memory of a strided pass: the padded buffer only if the layout transforms window [0,4).
+static size_t strided_smem(bool pad) { return (size_t)(pad ? TILE_PHYS : TILE) * sizeof(cplx); }
+
+static void launch_mid(const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, unsigned n_tiles, cudaStream_t stream) {
+  if (L.m0) pass_mid<true><<<dim3(n_tiles, 2), TPT, strided_smem(true), stream>>>(L, tm, tx, ty);
+  else pass_mid<false><<<dim3(n_tiles, 2), TPT, strided_smem(false), stream>>>(L, tm, tx, ty);
 }
 
 template <bool SHARDED, int W>
 static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, const PeerPtrs& pp,
                           int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream) {
+  sm = W == 8 ? 0 : strided_smem(W == 0);  // W == 8: the whole group sits in one register window, no staging at all
   if (collect_obs) pass_centre<SHARDED, true, W><<<dim3(n_tiles, 2), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
   else pass_centre<SHARDED, false, W><<<dim3(n_tiles, 2), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
 }
@@ -283,15 +292,23 @@ StridedFusion plan_fusion(const LargeGeom& g, int n_sms) {
   return fu;
 }
 
+// (No carve-out preference is set: the driver's default leaves the rest of the 256 KB to L1, and L1 capacity is what
+// bounds the loads in flight - with the maximum carve-out pass_mid drops from 6.7 to 5.2 TB/s.)
+template <typename K>
+static void tile_kernel_attrs(K kernel, int sm) {
+  cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+}
+
 void prepare_device() {
   const int sm = (int)((size_t)TILE_PHYS * sizeof(cplx));
-  cudaFuncSetAttribute(pass_first<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_first<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_last<0, 8, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_last<1, 4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_last<2, 4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_last<3, 4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
-  cudaFuncSetAttribute(pass_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, sm);
+  tile_kernel_attrs(pass_first<false>, sm);
+  tile_kernel_attrs(pass_first<true>, sm);
+  tile_kernel_attrs(pass_last<0, 8, 0>, sm);
+  tile_kernel_attrs(pass_last<1, 4, 2>, sm);
+  tile_kernel_attrs(pass_last<2, 4, 2>, sm);
+  tile_kernel_attrs(pass_last<3, 4, 2>, sm);
+  tile_kernel_attrs(pass_mid<true>, sm);
+  tile_kernel_attrs(pass_mid<false>, sm);
   set_centre_attrs<8>(sm);
   set_centre_attrs<4>(sm);
   set_centre_attrs<0>(sm);
@@ -411,17 +428,17 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
   if (fu && fu->on && g.world == 1 && centre_window(g.lay[centre]) != 0 && ensure_tile_maps(g, *fu, tx, ty)) {
     // layouts before f stay full-grid launches; f .. centre .. f is one persistent launch
     const int f = fu->spec.f;
-    for (int k = 1; k < f; ++k) { Timed t(1, stream, 4 * S); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+    for (int k = 1; k < f; ++k) { Timed t(1, stream, 4 * S); launch_mid(g.lay[k], all, tx, ty, n_tiles, stream); }
     {
       Timed t(6, stream, 4 * S);
       cudaMemsetAsync(fu->ctrl, 0, fu->ctrl_bytes, stream);
       if (centre_window(g.lay[centre]) == 8) launch_fused<8>(a, *fu, collect_obs, partials, stream);
       else launch_fused<4>(a, *fu, collect_obs, partials, stream);
     }
-    for (int k = f - 1; k >= 1; --k) { Timed t(1, stream, 4 * S); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+    for (int k = f - 1; k >= 1; --k) { Timed t(1, stream, 4 * S); launch_mid(g.lay[k], all, tx, ty, n_tiles, stream); }
     return QSB_OK;
   }
-  for (int k = 1; k < centre; ++k) { Timed t(1, stream, 4 * S); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+  for (int k = 1; k < centre; ++k) { Timed t(1, stream, 4 * S); launch_mid(g.lay[k], all, tx, ty, n_tiles, stream); }
   if (g.world == 1) {
     Timed t(2, stream, 4 * S);
     PeerPtrs none = {};
@@ -446,7 +463,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
     rc = link->sync(link->ctx);
     if (rc) return rc;
   }
-  for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream, 4 * S); pass_mid<<<dim3(n_tiles, 2), TPT, sm1, stream>>>(g.lay[k], all, tx, ty); }
+  for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream, 4 * S); launch_mid(g.lay[k], all, tx, ty, n_tiles, stream); }
   return QSB_OK;
 }
 
