@@ -92,8 +92,14 @@ class ClockSampler:
         mx = [float(r[2]) for r in rows if len(r) >= 8 and r[2].replace(".", "").isdigit()]
         names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
         reasons = sorted({n for r in rows if len(r) >= 8 for n, v in zip(names, r[4:8]) if v == "Active"})
+        pw = []
+        for r in rows:
+            try:
+                pw.append(float(r[3]))
+            except (ValueError, IndexError):
+                pass
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "power_w": statistics.median(pw) if pw else None}
 
 
 def measured_peak():
