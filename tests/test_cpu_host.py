@@ -434,3 +434,74 @@ def test_trajectory_cache_serves_repeated_and_interrupted_sweeps(tmp_path):
     p = DipolarRareParams(n_sea=6, is_spin_three_half=False)
     assert trajectory_key(p) != trajectory_key(dataclasses.replace(p, gamma_sea=np.nextafter(p.gamma_sea, np.inf)))
     assert trajectory_key(p, method="dp5") != trajectory_key(p, method="taylor")
+
+
+# ---- the reference's consumers, unchanged, on the engine's output files -------------------------------------------
+def _load_reference_script(name):
+    """Import one of the reference's report scripts (file names may start with a digit) on the inert plotting stubs."""
+    import importlib.util
+
+    from oracle import ref_loader
+
+    ref_loader.load_reference_sweep()           # fake qutip + inert matplotlib / tkinter on sys.path
+    alias = "ref_" + name.replace("2D", "twoD")
+    spec = importlib.util.spec_from_file_location(alias, os.path.join(ref_loader.REFERENCE_DIR, name + ".py"))
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[alias] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_reference_report_scripts_consume_the_engine_sweep_files(tmp_path):
+    """reprocess_sweep_results.py, reprocess_detuning_sweep_exponential.py and the two 2D_sweep_report*.py scripts
+    (pure file consumers) run UNCHANGED on what run_multi_sweep writes, and the numbers they
+    re-derive from the npz files equal the metrics the engine's driver stored."""
+    from oracle import ref_loader
+
+    if not ref_loader.reference_available():
+        pytest.skip("reference checkout not present")
+    from quantumsimulations_b200.sweep import run_multi_sweep
+
+    with open(os.path.join(GOLDEN, "sweep_small.json")) as f:
+        gp = json.load(f)["summary"]["global_params"]
+    common = dict(f_Az=gp["f_Az_Hz"], gamma_sea=gp["gamma_sea"], gamma_rare=gp["gamma_rare"], n_sea=gp["n_sea"],
+                  t_final=3.0e-3, steps=151, phi_sea=gp["phi_sea_rad"], phi_rare=gp["phi_rare_rad"],
+                  is_spin_three_half=False, solver_atol=gp["solver_atol"], solver_rtol=gp["solver_rtol"],
+                  solver_nsteps=gp["solver_nsteps"], solver_max_step=gp["solver_max_step"], coarse_window=5)
+    f1as = [20e3, 35e3]
+    root = str(tmp_path / "grid")
+    dirs = run_multi_sweep(f1A_values=f1as, detunings_for=lambda f: np.linspace(0.0, 3.0 * f, 3), out_root=root,
+                           simulate_batch=_oracle_batch, timestamp="20250101_000000", verbose=False, **common)
+    mine = {d: json.load(open(os.path.join(d, "summary.json"))) for d in dirs}
+
+    # 2D_sweep_report.py / 2D_sweep_report_stable_region.py: walk the root for summary.json (R2:199-303)
+    for script in ("2D_sweep_report", "2D_sweep_report_stable_region"):
+        r2 = _load_reference_script(script)
+        pts = r2.aggregate_points(root)
+        finite = [(s["global_params"]["f1A_Hz"], r) for s in mine.values() for r in s["sweep_results"]
+                  if np.isfinite(r["DeltaOmega_over_geff"]) and np.isfinite(r["contrast_rare_center"])]
+        assert len(pts) == len(finite) > 0
+        assert sorted({p["f1A_Hz"] for p in pts}) == f1as
+        assert sorted(p["contrast"] for p in pts) == sorted(r["contrast_rare_center"] for _, r in finite)
+    _load_reference_script("2D_sweep_report").make_plots(root, os.path.join(root, "report2d.pdf"))
+
+    # reprocess_sweep_results.py: re-reads summary.json + the three npz per detuning and recomputes the slopes (RS:95-)
+    rs = _load_reference_script("reprocess_sweep_results")
+    rs.reprocess_sweep(dirs[0], window=5)
+    with open(os.path.join(dirs[0], "summary_reprocessed_win5.json")) as f:
+        rep = json.load(f)
+    rows = rep["sweep_results"] if isinstance(rep, dict) else rep
+    assert len(rows) == 3
+    for got, want in zip(rows, mine[dirs[0]]["sweep_results"]):
+        assert got["delta_Hz"] == want["delta_Hz"]
+        for k in ("I_z_slope_off_center", "I_z_slope_on_center", "I_z_slope_off_sea_center"):
+            assert k in got
+            if np.isfinite(want[k]):
+                assert got[k] == pytest.approx(want[k], rel=1e-9, abs=1e-15), k
+
+    # reprocess_detuning_sweep_exponential.py: needs metrics.json + the two centre npz per detuning directory
+    rex = _load_reference_script("reprocess_detuning_sweep_exponential")
+    det_dirs = rex.discover_detuning_dirs(dirs[0])
+    assert len(det_dirs) == 3
+    t, obs = rex.load_npz(det_dirs[0], "center_on")
+    assert t.shape == (151,) and "Iz_sea" in obs
