@@ -277,6 +277,16 @@ def run_b200(args, rank, world, local_rank):
             "moved_frac_of_peak": moved_per_step * args.steps / (ms / 1e3) / 1e9 / peak,
             "dominant_kernel": dominant, "kernels": kernels,
         }
+        # FP64 co-bound: what the three-diagonal-form H-apply actually executes.  Per amplitude and
+        # apply: one complex add per butterfly stage (2 flops) over first 24 + mid 2 x 2 x |g1| + centre 2 x 2 x |g2| +
+        # last 24 stages, three diagonal forms (~10 flops each) and the epilogue (~10).
+        stages = 48 + 4 * (n - 12)
+        flops_apply = (2.0 * stages + 40.0) * (1 << n)
+        fp64_rate = n_rhs * flops_apply * args.steps / (ms / 1e3) / 1e12
+        roofline["fp64"] = {"flops_per_step": n_rhs * flops_apply, "achieved_TFLOPs": fp64_rate, "peak_TFLOPs": 40.0,
+                            "peak_source": "nominal B200 FP64 (datasheet; not measured on this box)",
+                            "frac": fp64_rate / 40.0,
+                            "binding": "hbm" if roofline["moved_frac_of_peak"] > fp64_rate / 40.0 else "fp64"}
     plan.session_end()
     plan.close()
 
