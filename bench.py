@@ -329,6 +329,22 @@ def run_b200(args, rank, world, local_rank):
         sweep_steps = float(tt.item())
         sweep_kernel_ms = allmax(sweep_kernel_ms)
 
+    # ---- C2 at the reference's FULL size (SW:1201-1252: t_final = 30 s, 20000 outputs) on the propagator path ----------
+    full = [sweep_params(6, d, v, t_final=30.0, steps=20000) for d in dets for v in ("center_off", "center_on", "shell_off")]
+    fmine = full[rank::world]
+    barrier()
+    t0 = time.perf_counter()
+    _, pci = simulate_rare_batch(mine, device=local_rank, method="propagator") if mine else ([], [])
+    sweep_prop_ci_s = allmax(time.perf_counter() - t0)
+    barrier()
+    t0 = time.perf_counter()
+    fres, fst = simulate_rare_batch(fmine, device=local_rank, method="propagator", raw_norm=True) if fmine else ([], [])
+    sweep_full_s = allmax(time.perf_counter() - t0)
+    full_kernel_ms = allmax(max([s.device_ms for s in fst], default=0.0))
+    full_rhs = float(sum(s.n_rhs for s in fst))
+    full_norm_dev = max([float(np.max(np.abs(r[1]["raw_norm"] - 1.0))) for r in fres], default=0.0)
+    del fres
+
     # ---- C3 grid (CI-sized window): 19 f1A x 13 detunings x 3 variants, cost-balanced over ranks, no collective ----
     grid = None
     if not args.no_grid:
@@ -348,7 +364,19 @@ def run_b200(args, rank, world, local_rank):
             tt = torch.tensor([gsteps, grhs], dtype=torch.float64, device="cuda")
             dist.all_reduce(tt)
             gsteps, grhs = float(tt[0].item()), float(tt[1].item())
-        grid = {"workload": "C3 (CI-sized): 19 f1A (5..50 kHz) x 13 detunings (0..3 f1A) x 3 variants, N=7, t_final=0.03 s, "
+        # the same grid at the reference's full trajectory size, propagator path
+        gfull = [sweep_params(6, d, v, f1a=f, t_final=30.0, steps=20000) for f in f1as
+                 for d in np.linspace(0.0, 3.0 * f, 13) for v in ("center_off", "center_on", "shell_off")]
+        gfmine = [gfull[i] for i in partition([estimate_cost(p) for p in gfull], world)[rank]]
+        barrier()
+        t0 = time.perf_counter()
+        _, gfst = simulate_rare_batch(gfmine, device=local_rank, method="propagator") if gfmine else ([], [])
+        grid_full_s = allmax(time.perf_counter() - t0)
+        grid_full_kernel_ms = allmax(max([s.device_ms for s in gfst], default=0.0))
+        grid = {"full_size": {"workload": "C3 at the reference's trajectory size (t_final = 30 s, 20000 outputs), "
+                                          "method 'propagator'", "trajectories": len(gfull), "wall_s": grid_full_s,
+                              "kernel_ms": grid_full_kernel_ms},
+                "workload": "C3 (CI-sized): 19 f1A (5..50 kHz) x 13 detunings (0..3 f1A) x 3 variants, N=7, t_final=0.03 s, "
                             "2000 outputs, one CTA per trajectory, API default integrator (Taylor 20)",
                 "trajectories": len(glist), "wall_s": grid_s, "trajectories_per_s": len(glist) / grid_s,
                 "step_attempts": gsteps, "h_applies_per_s": grhs / grid_s,
@@ -382,7 +410,17 @@ def run_b200(args, rank, world, local_rank):
                       "steps_per_s": sweep_steps / sweep_s, "total_steps": sweep_steps,
                       "wall_s_default_integrator": sweep_default_s,
                       "default_integrator": "taylor order 20, atol/rtol x 1e-3 (what simulate_rare runs)",
-                      "cpu_zvode": zv},
+                      "cpu_zvode": zv,
+                      "wall_s_propagator": sweep_prop_ci_s,
+                      "full_size": {
+                          "workload": "C2 at the reference's own size (SW:1201-1252): 13 detunings x 3 variants, N=7, "
+                                      "t_final=30 s, 20000 outputs, atol 1e-10 / rtol 1e-9, max_step 1e-5; method "
+                                      "'propagator' (128 Taylor(20) column trajectories over one output interval per "
+                                      "trajectory, then 19999 on-chip matvecs)",
+                          "trajectories": len(full), "wall_s": sweep_full_s, "kernel_ms": full_kernel_ms,
+                          "column_h_applies": full_rhs, "max_raw_norm_deviation": full_norm_dev,
+                          "cpu_zvode_extrapolated_s_per_trajectory_1core":
+                              (30.0 / zv["window_s"] * zv["n_steps"] / zv["steps_per_s_1core"]) if zv else None}},
             "grid": grid,
             "sharded": sharded,
         }

@@ -75,7 +75,8 @@ typedef struct {
   int64_t n_rhs;     /* H-applies                                              */
   double last_h;
   double device_ms;  /* CUDA-event time of the whole evolve on its stream      */
-  int32_t path;      /* 0 = on-chip small-N kernel, 1 = tiled HBM path         */
+  int32_t path;      /* 0 = on-chip small-N kernel, 1 = tiled HBM path, 2 = on-chip propagator (counters summed
+                        over the 2^n column trajectories that built U)         */
   int32_t status;    /* qsb_status of this trajectory (batch calls)            */
 } qsb_stats;
 
@@ -112,6 +113,27 @@ int qsb_evolve(qsb_plan* plan, uint64_t psi0_index, const double* psi0_host, int
 int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
                      const double* t_out, int32_t t_out_per_traj, const qsb_solver_opts* opts,
                      double* out_obs, qsb_stats* stats, int device);
+
+/* Constant-H propagator path for UNIFORM output grids (n <= QSB_SMALL_MAX_QUBITS, same n in every table of a call).
+ * The reference's grid is np.linspace(0, t_final, steps) (dipolar_ensemble_with_rare.py:626) and its Hamiltonian has
+ * no time dependence (:514, :570), so all output intervals share ONE propagator U = exp(-i H dt):
+ *   1. the 2^n columns of U are integrated over [0, dt] by the adaptive integrator opts[i] (same kernel, same error
+ *      control and nsteps / max_step semantics as qsb_evolve_batch; one CTA per column, all trajectories of the call
+ *      in one launch);
+ *   2. one CTA per trajectory applies psi_k = U psi_{k-1} for k = 1 .. n_out-1 and reduces the observables of every
+ *      psi_k exactly as qsb_evolve_batch reports them (U stays in shared memory / L2).
+ * A 20000-output, 30-second trajectory (sweep_sea_detuning.py:1201-1252) then costs 2^n integrations over 1.5 ms plus
+ * 2 * 10^4 dense 2^n x 2^n matvecs instead of ~10^9 integrator steps.  Output k is the state at t0 + k dt for any
+ * t0; dt is [n_traj] when dt_per_traj != 0, else one shared value.  out_obs: [n_traj][n_out][QSB_NOBS] host.       */
+int qsb_propagate_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
+                        const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, double* out_obs,
+                        qsb_stats* stats, int device);
+/* Step 1 alone, for parity tests: u_host[(j * 2^n + x) * 2 + {0,1}] = re, im of <x| exp(-i H dt) |j>.              */
+int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opts* opts, double* u_host,
+                         qsb_stats* stats, int device);
+/* Host-only: launch shape of step 2 for n qubits, out = {threads, column split, columns of U cached in shared
+ * memory, dynamic shared-memory bytes}.                                                                         */
+int qsb_debug_propagate_shape(int32_t n_qubits, int32_t* out /* [4] */);
 
 /* ---- pieces of the path, exposed for parity tests and the benchmark ---------------------------- */
 /* out = H psi on host vectors of 2^n complex128 (one H-apply through the same kernels evolve uses).  */

@@ -107,6 +107,25 @@ def initial_state_rare(params: DipolarRareParams) -> np.ndarray:
 DEFAULT_METHOD = "taylor"
 DEFAULT_TAYLOR_ORDER = 20
 DEFAULT_TOL_SCALE = {"taylor": 1e-3, "dp5": 1.0}
+# method = "propagator" (or "propagator-dp5"): N <= 10 only.  The reference's output grid is uniform (DE:626) and its
+# H constant, so U = exp(-i H dt) is integrated ONCE (2^N column trajectories over one output interval, by the
+# integrator named after the dash, default taylor) and every output is one dense matvec (engine.propagate_batch).
+# Cheaper than stepping whenever steps - 1 > 2^N; the sweep's own 20000-output, 30 s trajectories (SW:1201-1252) drop
+# from ~10^9 H-applies to 128 integrations over 1.5 ms + 2 x 10^4 matvecs.
+PROPAGATOR = "propagator"
+
+
+def split_method(method: Optional[str]) -> Tuple[str, bool]:
+    """(integrator, use_propagator) from a method string: "taylor", "dp5", "propagator", "propagator-dp5"."""
+    m = method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)
+    if m.startswith(PROPAGATOR):
+        rest = m[len(PROPAGATOR):].lstrip("-")
+        m, prop = (rest or "taylor"), True
+    else:
+        prop = False
+    if m not in DEFAULT_TOL_SCALE:
+        raise ValueError(f"unknown method {method!r}: taylor, dp5, propagator or propagator-dp5")
+    return m, prop
 
 
 def _options_from(params: DipolarRareParams, method: Optional[str], tol_scale: Optional[float] = None
@@ -123,7 +142,7 @@ def _options_from(params: DipolarRareParams, method: Optional[str], tol_scale: O
         o.nsteps = int(params.solver_nsteps)
     if params.solver_max_step is not None:
         o.max_step = params.solver_max_step
-    o.method = method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)
+    o.method = split_method(method)[0]
     o.order = int(os.environ.get("QSB200_TAYLOR_ORDER", str(DEFAULT_TAYLOR_ORDER)))
     if tol_scale is None:
         tol_scale = float(os.environ.get("QSB200_TOL_SCALE", DEFAULT_TOL_SCALE[o.method]))
@@ -152,7 +171,8 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
                   checkpoint: Optional[str] = None, checkpoint_every: int = 16):
     """Time evolution on the B200 engine; returns ``(t, {6 traces + state_norm})`` like DE:611-680.
 
-    ``method``: "taylor" (default, order 20) or "dp5".  ``tol_scale`` multiplies solver_atol/solver_rtol before
+    ``method``: "taylor" (default, order 20), "dp5", or "propagator" / "propagator-dp5" (N <= 10: one propagator per
+    trajectory, then one matvec per output time; see PROPAGATOR).  ``tol_scale`` multiplies solver_atol/solver_rtol before
     they reach the integrator (default 1e-3 for taylor, 1 for dp5; see DEFAULT_TOL_SCALE).
     ``raw_norm=True`` adds the integrator's own norm under an extra key (QuTiP discards it).
     ``checkpoint``: file the tiled path (N >= 11) writes its state to every ``checkpoint_every`` output times and
@@ -162,6 +182,10 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
     t = _check_grid(params)
     table = compile_table(params)
     opts, override = _options_from(params, method, tol_scale)
+    if split_method(method)[1]:
+        obs, stats = _propagate([table], [t], [opts], device)
+        out = _pack(obs[0], override, raw_norm)
+        return (t, out, stats[0]) if return_stats else (t, out)
     with engine.Plan(table, device) as plan:
         if checkpoint is not None and table.n > engine.SMALL_MAX_QUBITS:
             from .checkpoint import evolve_checkpointed
@@ -175,6 +199,16 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
     return t, out
 
 
+def _propagate(tables, grids, opts, device):
+    """Propagator path for trajectories of equal N and equal number of outputs (their dt may differ)."""
+    if tables[0].n > engine.SMALL_MAX_QUBITS:
+        raise ValueError(f"method 'propagator' holds a dense 2^N x 2^N matrix on chip: N <= {engine.SMALL_MAX_QUBITS}")
+    dts = [engine.uniform_step(g) for g in grids]
+    if any(d is None for d in dts):
+        raise ValueError("method 'propagator' needs a uniform output grid")
+    return engine.propagate_batch(tables, len(grids[0]), np.array(dts) if len(dts) > 1 else dts[0], opts, device)
+
+
 def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int = 0, method: Optional[str] = None,
                         tol_scale: Optional[float] = None, raw_norm: bool = False):
     """Independent trajectories; those with N <= 10 share ONE kernel launch (one CTA each)."""
@@ -183,14 +217,20 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
     grids = [_check_grid(p) for p in params_list]
     tables = [compile_table(p) for p in params_list]
     om = [_options_from(p, method, tol_scale) for p in params_list]
+    propagate = split_method(method)[1]
+    if propagate and any(t.n > engine.SMALL_MAX_QUBITS for t in tables):
+        raise ValueError(f"method 'propagator' holds a dense 2^N x 2^N matrix on chip: N <= {engine.SMALL_MAX_QUBITS}")
     small = [i for i in range(n) if tables[i].n <= engine.SMALL_MAX_QUBITS]
     groups: Dict[int, List[int]] = {}
     for i in small:
         groups.setdefault((tables[i].n, len(grids[i])), []).append(i)  # uniform n -> register-resident rows
     stats_out: List = [None] * n
     for _, idxs in groups.items():
-        tgrid = np.stack([grids[i] for i in idxs])
-        obs, stats = engine.evolve_batch([tables[i] for i in idxs], tgrid, [om[i][0] for i in idxs], device)
+        if propagate:
+            obs, stats = _propagate([tables[i] for i in idxs], [grids[i] for i in idxs], [om[i][0] for i in idxs], device)
+        else:
+            tgrid = np.stack([grids[i] for i in idxs])
+            obs, stats = engine.evolve_batch([tables[i] for i in idxs], tgrid, [om[i][0] for i in idxs], device)
         for j, i in enumerate(idxs):
             results[i] = (grids[i], _pack(obs[j], om[i][1], raw_norm))
             stats_out[i] = stats[j]

@@ -292,4 +292,130 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
 
 }  // extern "C"
 
+// Shared body of qsb_propagate_batch / qsb_build_propagator: columns of U = exp(-i H dt) through the on-chip
+// trajectory kernel (one CTA per column), then - when n_out > 0 - the matvec chain with observables.
+static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
+                          const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, double* out_obs,
+                          qsb_stats* stats, double* u_host, int device) {
+  const int n = tables[0].n_qubits;
+  for (int i = 0; i < n_traj; ++i) {
+    int rc = check_table(&tables[i]);
+    if (rc) return rc;
+    if (tables[i].n_qubits > QSB_SMALL_MAX_QUBITS)
+      return fail(QSB_ERR_UNSUPPORTED, "the propagator path handles n_qubits <= " + std::to_string(QSB_SMALL_MAX_QUBITS));
+    if (tables[i].n_qubits != n) return fail(QSB_ERR_BAD_ARG, "the propagator path needs the same n_qubits in every table of a call");
+    rc = check_opts(&opts[i]);
+    if (rc) return rc;
+    if (psi0_index && (psi0_index[i] >> n)) return fail(QSB_ERR_BAD_ARG, "psi0_index out of range");
+    const double h = dt[dt_per_traj ? i : 0];
+    if (!(h > 0.0) || !std::isfinite(h)) return fail(QSB_ERR_BAD_ARG, "dt must be finite and > 0");
+  }
+  int rc = pick_device(device);
+  if (rc) return rc;
+  const size_t dim = (size_t)1 << n;
+  const size_t u_bytes = sizeof(cplx) * dim * dim;
+  // trajectories per pass: keep the propagators of one pass within ~4 GiB
+  int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_traj, ((size_t)4 << 30) / u_bytes));
+
+  SmallDesc* d_desc = nullptr;
+  double *d_t = nullptr, *d_obs = nullptr;
+  SmallStats* d_stats = nullptr;
+  cplx* d_u = nullptr;
+  cudaStream_t st = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  struct Cleanup {
+    SmallDesc*& a; double*& b; double*& c; SmallStats*& d; cplx*& e; cudaStream_t& s; cudaEvent_t &x, &y;
+    ~Cleanup() {
+      cudaFree(a); cudaFree(b); cudaFree(c); cudaFree(d); cudaFree(e);
+      if (x) cudaEventDestroy(x);
+      if (y) cudaEventDestroy(y);
+      if (s) cudaStreamDestroy(s);
+    }
+  } cleanup{d_desc, d_t, d_obs, d_stats, d_u, st, e0, e1};
+  QSB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  QSB_CUDA(cudaEventCreate(&e0));
+  QSB_CUDA(cudaEventCreate(&e1));
+  QSB_CUDA(cudaMalloc(&d_desc, sizeof(SmallDesc) * chunk));
+  QSB_CUDA(cudaMalloc(&d_t, sizeof(double) * 2 * chunk));
+  QSB_CUDA(cudaMalloc(&d_stats, sizeof(SmallStats) * chunk * dim));
+  QSB_CUDA(cudaMalloc(&d_u, u_bytes * chunk));
+  if (n_out > 0) QSB_CUDA(cudaMalloc(&d_obs, sizeof(double) * chunk * n_out * QSB_NOBS));
+
+  std::vector<SmallDesc> descs(chunk);
+  std::vector<double> tp(2 * (size_t)chunk);
+  std::vector<SmallStats> hs((size_t)chunk * dim);
+  int worst = QSB_OK;
+  for (int base = 0; base < n_traj; base += chunk) {
+    const int m = std::min(chunk, n_traj - base);
+    for (int i = 0; i < m; ++i) {
+      compile_small(&tables[base + i], psi0_index ? psi0_index[base + i] : 0, &opts[base + i], 1, &descs[i]);
+      tp[2 * i] = 0.0;
+      tp[2 * i + 1] = dt[dt_per_traj ? base + i : 0];
+    }
+    QSB_CUDA(cudaMemcpyAsync(d_desc, descs.data(), sizeof(SmallDesc) * m, cudaMemcpyHostToDevice, st));
+    QSB_CUDA(cudaMemcpyAsync(d_t, tp.data(), sizeof(double) * 2 * m, cudaMemcpyHostToDevice, st));
+    QSB_CUDA(cudaEventRecord(e0, st));
+    launch_small_columns(d_desc, m, n, d_t, d_stats, d_u, st);
+    QSB_CUDA(cudaGetLastError());
+    if (n_out > 0) {
+      rc = launch_small_propagate(d_desc, m, n, d_u, n_out, d_obs, st);
+      if (rc) return rc;
+    }
+    QSB_CUDA(cudaEventRecord(e1, st));
+    QSB_CUDA(cudaMemcpyAsync(hs.data(), d_stats, sizeof(SmallStats) * m * dim, cudaMemcpyDeviceToHost, st));
+    if (n_out > 0)
+      QSB_CUDA(cudaMemcpyAsync(out_obs + (size_t)base * n_out * QSB_NOBS, d_obs, sizeof(double) * m * n_out * QSB_NOBS,
+                               cudaMemcpyDeviceToHost, st));
+    if (u_host)
+      QSB_CUDA(cudaMemcpyAsync(u_host + 2 * dim * dim * (size_t)base, d_u, u_bytes * m, cudaMemcpyDeviceToHost, st));
+    QSB_CUDA(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    for (int i = 0; i < m; ++i) {
+      qsb_stats acc = {0, 0, 0, 0.0, (double)ms, 2, QSB_OK};
+      for (size_t c = 0; c < dim; ++c) {
+        const SmallStats& s = hs[(size_t)i * dim + c];
+        acc.n_accepted += s.n_accepted; acc.n_rejected += s.n_rejected; acc.n_rhs += s.n_rhs;
+        acc.last_h = s.last_h;
+        if (s.status != QSB_OK && acc.status == QSB_OK) acc.status = s.status;
+      }
+      if (stats) stats[base + i] = acc;
+      if (acc.status != QSB_OK && worst == QSB_OK) {
+        worst = acc.status;
+        g_err = "propagator of trajectory " + std::to_string(base + i) + (acc.status == QSB_ERR_NSTEPS
+                    ? ": more than nsteps internal steps inside one output interval (excess work)"
+                    : ": step size underflow");
+      }
+    }
+  }
+  return worst;
+}
+
+extern "C" {
+
+int qsb_propagate_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
+                        const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, double* out_obs,
+                        qsb_stats* stats, int device) {
+  if (n_traj < 1 || !tables || !psi0_index || !opts || !out_obs || !dt || n_out < 1)
+    return fail(QSB_ERR_BAD_ARG, "qsb_propagate_batch: null argument, n_traj < 1 or n_out < 1");
+  return propagate_impl(n_traj, tables, psi0_index, n_out, dt, dt_per_traj, opts, out_obs, stats, nullptr, device);
+}
+
+int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opts* opts, double* u_host,
+                         qsb_stats* stats, int device) {
+  if (!table || !opts || !u_host) return fail(QSB_ERR_BAD_ARG, "qsb_build_propagator: null argument");
+  return propagate_impl(1, table, nullptr, 0, &dt, 0, opts, nullptr, stats, u_host, device);
+}
+
+int qsb_debug_propagate_shape(int32_t n_qubits, int32_t* out) {
+  if (!out || n_qubits < 1 || n_qubits > QSB_SMALL_MAX_QUBITS) return fail(QSB_ERR_BAD_ARG, "need 1 <= n_qubits <= 10 and out");
+  int th, sp, nc;
+  size_t smem;
+  small_propagate_shape(n_qubits, &th, &sp, &nc, &smem);
+  out[0] = th; out[1] = sp; out[2] = nc; out[3] = (int32_t)smem;
+  return QSB_OK;
+}
+
+}  // extern "C"
+
 #include "qsb_api_session.inl"

@@ -42,6 +42,19 @@ struct SmallStats {
 void launch_small_evolve(const SmallDesc* d_desc, int n_traj, int max_n, int uniform_n, const double* d_t_out,
                          int64_t n_out, double* d_obs, SmallStats* d_stats, cudaStream_t stream);
 
+// Propagator build: CTA b integrates basis state b % 2^n of trajectory b / 2^n (all n_traj tables have exactly n qubits)
+// over [t_pairs[2 traj], t_pairs[2 traj + 1]] and stores its final state in columns[b][0 .. 2^n), so that
+// columns[traj] is U = exp(-i H dt) column-major.  d_stats: [n_traj << n], one per column.  Descriptors must have
+// t_per_traj = 1.
+void launch_small_columns(const SmallDesc* d_desc, int n_traj, int n, const double* d_t_pairs, SmallStats* d_stats,
+                          cplx* d_columns, cudaStream_t stream);
+
+// psi_k = U psi_{k-1} for k < n_out with the observables of every psi_k (one CTA per trajectory, uniform n).
+int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cplx* d_columns, int64_t n_out,
+                           double* d_obs, cudaStream_t stream);
+// Launch shape of the propagate kernel for n qubits (host-only; exposed for tests).
+void small_propagate_shape(int n, int* threads, int* split, int* n_cache, size_t* smem);
+
 // out = H in for one n <= 10 table (test hook: same RHS routine the trajectory kernel uses).
 void launch_small_apply(const SmallDesc* d_desc, int n, const cplx* d_in, cplx* d_out, cudaStream_t stream);
 

@@ -2,14 +2,18 @@
 namespace qsb {
 namespace {
 
-template <class RHS, int MAXT>
+// COL = false: CTA b integrates trajectory b of the batch and reports its observables.
+// COL = true (propagator build): CTA b integrates column b % dim of trajectory b / dim's propagator, i.e. it starts
+// from basis state b % dim, reports no observables and leaves its final state in columns[b][0..dim).
+template <class RHS, int MAXT, bool COL>
 __global__ void __launch_bounds__(MAXT, 1)
 small_evolve_kernel(const SmallDesc* __restrict__ descs, const double* __restrict__ t_out_all, int64_t n_out,
-                    double* __restrict__ obs_all, SmallStats* __restrict__ stats) {
+                    double* __restrict__ obs_all, SmallStats* __restrict__ stats, cplx* __restrict__ columns,
+                    int col_dim) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   SmallShared& sh = *reinterpret_cast<SmallShared*>(smem_raw);
   cplx* buf0 = reinterpret_cast<cplx*>(smem_raw + ((sizeof(SmallShared) + 15) & ~size_t(15)));
-  const int traj = blockIdx.x;
+  const int traj = COL ? (int)(blockIdx.x / (unsigned)col_dim) : (int)blockIdx.x;
   {  // descriptor -> shared
     const int* src = reinterpret_cast<const int*>(descs + traj);
     int* dst = reinterpret_cast<int*>(&sh.d);
@@ -25,13 +29,14 @@ small_evolve_kernel(const SmallDesc* __restrict__ descs, const double* __restric
   double* rms_red = sh.red + 7 * 32 + 8;
   int flip = 0;
   const double* t_out = t_out_all + (d.t_per_traj ? (size_t)traj * n_out : 0);
-  double* obs = obs_all + (size_t)traj * n_out * QSB_NOBS;
+  double* obs = COL ? nullptr : obs_all + (size_t)traj * n_out * QSB_NOBS;
+  const uint32_t psi0 = COL ? blockIdx.x - (unsigned)traj * (unsigned)col_dim : d.psi0;
 
   RHS rhs;
   rhs.setup(d, xs);
 
   const DP5 T = dp5_tableau();
-  cplx y = mk(live && x == d.psi0 ? 1.0 : 0.0, 0.0);
+  cplx y = mk(live && x == psi0 ? 1.0 : 0.0, 0.0);
   cplx k[7];
   double t = t_out[0];
   int64_t n_acc = 0, n_rej = 0, n_rhs = 0;
@@ -45,7 +50,7 @@ small_evolve_kernel(const SmallDesc* __restrict__ descs, const double* __restric
   // output 0 and k1 = f(y0)
   buf0[x] = y;
   __syncthreads();
-  small_observe(buf0, x, live, d, sh.red, obs);
+  if (!COL) small_observe(buf0, x, live, d, sh.red, obs);
   k[0] = rhs(buf0);
   ++n_rhs;
   double h;
@@ -143,16 +148,87 @@ small_evolve_kernel(const SmallDesc* __restrict__ descs, const double* __restric
       }
     }
     if (status != QSB_OK) break;
+    if (COL) continue;
     cplx* b = cur ? buf1 : buf0;
     b[x] = y;
     __syncthreads();
     small_observe(b, x, live, d, sh.red, obs + io * QSB_NOBS);
     cur ^= 1;
   }
+  if (COL && live) columns[(size_t)blockIdx.x * dim + x] = y;
   if (threadIdx.x == 0) {
     SmallStats st;
     st.n_accepted = n_acc; st.n_rejected = n_rej; st.n_rhs = n_rhs; st.last_h = h; st.status = status; st.pad = 0;
-    stats[traj] = st;
+    stats[blockIdx.x] = st;
+  }
+}
+
+// psi_k = U psi_{k-1}, k = 1 .. n_out-1, with the six observables of every psi_k: the constant-H fast path for
+// uniform output grids (the reference's grid is np.linspace(0, t_final, steps), dipolar_ensemble_with_rare.py:626,
+// and its H has no time dependence, :514 / :570).  One CTA per trajectory.  U arrives column-major
+// (ut[j * dim + x] = <x|U|j>, the layout small_evolve_kernel<COL> leaves behind); the first n_cache columns are kept
+// in shared memory, the rest stream from L2 every step.  Thread (x, q) accumulates columns j = q (mod split) of row x;
+// the `split` partial sums of a row are added in q order, so results are bitwise reproducible.
+template <int MAXT>
+__global__ void __launch_bounds__(MAXT, 1)
+small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restrict__ ut_all, int64_t n_out,
+                       double* __restrict__ obs_all, int split, int n_cache) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  SmallShared& sh = *reinterpret_cast<SmallShared*>(smem_raw);
+  const int traj = blockIdx.x;
+  {
+    const int* src = reinterpret_cast<const int*>(descs + traj);
+    int* dst = reinterpret_cast<int*>(&sh.d);
+    for (int i = threadIdx.x; i < (int)(sizeof(SmallDesc) / 4); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  const SmallDesc& d = sh.d;
+  const int n = d.n, dim = 1 << n;
+  cplx* cur = reinterpret_cast<cplx*>(smem_raw + ((sizeof(SmallShared) + 15) & ~size_t(15)));
+  cplx* nxt = cur + dim;
+  cplx* part = nxt + dim;                      // [split][dim]
+  cplx* us = part + (size_t)split * dim;       // [n_cache][dim]
+  const cplx* __restrict__ ut = ut_all + ((size_t)traj << (2 * n));
+  const uint32_t x = threadIdx.x & (dim - 1);
+  const int q = threadIdx.x >> n;
+  const bool worker = q < split;               // idle lanes exist only when dim * split < 32
+  const bool owner = threadIdx.x < (uint32_t)dim;
+  double* obs = obs_all + (size_t)traj * n_out * QSB_NOBS;
+
+  for (int i = threadIdx.x; i < n_cache * dim; i += blockDim.x) us[i] = ut[i];
+  if (owner) cur[x] = mk(x == d.psi0 ? 1.0 : 0.0, 0.0);
+  __syncthreads();
+  small_observe(cur, x, owner, d, sh.red, obs);
+
+  for (int64_t io = 1; io < n_out; ++io) {
+    cplx a0 = mk(0, 0), a1 = mk(0, 0);
+    if (worker) {
+      int j = q;
+      for (; j + split < n_cache; j += 2 * split) {
+        caxpy(a0, us[(size_t)j * dim + x], cur[j]);
+        caxpy(a1, us[(size_t)(j + split) * dim + x], cur[j + split]);
+      }
+      if (j < n_cache) { caxpy(a0, us[(size_t)j * dim + x], cur[j]); j += split; }
+      for (; j + 3 * split < dim; j += 4 * split) {  // four independent L2 loads in flight per thread
+        cplx u0 = __ldg(ut + (size_t)j * dim + x), u1 = __ldg(ut + (size_t)(j + split) * dim + x);
+        cplx u2 = __ldg(ut + (size_t)(j + 2 * split) * dim + x), u3 = __ldg(ut + (size_t)(j + 3 * split) * dim + x);
+        caxpy(a0, u0, cur[j]);
+        caxpy(a1, u1, cur[j + split]);
+        caxpy(a0, u2, cur[j + 2 * split]);
+        caxpy(a1, u3, cur[j + 3 * split]);
+      }
+      for (; j < dim; j += split) caxpy(a0, __ldg(ut + (size_t)j * dim + x), cur[j]);
+      part[(size_t)q * dim + x] = a0 + a1;
+    }
+    __syncthreads();
+    if (owner) {
+      cplx s = part[x];
+      for (int r = 1; r < split; ++r) s = s + part[(size_t)r * dim + x];
+      nxt[x] = s;
+    }
+    __syncthreads();
+    small_observe(nxt, x, owner, d, sh.red, obs + io * QSB_NOBS);
+    cplx* t = cur; cur = nxt; nxt = t;
   }
 }
 
@@ -182,16 +258,17 @@ __global__ void small_apply_kernel(const SmallDesc* __restrict__ desc, const cpl
   if (live) out[x] = mk(-k.y, k.x);  // i * k = H psi
 }
 
-template <class RHS>
-static void launch_evolve_t(const SmallDesc* d_desc, int n_traj, int threads, const double* d_t_out, int64_t n_out,
-                            double* d_obs, SmallStats* d_stats, cudaStream_t stream) {
+// n_ctas = trajectories (COL = false) or trajectories x 2^n columns (COL = true, col_dim = 2^n).
+template <class RHS, bool COL, bool WIDE>
+static void launch_evolve_t(const SmallDesc* d_desc, int n_ctas, int threads, const double* d_t_out, int64_t n_out,
+                            double* d_obs, SmallStats* d_stats, cplx* d_columns, int col_dim, cudaStream_t stream) {
   size_t smem = ((sizeof(SmallShared) + 15) & ~size_t(15)) + 2 * sizeof(cplx) * threads;
-  if (threads > 512)  // 1024-thread CTAs are capped at 64 registers per thread (n = 10 only)
-    small_evolve_kernel<RHS, 1024><<<n_traj, threads, smem, stream>>>(d_desc, d_t_out, n_out, d_obs, d_stats);
-  else if (threads > 256)
-    small_evolve_kernel<RHS, 512><<<n_traj, threads, smem, stream>>>(d_desc, d_t_out, n_out, d_obs, d_stats);
+  if (WIDE && threads > 512)  // 1024-thread CTAs are capped at 64 registers per thread (n = 10 only)
+    small_evolve_kernel<RHS, WIDE ? 1024 : 256, COL><<<n_ctas, threads, smem, stream>>>(d_desc, d_t_out, n_out, d_obs, d_stats, d_columns, col_dim);
+  else if (WIDE && threads > 256)
+    small_evolve_kernel<RHS, WIDE ? 512 : 256, COL><<<n_ctas, threads, smem, stream>>>(d_desc, d_t_out, n_out, d_obs, d_stats, d_columns, col_dim);
   else
-    small_evolve_kernel<RHS, 256><<<n_traj, threads, smem, stream>>>(d_desc, d_t_out, n_out, d_obs, d_stats);
+    small_evolve_kernel<RHS, 256, COL><<<n_ctas, threads, smem, stream>>>(d_desc, d_t_out, n_out, d_obs, d_stats, d_columns, col_dim);
 }
 
 }  // namespace
@@ -204,14 +281,18 @@ void launch_small_apply(const SmallDesc* d_desc, int n, const cplx* d_in, cplx* 
   small_apply_kernel<<<1, threads, smem, stream>>>(d_desc, d_in, d_out, use_reg);
 }
 
-// `uniform_n`: every trajectory of the batch has exactly max_n qubits (required by the register-resident rows).
-void launch_small_evolve(const SmallDesc* d_desc, int n_traj, int max_n, int uniform_n, const double* d_t_out,
-                         int64_t n_out, double* d_obs, SmallStats* d_stats, cudaStream_t stream) {
+template <bool COL>
+static void launch_evolve_any(const SmallDesc* d_desc, int n_ctas, int max_n, int uniform_n, const double* d_t_out,
+                              int64_t n_out, double* d_obs, SmallStats* d_stats, cplx* d_columns, cudaStream_t stream) {
   int threads = 1 << max_n;
   if (threads < 32) threads = 32;
   const bool reg = uniform_n && !getenv("QSB200_SMALL_GENERIC");
-#define QSB_REG_CASE(NB)                                                                                     \
-  case NB: launch_evolve_t<RhsReg<NB>>(d_desc, n_traj, threads, d_t_out, n_out, d_obs, d_stats, stream); return;
+  const int col_dim = 1 << max_n;
+#define QSB_REG_CASE(NB)                                                                                         \
+  case NB:                                                                                                       \
+    launch_evolve_t<RhsReg<NB>, COL, false>(d_desc, n_ctas, threads, d_t_out, n_out, d_obs, d_stats, d_columns,  \
+                                            col_dim, stream);                                                    \
+    return;
   if (reg) {
     switch (max_n) {
       QSB_REG_CASE(2) QSB_REG_CASE(3) QSB_REG_CASE(4) QSB_REG_CASE(5) QSB_REG_CASE(6) QSB_REG_CASE(7) QSB_REG_CASE(8)
@@ -219,7 +300,51 @@ void launch_small_evolve(const SmallDesc* d_desc, int n_traj, int max_n, int uni
     }
   }
 #undef QSB_REG_CASE
-  launch_evolve_t<RhsGeneric>(d_desc, n_traj, threads, d_t_out, n_out, d_obs, d_stats, stream);
+  launch_evolve_t<RhsGeneric, COL, true>(d_desc, n_ctas, threads, d_t_out, n_out, d_obs, d_stats, d_columns, col_dim,
+                                         stream);
+}
+
+// `uniform_n`: every trajectory of the batch has exactly max_n qubits (required by the register-resident rows).
+void launch_small_evolve(const SmallDesc* d_desc, int n_traj, int max_n, int uniform_n, const double* d_t_out,
+                         int64_t n_out, double* d_obs, SmallStats* d_stats, cudaStream_t stream) {
+  launch_evolve_any<false>(d_desc, n_traj, max_n, uniform_n, d_t_out, n_out, d_obs, d_stats, nullptr, stream);
+}
+
+void launch_small_columns(const SmallDesc* d_desc, int n_traj, int n, const double* d_t_pairs, SmallStats* d_stats,
+                          cplx* d_columns, cudaStream_t stream) {
+  launch_evolve_any<true>(d_desc, n_traj << n, n, 1, d_t_pairs, 2, nullptr, d_stats, d_columns, stream);
+}
+
+static constexpr size_t PROPAGATE_SMEM_MAX = 226 * 1024;  // of the 227 KB a CTA may opt in to
+
+void small_propagate_shape(int n, int* threads, int* split, int* n_cache, size_t* smem) {
+  const int dim = 1 << n;
+  int sp = 512 / dim;
+  if (sp < 1) sp = 1;
+  if (sp > dim) sp = dim;
+  int th = dim * sp;
+  if (th < 32) th = 32;
+  const size_t fixed = ((sizeof(SmallShared) + 15) & ~size_t(15)) + (size_t)(2 + sp) * dim * sizeof(cplx);
+  size_t room = (PROPAGATE_SMEM_MAX - fixed) / ((size_t)dim * sizeof(cplx));
+  int nc = room > (size_t)dim ? dim : (int)room;
+  *threads = th; *split = sp; *n_cache = nc;
+  *smem = fixed + (size_t)nc * dim * sizeof(cplx);
+}
+
+int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cplx* d_columns, int64_t n_out,
+                           double* d_obs, cudaStream_t stream) {
+  int threads, split, n_cache;
+  size_t smem;
+  small_propagate_shape(n, &threads, &split, &n_cache, &smem);
+  if (threads > 512) {
+    QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    small_propagate_kernel<1024><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache);
+  } else {
+    QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    small_propagate_kernel<512><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache);
+  }
+  QSB_CUDA(cudaGetLastError());
+  return QSB_OK;
 }
 
 }  // namespace qsb

@@ -60,6 +60,7 @@ EXPORTS = (
     "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather",
+    "qsb_propagate_batch", "qsb_build_propagator", "qsb_debug_propagate_shape",
 )
 
 SHARD_BLOB_BYTES = 96
@@ -91,6 +92,10 @@ def load_library() -> C.CDLL:
     lib.qsb_evolve.argtypes = [vp, C.c_uint64, dp, C.c_int64, dp, C.POINTER(_Opts), dp, C.POINTER(_Stats)]
     lib.qsb_evolve_batch.argtypes = [C.c_int32, C.POINTER(_Table), C.POINTER(C.c_uint64), C.c_int64, dp, C.c_int32,
                                      C.POINTER(_Opts), dp, C.POINTER(_Stats), C.c_int]
+    lib.qsb_propagate_batch.argtypes = [C.c_int32, C.POINTER(_Table), C.POINTER(C.c_uint64), C.c_int64, dp, C.c_int32,
+                                        C.POINTER(_Opts), dp, C.POINTER(_Stats), C.c_int]
+    lib.qsb_build_propagator.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(_Opts), dp, C.POINTER(_Stats), C.c_int]
+    lib.qsb_debug_propagate_shape.argtypes = [C.c_int32, C.POINTER(C.c_int32)]
     lib.qsb_apply_h.argtypes = [vp, dp, dp]
     lib.qsb_session_begin.argtypes = [vp, C.c_uint64, dp, C.c_double, C.POINTER(_Opts)]
     lib.qsb_session_step.argtypes = [vp, C.c_int64, dp, C.POINTER(_Stats), dp]
@@ -383,3 +388,58 @@ def evolve_batch(tables: Sequence[SpinTable], t_out: np.ndarray, opts: Sequence[
     stats = [Stats.from_c(s) for s in cstats]
     _check(code)
     return obs, stats
+
+
+def uniform_step(t_out: np.ndarray, rel: float = 1e-9) -> Optional[float]:
+    """dt when ``t_out`` is a uniform grid (what np.linspace gives, DE:626), else None."""
+    t_out = np.asarray(t_out, dtype=np.float64)
+    if t_out.ndim != 1 or len(t_out) < 2:
+        return None
+    dt = (t_out[-1] - t_out[0]) / (len(t_out) - 1)
+    if not dt > 0.0:
+        return None
+    want = t_out[0] + dt * np.arange(len(t_out))
+    return float(dt) if np.max(np.abs(t_out - want)) <= rel * abs(t_out[-1] - t_out[0]) else None
+
+
+def propagate_batch(tables: Sequence[SpinTable], n_out: int, dt, opts: Sequence[SolverOptions], device: int = 0):
+    """Constant-H propagator path (qsb_propagate_batch): n <= 10, same n in every table, output k = state after k dt.
+    ``dt``: one float or one per trajectory.  Returns (obs [n_traj, n_out, NOBS], [Stats])."""
+    lib = load_library()
+    n = len(tables)
+    if n == 0:
+        return np.empty((0, 0, NOBS)), []
+    dts = np.ascontiguousarray(np.atleast_1d(dt), dtype=np.float64)
+    if dts.shape not in ((1,), (n,)):
+        raise ValueError("dt must be a scalar or one value per trajectory")
+    holders = [_TableHolder(t) for t in tables]
+    ctabs = (_Table * n)(*[h.c for h in holders])
+    psi0 = (C.c_uint64 * n)(*[t.psi0_index for t in tables])
+    copts = (_Opts * n)(*[o.to_c() for o in opts])
+    cstats = (_Stats * n)()
+    obs = np.empty((n, int(n_out), NOBS), dtype=np.float64)
+    code = lib.qsb_propagate_batch(n, ctabs, psi0, int(n_out), _dptr(dts), 1 if (dts.shape == (n,) and n > 1) else 0,
+                                   copts, _dptr(obs), cstats, int(device))
+    stats = [Stats.from_c(s) for s in cstats]
+    _check(code)
+    return obs, stats
+
+
+def build_propagator(table: SpinTable, dt: float, opts: SolverOptions, device: int = 0):
+    """U = exp(-i H dt) as a (2^n, 2^n) complex matrix in the table's own index convention (bit-major), built
+    column by column by the on-chip adaptive integrator (qsb_build_propagator).  Returns (U, Stats)."""
+    lib = load_library()
+    holder = _TableHolder(table)
+    copts = opts.to_c()
+    st = _Stats()
+    ut = np.empty((table.dim, table.dim), dtype=np.complex128)  # ut[j, x] = <x|U|j>
+    _check(lib.qsb_build_propagator(C.byref(holder.c), float(dt), C.byref(copts), _dptr(ut.view(np.float64)),
+                                    C.byref(st), int(device)))
+    return np.ascontiguousarray(ut.T), Stats.from_c(st)
+
+
+def propagate_shape(n_qubits: int):
+    """{threads, split, cached_columns, smem_bytes} of the propagate kernel for n qubits (host-only query)."""
+    out = (C.c_int32 * 4)()
+    _check(load_library().qsb_debug_propagate_shape(int(n_qubits), out))
+    return {"threads": out[0], "split": out[1], "cached_columns": out[2], "smem_bytes": out[3]}

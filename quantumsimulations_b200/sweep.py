@@ -58,18 +58,20 @@ def sweep_point_params(*, n_sea, gamma_sea, gamma_rare, B0_common, B1_sea, B1_ra
     }
 
 
-def _with_cache(batch: BatchFn, cache_dir: Optional[str]) -> BatchFn:
+def _with_cache(batch: BatchFn, cache_dir: Optional[str], method: Optional[str] = None) -> BatchFn:
     if not cache_dir:
         return batch
     from .checkpoint import TrajectoryCache, cached_batch
 
-    return cached_batch(batch, TrajectoryCache(cache_dir))
+    solver = {"method": method} if method else {}  # part of the cache key: different numerics, different entry
+    return cached_batch(batch, TrajectoryCache(cache_dir), **solver)
 
 
-def _default_batch(devices: Optional[Sequence[int]]) -> BatchFn:
+def _default_batch(devices: Optional[Sequence[int]], method: Optional[str] = None) -> BatchFn:
     from .dist import simulate_on_devices
 
-    return lambda plist: simulate_on_devices(plist, devices)
+    kw = {"method": method} if method else {}
+    return lambda plist: simulate_on_devices(plist, devices, **kw)
 
 
 def run_sweep_sea_detuning(
@@ -97,12 +99,14 @@ def run_sweep_sea_detuning(
     timestamp: Optional[str] = None,
     verbose: bool = True,
     cache_dir: Optional[str] = None,
+    method: Optional[str] = None,
     _defer: bool = False,
 ):
     """Reference keyword arguments (SW:356-376) + ``devices`` (GPUs to spread trajectories over),
     ``simulate_batch`` (override of the batch solver: list[params] -> list[(t, obs)]), ``timestamp`` and
     ``cache_dir`` (finished trajectories are kept there, keyed by their parameters, and an interrupted or repeated
-    sweep integrates only what is missing; the reference starts every run from zero, SW:483-485).
+    sweep integrates only what is missing; the reference starts every run from zero, SW:483-485) and ``method``
+    (integrator of the default batch solver: "taylor", "dp5", "propagator" ...; see ``api.simulate_rare``).
     Returns the sweep directory.  (``_defer``: return ``(plist, finish)`` instead of integrating, so that
     ``run_multi_sweep`` can put the trajectories of many sweeps into one batch.)"""
     say = print if verbose else (lambda *a, **k: None)
@@ -175,7 +179,7 @@ def run_sweep_sea_detuning(
     if _defer:
         return plist, finish
     t0 = time.perf_counter()
-    results = _with_cache(simulate_batch or _default_batch(devices), cache_dir)(plist)
+    results = _with_cache(simulate_batch or _default_batch(devices, method), cache_dir, method)(plist)
     say(f"  integrated in {time.perf_counter() - t0:.2f} s", flush=True)
     return finish(results)
 
@@ -234,6 +238,7 @@ def run_multi_sweep(
     timestamp: Optional[str] = None,
     verbose: bool = True,
     cache_dir: Optional[str] = None,
+    method: Optional[str] = None,
     **sweep_kwargs,
 ) -> List[str]:
     """The 2D grid that ``2D_sweep_report.py`` consumes: one detuning sweep per sea drive amplitude f1A, each
@@ -259,7 +264,7 @@ def run_multi_sweep(
         plist.extend(sub)
     say(f"2D grid: {len(parts)} sweeps, {len(plist)} trajectories in one batch", flush=True)
     t0 = time.perf_counter()
-    results = _with_cache(simulate_batch or _default_batch(devices), cache_dir)(plist)
+    results = _with_cache(simulate_batch or _default_batch(devices, method), cache_dir, method)(plist)
     say(f"  integrated in {time.perf_counter() - t0:.2f} s", flush=True)
     return [finish(results[a:a + n]) for a, n, finish in parts]
 

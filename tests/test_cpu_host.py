@@ -505,3 +505,90 @@ def test_reference_report_scripts_consume_the_engine_sweep_files(tmp_path):
     assert len(det_dirs) == 3
     t, obs = rex.load_npz(det_dirs[0], "center_on")
     assert t.shape == (151,) and "Iz_sea" in obs
+
+
+# ---- propagator path: host-side logic (the kernels themselves are covered by tests/test_gpu_propagator.py) -----------
+def test_method_strings_and_uniform_grid_detection(monkeypatch):
+    from quantumsimulations_b200 import api, engine
+
+    monkeypatch.delenv("QSB200_METHOD", raising=False)
+    assert api.split_method(None) == ("taylor", False)
+    assert api.split_method("dp5") == ("dp5", False)
+    assert api.split_method("propagator") == ("taylor", True)
+    assert api.split_method("propagator-dp5") == ("dp5", True)
+    monkeypatch.setenv("QSB200_METHOD", "propagator")
+    assert api.split_method(None) == ("taylor", True)
+    with pytest.raises(ValueError, match="unknown method"):
+        api.split_method("zvode")
+    # np.linspace grids (DE:626) are uniform; anything else is refused by the propagator path
+    assert engine.uniform_step(np.linspace(0.0, 30.0, 20000)) == pytest.approx(30.0 / 19999, rel=1e-14)
+    assert engine.uniform_step(np.linspace(1.0, 1.5, 7)) == pytest.approx(0.5 / 6)
+    assert engine.uniform_step(np.array([0.0, 1.0, 3.0])) is None
+    assert engine.uniform_step(np.array([0.0])) is None
+    # the integrator options of the column trajectories are those of the stepping path
+    p = api.DipolarRareParams(n_sea=6, is_spin_three_half=False, solver_atol=1e-10, solver_rtol=1e-9)
+    o, override = api._options_from(p, "propagator")
+    assert (o.method, o.order, override) == ("taylor", 20, True) and o.atol == pytest.approx(1e-13)
+    o, _ = api._options_from(p, "propagator-dp5")
+    assert o.method == "dp5" and o.atol == 1e-10
+
+
+def test_propagate_kernel_launch_shapes():
+    """Host-only query: threads = 2^n x split (>= 32), split a power of two, cached columns fit the opt-in shared
+    memory, and the whole propagator is cached whenever it fits (n <= 6)."""
+    from quantumsimulations_b200 import engine
+
+    for n in range(1, engine.SMALL_MAX_QUBITS + 1):
+        s = engine.propagate_shape(n)
+        dim = 1 << n
+        assert s["threads"] == max(32, dim * s["split"]) and s["threads"] <= 1024
+        assert s["split"] & (s["split"] - 1) == 0 and 1 <= s["split"] <= dim
+        assert 1 <= s["cached_columns"] <= dim
+        assert s["smem_bytes"] <= 227 * 1024
+        if n <= 6:
+            assert s["cached_columns"] == dim
+    with pytest.raises(ValueError):
+        engine.propagate_shape(11)
+
+
+def test_propagator_needs_small_n_and_no_device_fails_loudly():
+    from quantumsimulations_b200 import DipolarRareParams, engine, simulate_rare, simulate_rare_batch
+
+    big = DipolarRareParams(n_sea=12, is_spin_three_half=False)
+    with pytest.raises(ValueError, match="N <= 10"):
+        simulate_rare(big, method="propagator")
+    with pytest.raises(ValueError, match="N <= 10"):
+        simulate_rare_batch([big], method="propagator")
+    if engine.device_count() == 0:
+        with pytest.raises(engine.EngineError, match="no CUDA device"):
+            simulate_rare(DipolarRareParams(n_sea=6, is_spin_three_half=False), method="propagator")
+
+
+def test_sweep_driver_forwards_method_to_the_batch_solver(tmp_path, monkeypatch):
+    """run_sweep_sea_detuning(method=...) reaches simulate_rare_batch and becomes part of the cache key."""
+    from quantumsimulations_b200 import dist, sweep
+
+    seen = []
+
+    def fake_batch(plist, device=0, **kw):
+        seen.append(kw)
+        return _oracle_batch(plist), [None] * len(plist)
+
+    monkeypatch.setattr("quantumsimulations_b200.api.simulate_rare_batch", fake_batch)
+    with open(os.path.join(GOLDEN, "sweep_small.json")) as f:
+        gp = json.load(f)["summary"]["global_params"]
+    kw = dict(f_Az=gp["f_Az_Hz"], f1A=gp["f1A_Hz"], target_sea_detuning=gp["target_sea_detuning"],
+              gamma_sea=gp["gamma_sea"], gamma_rare=gp["gamma_rare"], sea_detunings_Hz=[0.0, 50e3], n_sea=gp["n_sea"],
+              t_final=1.0e-3, steps=51, phi_sea=gp["phi_sea_rad"], phi_rare=gp["phi_rare_rad"],
+              is_spin_three_half=False, solver_atol=gp["solver_atol"], solver_rtol=gp["solver_rtol"],
+              solver_nsteps=gp["solver_nsteps"], solver_max_step=gp["solver_max_step"], coarse_window=5, verbose=False)
+    cache = str(tmp_path / "cache")
+    sweep.run_sweep_sea_detuning(out_root=str(tmp_path / "a"), method="propagator", cache_dir=cache, **kw)
+    assert seen == [{"method": "propagator"}]
+    n_prop = len(os.listdir(cache))
+    assert n_prop == 6
+    sweep.run_sweep_sea_detuning(out_root=str(tmp_path / "b"), cache_dir=cache, **kw)   # default method: new entries
+    assert seen[1] == {} and len(os.listdir(cache)) == 2 * n_prop
+    sweep.run_sweep_sea_detuning(out_root=str(tmp_path / "c"), method="propagator", cache_dir=cache, **kw)
+    assert len(seen) == 2                                                                 # served from the cache
+    assert dist is not None

@@ -1,0 +1,151 @@
+"""GPU parity of the constant-H propagator path (qsb_propagate_batch / qsb_build_propagator) against the exact
+oracle, the reference-generated goldens and the engine's own stepping integrators."""
+import dataclasses
+
+import numpy as np
+import pytest
+
+from conftest import exact_traces, params_from_meta, random_table
+
+pytestmark = pytest.mark.gpu
+KEYS = ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R")
+TOL = 1e-6  # north_star: <= 1e-6 absolute on the normalised magnetisation traces
+
+
+def _tight(method="taylor"):
+    from quantumsimulations_b200.engine import SolverOptions
+
+    return SolverOptions(atol=1e-13, rtol=1e-12, nsteps=1000000, method=method, order=20 if method == "taylor" else 0)
+
+
+def _dense_h(table):
+    from oracle import dense
+
+    bm = table.bit_major()
+    return np.asarray(dense.csr_from_table(bm["h"], bm["J"]).todense())
+
+
+@pytest.mark.parametrize("n", [2, 3, 5, 7, 8, 9, 10])
+@pytest.mark.parametrize("method", ["taylor", "dp5"])
+def test_propagator_is_exp_minus_iHdt(n, method):
+    """U built column by column on the GPU vs exp(-i H dt) from a dense eigendecomposition; U must be unitary."""
+    from quantumsimulations_b200 import engine
+
+    if method == "dp5" and n > 7:
+        pytest.skip("one integrator is enough for the wide tables")
+    table = random_table(n, 100 + n)
+    H = _dense_h(table)
+    w, v = np.linalg.eigh(H)
+    dt = 4.0 / max(1.0, float(np.max(np.abs(w))))
+    want = (v * np.exp(-1j * w * dt)) @ v.conj().T
+    U, st = engine.build_propagator(table, dt, _tight(method))
+    assert st.path == 2 and st.n_rhs > 0 and st.status == 0
+    assert np.max(np.abs(U - want)) < 1e-9
+    assert np.max(np.abs(U.conj().T @ U - np.eye(table.dim))) < 1e-9
+
+
+@pytest.mark.parametrize("n", [2, 4, 6, 7, 8, 9, 10])
+def test_random_tables_match_exact(n):
+    """Traces of psi_k = U^k psi0 (all three axes populated, random basis state) vs oracle X."""
+    from quantumsimulations_b200 import engine
+
+    tables = [random_table(n, 7 * n + s) for s in range(3)]
+    n_out, dt = 41, 0.11
+    obs, stats = engine.propagate_batch(tables, n_out, dt, [_tight()] * len(tables))
+    t = dt * np.arange(n_out)
+    for table, o, st in zip(tables, obs, stats):
+        want = exact_traces(table, t)
+        for i, k in enumerate(KEYS):
+            assert np.max(np.abs(o[:, i] - want[k])) < 1e-8, (n, k)
+        assert np.all(o[:, 6] == 1.0)
+        assert np.max(np.abs(o[:, 7] - 1.0)) < 1e-9   # raw norm: U is unitary to the integrator's tolerance
+        assert st.path == 2
+
+
+@pytest.mark.parametrize("method", ["propagator", "propagator-dp5"])
+def test_n7_sweep_points_vs_reference_goldens(golden_cases, method):
+    """The sweep's own N = 7 points (reference-built H, exact propagation) through simulate_rare_batch."""
+    from quantumsimulations_b200 import simulate_rare_batch
+
+    meta, arrs = golden_cases
+    names = [k for k in meta if k.startswith("n7_d") and meta[k]["backend"] == "exact"]
+    plist = [params_from_meta(meta[k]) for k in names]
+    if method.endswith("dp5"):
+        plist = [dataclasses.replace(p, solver_atol=1e-13, solver_rtol=1e-12) for p in plist]
+    res, stats = simulate_rare_batch(plist, method=method)
+    for name, (t, out), st in zip(names, res, stats):
+        assert np.array_equal(t, arrs[f"{name}/t"])
+        dev = max(float(np.max(np.abs(out[k] - arrs[f"{name}/{k}"]))) for k in KEYS)
+        assert dev < TOL, f"{name} [{method}]: {dev:.2e} ({st})"
+        assert np.all(out["state_norm"] == 1.0)
+        assert st.path == 2
+
+
+@pytest.mark.parametrize("name", ["n4_fib3_default_opts", "n5_tetra", "n6_fib5_shell_off", "n9_cube", "n7_spin_up_phases"])
+def test_other_geometries(golden_cases, name):
+    from quantumsimulations_b200 import simulate_rare
+
+    meta, arrs = golden_cases
+    p = params_from_meta(meta[name])
+    t, out = simulate_rare(p, method="propagator")
+    dev = max(float(np.max(np.abs(out[k] - arrs[f"{name}/{k}"]))) for k in KEYS)
+    assert dev < (TOL if p.solver_atol is not None else 2e-4)
+    if p.solver_atol is None:
+        assert out["state_norm"].size == 0
+
+
+def test_agrees_with_stepping_integrator(golden_cases):
+    """Same parameters through the stepping Taylor integrator and through the propagator: <= 1e-8 apart."""
+    from quantumsimulations_b200 import simulate_rare
+
+    meta, _ = golden_cases
+    p = params_from_meta(meta["n7_d050k_center_on"])
+    _, a = simulate_rare(p, method="taylor")
+    _, b, st = simulate_rare(p, method="propagator", return_stats=True)
+    assert max(float(np.max(np.abs(a[k] - b[k]))) for k in KEYS) < 1e-8
+    assert st.path == 2
+
+
+def test_full_size_reference_trajectory(golden_cases):
+    """One trajectory at the reference's FULL size (SW:1201-1252: t_final = 30 s, 20000 outputs, atol 1e-10,
+    rtol 1e-9, max_step 1e-5, nsteps 1e7) vs oracle X; ~10^9 integrator steps for QuTiP, 128 short integrations +
+    19999 matvecs here."""
+    from quantumsimulations_b200 import compile_table, simulate_rare
+
+    meta, _ = golden_cases
+    p = dataclasses.replace(params_from_meta(meta["n7_d050k_center_on"]), t_final=30.0, steps=20000,
+                            solver_atol=1e-10, solver_rtol=1e-9, solver_nsteps=10_000_000, solver_max_step=1e-5)
+    t, out, st = simulate_rare(p, method="propagator", return_stats=True, raw_norm=True)
+    want = exact_traces(compile_table(p), t)
+    dev = max(float(np.max(np.abs(out[k] - want[k]))) for k in KEYS)
+    assert dev < TOL, f"{dev:.2e} {st}"
+    assert np.max(np.abs(out["raw_norm"] - 1.0)) < 1e-7
+
+
+def test_per_trajectory_dt_and_determinism():
+    from quantumsimulations_b200 import engine
+
+    tables = [random_table(6, 40 + s) for s in range(4)]
+    dts = np.array([0.05, 0.1, 0.2, 0.07])
+    a, _ = engine.propagate_batch(tables, 25, dts, [_tight()] * 4)
+    b, _ = engine.propagate_batch(tables, 25, dts, [_tight()] * 4)
+    assert np.array_equal(a, b)
+    for i in range(4):
+        one, _ = engine.propagate_batch([tables[i]], 25, float(dts[i]), [_tight()])
+        assert np.array_equal(one[0], a[i])
+        want = exact_traces(tables[i], dts[i] * np.arange(25))
+        assert max(float(np.max(np.abs(a[i][:, j] - want[k]))) for j, k in enumerate(KEYS)) < 1e-8
+
+
+def test_errors():
+    from quantumsimulations_b200 import DipolarRareParams, engine, simulate_rare
+    from quantumsimulations_b200.engine import IntegratorError, SolverOptions
+
+    with pytest.raises(ValueError, match="same n_qubits"):
+        engine.propagate_batch([random_table(4, 1), random_table(5, 2)], 5, 0.1, [_tight()] * 2)
+    with pytest.raises(ValueError, match="dt must be"):
+        engine.propagate_batch([random_table(4, 1)], 5, -1.0, [_tight()])
+    with pytest.raises(IntegratorError):
+        engine.propagate_batch([random_table(6, 3)], 5, 50.0, [SolverOptions(atol=1e-12, rtol=1e-11, nsteps=3)])
+    with pytest.raises(ValueError, match="N <= 10"):
+        simulate_rare(DipolarRareParams(n_sea=12, is_spin_three_half=False), method="propagator")
