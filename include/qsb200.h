@@ -117,20 +117,24 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
 /* Constant-H propagator path for UNIFORM output grids (n <= QSB_SMALL_MAX_QUBITS, same n in every table of a call).
  * The reference's grid is np.linspace(0, t_final, steps) (dipolar_ensemble_with_rare.py:626) and its Hamiltonian has
  * no time dependence (:514, :570), so all output intervals share ONE propagator U = exp(-i H dt):
- *   1. the 2^n columns of U are integrated over [0, dt] by the adaptive integrator opts[i] (same kernel, same error
- *      control and nsteps / max_step semantics as qsb_evolve_batch; one CTA per column, all trajectories of the call
- *      in one launch);
+ *   1. the 2^n columns of exp(-i H dt / 2^s) are integrated by the adaptive integrator opts[i] (same kernel, same
+ *      error control and nsteps / max_step semantics as qsb_evolve_batch; one CTA per column, all trajectories of the
+ *      call in one launch), and the matrix is squared s times on chip (scaling and squaring).  s is chosen per
+ *      trajectory so that ||H|| dt / 2^s <= ~8 (qsb_debug_squarings), capped by max_squarings (< 0: no cap; 0: the
+ *      columns are integrated over the whole interval);
  *   2. one CTA per trajectory applies psi_k = U psi_{k-1} for k = 1 .. n_out-1 and reduces the observables of every
  *      psi_k exactly as qsb_evolve_batch reports them (U stays in shared memory / L2).
- * A 20000-output, 30-second trajectory (sweep_sea_detuning.py:1201-1252) then costs 2^n integrations over 1.5 ms plus
- * 2 * 10^4 dense 2^n x 2^n matvecs instead of ~10^9 integrator steps.  Output k is the state at t0 + k dt for any
+ * A 20000-output, 30-second trajectory (sweep_sea_detuning.py:1201-1252) then costs 2^n integrations over a few
+ * integrator steps, ~10 dense squarings and 2 * 10^4 dense 2^n x 2^n matvecs instead of ~10^9 integrator steps.  Output k is the state at t0 + k dt for any
  * t0; dt is [n_traj] when dt_per_traj != 0, else one shared value.  out_obs: [n_traj][n_out][QSB_NOBS] host.       */
 int qsb_propagate_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
-                        const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, double* out_obs,
-                        qsb_stats* stats, int device);
+                        const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
+                        double* out_obs, qsb_stats* stats, int device);
 /* Step 1 alone, for parity tests: u_host[(j * 2^n + x) * 2 + {0,1}] = re, im of <x| exp(-i H dt) |j>.              */
-int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opts* opts, double* u_host,
-                         qsb_stats* stats, int device);
+int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opts* opts, int32_t max_squarings,
+                         double* u_host, qsb_stats* stats, int device);
+/* Host-only: the number of squarings step 1 uses for this table and interval when max_squarings < 0.               */
+int qsb_debug_squarings(const qsb_table* table, double dt, int32_t* n_squarings);
 /* Host-only: launch shape of step 2 for n qubits, out = {threads, column split, columns of U cached in shared
  * memory, dynamic shared-memory bytes}.                                                                         */
 int qsb_debug_propagate_shape(int32_t n_qubits, int32_t* out /* [4] */);

@@ -113,6 +113,10 @@ DEFAULT_TOL_SCALE = {"taylor": 1e-3, "dp5": 1.0}
 # Cheaper than stepping whenever steps - 1 > 2^N; the sweep's own 20000-output, 30 s trajectories (SW:1201-1252) drop
 # from ~10^9 H-applies to 128 integrations over 1.5 ms + 2 x 10^4 matvecs.
 PROPAGATOR = "propagator"
+# The propagator's error is applied steps - 1 times, so the columns are integrated tighter than a stepped trajectory
+# would be: measured at the reference's full size (20000 applications) tol x 1e-3 leaves 2.3e-6 on the traces, and the
+# Taylor pair's cost grows only logarithmically with the tolerance.
+PROPAGATOR_TOL_SCALE = {"taylor": 1e-5, "dp5": 1.0}
 
 
 def split_method(method: Optional[str]) -> Tuple[str, bool]:
@@ -145,7 +149,8 @@ def _options_from(params: DipolarRareParams, method: Optional[str], tol_scale: O
     o.method = split_method(method)[0]
     o.order = int(os.environ.get("QSB200_TAYLOR_ORDER", str(DEFAULT_TAYLOR_ORDER)))
     if tol_scale is None:
-        tol_scale = float(os.environ.get("QSB200_TOL_SCALE", DEFAULT_TOL_SCALE[o.method]))
+        table = PROPAGATOR_TOL_SCALE if split_method(method)[1] else DEFAULT_TOL_SCALE
+        tol_scale = float(os.environ.get("QSB200_TOL_SCALE", table[o.method]))
     o.atol = max(o.atol * tol_scale, 1e-300)
     o.rtol = max(o.rtol * tol_scale, 1e-14) if o.rtol > 0 else 0.0
     return o, override

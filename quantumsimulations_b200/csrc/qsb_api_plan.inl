@@ -294,9 +294,30 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
 
 // Shared body of qsb_propagate_batch / qsb_build_propagator: columns of U = exp(-i H dt) through the on-chip
 // trajectory kernel (one CTA per column), then - when n_out > 0 - the matvec chain with observables.
+// Upper bound on ||H||: every one-site operator has norm 1/2, every pair product 1/4.
+static double table_norm_bound(const qsb_table* t) {
+  const int n = t->n_qubits;
+  double s = 0.0;
+  for (int a = 0; a < 3; ++a)
+    for (int b = 0; b < n; ++b) {
+      s += 0.5 * std::fabs(t->h[a * n + b]);
+      for (int c = b + 1; c < n; ++c) s += 0.25 * std::fabs(t->J[((size_t)a * n + b) * n + c]);
+    }
+  return s;
+}
+
+// Squarings for one propagator: the columns are integrated over dt / 2^s with ||H|| dt / 2^s <= ~8 (a handful of
+// Taylor(20) steps, enough for the controller to settle), then U is squared s times.
+static int auto_squarings(const qsb_table* t, double dt) {
+  const double x = table_norm_bound(t) * dt / 8.0;
+  int s = 0;
+  while (s < 40 && std::ldexp(1.0, s) < x) ++s;
+  return s;
+}
+
 static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
-                          const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, double* out_obs,
-                          qsb_stats* stats, double* u_host, int device) {
+                          const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
+                          double* out_obs, qsb_stats* stats, double* u_host, int device) {
   const int n = tables[0].n_qubits;
   for (int i = 0; i < n_traj; ++i) {
     int rc = check_table(&tables[i]);
@@ -320,18 +341,28 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
   SmallDesc* d_desc = nullptr;
   double *d_t = nullptr, *d_obs = nullptr;
   SmallStats* d_stats = nullptr;
-  cplx* d_u = nullptr;
+  cplx *d_u = nullptr, *d_tmp = nullptr;
+  int32_t* d_sq = nullptr;
   cudaStream_t st = nullptr;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   struct Cleanup {
-    SmallDesc*& a; double*& b; double*& c; SmallStats*& d; cplx*& e; cudaStream_t& s; cudaEvent_t &x, &y;
+    SmallDesc*& a; double*& b; double*& c; SmallStats*& d; cplx*& e; cplx*& f; int32_t*& g; cudaStream_t& s;
+    cudaEvent_t &x, &y;
     ~Cleanup() {
-      cudaFree(a); cudaFree(b); cudaFree(c); cudaFree(d); cudaFree(e);
+      cudaFree(a); cudaFree(b); cudaFree(c); cudaFree(d); cudaFree(e); cudaFree(f); cudaFree(g);
       if (x) cudaEventDestroy(x);
       if (y) cudaEventDestroy(y);
       if (s) cudaStreamDestroy(s);
     }
-  } cleanup{d_desc, d_t, d_obs, d_stats, d_u, st, e0, e1};
+  } cleanup{d_desc, d_t, d_obs, d_stats, d_u, d_tmp, d_sq, st, e0, e1};
+  std::vector<int32_t> n_sq(n_traj, 0);
+  bool any_sq = false;
+  for (int i = 0; i < n_traj; ++i) {
+    int s = max_squarings == 0 ? 0 : auto_squarings(&tables[i], dt[dt_per_traj ? i : 0]);
+    if (max_squarings > 0 && s > max_squarings) s = max_squarings;
+    n_sq[i] = s;
+    any_sq = any_sq || s > 0;
+  }
   QSB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
   QSB_CUDA(cudaEventCreate(&e0));
   QSB_CUDA(cudaEventCreate(&e1));
@@ -339,6 +370,10 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
   QSB_CUDA(cudaMalloc(&d_t, sizeof(double) * 2 * chunk));
   QSB_CUDA(cudaMalloc(&d_stats, sizeof(SmallStats) * chunk * dim));
   QSB_CUDA(cudaMalloc(&d_u, u_bytes * chunk));
+  if (any_sq) {
+    QSB_CUDA(cudaMalloc(&d_tmp, u_bytes * chunk));
+    QSB_CUDA(cudaMalloc(&d_sq, sizeof(int32_t) * chunk));
+  }
   if (n_out > 0) QSB_CUDA(cudaMalloc(&d_obs, sizeof(double) * chunk * n_out * QSB_NOBS));
 
   std::vector<SmallDesc> descs(chunk);
@@ -350,13 +385,19 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
     for (int i = 0; i < m; ++i) {
       compile_small(&tables[base + i], psi0_index ? psi0_index[base + i] : 0, &opts[base + i], 1, &descs[i]);
       tp[2 * i] = 0.0;
-      tp[2 * i + 1] = dt[dt_per_traj ? base + i : 0];
+      tp[2 * i + 1] = std::ldexp(dt[dt_per_traj ? base + i : 0], -n_sq[base + i]);
     }
+    if (any_sq)
+      QSB_CUDA(cudaMemcpyAsync(d_sq, n_sq.data() + base, sizeof(int32_t) * m, cudaMemcpyHostToDevice, st));
     QSB_CUDA(cudaMemcpyAsync(d_desc, descs.data(), sizeof(SmallDesc) * m, cudaMemcpyHostToDevice, st));
     QSB_CUDA(cudaMemcpyAsync(d_t, tp.data(), sizeof(double) * 2 * m, cudaMemcpyHostToDevice, st));
     QSB_CUDA(cudaEventRecord(e0, st));
     launch_small_columns(d_desc, m, n, d_t, d_stats, d_u, st);
     QSB_CUDA(cudaGetLastError());
+    if (any_sq) {
+      launch_small_square(d_u, d_tmp, d_sq, m, n, st);
+      QSB_CUDA(cudaGetLastError());
+    }
     if (n_out > 0) {
       rc = launch_small_propagate(d_desc, m, n, d_u, n_out, d_obs, st);
       if (rc) return rc;
@@ -394,17 +435,26 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
 extern "C" {
 
 int qsb_propagate_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
-                        const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, double* out_obs,
-                        qsb_stats* stats, int device) {
+                        const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
+                        double* out_obs, qsb_stats* stats, int device) {
   if (n_traj < 1 || !tables || !psi0_index || !opts || !out_obs || !dt || n_out < 1)
     return fail(QSB_ERR_BAD_ARG, "qsb_propagate_batch: null argument, n_traj < 1 or n_out < 1");
-  return propagate_impl(n_traj, tables, psi0_index, n_out, dt, dt_per_traj, opts, out_obs, stats, nullptr, device);
+  return propagate_impl(n_traj, tables, psi0_index, n_out, dt, dt_per_traj, opts, max_squarings, out_obs, stats, nullptr,
+                        device);
 }
 
-int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opts* opts, double* u_host,
-                         qsb_stats* stats, int device) {
+int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opts* opts, int32_t max_squarings,
+                         double* u_host, qsb_stats* stats, int device) {
   if (!table || !opts || !u_host) return fail(QSB_ERR_BAD_ARG, "qsb_build_propagator: null argument");
-  return propagate_impl(1, table, nullptr, 0, &dt, 0, opts, nullptr, stats, u_host, device);
+  return propagate_impl(1, table, nullptr, 0, &dt, 0, opts, max_squarings, nullptr, stats, u_host, device);
+}
+
+int qsb_debug_squarings(const qsb_table* table, double dt, int32_t* n_squarings) {
+  if (!n_squarings) return fail(QSB_ERR_BAD_ARG, "null argument");
+  int rc = check_table(table);
+  if (rc) return rc;
+  *n_squarings = auto_squarings(table, dt);
+  return QSB_OK;
 }
 
 int qsb_debug_propagate_shape(int32_t n_qubits, int32_t* out) {

@@ -49,6 +49,10 @@ void launch_small_evolve(const SmallDesc* d_desc, int n_traj, int max_n, int uni
 void launch_small_columns(const SmallDesc* d_desc, int n_traj, int n, const double* d_t_pairs, SmallStats* d_stats,
                           cplx* d_columns, cudaStream_t stream);
 
+// columns[traj] <- columns[traj]^(2^n_sq[traj]) (dense complex matrix squarings, one CTA per trajectory);
+// d_tmp: scratch of the same size as d_columns.
+void launch_small_square(cplx* d_columns, cplx* d_tmp, const int32_t* d_n_sq, int n_traj, int n, cudaStream_t stream);
+
 // psi_k = U psi_{k-1} for k < n_out with the observables of every psi_k (one CTA per trajectory, uniform n).
 int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cplx* d_columns, int64_t n_out,
                            double* d_obs, cudaStream_t stream);

@@ -167,9 +167,10 @@ small_evolve_kernel(const SmallDesc* __restrict__ descs, const double* __restric
 // uniform output grids (the reference's grid is np.linspace(0, t_final, steps), dipolar_ensemble_with_rare.py:626,
 // and its H has no time dependence, :514 / :570).  One CTA per trajectory.  U arrives column-major
 // (ut[j * dim + x] = <x|U|j>, the layout small_evolve_kernel<COL> leaves behind); the first n_cache columns are kept
-// in shared memory, the rest stream from L2 every step.  Thread (x, q) accumulates columns j = q (mod split) of row x;
+// in shared memory, each thread keeps its next NREG columns in registers (at n = 7 that is all of U: 104 + 4 x 6), and
+// whatever is left streams from L2 every step.  Thread (x, q) accumulates columns j = q (mod split) of row x;
 // the `split` partial sums of a row are added in q order, so results are bitwise reproducible.
-template <int MAXT>
+template <int MAXT, int NREG>
 __global__ void __launch_bounds__(MAXT, 1)
 small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restrict__ ut_all, int64_t n_out,
                        double* __restrict__ obs_all, int split, int n_cache) {
@@ -197,6 +198,15 @@ small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restri
 
   for (int i = threadIdx.x; i < n_cache * dim; i += blockDim.x) us[i] = ut[i];
   if (owner) cur[x] = mk(x == d.psi0 ? 1.0 : 0.0, 0.0);
+  // first column of this thread that is not in shared memory, and the register-resident columns from there on
+  int j_tail = q;
+  while (j_tail < n_cache) j_tail += split;
+  cplx ureg[NREG > 0 ? NREG : 1];
+#pragma unroll
+  for (int r = 0; r < NREG; ++r) {
+    const int j = j_tail + r * split;
+    ureg[r] = (worker && j < dim) ? ut[(size_t)j * dim + x] : mk(0, 0);
+  }
   __syncthreads();
   small_observe(cur, x, owner, d, sh.red, obs);
 
@@ -209,6 +219,11 @@ small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restri
         caxpy(a1, us[(size_t)(j + split) * dim + x], cur[j + split]);
       }
       if (j < n_cache) { caxpy(a0, us[(size_t)j * dim + x], cur[j]); j += split; }
+#pragma unroll
+      for (int r = 0; r < NREG; ++r) {
+        if (j < dim) caxpy((r & 1) ? a1 : a0, ureg[r], cur[j]);
+        j += split;
+      }
       for (; j + 3 * split < dim; j += 4 * split) {  // four independent L2 loads in flight per thread
         cplx u0 = __ldg(ut + (size_t)j * dim + x), u1 = __ldg(ut + (size_t)(j + split) * dim + x);
         cplx u2 = __ldg(ut + (size_t)(j + 2 * split) * dim + x), u3 = __ldg(ut + (size_t)(j + 3 * split) * dim + x);
@@ -229,6 +244,46 @@ small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restri
     __syncthreads();
     small_observe(nxt, x, owner, d, sh.red, obs + io * QSB_NOBS);
     cplx* t = cur; cur = nxt; nxt = t;
+  }
+}
+
+// U <- U^(2^s): s = n_sq[traj] in-place squarings of one column-major propagator per CTA (scaling and squaring: the
+// columns were integrated over dt / 2^s only).  C[x][j] = sum_k A[x][k] A[k][j]; thread (x, q) owns row x of the
+// columns j = 4 (q + split i) .. +3, so the A[x][k] load is coalesced over x and shared by four accumulators while
+// A[k][j] is a warp-uniform load; both operands stay in L1/L2 (the matrix is 256 KB at n = 7).  The two buffers
+// swap roles after every squaring; results land back in `u_all`.  No __restrict__ / __ldg: the kernel reads what its
+// own CTA wrote before the last barrier.
+template <int MAXT>
+__global__ void __launch_bounds__(MAXT, 1)
+small_square_kernel(cplx* u_all, cplx* tmp_all, const int32_t* __restrict__ n_sq, int n, int split) {
+  const int dim = 1 << n;
+  const size_t off = (size_t)blockIdx.x << (2 * n);
+  cplx* a = u_all + off;
+  cplx* b = tmp_all + off;
+  const int x = threadIdx.x & (dim - 1);
+  const int q = threadIdx.x >> n;
+  const int s_total = n_sq[blockIdx.x];
+  for (int s = 0; s < s_total; ++s) {
+    if (q < split) {
+      for (int j0 = 4 * q; j0 < dim; j0 += 4 * split) {
+        cplx acc[4] = {mk(0, 0), mk(0, 0), mk(0, 0), mk(0, 0)};
+#pragma unroll 4
+        for (int k = 0; k < dim; ++k) {
+          const cplx ax = a[(size_t)k * dim + x];
+#pragma unroll
+          for (int r = 0; r < 4; ++r)
+            if (j0 + r < dim) caxpy(acc[r], ax, a[(size_t)(j0 + r) * dim + k]);
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+          if (j0 + r < dim) b[(size_t)(j0 + r) * dim + x] = acc[r];
+      }
+    }
+    __syncthreads();
+    cplx* t = a; a = b; b = t;
+  }
+  if (s_total & 1) {  // the result sits in tmp: copy it home
+    for (int i = threadIdx.x; i < dim * dim; i += blockDim.x) b[i] = a[i];
   }
 }
 
@@ -331,17 +386,27 @@ void small_propagate_shape(int n, int* threads, int* split, int* n_cache, size_t
   *smem = fixed + (size_t)nc * dim * sizeof(cplx);
 }
 
+void launch_small_square(cplx* d_columns, cplx* d_tmp, const int32_t* d_n_sq, int n_traj, int n, cudaStream_t stream) {
+  int threads, split, n_cache;
+  size_t smem;
+  small_propagate_shape(n, &threads, &split, &n_cache, &smem);
+  if (threads > 512)
+    small_square_kernel<1024><<<n_traj, threads, 0, stream>>>(d_columns, d_tmp, d_n_sq, n, split);
+  else
+    small_square_kernel<512><<<n_traj, threads, 0, stream>>>(d_columns, d_tmp, d_n_sq, n, split);
+}
+
 int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cplx* d_columns, int64_t n_out,
                            double* d_obs, cudaStream_t stream) {
   int threads, split, n_cache;
   size_t smem;
   small_propagate_shape(n, &threads, &split, &n_cache, &smem);
   if (threads > 512) {
-    QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_propagate_kernel<1024><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache);
+    QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<1024, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    small_propagate_kernel<1024, 0><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache);
   } else {
-    QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_propagate_kernel<512><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache);
+    QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    small_propagate_kernel<512, 8><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache);
   }
   QSB_CUDA(cudaGetLastError());
   return QSB_OK;

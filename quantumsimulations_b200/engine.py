@@ -60,7 +60,7 @@ EXPORTS = (
     "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather",
-    "qsb_propagate_batch", "qsb_build_propagator", "qsb_debug_propagate_shape",
+    "qsb_propagate_batch", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
 )
 
 SHARD_BLOB_BYTES = 96
@@ -93,8 +93,10 @@ def load_library() -> C.CDLL:
     lib.qsb_evolve_batch.argtypes = [C.c_int32, C.POINTER(_Table), C.POINTER(C.c_uint64), C.c_int64, dp, C.c_int32,
                                      C.POINTER(_Opts), dp, C.POINTER(_Stats), C.c_int]
     lib.qsb_propagate_batch.argtypes = [C.c_int32, C.POINTER(_Table), C.POINTER(C.c_uint64), C.c_int64, dp, C.c_int32,
-                                        C.POINTER(_Opts), dp, C.POINTER(_Stats), C.c_int]
-    lib.qsb_build_propagator.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(_Opts), dp, C.POINTER(_Stats), C.c_int]
+                                        C.POINTER(_Opts), C.c_int32, dp, C.POINTER(_Stats), C.c_int]
+    lib.qsb_build_propagator.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(_Opts), C.c_int32, dp,
+                                         C.POINTER(_Stats), C.c_int]
+    lib.qsb_debug_squarings.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(C.c_int32)]
     lib.qsb_debug_propagate_shape.argtypes = [C.c_int32, C.POINTER(C.c_int32)]
     lib.qsb_apply_h.argtypes = [vp, dp, dp]
     lib.qsb_session_begin.argtypes = [vp, C.c_uint64, dp, C.c_double, C.POINTER(_Opts)]
@@ -402,9 +404,15 @@ def uniform_step(t_out: np.ndarray, rel: float = 1e-9) -> Optional[float]:
     return float(dt) if np.max(np.abs(t_out - want)) <= rel * abs(t_out[-1] - t_out[0]) else None
 
 
-def propagate_batch(tables: Sequence[SpinTable], n_out: int, dt, opts: Sequence[SolverOptions], device: int = 0):
+def _max_squarings(value: Optional[int]) -> int:
+    return int(os.environ.get("QSB200_PROP_SQUARINGS", "-1")) if value is None else int(value)
+
+
+def propagate_batch(tables: Sequence[SpinTable], n_out: int, dt, opts: Sequence[SolverOptions], device: int = 0,
+                    max_squarings: Optional[int] = None):
     """Constant-H propagator path (qsb_propagate_batch): n <= 10, same n in every table, output k = state after k dt.
-    ``dt``: one float or one per trajectory.  Returns (obs [n_traj, n_out, NOBS], [Stats])."""
+    ``dt``: one float or one per trajectory.  ``max_squarings``: cap on the scaling-and-squaring depth (None / < 0:
+    automatic, 0: integrate the columns over the whole dt).  Returns (obs [n_traj, n_out, NOBS], [Stats])."""
     lib = load_library()
     n = len(tables)
     if n == 0:
@@ -419,13 +427,14 @@ def propagate_batch(tables: Sequence[SpinTable], n_out: int, dt, opts: Sequence[
     cstats = (_Stats * n)()
     obs = np.empty((n, int(n_out), NOBS), dtype=np.float64)
     code = lib.qsb_propagate_batch(n, ctabs, psi0, int(n_out), _dptr(dts), 1 if (dts.shape == (n,) and n > 1) else 0,
-                                   copts, _dptr(obs), cstats, int(device))
+                                   copts, _max_squarings(max_squarings), _dptr(obs), cstats, int(device))
     stats = [Stats.from_c(s) for s in cstats]
     _check(code)
     return obs, stats
 
 
-def build_propagator(table: SpinTable, dt: float, opts: SolverOptions, device: int = 0):
+def build_propagator(table: SpinTable, dt: float, opts: SolverOptions, device: int = 0,
+                     max_squarings: Optional[int] = None):
     """U = exp(-i H dt) as a (2^n, 2^n) complex matrix in the table's own index convention (bit-major), built
     column by column by the on-chip adaptive integrator (qsb_build_propagator).  Returns (U, Stats)."""
     lib = load_library()
@@ -433,9 +442,17 @@ def build_propagator(table: SpinTable, dt: float, opts: SolverOptions, device: i
     copts = opts.to_c()
     st = _Stats()
     ut = np.empty((table.dim, table.dim), dtype=np.complex128)  # ut[j, x] = <x|U|j>
-    _check(lib.qsb_build_propagator(C.byref(holder.c), float(dt), C.byref(copts), _dptr(ut.view(np.float64)),
-                                    C.byref(st), int(device)))
+    _check(lib.qsb_build_propagator(C.byref(holder.c), float(dt), C.byref(copts), _max_squarings(max_squarings),
+                                    _dptr(ut.view(np.float64)), C.byref(st), int(device)))
     return np.ascontiguousarray(ut.T), Stats.from_c(st)
+
+
+def propagator_squarings(table: SpinTable, dt: float) -> int:
+    """Scaling-and-squaring depth the propagator build picks for this table and interval (host-only query)."""
+    holder = _TableHolder(table)
+    s = C.c_int32(0)
+    _check(load_library().qsb_debug_squarings(C.byref(holder.c), float(dt), C.byref(s)))
+    return s.value
 
 
 def propagate_shape(n_qubits: int):

@@ -47,11 +47,13 @@ plist = c2(**FULL)
 tables = [compile_table(p) for p in plist]
 opts = [api._options_from(p, "propagator")[0] for p in plist]
 dt = 30.0 / 19999
-for name, n_out in (("columns_only", 1), ("columns_plus_chain", 20000)):
+out["c2_full_squarings"] = [engine.propagator_squarings(t, dt) for t in tables[::3]]
+for name, n_out, cap in (("build_only", 1, None), ("build_plus_chain", 20000, None), ("build_only_no_squaring", 1, 0)):
     t0 = time.perf_counter()
-    _, st = engine.propagate_batch(tables, n_out, dt, opts)
+    _, st = engine.propagate_batch(tables, n_out, dt, opts, max_squarings=cap)
     out[f"c2_full_{name}_s"] = round(time.perf_counter() - t0, 4)
     out[f"c2_full_{name}_kernel_ms"] = round(st[0].device_ms, 2)
+    out[f"c2_full_{name}_column_h_applies"] = int(sum(s.n_rhs for s in st))
 if "--no-grid" not in sys.argv:
     out["c3_ci_taylor_s"], out["c3_ci_taylor_kernel_ms"], _, _ = timed(c3())
     out["c3_ci_propagator_s"], out["c3_ci_propagator_kernel_ms"], _, _ = timed(c3(), method="propagator")

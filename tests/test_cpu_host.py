@@ -528,7 +528,7 @@ def test_method_strings_and_uniform_grid_detection(monkeypatch):
     # the integrator options of the column trajectories are those of the stepping path
     p = api.DipolarRareParams(n_sea=6, is_spin_three_half=False, solver_atol=1e-10, solver_rtol=1e-9)
     o, override = api._options_from(p, "propagator")
-    assert (o.method, o.order, override) == ("taylor", 20, True) and o.atol == pytest.approx(1e-13)
+    assert (o.method, o.order, override) == ("taylor", 20, True) and o.atol == pytest.approx(1e-15)
     o, _ = api._options_from(p, "propagator-dp5")
     assert o.method == "dp5" and o.atol == 1e-10
 

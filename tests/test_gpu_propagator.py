@@ -38,10 +38,34 @@ def test_propagator_is_exp_minus_iHdt(n, method):
     w, v = np.linalg.eigh(H)
     dt = 4.0 / max(1.0, float(np.max(np.abs(w))))
     want = (v * np.exp(-1j * w * dt)) @ v.conj().T
-    U, st = engine.build_propagator(table, dt, _tight(method))
+    U, st = engine.build_propagator(table, dt, _tight(method), max_squarings=0)
     assert st.path == 2 and st.n_rhs > 0 and st.status == 0
     assert np.max(np.abs(U - want)) < 1e-9
     assert np.max(np.abs(U.conj().T @ U - np.eye(table.dim))) < 1e-9
+
+
+@pytest.mark.parametrize("n", [2, 4, 6, 7, 8, 9, 10])
+def test_scaling_and_squaring(n):
+    """||H|| dt ~ 300: the columns are integrated over dt / 2^s and the matrix squared s times on chip; the result must
+    equal exp(-i H dt) and the propagator integrated over the whole interval."""
+    from quantumsimulations_b200 import engine
+
+    table = random_table(n, 300 + n)
+    w, v = np.linalg.eigh(_dense_h(table))
+    dt = 300.0 / float(np.max(np.abs(w)))
+    want = (v * np.exp(-1j * w * dt)) @ v.conj().T
+    s = engine.propagator_squarings(table, dt)
+    assert 5 <= s <= 12
+    U, st = engine.build_propagator(table, dt, _tight())
+    assert np.max(np.abs(U - want)) < 1e-9
+    for cap in (1, 4) if n <= 7 else ():   # odd and even depths exercise both buffer parities
+        Uc, stc = engine.build_propagator(table, dt, _tight(), max_squarings=cap)
+        assert np.max(np.abs(Uc - want)) < 1e-9
+        assert stc.n_rhs > st.n_rhs
+    if n <= 7:
+        U0, st0 = engine.build_propagator(table, dt, _tight(), max_squarings=0)
+        assert np.max(np.abs(U0 - U)) < 1e-10
+        assert st0.n_rhs > 2 * st.n_rhs
 
 
 @pytest.mark.parametrize("n", [2, 4, 6, 7, 8, 9, 10])
@@ -127,6 +151,8 @@ def test_per_trajectory_dt_and_determinism():
 
     tables = [random_table(6, 40 + s) for s in range(4)]
     dts = np.array([0.05, 0.1, 0.2, 0.07])
+    tables[1] = dataclasses.replace(tables[1], hz=tables[1].hz * 40.0)   # different squaring depths inside one batch
+    assert engine.propagator_squarings(tables[1], 0.1) > engine.propagator_squarings(tables[0], 0.05)
     a, _ = engine.propagate_batch(tables, 25, dts, [_tight()] * 4)
     b, _ = engine.propagate_batch(tables, 25, dts, [_tight()] * 4)
     assert np.array_equal(a, b)
@@ -146,6 +172,7 @@ def test_errors():
     with pytest.raises(ValueError, match="dt must be"):
         engine.propagate_batch([random_table(4, 1)], 5, -1.0, [_tight()])
     with pytest.raises(IntegratorError):
-        engine.propagate_batch([random_table(6, 3)], 5, 50.0, [SolverOptions(atol=1e-12, rtol=1e-11, nsteps=3)])
+        engine.propagate_batch([random_table(6, 3)], 5, 50.0, [SolverOptions(atol=1e-12, rtol=1e-11, nsteps=3)],
+                               max_squarings=0)
     with pytest.raises(ValueError, match="N <= 10"):
         simulate_rare(DipolarRareParams(n_sea=12, is_spin_three_half=False), method="propagator")
