@@ -319,7 +319,7 @@ def run_b200(args, rank, world, local_rank):
     sweep_s = allmax(time.perf_counter() - t0)
     barrier()
     t0 = time.perf_counter()
-    _, tst = simulate_rare_batch(mine, device=local_rank) if mine else ([], [])   # API default: Taylor(20), tol x1e-3
+    _, tst = simulate_rare_batch(mine, device=local_rank, method="taylor") if mine else ([], [])   # Taylor(20), tol x1e-3
     sweep_default_s = allmax(time.perf_counter() - t0)
     sweep_steps = float(sum(s.n_accepted + s.n_rejected for s in sst))
     sweep_kernel_ms = max([s.device_ms for s in sst], default=0.0)
@@ -334,11 +334,11 @@ def run_b200(args, rank, world, local_rank):
     fmine = full[rank::world]
     barrier()
     t0 = time.perf_counter()
-    _, pci = simulate_rare_batch(mine, device=local_rank, method="propagator") if mine else ([], [])
+    _, pci = simulate_rare_batch(mine, device=local_rank) if mine else ([], [])   # API default: "auto" -> propagator
     sweep_prop_ci_s = allmax(time.perf_counter() - t0)
     barrier()
     t0 = time.perf_counter()
-    fres, fst = simulate_rare_batch(fmine, device=local_rank, method="propagator", raw_norm=True) if fmine else ([], [])
+    fres, fst = simulate_rare_batch(fmine, device=local_rank, raw_norm=True) if fmine else ([], [])
     sweep_full_s = allmax(time.perf_counter() - t0)
     full_kernel_ms = allmax(max([s.device_ms for s in fst], default=0.0))
     full_rhs = float(sum(s.n_rhs for s in fst))
@@ -356,8 +356,12 @@ def run_b200(args, rank, world, local_rank):
         gmine = [glist[i] for i in partition([estimate_cost(p) for p in glist], world)[rank]]
         barrier()
         t0 = time.perf_counter()
-        _, gst = simulate_rare_batch(gmine, device=local_rank) if gmine else ([], [])
+        _, gst = simulate_rare_batch(gmine, device=local_rank, method="taylor") if gmine else ([], [])
         grid_s = allmax(time.perf_counter() - t0)
+        barrier()
+        t0 = time.perf_counter()
+        _ = simulate_rare_batch(gmine, device=local_rank) if gmine else None
+        grid_default_s = allmax(time.perf_counter() - t0)
         gsteps = float(sum(s.n_accepted + s.n_rejected for s in gst))
         grhs = float(sum(s.n_rhs for s in gst))
         if dist is not None:
@@ -370,14 +374,15 @@ def run_b200(args, rank, world, local_rank):
         gfmine = [gfull[i] for i in partition([estimate_cost(p) for p in gfull], world)[rank]]
         barrier()
         t0 = time.perf_counter()
-        _, gfst = simulate_rare_batch(gfmine, device=local_rank, method="propagator") if gfmine else ([], [])
+        _, gfst = simulate_rare_batch(gfmine, device=local_rank) if gfmine else ([], [])
         grid_full_s = allmax(time.perf_counter() - t0)
         grid_full_kernel_ms = allmax(max([s.device_ms for s in gfst], default=0.0))
         grid = {"full_size": {"workload": "C3 at the reference's trajectory size (t_final = 30 s, 20000 outputs), "
-                                          "method 'propagator'", "trajectories": len(gfull), "wall_s": grid_full_s,
-                              "kernel_ms": grid_full_kernel_ms},
+                                          "API default method (auto -> propagator)", "trajectories": len(gfull),
+                              "wall_s": grid_full_s, "kernel_ms": grid_full_kernel_ms},
+                "wall_s_default_method": grid_default_s,
                 "workload": "C3 (CI-sized): 19 f1A (5..50 kHz) x 13 detunings (0..3 f1A) x 3 variants, N=7, t_final=0.03 s, "
-                            "2000 outputs, one CTA per trajectory, API default integrator (Taylor 20)",
+                            "2000 outputs, one CTA per trajectory, stepping Taylor(20) integrator (method='taylor')",
                 "trajectories": len(glist), "wall_s": grid_s, "trajectories_per_s": len(glist) / grid_s,
                 "step_attempts": gsteps, "h_applies_per_s": grhs / grid_s,
                 "parallelism": f"longest-first partition over {world} GPU(s), no collective"}
@@ -408,15 +413,17 @@ def run_b200(args, rank, world, local_rank):
                                   "atol 1e-10 / rtol 1e-9, one CTA per trajectory",
                       "trajectories": len(plist), "wall_s": sweep_s, "kernel_ms": sweep_kernel_ms, "method": "dp5",
                       "steps_per_s": sweep_steps / sweep_s, "total_steps": sweep_steps,
-                      "wall_s_default_integrator": sweep_default_s,
-                      "default_integrator": "taylor order 20, atol/rtol x 1e-3 (what simulate_rare runs)",
+                      "wall_s_taylor": sweep_default_s,
+                      "taylor": "stepping Taylor order 20, atol/rtol x 1e-3 (method='taylor')",
                       "cpu_zvode": zv,
-                      "wall_s_propagator": sweep_prop_ci_s,
+                      "wall_s_default_method": sweep_prop_ci_s,
+                      "default_method": "auto = Taylor(20) columns of exp(-iH dt/2^s), s on-chip squarings, one matvec per "
+                                        "output (what simulate_rare runs when steps - 1 > 2^N)",
                       "full_size": {
                           "workload": "C2 at the reference's own size (SW:1201-1252): 13 detunings x 3 variants, N=7, "
-                                      "t_final=30 s, 20000 outputs, atol 1e-10 / rtol 1e-9, max_step 1e-5; method "
-                                      "'propagator' (128 Taylor(20) column trajectories over one output interval per "
-                                      "trajectory, then 19999 on-chip matvecs)",
+                                      "t_final=30 s, 20000 outputs, atol 1e-10 / rtol 1e-9, max_step 1e-5; API default "
+                                      "method (auto -> propagator: 128 Taylor(20) column trajectories over dt/2^s, s = "
+                                      "8..10 on-chip squarings, then 19999 on-chip matvecs per trajectory)",
                           "trajectories": len(full), "wall_s": sweep_full_s, "kernel_ms": full_kernel_ms,
                           "column_h_applies": full_rhs, "max_raw_norm_deviation": full_norm_dev,
                           "cpu_zvode_extrapolated_s_per_trajectory_1core":

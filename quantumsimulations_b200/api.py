@@ -104,7 +104,9 @@ def initial_state_rare(params: DipolarRareParams) -> np.ndarray:
 # ~10x fewer H-applies than DP5 at equal tolerances.  Its cost grows only logarithmically with the tolerance
 # (1.4x for 1000x tighter), while the reference's own trajectories are integrator-error-limited at its tolerances
 # (SURVEY.md TL;DR 6), so the requested atol/rtol are tightened by DEFAULT_TOL_SCALE before they reach the C ABI.
-DEFAULT_METHOD = "taylor"
+# "auto" = the Taylor integrator, used through the propagator path (below) wherever that is the cheaper way to the
+# same traces: N <= 10 and more output intervals than basis states (steps - 1 > 2^N).
+DEFAULT_METHOD = "auto"
 DEFAULT_TAYLOR_ORDER = 20
 DEFAULT_TOL_SCALE = {"taylor": 1e-3, "dp5": 1.0}
 # method = "propagator" (or "propagator-dp5"): N <= 10 only.  The reference's output grid is uniform (DE:626) and its
@@ -119,22 +121,31 @@ PROPAGATOR = "propagator"
 PROPAGATOR_TOL_SCALE = {"taylor": 1e-5, "dp5": 1.0}
 
 
-def split_method(method: Optional[str]) -> Tuple[str, bool]:
-    """(integrator, use_propagator) from a method string: "taylor", "dp5", "propagator", "propagator-dp5"."""
+def split_method(method: Optional[str], n_qubits: Optional[int] = None, steps: Optional[int] = None) -> Tuple[str, bool]:
+    """(integrator, use_propagator) from a method string: "auto", "taylor", "dp5", "propagator", "propagator-dp5".
+    "auto" needs the trajectory's size (``n_qubits``, ``steps``) to choose; without it, it means stepping."""
     m = method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)
+    if m == "auto":
+        fits = n_qubits is not None and steps is not None and n_qubits <= engine.SMALL_MAX_QUBITS
+        return "taylor", bool(fits and steps - 1 > (1 << n_qubits))
     if m.startswith(PROPAGATOR):
         rest = m[len(PROPAGATOR):].lstrip("-")
         m, prop = (rest or "taylor"), True
     else:
         prop = False
     if m not in DEFAULT_TOL_SCALE:
-        raise ValueError(f"unknown method {method!r}: taylor, dp5, propagator or propagator-dp5")
+        raise ValueError(f"unknown method {method!r}: auto, taylor, dp5, propagator or propagator-dp5")
     return m, prop
+
+
+def _size_of(params: DipolarRareParams) -> Tuple[int, int]:
+    return params.n_sea + 1, params.steps
 
 
 def _options_from(params: DipolarRareParams, method: Optional[str], tol_scale: Optional[float] = None
                   ) -> Tuple[engine.SolverOptions, bool]:
     """Map the reference's solver_* fields (DE:629-651); returns (options, any_override)."""
+    integrator, propagate = split_method(method, *_size_of(params))
     knobs = (params.solver_atol, params.solver_rtol, params.solver_nsteps, params.solver_max_step)
     override = any(v is not None for v in knobs)
     o = engine.SolverOptions()
@@ -146,10 +157,10 @@ def _options_from(params: DipolarRareParams, method: Optional[str], tol_scale: O
         o.nsteps = int(params.solver_nsteps)
     if params.solver_max_step is not None:
         o.max_step = params.solver_max_step
-    o.method = split_method(method)[0]
+    o.method = integrator
     o.order = int(os.environ.get("QSB200_TAYLOR_ORDER", str(DEFAULT_TAYLOR_ORDER)))
     if tol_scale is None:
-        table = PROPAGATOR_TOL_SCALE if split_method(method)[1] else DEFAULT_TOL_SCALE
+        table = PROPAGATOR_TOL_SCALE if propagate else DEFAULT_TOL_SCALE
         tol_scale = float(os.environ.get("QSB200_TOL_SCALE", table[o.method]))
     o.atol = max(o.atol * tol_scale, 1e-300)
     o.rtol = max(o.rtol * tol_scale, 1e-14) if o.rtol > 0 else 0.0
@@ -176,8 +187,9 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
                   checkpoint: Optional[str] = None, checkpoint_every: int = 16):
     """Time evolution on the B200 engine; returns ``(t, {6 traces + state_norm})`` like DE:611-680.
 
-    ``method``: "taylor" (default, order 20), "dp5", or "propagator" / "propagator-dp5" (N <= 10: one propagator per
-    trajectory, then one matvec per output time; see PROPAGATOR).  ``tol_scale`` multiplies solver_atol/solver_rtol before
+    ``method``: "auto" (default: Taylor order 20, through the propagator path when N <= 10 and steps - 1 > 2^N),
+    "taylor", "dp5", or "propagator" / "propagator-dp5" (N <= 10: one propagator per trajectory, then one matvec per
+    output time; see PROPAGATOR).  ``tol_scale`` multiplies solver_atol/solver_rtol before
     they reach the integrator (default 1e-3 for taylor, 1 for dp5; see DEFAULT_TOL_SCALE).
     ``raw_norm=True`` adds the integrator's own norm under an extra key (QuTiP discards it).
     ``checkpoint``: file the tiled path (N >= 11) writes its state to every ``checkpoint_every`` output times and
@@ -187,7 +199,7 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
     t = _check_grid(params)
     table = compile_table(params)
     opts, override = _options_from(params, method, tol_scale)
-    if split_method(method)[1]:
+    if split_method(method, table.n, len(t))[1]:
         obs, stats = _propagate([table], [t], [opts], device)
         out = _pack(obs[0], override, raw_norm)
         return (t, out, stats[0]) if return_stats else (t, out)
@@ -222,8 +234,7 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
     grids = [_check_grid(p) for p in params_list]
     tables = [compile_table(p) for p in params_list]
     om = [_options_from(p, method, tol_scale) for p in params_list]
-    propagate = split_method(method)[1]
-    if propagate and any(t.n > engine.SMALL_MAX_QUBITS for t in tables):
+    if any(split_method(method, t.n, len(g))[1] and t.n > engine.SMALL_MAX_QUBITS for t, g in zip(tables, grids)):
         raise ValueError(f"method 'propagator' holds a dense 2^N x 2^N matrix on chip: N <= {engine.SMALL_MAX_QUBITS}")
     small = [i for i in range(n) if tables[i].n <= engine.SMALL_MAX_QUBITS]
     groups: Dict[int, List[int]] = {}
@@ -231,7 +242,7 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
         groups.setdefault((tables[i].n, len(grids[i])), []).append(i)  # uniform n -> register-resident rows
     stats_out: List = [None] * n
     for _, idxs in groups.items():
-        if propagate:
+        if split_method(method, tables[idxs[0]].n, len(grids[idxs[0]]))[1]:   # one (N, steps) per group
             obs, stats = _propagate([tables[i] for i in idxs], [grids[i] for i in idxs], [om[i][0] for i in idxs], device)
         else:
             tgrid = np.stack([grids[i] for i in idxs])

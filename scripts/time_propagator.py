@@ -36,7 +36,7 @@ def timed(plist, **kw):
 FULL = dict(t_final=30.0, steps=20000)
 simulate_rare_batch(c2()[:3], method="propagator")  # context + module load
 out = {}
-out["c2_ci_taylor_s"], out["c2_ci_taylor_kernel_ms"], ref, _ = timed(c2())
+out["c2_ci_taylor_s"], out["c2_ci_taylor_kernel_ms"], ref, _ = timed(c2(), method="taylor")
 out["c2_ci_propagator_s"], out["c2_ci_propagator_kernel_ms"], res, _ = timed(c2(), method="propagator")
 out["c2_ci_max_dev_vs_taylor"] = max(float(np.max(np.abs(a[1][k] - b[1][k]))) for a, b in zip(ref, res) for k in api.TRACE_KEYS)
 out["c2_full_propagator_s"], out["c2_full_propagator_kernel_ms"], res, st = timed(c2(**FULL), method="propagator", raw_norm=True)
@@ -55,7 +55,7 @@ for name, n_out, cap in (("build_only", 1, None), ("build_plus_chain", 20000, No
     out[f"c2_full_{name}_kernel_ms"] = round(st[0].device_ms, 2)
     out[f"c2_full_{name}_column_h_applies"] = int(sum(s.n_rhs for s in st))
 if "--no-grid" not in sys.argv:
-    out["c3_ci_taylor_s"], out["c3_ci_taylor_kernel_ms"], _, _ = timed(c3())
+    out["c3_ci_taylor_s"], out["c3_ci_taylor_kernel_ms"], _, _ = timed(c3(), method="taylor")
     out["c3_ci_propagator_s"], out["c3_ci_propagator_kernel_ms"], _, _ = timed(c3(), method="propagator")
     out["c3_full_propagator_s"], out["c3_full_propagator_kernel_ms"], _, _ = timed(c3(**FULL), method="propagator")
 print(json.dumps(out))

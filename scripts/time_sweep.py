@@ -19,7 +19,7 @@ c2 = [sweep_params(6, d, v) for d in np.linspace(0.0, 3.0 * F1A, 13) for v in V]
 c3 = [sweep_params(6, d, v, f1a=f) for f in np.arange(5e3, 50e3 + 1, 2.5e3) for d in np.linspace(0.0, 3.0 * f, 13) for v in V]
 simulate_rare_batch(c2[:3])  # context + module load
 out = {}
-for name, plist, kw in (("c2_taylor", c2, {}), ("c2_dp5", c2, {"method": "dp5"}), ("c3_taylor", c3, {})):
+for name, plist, kw in (("c2_taylor", c2, {"method": "taylor"}), ("c2_dp5", c2, {"method": "dp5"}), ("c3_taylor", c3, {"method": "taylor"})):
     t0 = time.perf_counter()
     res, st = simulate_rare_batch(plist, **kw)
     out[name + "_s"] = round(time.perf_counter() - t0, 4)

@@ -512,7 +512,12 @@ def test_method_strings_and_uniform_grid_detection(monkeypatch):
     from quantumsimulations_b200 import api, engine
 
     monkeypatch.delenv("QSB200_METHOD", raising=False)
-    assert api.split_method(None) == ("taylor", False)
+    assert api.split_method(None) == ("taylor", False)            # "auto" without a size: stepping
+    assert api.split_method(None, 7, 2000) == ("taylor", True)    # more output intervals than basis states
+    assert api.split_method("auto", 7, 129) == ("taylor", False)
+    assert api.split_method("auto", 7, 130) == ("taylor", True)
+    assert api.split_method("auto", 13, 20000) == ("taylor", False)  # tiled path: no dense propagator
+    assert api.split_method("taylor", 7, 2000) == ("taylor", False)
     assert api.split_method("dp5") == ("dp5", False)
     assert api.split_method("propagator") == ("taylor", True)
     assert api.split_method("propagator-dp5") == ("dp5", True)
@@ -531,6 +536,11 @@ def test_method_strings_and_uniform_grid_detection(monkeypatch):
     assert (o.method, o.order, override) == ("taylor", 20, True) and o.atol == pytest.approx(1e-15)
     o, _ = api._options_from(p, "propagator-dp5")
     assert o.method == "dp5" and o.atol == 1e-10
+    monkeypatch.delenv("QSB200_METHOD")
+    o, _ = api._options_from(dataclasses.replace(p, steps=2000), None)      # auto -> propagator tolerances
+    assert o.method == "taylor" and o.atol == pytest.approx(1e-15)
+    o, _ = api._options_from(dataclasses.replace(p, steps=100), None)       # auto -> stepping tolerances
+    assert o.method == "taylor" and o.atol == pytest.approx(1e-13)
 
 
 def test_propagate_kernel_launch_shapes():
