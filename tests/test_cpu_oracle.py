@@ -184,3 +184,34 @@ def test_restatements_against_live_reference():
     for args in ((1.0, 2.0, 3.0, 0.5), (1.0, -2.0, 0.2, 0.3), (float("nan"), 1.0, 2.0, 2.0), (2.0, 1.0, 5.0, 5.0)):
         ra, rb = sw.contrast_michelson_with_t_gate(*args), om.gated_contrast(*args)
         assert (np.isnan(ra) and np.isnan(rb)) or ra == rb
+
+
+def test_exact_oracle_matches_full_size_reference_sweep_samples():
+    """tests/golden/sweep_full.json: the reference's unchanged driver at its own __main__ size (30 s, 20000 outputs,
+    SW:1199-1252) on exact propagation.  The oracle's table + exact solver must reproduce the stored trace samples
+    of all 39 trajectories (out to t = 30 s, i.e. phases of ~10^8 rad)."""
+    import json
+
+    from conftest import GOLDEN, exact_traces
+    from quantumsimulations_b200 import compile_table
+    from quantumsimulations_b200.metrics import detuning_label
+    from quantumsimulations_b200.sweep import sweep_point_params
+
+    with open(os.path.join(GOLDEN, "sweep_full.json")) as f:
+        gold = json.load(f)
+    gp = gold["summary"]["global_params"]
+    t = np.linspace(0.0, gp["t_final_s"], gp["steps"])
+    assert len(gold["samples"]) == 39
+    for delta in gp["sea_detunings_Hz"]:
+        variants = sweep_point_params(
+            n_sea=gp["n_sea"], gamma_sea=gp["gamma_sea"], gamma_rare=gp["gamma_rare"], B0_common=gp["B0_common_T"],
+            B1_sea=gp["B1_sea_T"], B1_rare=gp["B1_rare_T"], omega_rf_sea=2 * np.pi * (gp["f_Az_Hz"] - delta),
+            omega_rf_rare=2 * np.pi * gp["f_Rz_Hz"], phi_sea=gp["phi_sea_rad"], phi_rare=gp["phi_rare_rad"],
+            dipolar_scale=gp["dipolar_scale_SI"], shell_scale=gp["shell_scale_m"], t_final=gp["t_final_s"],
+            steps=gp["steps"], is_spin_three_half=False, solver_atol=gp["solver_atol"], solver_rtol=gp["solver_rtol"],
+            solver_nsteps=gp["solver_nsteps"], solver_max_step=gp["solver_max_step"])
+        for tag, p in variants.items():
+            s = gold["samples"][f"{detuning_label(delta)}/{tag}"]
+            got = exact_traces(compile_table(p), t[s["index"]])
+            assert np.max(np.abs(got["Iz_sea"] - np.array(s["Iz_sea"]))) < 1e-7, (delta, tag)
+            assert np.max(np.abs(got["Iz_R"] - np.array(s["Iz_R"]))) < 1e-7, (delta, tag)

@@ -176,3 +176,47 @@ def test_errors():
                                max_squarings=0)
     with pytest.raises(ValueError, match="N <= 10"):
         simulate_rare(DipolarRareParams(n_sea=12, is_spin_three_half=False), method="propagator")
+
+
+def test_full_size_sweep_reproduces_reference_metrics(tmp_path):
+    """north_star target: the sweep at the reference's own __main__ size (SW:1199-1252: 13 detunings x 3 variants,
+    30 s, 20000 outputs, coarse_window 100) through the engine's driver with the API default method, against the
+    metrics rows and trace samples the reference's unchanged driver produced on exact propagation
+    (tests/golden/sweep_full.json, oracle/make_golden_full_sweep.py)."""
+    import json
+    import os
+
+    from conftest import GOLDEN
+    from quantumsimulations_b200.sweep import run_sweep_sea_detuning
+
+    with open(os.path.join(GOLDEN, "sweep_full.json")) as f:
+        gold = json.load(f)
+    gp = gold["summary"]["global_params"]
+    base = run_sweep_sea_detuning(
+        f_Az=gp["f_Az_Hz"], f1A=gp["f1A_Hz"], target_sea_detuning=gp["target_sea_detuning"],
+        gamma_sea=gp["gamma_sea"], gamma_rare=gp["gamma_rare"], sea_detunings_Hz=gp["sea_detunings_Hz"],
+        n_sea=gp["n_sea"], t_final=gp["t_final_s"], steps=gp["steps"], phi_sea=gp["phi_sea_rad"],
+        phi_rare=gp["phi_rare_rad"], out_root=str(tmp_path), is_spin_three_half=False,
+        solver_atol=gp["solver_atol"], solver_rtol=gp["solver_rtol"], solver_nsteps=gp["solver_nsteps"],
+        solver_max_step=gp["solver_max_step"], coarse_window=gp["coarse_window"], timestamp="full", verbose=False)
+    for key, s in gold["samples"].items():
+        d, tag = key.split("/")
+        with np.load(os.path.join(base, d, f"time_and_obs_{tag}.npz")) as z:
+            assert z["t"].shape == (20000,) and z["state_norm"].shape == (20000,)
+            for k in ("Iz_sea", "Iz_R"):
+                assert np.max(np.abs(z[k][s["index"]] - np.array(s[k]))) < TOL, (key, k)
+    with open(os.path.join(base, "summary.json")) as f:
+        mine = json.load(f)
+    assert len(mine["sweep_results"]) == 13
+    for got, want in zip(mine["sweep_results"], gold["summary"]["sweep_results"]):
+        for k in want:
+            if k.startswith("I_z_slope"):
+                assert abs(got[k] - want[k]) < 1e-7, (k, got[k], want[k])     # traces within 1e-6 over a 30 s baseline
+            elif k.startswith("t_") or k.startswith("R_"):
+                assert got[k] == pytest.approx(want[k], rel=2e-3, abs=2e-4), k
+            elif k.startswith("contrast"):
+                ts = [want[x] for x in ("t_on_center", "t_off_center", "t_off_sea_center")]
+                if all(abs(abs(t) - 1.0) > 0.01 for t in ts):   # discontinuous at |t| = 1 (SW:308-309)
+                    assert got[k] == pytest.approx(want[k], abs=2e-3), k
+            else:
+                assert got[k] == pytest.approx(want[k], rel=1e-9, abs=1e-12), k
