@@ -136,8 +136,8 @@ int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opt
 /* Host-only: the number of squarings step 1 uses for this table and interval when max_squarings < 0.               */
 int qsb_debug_squarings(const qsb_table* table, double dt, int32_t* n_squarings);
 /* Host-only: launch shape of step 2 for n qubits, out = {threads, column split, columns of U cached in shared
- * memory, dynamic shared-memory bytes}.                                                                         */
-int qsb_debug_propagate_shape(int32_t n_qubits, int32_t* out /* [4] */);
+ * memory, dynamic shared-memory bytes, slots of the state ring between two rounds of observable reductions}.   */
+int qsb_debug_propagate_shape(int32_t n_qubits, int32_t* out /* [5] */);
 
 /* ---- pieces of the path, exposed for parity tests and the benchmark ---------------------------- */
 /* out = H psi on host vectors of 2^n complex128 (one H-apply through the same kernels evolve uses).  */

@@ -459,10 +459,10 @@ int qsb_debug_squarings(const qsb_table* table, double dt, int32_t* n_squarings)
 
 int qsb_debug_propagate_shape(int32_t n_qubits, int32_t* out) {
   if (!out || n_qubits < 1 || n_qubits > QSB_SMALL_MAX_QUBITS) return fail(QSB_ERR_BAD_ARG, "need 1 <= n_qubits <= 10 and out");
-  int th, sp, nc;
+  int th, sp, nc, rg;
   size_t smem;
-  small_propagate_shape(n_qubits, &th, &sp, &nc, &smem);
-  out[0] = th; out[1] = sp; out[2] = nc; out[3] = (int32_t)smem;
+  small_propagate_shape(n_qubits, &th, &sp, &nc, &rg, &smem);
+  out[0] = th; out[1] = sp; out[2] = nc; out[3] = (int32_t)smem; out[4] = rg;
   return QSB_OK;
 }
 

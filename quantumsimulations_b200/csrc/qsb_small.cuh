@@ -57,7 +57,7 @@ void launch_small_square(cplx* d_columns, cplx* d_tmp, const int32_t* d_n_sq, in
 int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cplx* d_columns, int64_t n_out,
                            double* d_obs, cudaStream_t stream);
 // Launch shape of the propagate kernel for n qubits (host-only; exposed for tests).
-void small_propagate_shape(int n, int* threads, int* split, int* n_cache, size_t* smem);
+void small_propagate_shape(int n, int* threads, int* split, int* n_cache, int* ring, size_t* smem);
 
 // out = H in for one n <= 10 table (test hook: same RHS routine the trajectory kernel uses).
 void launch_small_apply(const SmallDesc* d_desc, int n, const cplx* d_in, cplx* d_out, cudaStream_t stream);

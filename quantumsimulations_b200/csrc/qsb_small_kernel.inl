@@ -163,17 +163,63 @@ small_evolve_kernel(const SmallDesc* __restrict__ descs, const double* __restric
   }
 }
 
+// Observable sums of one state by ONE warp (shuffle tree only, fixed order): lane l owns amplitudes l, l + 32, ...
+// Same sums and output columns as small_observe.
+__device__ __forceinline__ void warp_observe(const cplx* __restrict__ v, int dim, const SmallDesc& d,
+                                             double* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  double s[7] = {0, 0, 0, 0, 0, 0, 0};  // nrm2, zsea, zrare, csea.re, csea.im, crare.re, crare.im
+  for (uint32_t x = lane; x < (uint32_t)dim; x += 32) {
+    cplx me = v[x];
+    double p = norm2(me);
+    s[0] += p;
+    s[1] += p * (double)(__popc(d.sea_mask) - 2 * __popc(x & d.sea_mask));
+    s[2] += (x & d.rare_mask) ? -p : p;
+    for (int b = 0; b < d.n; ++b) {
+      uint32_t m = 1u << b;
+      if (x & m) continue;
+      bool is_sea = d.sea_mask & m, is_rare = d.rare_mask & m;
+      if (!is_sea && !is_rare) continue;
+      cplx u = v[x | m];  // conj(me) * u
+      double re = fma(me.x, u.x, me.y * u.y), im = fma(me.x, u.y, -me.y * u.x);
+      if (is_sea) { s[3] += re; s[4] += im; }
+      if (is_rare) { s[5] += re; s[6] += im; }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 7; ++k) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s[k] += __shfl_xor_sync(0xffffffffu, s[k], off);
+  }
+  if (lane == 0) {
+    double inv = 1.0 / s[0];
+    out[0] = s[3] * inv;        // Ix_sea
+    out[1] = s[4] * inv;        // Iy_sea
+    out[2] = 0.5 * s[1] * inv;  // Iz_sea
+    out[3] = 0.5 * s[2] * inv;  // Iz_R
+    out[4] = s[5] * inv;        // Ix_R
+    out[5] = s[6] * inv;        // Iy_R
+    out[6] = 1.0;               // norm of the output-normalised ket
+    out[7] = sqrt(s[0]);        // raw norm
+  }
+}
+
 // psi_k = U psi_{k-1}, k = 1 .. n_out-1, with the six observables of every psi_k: the constant-H fast path for
 // uniform output grids (the reference's grid is np.linspace(0, t_final, steps), dipolar_ensemble_with_rare.py:626,
 // and its H has no time dependence, :514 / :570).  One CTA per trajectory.  U arrives column-major
-// (ut[j * dim + x] = <x|U|j>, the layout small_evolve_kernel<COL> leaves behind); the first n_cache columns are kept
-// in shared memory, each thread keeps its next NREG columns in registers (at n = 7 that is all of U: 104 + 4 x 6), and
-// whatever is left streams from L2 every step.  Thread (x, q) accumulates columns j = q (mod split) of row x;
-// the `split` partial sums of a row are added in q order, so results are bitwise reproducible.
+// (ut[j * dim + x] = <x|U|j>, the layout small_evolve_kernel<COL> leaves behind) and stays on the SM: the first
+// n_cache columns in shared memory, each thread's next NREG columns in registers (at n = 7 that is all of U), and
+// only what is left streams from L2 every step.
+// Lane l of warp w is (xl = l & 7, ql = l >> 3): it accumulates the columns j = q (mod split) of row x with
+// q = ql & (split - 1), x = 8 (w 4/split + ql / split) + xl, so a quarter warp reads 128 contiguous bytes of a
+// column (conflict-free LDS.128) and the `split` partial sums of a row meet in one warp: they are added by a fixed
+// xor-shuffle tree (bitwise reproducible) and psi_k costs ONE barrier.  The states go into a ring of `ring` slots;
+// whenever it is full, warp r reduces the observables of slot r (warp_observe), so the reductions need no barriers
+// of their own.
 template <int MAXT, int NREG>
 __global__ void __launch_bounds__(MAXT, 1)
 small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restrict__ ut_all, int64_t n_out,
-                       double* __restrict__ obs_all, int split, int n_cache) {
+                       double* __restrict__ obs_all, int split, int n_cache, int ring) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   SmallShared& sh = *reinterpret_cast<SmallShared*>(smem_raw);
   const int traj = blockIdx.x;
@@ -185,19 +231,18 @@ small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restri
   __syncthreads();
   const SmallDesc& d = sh.d;
   const int n = d.n, dim = 1 << n;
-  cplx* cur = reinterpret_cast<cplx*>(smem_raw + ((sizeof(SmallShared) + 15) & ~size_t(15)));
-  cplx* nxt = cur + dim;
-  cplx* part = nxt + dim;                      // [split][dim]
-  cplx* us = part + (size_t)split * dim;       // [n_cache][dim]
+  cplx* states = reinterpret_cast<cplx*>(smem_raw + ((sizeof(SmallShared) + 15) & ~size_t(15)));  // [ring][dim]
+  cplx* us = states + (size_t)ring * dim;                                                       // [n_cache][dim]
   const cplx* __restrict__ ut = ut_all + ((size_t)traj << (2 * n));
-  const uint32_t x = threadIdx.x & (dim - 1);
-  const int q = threadIdx.x >> n;
-  const bool worker = q < split;               // idle lanes exist only when dim * split < 32
-  const bool owner = threadIdx.x < (uint32_t)dim;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const int xl = lane & 7, ql = lane >> 3;
+  const int q = ql & (split - 1);
+  const int x = 8 * (warp * (4 / split) + ql / split) + xl;
+  const bool worker = x < dim;
   double* obs = obs_all + (size_t)traj * n_out * QSB_NOBS;
 
   for (int i = threadIdx.x; i < n_cache * dim; i += blockDim.x) us[i] = ut[i];
-  if (owner) cur[x] = mk(x == d.psi0 ? 1.0 : 0.0, 0.0);
+  for (int i = threadIdx.x; i < dim; i += blockDim.x) states[i] = mk((uint32_t)i == d.psi0 ? 1.0 : 0.0, 0.0);
   // first column of this thread that is not in shared memory, and the register-resident columns from there on
   int j_tail = q;
   while (j_tail < n_cache) j_tail += split;
@@ -208,42 +253,44 @@ small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restri
     ureg[r] = (worker && j < dim) ? ut[(size_t)j * dim + x] : mk(0, 0);
   }
   __syncthreads();
-  small_observe(cur, x, owner, d, sh.red, obs);
 
-  for (int64_t io = 1; io < n_out; ++io) {
-    cplx a0 = mk(0, 0), a1 = mk(0, 0);
-    if (worker) {
-      int j = q;
-      for (; j + split < n_cache; j += 2 * split) {
-        caxpy(a0, us[(size_t)j * dim + x], cur[j]);
-        caxpy(a1, us[(size_t)(j + split) * dim + x], cur[j + split]);
-      }
-      if (j < n_cache) { caxpy(a0, us[(size_t)j * dim + x], cur[j]); j += split; }
+  for (int64_t base = 0; base < n_out; base += ring) {  // slot r of this round holds psi_{base + r}
+    const int count = (int)((n_out - base < ring) ? n_out - base : ring);
+    for (int r = (base == 0 ? 1 : 0); r < count; ++r) {
+      const cplx* cur = states + (size_t)(r == 0 ? ring - 1 : r - 1) * dim;
+      cplx a0 = mk(0, 0), a1 = mk(0, 0);
+      if (worker) {
+        int j = q;
+        for (; j + split < n_cache; j += 2 * split) {
+          caxpy(a0, us[(size_t)j * dim + x], cur[j]);
+          caxpy(a1, us[(size_t)(j + split) * dim + x], cur[j + split]);
+        }
+        if (j < n_cache) { caxpy(a0, us[(size_t)j * dim + x], cur[j]); j += split; }
 #pragma unroll
-      for (int r = 0; r < NREG; ++r) {
-        if (j < dim) caxpy((r & 1) ? a1 : a0, ureg[r], cur[j]);
-        j += split;
+        for (int rr = 0; rr < NREG; ++rr) {
+          if (j < dim) caxpy((rr & 1) ? a1 : a0, ureg[rr], cur[j]);
+          j += split;
+        }
+        for (; j + 3 * split < dim; j += 4 * split) {  // four independent L2 loads in flight per thread
+          cplx u0 = __ldg(ut + (size_t)j * dim + x), u1 = __ldg(ut + (size_t)(j + split) * dim + x);
+          cplx u2 = __ldg(ut + (size_t)(j + 2 * split) * dim + x), u3 = __ldg(ut + (size_t)(j + 3 * split) * dim + x);
+          caxpy(a0, u0, cur[j]);
+          caxpy(a1, u1, cur[j + split]);
+          caxpy(a0, u2, cur[j + 2 * split]);
+          caxpy(a1, u3, cur[j + 3 * split]);
+        }
+        for (; j < dim; j += split) caxpy(a0, __ldg(ut + (size_t)j * dim + x), cur[j]);
       }
-      for (; j + 3 * split < dim; j += 4 * split) {  // four independent L2 loads in flight per thread
-        cplx u0 = __ldg(ut + (size_t)j * dim + x), u1 = __ldg(ut + (size_t)(j + split) * dim + x);
-        cplx u2 = __ldg(ut + (size_t)(j + 2 * split) * dim + x), u3 = __ldg(ut + (size_t)(j + 3 * split) * dim + x);
-        caxpy(a0, u0, cur[j]);
-        caxpy(a1, u1, cur[j + split]);
-        caxpy(a0, u2, cur[j + 2 * split]);
-        caxpy(a1, u3, cur[j + 3 * split]);
+      cplx sum = a0 + a1;
+      for (int off = 8; off < 8 * split; off <<= 1) {  // the split partial sums of row x: lanes differing in q
+        sum.x += __shfl_xor_sync(0xffffffffu, sum.x, off);
+        sum.y += __shfl_xor_sync(0xffffffffu, sum.y, off);
       }
-      for (; j < dim; j += split) caxpy(a0, __ldg(ut + (size_t)j * dim + x), cur[j]);
-      part[(size_t)q * dim + x] = a0 + a1;
+      if (worker && q == 0) states[(size_t)r * dim + x] = sum;
+      __syncthreads();
     }
+    for (int r = warp; r < count; r += nwarp) warp_observe(states + (size_t)r * dim, dim, d, obs + (base + r) * QSB_NOBS);
     __syncthreads();
-    if (owner) {
-      cplx s = part[x];
-      for (int r = 1; r < split; ++r) s = s + part[(size_t)r * dim + x];
-      nxt[x] = s;
-    }
-    __syncthreads();
-    small_observe(nxt, x, owner, d, sh.red, obs + io * QSB_NOBS);
-    cplx* t = cur; cur = nxt; nxt = t;
   }
 }
 
@@ -371,25 +418,30 @@ void launch_small_columns(const SmallDesc* d_desc, int n_traj, int n, const doub
 }
 
 static constexpr size_t PROPAGATE_SMEM_MAX = 226 * 1024;  // of the 227 KB a CTA may opt in to
+static constexpr int PROPAGATE_NREG = 8;                   // columns of U per thread kept in registers (<= 512 threads)
 
-void small_propagate_shape(int n, int* threads, int* split, int* n_cache, size_t* smem) {
+void small_propagate_shape(int n, int* threads, int* split, int* n_cache, int* ring, size_t* smem) {
   const int dim = 1 << n;
-  int sp = 512 / dim;
-  if (sp < 1) sp = 1;
+  int sp = dim >= 512 ? 1 : (dim > 128 ? 2 : 4);  // partial sums of a row live in one warp: 1, 2 or 4
   if (sp > dim) sp = dim;
   int th = dim * sp;
   if (th < 32) th = 32;
-  const size_t fixed = ((sizeof(SmallShared) + 15) & ~size_t(15)) + (size_t)(2 + sp) * dim * sizeof(cplx);
+  // ring of states between two rounds of observable reductions: one slot per warp, at most 16 KB, at least 2
+  int rg = th / 32;
+  const int fit = (int)(16384 / ((size_t)dim * sizeof(cplx)));
+  if (rg > fit) rg = fit;
+  if (rg < 2) rg = 2;
+  const size_t fixed = ((sizeof(SmallShared) + 15) & ~size_t(15)) + (size_t)rg * dim * sizeof(cplx);
   size_t room = (PROPAGATE_SMEM_MAX - fixed) / ((size_t)dim * sizeof(cplx));
   int nc = room > (size_t)dim ? dim : (int)room;
-  *threads = th; *split = sp; *n_cache = nc;
+  *threads = th; *split = sp; *n_cache = nc; *ring = rg;
   *smem = fixed + (size_t)nc * dim * sizeof(cplx);
 }
 
 void launch_small_square(cplx* d_columns, cplx* d_tmp, const int32_t* d_n_sq, int n_traj, int n, cudaStream_t stream) {
-  int threads, split, n_cache;
+  int threads, split, n_cache, ring;
   size_t smem;
-  small_propagate_shape(n, &threads, &split, &n_cache, &smem);
+  small_propagate_shape(n, &threads, &split, &n_cache, &ring, &smem);
   if (threads > 512)
     small_square_kernel<1024><<<n_traj, threads, 0, stream>>>(d_columns, d_tmp, d_n_sq, n, split);
   else
@@ -398,15 +450,15 @@ void launch_small_square(cplx* d_columns, cplx* d_tmp, const int32_t* d_n_sq, in
 
 int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cplx* d_columns, int64_t n_out,
                            double* d_obs, cudaStream_t stream) {
-  int threads, split, n_cache;
+  int threads, split, n_cache, ring;
   size_t smem;
-  small_propagate_shape(n, &threads, &split, &n_cache, &smem);
+  small_propagate_shape(n, &threads, &split, &n_cache, &ring, &smem);
   if (threads > 512) {
     QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<1024, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_propagate_kernel<1024, 0><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache);
+    small_propagate_kernel<1024, 0><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache, ring);
   } else {
-    QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<512, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_propagate_kernel<512, 8><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache);
+    QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<512, PROPAGATE_NREG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    small_propagate_kernel<512, PROPAGATE_NREG><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache, ring);
   }
   QSB_CUDA(cudaGetLastError());
   return QSB_OK;

@@ -456,7 +456,7 @@ def propagator_squarings(table: SpinTable, dt: float) -> int:
 
 
 def propagate_shape(n_qubits: int):
-    """{threads, split, cached_columns, smem_bytes} of the propagate kernel for n qubits (host-only query)."""
-    out = (C.c_int32 * 4)()
+    """{threads, split, cached_columns, smem_bytes, ring} of the propagate kernel for n qubits (host-only query)."""
+    out = (C.c_int32 * 5)()
     _check(load_library().qsb_debug_propagate_shape(int(n_qubits), out))
-    return {"threads": out[0], "split": out[1], "cached_columns": out[2], "smem_bytes": out[3]}
+    return {"threads": out[0], "split": out[1], "cached_columns": out[2], "smem_bytes": out[3], "ring": out[4]}
