@@ -46,6 +46,17 @@ LargeGeom make_geometry(int n, int rank, int world) {
     int ng = (rest + gmax - 1) / gmax;
     if (ng > MAX_LAYOUTS - 1) ng = MAX_LAYOUTS - 1;
     int last = std::max(wl, (rest + ng - 1) / ng);
+    if (world > 1 && ng * gmax >= rest) {  // (not when MAX_LAYOUTS already forces oversized groups: test knob only)
+      // Sharded: the centre pass is NVLink-bound and its P2P throughput falls with the number of far-apart rows a
+      // tile gathers (2^last rows, 2^(n_loc ...) bytes apart): measured at 2^30 amplitudes per GPU on 2 B200s, 3-5
+      // group bits reach 91 % of the peer-copy peak, 6 bits 82 %, 7 bits 65 %, 8 bits 49 %
+      // (profiles/r1zz_centre_group_2gpu.log).  So the centre group is capped at 5 bits wherever that does not add
+      // a layout (= one more pair of HBM passes).
+      const int need = rest - (ng - 1) * gmax;  // fewest bits the last group can take with ng groups
+      last = std::max(std::max(wl, need), std::min(last, 5));
+    }
+    // experiment knob: size of the centre group (rows per centre tile = 2^last, run length 2^(12-last) amplitudes)
+    if (const char* e = std::getenv("QSB200_CENTRE_GROUP")) last = std::max(std::max(1, wl), std::min(gmax, atoi(e)));
     if (last > rest) last = rest;
     int others = rest - last;
     ng = 1 + (others + gmax - 1) / gmax;
