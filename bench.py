@@ -175,6 +175,12 @@ def cpu_zvode_rate(window=2.0e-3):
 
 
 # --------------------------------------------------------------------------------------------------------
+def workload_text(n, method):
+    """config.workload shared by both arms (the driver compares the two lines on the same config)."""
+    return (f"C4: single trajectory per GPU, N={n} spins (n_sea={n - 1}, Ga/Al constants, "
+            f"delta=50 kHz + 12.5 kHz*rank, rare drive ON), {method} step attempts")
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -185,8 +191,10 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": "ODE steps/s", "value": base["value"], "unit": "ODE steps/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"C4: single trajectory N={args.n_qubits} (n_sea={n_sea}), DP5 step attempts, CPU port",
-                   "n_qubits": args.n_qubits, "timing": "bounded row sample of one H-apply per step, extrapolated"},
+        "config": {"workload": workload_text(args.n_qubits, args.method), "n_qubits": args.n_qubits,
+                   "state_bytes": 16.0 * (1 << args.n_qubits), "method": args.method, "atol": 1e-10, "rtol": 1e-9,
+                   "arm": "CPU port of the reference's CSR row product (oracle/c), all host threads",
+                   "timing": "bounded row sample of one H-apply per step, scaled to 6 H-applies per step attempt"},
         "cpu_baseline": base,
         "e2e": {"value": base["value"], "unit": "ODE steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -401,9 +409,7 @@ def run_b200(args, rank, world, local_rank):
             "metric": "ODE steps/s", "value": value, "unit": "ODE steps/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"C4: single trajectory per GPU, N={n} spins (n_sea={n_sea}, Ga/Al constants, "
-                                   f"delta=50 kHz + 12.5 kHz*rank, rare drive ON), {args.method} step attempts",
-                       "n_qubits": n, "state_bytes": S, "method": args.method, "atol": 1e-10, "rtol": 1e-9,
+            "config": {"workload": workload_text(n, args.method), "n_qubits": n, "state_bytes": S, "method": args.method, "atol": 1e-10, "rtol": 1e-9,
                        "l2": "inputs larger than L2 (4.3 GB vectors vs 126 MB)", "parallelism": f"independent sweep points x{world}"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps),
             "clocks": clk.summary(),
