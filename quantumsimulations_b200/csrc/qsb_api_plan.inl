@@ -337,6 +337,11 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
   const size_t u_bytes = sizeof(cplx) * dim * dim;
   // trajectories per pass: keep the propagators of one pass within ~4 GiB
   int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n_traj, ((size_t)4 << 30) / u_bytes));
+  if (const char* e = getenv("QSB200_PROP_CHUNK")) chunk = std::max(1, std::min(chunk, atoi(e)));  // test knob
+  if (n_out > 0) {  // ... and their observable traces within ~2 GiB
+    const size_t per_traj = sizeof(double) * (size_t)n_out * QSB_NOBS;
+    chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)chunk, ((size_t)2 << 30) / per_traj));
+  }
 
   SmallDesc* d_desc = nullptr;
   double *d_t = nullptr, *d_obs = nullptr;

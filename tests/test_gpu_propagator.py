@@ -146,7 +146,7 @@ def test_full_size_reference_trajectory(golden_cases):
     assert np.max(np.abs(out["raw_norm"] - 1.0)) < 1e-7
 
 
-def test_per_trajectory_dt_and_determinism():
+def test_per_trajectory_dt_and_determinism(monkeypatch):
     from quantumsimulations_b200 import engine
 
     tables = [random_table(6, 40 + s) for s in range(4)]
@@ -156,6 +156,11 @@ def test_per_trajectory_dt_and_determinism():
     a, _ = engine.propagate_batch(tables, 25, dts, [_tight()] * 4)
     b, _ = engine.propagate_batch(tables, 25, dts, [_tight()] * 4)
     assert np.array_equal(a, b)
+    for chunk in ("3", "1"):   # several passes over the batch (what a grid too large for one pass gets)
+        monkeypatch.setenv("QSB200_PROP_CHUNK", chunk)
+        c, cst = engine.propagate_batch(tables, 25, dts, [_tight()] * 4)
+        assert np.array_equal(a, c) and all(s.path == 2 and s.n_rhs > 0 for s in cst)
+    monkeypatch.delenv("QSB200_PROP_CHUNK")
     for i in range(4):
         one, _ = engine.propagate_batch([tables[i]], 25, float(dts[i]), [_tight()])
         assert np.array_equal(one[0], a[i])
