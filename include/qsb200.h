@@ -126,10 +126,12 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
  *      psi_k exactly as qsb_evolve_batch reports them (U stays in shared memory / L2).
  * A 20000-output, 30-second trajectory (sweep_sea_detuning.py:1201-1252) then costs 2^n integrations over a few
  * integrator steps, ~10 dense squarings and 2 * 10^4 dense 2^n x 2^n matvecs instead of ~10^9 integrator steps.  Output k is the state at t0 + k dt for any
- * t0; dt is [n_traj] when dt_per_traj != 0, else one shared value.  out_obs: [n_traj][n_out][QSB_NOBS] host.       */
+ * t0; dt is [n_traj] when dt_per_traj != 0, else one shared value.  out_obs (host): [n_traj][n_out][QSB_NOBS], or
+ * [n_traj][QSB_NOBS][n_out] when obs_by_column != 0 (one contiguous trace per observable, the shape simulate_rare
+ * hands back, dipolar_ensemble_with_rare.py:671-679).                                                              */
 int qsb_propagate_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
                         const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
-                        double* out_obs, qsb_stats* stats, int device);
+                        int32_t obs_by_column, double* out_obs, qsb_stats* stats, int device);
 /* Step 1 alone, for parity tests: u_host[(j * 2^n + x) * 2 + {0,1}] = re, im of <x| exp(-i H dt) |j>.              */
 int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opts* opts, int32_t max_squarings,
                          double* u_host, qsb_stats* stats, int device);

@@ -173,12 +173,14 @@ def _check_grid(params: DipolarRareParams) -> np.ndarray:
     return np.linspace(0.0, params.t_final, params.steps)
 
 
-def _pack(obs: np.ndarray, override: bool, extra: bool) -> Dict[str, np.ndarray]:
-    out = {k: np.ascontiguousarray(obs[:, i]) for i, k in enumerate(TRACE_KEYS)}
+def _pack(obs: np.ndarray, override: bool, extra: bool, by_column: bool = False) -> Dict[str, np.ndarray]:
+    """``obs``: (n_out, NOBS), or (NOBS, n_out) with ``by_column`` (the propagator path's device layout: no copy)."""
+    cols = obs if by_column else np.ascontiguousarray(obs.T)   # the traces are the (contiguous) rows of cols
+    out = {k: cols[i] for i, k in enumerate(TRACE_KEYS)}
     # DE:669: norms of the stored (output-normalised) states; no states are stored when options is None
-    out["state_norm"] = np.ascontiguousarray(obs[:, 6]) if override else np.array([])
+    out["state_norm"] = cols[6] if override else np.array([])
     if extra:
-        out["raw_norm"] = np.ascontiguousarray(obs[:, 7])
+        out["raw_norm"] = cols[7]
     return out
 
 
@@ -201,7 +203,7 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
     opts, override = _options_from(params, method, tol_scale)
     if split_method(method, table.n, len(t))[1]:
         obs, stats = _propagate([table], [t], [opts], device)
-        out = _pack(obs[0], override, raw_norm)
+        out = _pack(obs[0], override, raw_norm, by_column=True)
         return (t, out, stats[0]) if return_stats else (t, out)
     with engine.Plan(table, device) as plan:
         if checkpoint is not None and table.n > engine.SMALL_MAX_QUBITS:
@@ -220,10 +222,17 @@ def _propagate(tables, grids, opts, device):
     """Propagator path for trajectories of equal N and equal number of outputs (their dt may differ)."""
     if tables[0].n > engine.SMALL_MAX_QUBITS:
         raise ValueError(f"method 'propagator' holds a dense 2^N x 2^N matrix on chip: N <= {engine.SMALL_MAX_QUBITS}")
-    dts = [engine.uniform_step(g) for g in grids]
+    seen: Dict[Tuple[float, float, int], Optional[float]] = {}   # sweeps share one grid: check each distinct one once
+    dts = []
+    for g in grids:
+        key = (float(g[0]), float(g[-1]), len(g))
+        if key not in seen:
+            seen[key] = engine.uniform_step(g)
+        dts.append(seen[key])
     if any(d is None for d in dts):
         raise ValueError("method 'propagator' needs a uniform output grid")
-    return engine.propagate_batch(tables, len(grids[0]), np.array(dts) if len(dts) > 1 else dts[0], opts, device)
+    return engine.propagate_batch(tables, len(grids[0]), np.array(dts) if len(dts) > 1 else dts[0], opts, device,
+                                  by_column=True)
 
 
 def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int = 0, method: Optional[str] = None,
@@ -242,13 +251,14 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
         groups.setdefault((tables[i].n, len(grids[i])), []).append(i)  # uniform n -> register-resident rows
     stats_out: List = [None] * n
     for _, idxs in groups.items():
-        if split_method(method, tables[idxs[0]].n, len(grids[idxs[0]]))[1]:   # one (N, steps) per group
+        prop = split_method(method, tables[idxs[0]].n, len(grids[idxs[0]]))[1]   # one (N, steps) per group
+        if prop:
             obs, stats = _propagate([tables[i] for i in idxs], [grids[i] for i in idxs], [om[i][0] for i in idxs], device)
         else:
             tgrid = np.stack([grids[i] for i in idxs])
             obs, stats = engine.evolve_batch([tables[i] for i in idxs], tgrid, [om[i][0] for i in idxs], device)
         for j, i in enumerate(idxs):
-            results[i] = (grids[i], _pack(obs[j], om[i][1], raw_norm))
+            results[i] = (grids[i], _pack(obs[j], om[i][1], raw_norm, by_column=prop))
             stats_out[i] = stats[j]
     for i in range(n):
         if results[i] is None:

@@ -317,7 +317,7 @@ static int auto_squarings(const qsb_table* t, double dt) {
 
 static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
                           const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
-                          double* out_obs, qsb_stats* stats, double* u_host, int device) {
+                          int32_t obs_by_column, double* out_obs, qsb_stats* stats, double* u_host, int device) {
   const int n = tables[0].n_qubits;
   for (int i = 0; i < n_traj; ++i) {
     int rc = check_table(&tables[i]);
@@ -404,7 +404,7 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
       QSB_CUDA(cudaGetLastError());
     }
     if (n_out > 0) {
-      rc = launch_small_propagate(d_desc, m, n, d_u, n_out, d_obs, st);
+      rc = launch_small_propagate(d_desc, m, n, d_u, n_out, d_obs, obs_by_column != 0, st);
       if (rc) return rc;
     }
     QSB_CUDA(cudaEventRecord(e1, st));
@@ -441,17 +441,17 @@ extern "C" {
 
 int qsb_propagate_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
                         const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
-                        double* out_obs, qsb_stats* stats, int device) {
+                        int32_t obs_by_column, double* out_obs, qsb_stats* stats, int device) {
   if (n_traj < 1 || !tables || !psi0_index || !opts || !out_obs || !dt || n_out < 1)
     return fail(QSB_ERR_BAD_ARG, "qsb_propagate_batch: null argument, n_traj < 1 or n_out < 1");
-  return propagate_impl(n_traj, tables, psi0_index, n_out, dt, dt_per_traj, opts, max_squarings, out_obs, stats, nullptr,
-                        device);
+  return propagate_impl(n_traj, tables, psi0_index, n_out, dt, dt_per_traj, opts, max_squarings, obs_by_column, out_obs,
+                        stats, nullptr, device);
 }
 
 int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opts* opts, int32_t max_squarings,
                          double* u_host, qsb_stats* stats, int device) {
   if (!table || !opts || !u_host) return fail(QSB_ERR_BAD_ARG, "qsb_build_propagator: null argument");
-  return propagate_impl(1, table, nullptr, 0, &dt, 0, opts, max_squarings, nullptr, stats, u_host, device);
+  return propagate_impl(1, table, nullptr, 0, &dt, 0, opts, max_squarings, 0, nullptr, stats, u_host, device);
 }
 
 int qsb_debug_squarings(const qsb_table* table, double dt, int32_t* n_squarings) {

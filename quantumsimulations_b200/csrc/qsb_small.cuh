@@ -54,8 +54,9 @@ void launch_small_columns(const SmallDesc* d_desc, int n_traj, int n, const doub
 void launch_small_square(cplx* d_columns, cplx* d_tmp, const int32_t* d_n_sq, int n_traj, int n, cudaStream_t stream);
 
 // psi_k = U psi_{k-1} for k < n_out with the observables of every psi_k (one CTA per trajectory, uniform n).
+// by_column != 0: d_obs is [n_traj][QSB_NOBS][n_out] instead of [n_traj][n_out][QSB_NOBS].
 int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cplx* d_columns, int64_t n_out,
-                           double* d_obs, cudaStream_t stream);
+                           double* d_obs, int by_column, cudaStream_t stream);
 // Launch shape of the propagate kernel for n qubits (host-only; exposed for tests).
 void small_propagate_shape(int n, int* threads, int* split, int* n_cache, int* ring, size_t* smem);
 

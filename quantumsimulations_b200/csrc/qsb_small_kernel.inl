@@ -166,7 +166,7 @@ small_evolve_kernel(const SmallDesc* __restrict__ descs, const double* __restric
 // Observable sums of one state by ONE warp (shuffle tree only, fixed order): lane l owns amplitudes l, l + 32, ...
 // Same sums and output columns as small_observe.
 __device__ __forceinline__ void warp_observe(const cplx* __restrict__ v, int dim, const SmallDesc& d,
-                                             double* __restrict__ out) {
+                                             double* __restrict__ out, int64_t ks) {  // column k goes to out[k * ks]
   const int lane = threadIdx.x & 31;
   double s[7] = {0, 0, 0, 0, 0, 0, 0};  // nrm2, zsea, zrare, csea.re, csea.im, crare.re, crare.im
   for (uint32_t x = lane; x < (uint32_t)dim; x += 32) {
@@ -193,14 +193,14 @@ __device__ __forceinline__ void warp_observe(const cplx* __restrict__ v, int dim
   }
   if (lane == 0) {
     double inv = 1.0 / s[0];
-    out[0] = s[3] * inv;        // Ix_sea
-    out[1] = s[4] * inv;        // Iy_sea
-    out[2] = 0.5 * s[1] * inv;  // Iz_sea
-    out[3] = 0.5 * s[2] * inv;  // Iz_R
-    out[4] = s[5] * inv;        // Ix_R
-    out[5] = s[6] * inv;        // Iy_R
-    out[6] = 1.0;               // norm of the output-normalised ket
-    out[7] = sqrt(s[0]);        // raw norm
+    out[0] = s[3] * inv;             // Ix_sea
+    out[ks] = s[4] * inv;            // Iy_sea
+    out[2 * ks] = 0.5 * s[1] * inv;  // Iz_sea
+    out[3 * ks] = 0.5 * s[2] * inv;  // Iz_R
+    out[4 * ks] = s[5] * inv;        // Ix_R
+    out[5 * ks] = s[6] * inv;        // Iy_R
+    out[6 * ks] = 1.0;               // norm of the output-normalised ket
+    out[7 * ks] = sqrt(s[0]);        // raw norm
   }
 }
 
@@ -219,7 +219,7 @@ __device__ __forceinline__ void warp_observe(const cplx* __restrict__ v, int dim
 template <int MAXT, int NREG>
 __global__ void __launch_bounds__(MAXT, 1)
 small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restrict__ ut_all, int64_t n_out,
-                       double* __restrict__ obs_all, int split, int n_cache, int ring) {
+                       double* __restrict__ obs_all, int split, int n_cache, int ring, int by_column) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   SmallShared& sh = *reinterpret_cast<SmallShared*>(smem_raw);
   const int traj = blockIdx.x;
@@ -289,7 +289,9 @@ small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restri
       if (worker && q == 0) states[(size_t)r * dim + x] = sum;
       __syncthreads();
     }
-    for (int r = warp; r < count; r += nwarp) warp_observe(states + (size_t)r * dim, dim, d, obs + (base + r) * QSB_NOBS);
+    // by_column: obs[traj][k][output] (what a caller that wants one contiguous trace per observable asks for)
+    for (int r = warp; r < count; r += nwarp)
+      warp_observe(states + (size_t)r * dim, dim, d, obs + (base + r) * (by_column ? 1 : QSB_NOBS), by_column ? n_out : 1);
     __syncthreads();
   }
 }
@@ -449,16 +451,16 @@ void launch_small_square(cplx* d_columns, cplx* d_tmp, const int32_t* d_n_sq, in
 }
 
 int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cplx* d_columns, int64_t n_out,
-                           double* d_obs, cudaStream_t stream) {
+                           double* d_obs, int by_column, cudaStream_t stream) {
   int threads, split, n_cache, ring;
   size_t smem;
   small_propagate_shape(n, &threads, &split, &n_cache, &ring, &smem);
   if (threads > 512) {
     QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<1024, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_propagate_kernel<1024, 0><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache, ring);
+    small_propagate_kernel<1024, 0><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache, ring, by_column);
   } else {
     QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<512, PROPAGATE_NREG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_propagate_kernel<512, PROPAGATE_NREG><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache, ring);
+    small_propagate_kernel<512, PROPAGATE_NREG><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache, ring, by_column);
   }
   QSB_CUDA(cudaGetLastError());
   return QSB_OK;

@@ -93,7 +93,7 @@ def load_library() -> C.CDLL:
     lib.qsb_evolve_batch.argtypes = [C.c_int32, C.POINTER(_Table), C.POINTER(C.c_uint64), C.c_int64, dp, C.c_int32,
                                      C.POINTER(_Opts), dp, C.POINTER(_Stats), C.c_int]
     lib.qsb_propagate_batch.argtypes = [C.c_int32, C.POINTER(_Table), C.POINTER(C.c_uint64), C.c_int64, dp, C.c_int32,
-                                        C.POINTER(_Opts), C.c_int32, dp, C.POINTER(_Stats), C.c_int]
+                                        C.POINTER(_Opts), C.c_int32, C.c_int32, dp, C.POINTER(_Stats), C.c_int]
     lib.qsb_build_propagator.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(_Opts), C.c_int32, dp,
                                          C.POINTER(_Stats), C.c_int]
     lib.qsb_debug_squarings.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(C.c_int32)]
@@ -409,10 +409,11 @@ def _max_squarings(value: Optional[int]) -> int:
 
 
 def propagate_batch(tables: Sequence[SpinTable], n_out: int, dt, opts: Sequence[SolverOptions], device: int = 0,
-                    max_squarings: Optional[int] = None):
+                    max_squarings: Optional[int] = None, by_column: bool = False):
     """Constant-H propagator path (qsb_propagate_batch): n <= 10, same n in every table, output k = state after k dt.
     ``dt``: one float or one per trajectory.  ``max_squarings``: cap on the scaling-and-squaring depth (None / < 0:
-    automatic, 0: integrate the columns over the whole dt).  Returns (obs [n_traj, n_out, NOBS], [Stats])."""
+    automatic, 0: integrate the columns over the whole dt).  Returns (obs [n_traj, n_out, NOBS], [Stats]), or with
+    ``by_column`` obs [n_traj, NOBS, n_out] (the device writes one contiguous trace per observable)."""
     lib = load_library()
     n = len(tables)
     if n == 0:
@@ -425,9 +426,10 @@ def propagate_batch(tables: Sequence[SpinTable], n_out: int, dt, opts: Sequence[
     psi0 = (C.c_uint64 * n)(*[t.psi0_index for t in tables])
     copts = (_Opts * n)(*[o.to_c() for o in opts])
     cstats = (_Stats * n)()
-    obs = np.empty((n, int(n_out), NOBS), dtype=np.float64)
+    obs = np.empty((n, NOBS, int(n_out)) if by_column else (n, int(n_out), NOBS), dtype=np.float64)
     code = lib.qsb_propagate_batch(n, ctabs, psi0, int(n_out), _dptr(dts), 1 if (dts.shape == (n,) and n > 1) else 0,
-                                   copts, _max_squarings(max_squarings), _dptr(obs), cstats, int(device))
+                                   copts, _max_squarings(max_squarings), 1 if by_column else 0, _dptr(obs), cstats,
+                                   int(device))
     stats = [Stats.from_c(s) for s in cstats]
     _check(code)
     return obs, stats

@@ -161,6 +161,8 @@ def test_per_trajectory_dt_and_determinism(monkeypatch):
         c, cst = engine.propagate_batch(tables, 25, dts, [_tight()] * 4)
         assert np.array_equal(a, c) and all(s.path == 2 and s.n_rhs > 0 for s in cst)
     monkeypatch.delenv("QSB200_PROP_CHUNK")
+    cc, _ = engine.propagate_batch(tables, 25, dts, [_tight()] * 4, by_column=True)   # one contiguous trace per observable
+    assert cc.shape == (4, 8, 25) and np.array_equal(cc.transpose(0, 2, 1), a)
     for i in range(4):
         one, _ = engine.propagate_batch([tables[i]], 25, float(dts[i]), [_tight()])
         assert np.array_equal(one[0], a[i])
