@@ -240,7 +240,13 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
     """Independent trajectories; those with N <= 10 share ONE kernel launch (one CTA each)."""
     n = len(params_list)
     results: List = [None] * n
-    grids = [_check_grid(p) for p in params_list]
+    base_grids: Dict[Tuple[float, int], np.ndarray] = {}   # a sweep's trajectories share one grid: build it once
+    grids = []
+    for p in params_list:
+        key = (float(p.t_final), int(p.steps))
+        if key not in base_grids:
+            base_grids[key] = _check_grid(p)
+        grids.append(base_grids[key])
     tables = [compile_table(p) for p in params_list]
     om = [_options_from(p, method, tol_scale) for p in params_list]
     if any(split_method(method, t.n, len(g))[1] and t.n > engine.SMALL_MAX_QUBITS for t, g in zip(tables, grids)):
@@ -258,12 +264,12 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
             tgrid = np.stack([grids[i] for i in idxs])
             obs, stats = engine.evolve_batch([tables[i] for i in idxs], tgrid, [om[i][0] for i in idxs], device)
         for j, i in enumerate(idxs):
-            results[i] = (grids[i], _pack(obs[j], om[i][1], raw_norm, by_column=prop))
+            results[i] = (grids[i].copy(), _pack(obs[j], om[i][1], raw_norm, by_column=prop))
             stats_out[i] = stats[j]
     for i in range(n):
         if results[i] is None:
             with engine.Plan(tables[i], device) as plan:
                 obs, st = plan.evolve(grids[i], om[i][0])
-            results[i] = (grids[i], _pack(obs, om[i][1], raw_norm))
+            results[i] = (grids[i].copy(), _pack(obs, om[i][1], raw_norm))
             stats_out[i] = st
     return results, stats_out
