@@ -381,6 +381,38 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
   }
   if (n_out > 0) QSB_CUDA(cudaMalloc(&d_obs, sizeof(double) * chunk * n_out * QSB_NOBS));
 
+  // Time-split chains: a trajectory's outputs are cut into segments of 2^seg_lb outputs that run as separate CTAs, each
+  // from its own seed psi_{c 2^seg_lb} = (U^(2^seg_lb))^c psi_0 (seg_lb more squarings of a copy of U, then a chain of
+  // n_seg matvecs that stores states).  The segment length depends on n_out ONLY (~128 segments, at least 64 outputs
+  // each), so a trajectory's traces do not depend on what else is in the batch.
+  int seg_lb = 0, n_seg = 1;
+  int64_t seg_len = n_out;
+  if (n_out >= 256) {
+    seg_lb = 6;
+    while (((int64_t)1 << seg_lb) * 128 < n_out) ++seg_lb;
+    if (const char* e = getenv("QSB200_PROP_SEGMENT")) seg_lb = std::max(0, std::min(40, atoi(e)));  // 0: no split
+    if (seg_lb > 0 && ((int64_t)1 << seg_lb) < n_out) {
+      seg_len = (int64_t)1 << seg_lb;
+      n_seg = (int)((n_out + seg_len - 1) / seg_len);
+    } else {
+      seg_lb = 0;
+    }
+  }
+  struct FreeList { std::vector<void*> p; ~FreeList() { for (void* q : p) cudaFree(q); } } extra;
+  cplx *d_v = nullptr, *d_seeds = nullptr;
+  int32_t* d_seg_sq = nullptr;
+  std::vector<int32_t> seg_sq(chunk, seg_lb);
+  if (n_seg > 1) {
+    QSB_CUDA(cudaMalloc(&d_v, u_bytes * chunk));
+    extra.p.push_back(d_v);
+    QSB_CUDA(cudaMalloc(&d_seeds, sizeof(cplx) * dim * (size_t)n_seg * chunk));
+    extra.p.push_back(d_seeds);
+    QSB_CUDA(cudaMalloc(&d_seg_sq, sizeof(int32_t) * chunk));
+    extra.p.push_back(d_seg_sq);
+    if (!d_tmp) QSB_CUDA(cudaMalloc(&d_tmp, u_bytes * chunk));  // freed by `cleanup`
+    QSB_CUDA(cudaMemcpyAsync(d_seg_sq, seg_sq.data(), sizeof(int32_t) * chunk, cudaMemcpyHostToDevice, st));
+  }
+
   std::vector<SmallDesc> descs(chunk);
   std::vector<double> tp(2 * (size_t)chunk);
   std::vector<SmallStats> hs((size_t)chunk * dim);
@@ -403,7 +435,15 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
       launch_small_square(d_u, d_tmp, d_sq, m, n, st);
       QSB_CUDA(cudaGetLastError());
     }
-    if (n_out > 0) {
+    if (n_out > 0 && n_seg > 1) {
+      QSB_CUDA(cudaMemcpyAsync(d_v, d_u, u_bytes * m, cudaMemcpyDeviceToDevice, st));
+      launch_small_square(d_v, d_tmp, d_seg_sq, m, n, st);                                        // V = U^seg_len
+      QSB_CUDA(cudaGetLastError());
+      rc = launch_small_propagate(d_desc, m, n, d_v, n_seg, nullptr, 0, st, nullptr, 1, n_seg, d_seeds);  // seeds
+      if (rc) return rc;
+      rc = launch_small_propagate(d_desc, m, n, d_u, n_out, d_obs, obs_by_column != 0, st, d_seeds, n_seg, seg_len, nullptr);
+      if (rc) return rc;
+    } else if (n_out > 0) {
       rc = launch_small_propagate(d_desc, m, n, d_u, n_out, d_obs, obs_by_column != 0, st);
       if (rc) return rc;
     }

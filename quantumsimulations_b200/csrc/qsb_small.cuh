@@ -55,8 +55,12 @@ void launch_small_square(cplx* d_columns, cplx* d_tmp, const int32_t* d_n_sq, in
 
 // psi_k = U psi_{k-1} for k < n_out with the observables of every psi_k (one CTA per trajectory, uniform n).
 // by_column != 0: d_obs is [n_traj][QSB_NOBS][n_out] instead of [n_traj][n_out][QSB_NOBS].
+// Time-split chains: with d_seeds (psi at the first output of each of the n_seg segments of seg_len outputs,
+// [n_traj][n_seg][2^n]) the launch has n_traj * n_seg CTAs.  d_states_out != nullptr: store the states instead of the
+// observables ([n_traj][n_out][2^n]); that is how the seeds are produced, from U^seg_len and n_out = n_seg.
 int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cplx* d_columns, int64_t n_out,
-                           double* d_obs, int by_column, cudaStream_t stream);
+                           double* d_obs, int by_column, cudaStream_t stream, const cplx* d_seeds = nullptr,
+                           int n_seg = 1, int64_t seg_len = 0, cplx* d_states_out = nullptr);
 // Launch shape of the propagate kernel for n qubits (host-only; exposed for tests).
 void small_propagate_shape(int n, int* threads, int* split, int* n_cache, int* ring, size_t* smem);
 

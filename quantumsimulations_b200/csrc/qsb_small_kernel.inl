@@ -219,10 +219,15 @@ __device__ __forceinline__ void warp_observe(const cplx* __restrict__ v, int dim
 template <int MAXT, int NREG>
 __global__ void __launch_bounds__(MAXT, 1)
 small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restrict__ ut_all, int64_t n_out,
-                       double* __restrict__ obs_all, int split, int n_cache, int ring, int by_column) {
+                       double* __restrict__ obs_all, int split, int n_cache, int ring, int by_column,
+                       const cplx* __restrict__ seeds, int n_seg, int64_t seg_len, cplx* __restrict__ states_out) {
+  // Time-split chains: CTA b works on segment c = b % n_seg of trajectory b / n_seg, i.e. on the outputs
+  // [c seg_len, min((c + 1) seg_len, n_out)), starting from seeds[b] = psi_{c seg_len} (seeds == nullptr, n_seg == 1: the
+  // whole chain from the basis state).  states_out != nullptr: the states themselves are stored instead of their
+  // observables (states_out[traj][output][x]) - how the seeds are made, with U^seg_len in place of U.
   extern __shared__ __align__(16) unsigned char smem_raw[];
   SmallShared& sh = *reinterpret_cast<SmallShared*>(smem_raw);
-  const int traj = blockIdx.x;
+  const int traj = blockIdx.x / n_seg, seg = blockIdx.x - traj * n_seg;
   {
     const int* src = reinterpret_cast<const int*>(descs + traj);
     int* dst = reinterpret_cast<int*>(&sh.d);
@@ -239,10 +244,13 @@ small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restri
   const int q = ql & (split - 1);
   const int x = 8 * (warp * (4 / split) + ql / split) + xl;
   const bool worker = x < dim;
+  const int64_t o0 = (int64_t)seg * seg_len;                                  // first output of this CTA
+  const int64_t n_mine = (n_out - o0 < seg_len) ? n_out - o0 : seg_len;       // outputs of this CTA
   double* obs = obs_all + (size_t)traj * n_out * QSB_NOBS;
 
   for (int i = threadIdx.x; i < n_cache * dim; i += blockDim.x) us[i] = ut[i];
-  for (int i = threadIdx.x; i < dim; i += blockDim.x) states[i] = mk((uint32_t)i == d.psi0 ? 1.0 : 0.0, 0.0);
+  for (int i = threadIdx.x; i < dim; i += blockDim.x)
+    states[i] = seeds ? seeds[(size_t)blockIdx.x * dim + i] : mk((uint32_t)i == d.psi0 ? 1.0 : 0.0, 0.0);
   // first column of this thread that is not in shared memory, and the register-resident columns from there on
   int j_tail = q;
   while (j_tail < n_cache) j_tail += split;
@@ -254,8 +262,8 @@ small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restri
   }
   __syncthreads();
 
-  for (int64_t base = 0; base < n_out; base += ring) {  // slot r of this round holds psi_{base + r}
-    const int count = (int)((n_out - base < ring) ? n_out - base : ring);
+  for (int64_t base = 0; base < n_mine; base += ring) {  // slot r of this round holds psi_{o0 + base + r}
+    const int count = (int)((n_mine - base < ring) ? n_mine - base : ring);
     for (int r = (base == 0 ? 1 : 0); r < count; ++r) {
       const cplx* cur = states + (size_t)(r == 0 ? ring - 1 : r - 1) * dim;
       cplx a0 = mk(0, 0), a1 = mk(0, 0);
@@ -290,8 +298,14 @@ small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restri
       __syncthreads();
     }
     // by_column: obs[traj][k][output] (what a caller that wants one contiguous trace per observable asks for)
-    for (int r = warp; r < count; r += nwarp)
-      warp_observe(states + (size_t)r * dim, dim, d, obs + (base + r) * (by_column ? 1 : QSB_NOBS), by_column ? n_out : 1);
+    if (states_out) {
+      cplx* dst = states_out + ((size_t)traj * n_out + o0 + base) * dim;
+      for (int i = threadIdx.x; i < count * dim; i += blockDim.x) dst[i] = states[i];
+    } else {
+      for (int r = warp; r < count; r += nwarp)
+        warp_observe(states + (size_t)r * dim, dim, d, obs + (o0 + base + r) * (by_column ? 1 : QSB_NOBS),
+                     by_column ? n_out : 1);
+    }
     __syncthreads();
   }
 }
@@ -451,16 +465,22 @@ void launch_small_square(cplx* d_columns, cplx* d_tmp, const int32_t* d_n_sq, in
 }
 
 int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cplx* d_columns, int64_t n_out,
-                           double* d_obs, int by_column, cudaStream_t stream) {
+                           double* d_obs, int by_column, cudaStream_t stream, const cplx* d_seeds, int n_seg,
+                           int64_t seg_len, cplx* d_states_out) {
   int threads, split, n_cache, ring;
   size_t smem;
   small_propagate_shape(n, &threads, &split, &n_cache, &ring, &smem);
+  if (n_seg < 1) n_seg = 1;
+  if (seg_len < 1) seg_len = n_out;
+  const unsigned grid = (unsigned)n_traj * (unsigned)n_seg;
   if (threads > 512) {
     QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<1024, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_propagate_kernel<1024, 0><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache, ring, by_column);
+    small_propagate_kernel<1024, 0><<<grid, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache, ring,
+                                                                     by_column, d_seeds, n_seg, seg_len, d_states_out);
   } else {
     QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<512, PROPAGATE_NREG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    small_propagate_kernel<512, PROPAGATE_NREG><<<n_traj, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache, ring, by_column);
+    small_propagate_kernel<512, PROPAGATE_NREG><<<grid, threads, smem, stream>>>(
+        d_desc, d_columns, n_out, d_obs, split, n_cache, ring, by_column, d_seeds, n_seg, seg_len, d_states_out);
   }
   QSB_CUDA(cudaGetLastError());
   return QSB_OK;

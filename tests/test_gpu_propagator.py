@@ -227,3 +227,29 @@ def test_full_size_sweep_reproduces_reference_metrics(tmp_path):
                     assert got[k] == pytest.approx(want[k], abs=2e-3), k
             else:
                 assert got[k] == pytest.approx(want[k], rel=1e-9, abs=1e-12), k
+
+
+@pytest.mark.parametrize("n", [3, 6, 7, 9])
+def test_time_split_chain_matches_unsplit(n, monkeypatch):
+    """Chains of >= 256 outputs are cut into segments that run as separate CTAs from seeds (U^L)^c psi_0.  The result
+    must equal the single sequential chain to rounding, for any segment length, with a ragged last segment, in both
+    observable layouts, and must not depend on the batch a trajectory is part of."""
+    from quantumsimulations_b200 import engine
+
+    tables = [random_table(n, 900 + 10 * n + s) for s in range(3)]
+    n_out, dt = 1000, 0.05          # default: 64-output segments -> 15 full ones + 40 outputs
+    monkeypatch.delenv("QSB200_PROP_SEGMENT", raising=False)
+    a, _ = engine.propagate_batch(tables, n_out, dt, [_tight()] * 3)
+    one, _ = engine.propagate_batch(tables[1:2], n_out, dt, [_tight()])
+    assert np.array_equal(one[0], a[1])
+    col, _ = engine.propagate_batch(tables, n_out, dt, [_tight()] * 3, by_column=True)
+    assert np.array_equal(col.transpose(0, 2, 1), a)
+    monkeypatch.setenv("QSB200_PROP_SEGMENT", "0")
+    whole, _ = engine.propagate_batch(tables, n_out, dt, [_tight()] * 3)
+    assert np.max(np.abs(a - whole)) < 1e-10 and not np.array_equal(a, whole)
+    for lb in ("7", "9"):
+        monkeypatch.setenv("QSB200_PROP_SEGMENT", lb)
+        other, _ = engine.propagate_batch(tables, n_out, dt, [_tight()] * 3)
+        assert np.max(np.abs(other - whole)) < 1e-10
+    want = exact_traces(tables[0], dt * np.arange(n_out))
+    assert max(float(np.max(np.abs(a[0][:, j] - want[k]))) for j, k in enumerate(KEYS)) < 1e-8
