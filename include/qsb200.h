@@ -122,11 +122,12 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
  *      call in one launch), and the matrix is squared s times on chip (scaling and squaring).  s is chosen per
  *      trajectory so that ||H|| dt / 2^s <= ~8 (qsb_debug_squarings), capped by max_squarings (< 0: no cap; 0: the
  *      columns are integrated over the whole interval);
- *   2. one CTA per trajectory applies psi_k = U psi_{k-1} for k = 1 .. n_out-1 and reduces the observables of every
- *      psi_k exactly as qsb_evolve_batch reports them (U stays in shared memory / L2).
+ *   2. psi_k = U psi_{k-1} for k = 1 .. n_out-1 with the observables of every psi_k reduced exactly as
+ *      qsb_evolve_batch reports them (U stays in shared memory / registers / L2).  Chains of >= 256 outputs are cut
+ *      into ~128 segments of 2^k outputs, each its own CTA, seeded with (U^(2^k))^c psi_0; k depends on n_out only.
  * A 20000-output, 30-second trajectory (sweep_sea_detuning.py:1201-1252) then costs 2^n integrations over a few
- * integrator steps, ~10 dense squarings and 2 * 10^4 dense 2^n x 2^n matvecs instead of ~10^9 integrator steps.  Output k is the state at t0 + k dt for any
- * t0; dt is [n_traj] when dt_per_traj != 0, else one shared value.  out_obs (host): [n_traj][n_out][QSB_NOBS], or
+ * integrator steps, ~20 dense squarings and 2 * 10^4 dense 2^n x 2^n matvecs instead of ~10^9 integrator steps.
+ * Output k is the state at t0 + k dt for any t0; dt is [n_traj] when dt_per_traj != 0, else one shared value.  out_obs (host): [n_traj][n_out][QSB_NOBS], or
  * [n_traj][QSB_NOBS][n_out] when obs_by_column != 0 (one contiguous trace per observable, the shape simulate_rare
  * hands back, dipolar_ensemble_with_rare.py:671-679).                                                              */
 int qsb_propagate_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
