@@ -310,6 +310,112 @@ small_propagate_kernel(const SmallDesc* __restrict__ descs, const cplx* __restri
   }
 }
 
+// n = 7 (the reference's sweep geometry) variant of small_propagate_kernel with TWO rows per thread, which halves the
+// psi_j operand loads (45 % of the shared-memory wavefronts of the one-row kernel).  512 threads; lane l of warp w is
+// (xl = l & 3, q = l >> 2): rows x = 4 w + xl and x + 64, columns j = q (mod 8).  A quarter warp reads two 64-byte
+// pieces of neighbouring columns; the cached columns are stored with a stride of 128 + 4 elements so that those two
+// pieces fall into different halves of the 32 banks.  Everything else (ring of states, per-warp observables, time-split
+// segments, seeds, bitwise-fixed reduction order) is as in the general kernel.
+constexpr int P2_DIM = 128, P2_CS = P2_DIM + 4, P2_SPLIT = 8, P2_NREG = 4, P2_THREADS = 512;
+
+__global__ void __launch_bounds__(P2_THREADS, 1)
+small_propagate_kernel_n7(const SmallDesc* __restrict__ descs, const cplx* __restrict__ ut_all, int64_t n_out,
+                          double* __restrict__ obs_all, int n_cache, int ring, int by_column,
+                          const cplx* __restrict__ seeds, int n_seg, int64_t seg_len, cplx* __restrict__ states_out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  SmallShared& sh = *reinterpret_cast<SmallShared*>(smem_raw);
+  const int traj = blockIdx.x / n_seg, seg = blockIdx.x - traj * n_seg;
+  {
+    const int* src = reinterpret_cast<const int*>(descs + traj);
+    int* dst = reinterpret_cast<int*>(&sh.d);
+    for (int i = threadIdx.x; i < (int)(sizeof(SmallDesc) / 4); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  const SmallDesc& d = sh.d;
+  constexpr int dim = P2_DIM;
+  cplx* states = reinterpret_cast<cplx*>(smem_raw + ((sizeof(SmallShared) + 15) & ~size_t(15)));  // [ring][dim]
+  cplx* us = states + (size_t)ring * dim;                                                       // [n_cache][P2_CS]
+  const cplx* __restrict__ ut = ut_all + (size_t)traj * dim * dim;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = P2_THREADS / 32;
+  const int q = lane >> 2;
+  const int x = 4 * warp + (lane & 3);  // second row: x + 64
+  const int64_t o0 = (int64_t)seg * seg_len;
+  const int64_t n_mine = (n_out - o0 < seg_len) ? n_out - o0 : seg_len;
+  double* obs = obs_all + (size_t)traj * n_out * QSB_NOBS;
+
+  for (int i = threadIdx.x; i < n_cache * dim; i += blockDim.x) us[(i >> 7) * P2_CS + (i & (dim - 1))] = ut[i];
+  for (int i = threadIdx.x; i < dim; i += blockDim.x)
+    states[i] = seeds ? seeds[(size_t)blockIdx.x * dim + i] : mk((uint32_t)i == d.psi0 ? 1.0 : 0.0, 0.0);
+  int j_tail = q;
+  while (j_tail < n_cache) j_tail += P2_SPLIT;
+  cplx ur0[P2_NREG], ur1[P2_NREG];  // register-resident columns j_tail + 8 r of both rows
+#pragma unroll
+  for (int r = 0; r < P2_NREG; ++r) {
+    const int j = j_tail + r * P2_SPLIT;
+    ur0[r] = j < dim ? ut[(size_t)j * dim + x] : mk(0, 0);
+    ur1[r] = j < dim ? ut[(size_t)j * dim + x + 64] : mk(0, 0);
+  }
+  __syncthreads();
+
+  for (int64_t base = 0; base < n_mine; base += ring) {
+    const int count = (int)((n_mine - base < ring) ? n_mine - base : ring);
+    for (int r = (base == 0 ? 1 : 0); r < count; ++r) {
+      const cplx* cur = states + (size_t)(r == 0 ? ring - 1 : r - 1) * dim;
+      cplx a0 = mk(0, 0), a1 = mk(0, 0), b0 = mk(0, 0), b1 = mk(0, 0);
+      int j = q;
+      for (; j + P2_SPLIT < n_cache; j += 2 * P2_SPLIT) {
+        const cplx p0 = cur[j], p1 = cur[j + P2_SPLIT];
+        caxpy(a0, us[j * P2_CS + x], p0);
+        caxpy(b0, us[j * P2_CS + x + 64], p0);
+        caxpy(a1, us[(j + P2_SPLIT) * P2_CS + x], p1);
+        caxpy(b1, us[(j + P2_SPLIT) * P2_CS + x + 64], p1);
+      }
+      if (j < n_cache) {
+        const cplx p0 = cur[j];
+        caxpy(a0, us[j * P2_CS + x], p0);
+        caxpy(b0, us[j * P2_CS + x + 64], p0);
+        j += P2_SPLIT;
+      }
+#pragma unroll
+      for (int rr = 0; rr < P2_NREG; ++rr) {
+        if (j < dim) {
+          const cplx p0 = cur[j];
+          caxpy((rr & 1) ? a1 : a0, ur0[rr], p0);
+          caxpy((rr & 1) ? b1 : b0, ur1[rr], p0);
+        }
+        j += P2_SPLIT;
+      }
+      for (; j < dim; j += P2_SPLIT) {  // only if fewer columns are cached than the launcher normally arranges
+        const cplx p0 = cur[j];
+        caxpy(a0, __ldg(ut + (size_t)j * dim + x), p0);
+        caxpy(b0, __ldg(ut + (size_t)j * dim + x + 64), p0);
+      }
+      cplx sa = a0 + a1, sb = b0 + b1;
+#pragma unroll
+      for (int off = 4; off < 32; off <<= 1) {  // the 8 partial sums of a row: lanes differing in q
+        sa.x += __shfl_xor_sync(0xffffffffu, sa.x, off);
+        sa.y += __shfl_xor_sync(0xffffffffu, sa.y, off);
+        sb.x += __shfl_xor_sync(0xffffffffu, sb.x, off);
+        sb.y += __shfl_xor_sync(0xffffffffu, sb.y, off);
+      }
+      if (q == 0) {
+        states[(size_t)r * dim + x] = sa;
+        states[(size_t)r * dim + x + 64] = sb;
+      }
+      __syncthreads();
+    }
+    if (states_out) {
+      cplx* dst = states_out + ((size_t)traj * n_out + o0 + base) * dim;
+      for (int i = threadIdx.x; i < count * dim; i += blockDim.x) dst[i] = states[i];
+    } else {
+      for (int r = warp; r < count; r += nwarp)
+        warp_observe(states + (size_t)r * dim, dim, d, obs + (o0 + base + r) * (by_column ? 1 : QSB_NOBS),
+                     by_column ? n_out : 1);
+    }
+    __syncthreads();
+  }
+}
+
 // U <- U^(2^s): s = n_sq[traj] in-place squarings of one column-major propagator per CTA (scaling and squaring: the
 // columns were integrated over dt / 2^s only).  C[x][j] = sum_k A[x][k] A[k][j]; thread (x, q) owns row x of the
 // columns j = 4 (q + split i) .. +3, so the A[x][k] load is coalesced over x and shared by four accumulators while
@@ -473,6 +579,17 @@ int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cpl
   if (n_seg < 1) n_seg = 1;
   if (seg_len < 1) seg_len = n_out;
   const unsigned grid = (unsigned)n_traj * (unsigned)n_seg;
+  if (n == 7 && !getenv("QSB200_PROP_ONE_ROW")) {  // two rows per thread, padded column stride
+    const size_t fixed = ((sizeof(SmallShared) + 15) & ~size_t(15)) + (size_t)ring * P2_DIM * sizeof(cplx);
+    int nc = (int)((PROPAGATE_SMEM_MAX - fixed) / ((size_t)P2_CS * sizeof(cplx)));
+    if (nc > P2_DIM) nc = P2_DIM;
+    const size_t smem2 = fixed + (size_t)nc * P2_CS * sizeof(cplx);
+    QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel_n7, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    small_propagate_kernel_n7<<<grid, P2_THREADS, smem2, stream>>>(d_desc, d_columns, n_out, d_obs, nc, ring, by_column,
+                                                                   d_seeds, n_seg, seg_len, d_states_out);
+    QSB_CUDA(cudaGetLastError());
+    return QSB_OK;
+  }
   if (threads > 512) {
     QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel<1024, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     small_propagate_kernel<1024, 0><<<grid, threads, smem, stream>>>(d_desc, d_columns, n_out, d_obs, split, n_cache, ring,
