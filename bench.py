@@ -122,36 +122,51 @@ def ncu_traffic():
 # --------------------------------------------------------------------------------------------------------
 # CPU baseline (oracle port): the row-gather product a CSR matvec performs, matrix-free, OpenMP on all cores
 # --------------------------------------------------------------------------------------------------------
-def cpu_port_step_rate(n_sea, delta_hz, budget_s=15.0, samples=1):
-    from oracle.c import build as oc
-    from quantumsimulations_b200 import compile_table
+class CpuPort:
+    """oracle/c on the C4 table with every host core (the team size is forced: torchrun exports OMP_NUM_THREADS=1)."""
 
-    table = compile_table(sweep_params(n_sea, delta_hz))
-    bm = table.bit_major()
-    n = table.n
-    psi = np.zeros(1 << n, dtype=np.complex128)
-    rng = np.random.default_rng(0)
-    psi[: 1 << 20] = rng.normal(size=1 << 20) + 1j * rng.normal(size=1 << 20)
-    psi[table.psi0_index] = 1.0
-    rows = 1 << 16
-    t0 = time.perf_counter()
-    oc.apply_h(bm["h"], bm["J"], psi, 0, rows)
-    per_row = (time.perf_counter() - t0) / rows
-    rows = int(min(1 << n, max(1 << 16, budget_s / samples / per_row)))
-    rows = 1 << (rows.bit_length() - 1)
-    rates, secs = [], []
-    for s in range(samples):
-        row0 = (s * rows) % (1 << n)
+    def __init__(self, n_sea, delta_hz):
+        from oracle.c import build as oc
+        from quantumsimulations_b200 import compile_table
+
+        self.oc = oc
+        self.cores = oc.set_threads(os.cpu_count() or 1)
+        table = compile_table(sweep_params(n_sea, delta_hz))
+        self.bm = table.bit_major()
+        self.n = table.n
+        self.psi = np.zeros(1 << self.n, dtype=np.complex128)
+        rng = np.random.default_rng(0)
+        self.psi[: 1 << 20] = rng.normal(size=1 << 20) + 1j * rng.normal(size=1 << 20)
+        self.psi[table.psi0_index] = 1.0
+
+    def seconds(self, row0, rows):
         t0 = time.perf_counter()
-        oc.apply_h(bm["h"], bm["J"], psi, row0, row0 + rows)
-        dt = time.perf_counter() - t0
-        secs.append(dt)
-        rates.append(1.0 / (6.0 * dt * (1 << n) / rows))   # 6 H-applies per DP5 step attempt; axpys not charged
-    return {"value": float(np.mean(rates)), "unit": "ODE steps/s", "cores": oc.max_threads(), "kind": "port",
-            "sample": f"rows [0,2^{rows.bit_length()-1}) of one matrix-free H-apply at N={n} "
-                      f"({np.mean(secs):.1f} s each, x{samples}), scaled to 6 full H-applies per DP5 step; "
-                      "stage axpys not charged to the CPU",
-            "seconds_per_sample": secs}
+        self.oc.apply_h(self.bm["h"], self.bm["J"], self.psi, row0, row0 + rows)
+        return time.perf_counter() - t0
+
+    def rows_for(self, budget_s):
+        """Largest power-of-two row count (at most the whole vector) whose H-apply fits budget_s."""
+        self.seconds(0, 1 << 14)                      # first touch / thread start-up
+        per_row = self.seconds(0, 1 << 18) / (1 << 18)
+        rows = int(min(1 << self.n, max(1 << 18, budget_s / per_row)))
+        return 1 << (rows.bit_length() - 1)
+
+    def sample_text(self, rows, secs):
+        whole = rows == 1 << self.n
+        what = (f"one COMPLETE matrix-free H-apply (all 2^{self.n} rows)" if whole else
+                f"EXTRAPOLATED from rows [0,2^{rows.bit_length() - 1}) of one matrix-free H-apply at N={self.n}")
+        return (f"{what}, {np.mean(secs):.1f} s each x{len(secs)}, scaled to the 6 H-applies of a DP5 step attempt; "
+                "the stage axpys / error norm of the step are not charged to the CPU")
+
+
+def cpu_port_step_rate(n_sea, delta_hz, budget_s=25.0, samples=1):
+    port = CpuPort(n_sea, delta_hz)
+    rows = port.rows_for(budget_s / samples)
+    secs = [port.seconds((s * rows) % (1 << port.n), rows) for s in range(samples)]
+    rates = [1.0 / (6.0 * dt * (1 << port.n) / rows) for dt in secs]   # 6 H-applies per DP5 step attempt
+    return {"value": float(np.mean(rates)), "unit": "ODE steps/s", "cores": port.cores, "kind": "port",
+            "sample": port.sample_text(rows, secs), "extrapolated": rows != 1 << port.n,
+            "rows_timed": rows, "seconds_per_sample": secs}
 
 
 def cpu_zvode_rate(window=2.0e-3):
@@ -174,6 +189,112 @@ def cpu_zvode_rate(window=2.0e-3):
             "n_steps": st["n_steps"], "kind": "port (SciPy zvode-Adams, QuTiP's default integrator)"}
 
 
+def _zvode_one(args):
+    """One N=7 sweep point on the reference-equivalent integrator over a bounded window (worker of the all-cores leg)."""
+    delta, variant, window = args
+    from oracle import dense, solvers
+    from quantumsimulations_b200 import compile_table
+
+    p = sweep_params(6, delta, variant, t_final=window, steps=5)
+    table = compile_table(p)
+    bm = table.bit_major()
+    H = dense.csr_from_table(bm["h"], bm["J"])
+    psi0 = np.zeros(table.dim, complex)
+    psi0[table.psi0_index] = 1.0
+    _, _, _, st = solvers.evolve_csr(H, psi0, np.linspace(0, p.t_final, p.steps), [], backend="zvode", atol=p.solver_atol,
+                                     rtol=p.solver_rtol, nsteps=p.solver_nsteps, max_step=p.solver_max_step)
+    return st["n_steps"], st["n_rhs"]
+
+
+def cpu_zvode_sweep_all_cores(window=1.0e-3):
+    """SURVEY 8(d) CPU baseline (ii): the 39-trajectory C2 sweep as independent processes on ALL host cores, each
+    trajectory integrated by SciPy zvode-Adams (what QuTiP drives) over a bounded window; the full-size wall is the
+    window's wall scaled by 30 s / window."""
+    cores = os.cpu_count() or 1
+    env = dict(os.environ, OMP_NUM_THREADS="1", OPENBLAS_NUM_THREADS="1", MKL_NUM_THREADS="1", CUDA_VISIBLE_DEVICES="")
+    t0 = time.perf_counter()
+    procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--zvode-worker", f"{i}/{cores}/{window}"],
+                              stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, env=env) for i in range(cores)]
+    outs = [p.communicate()[0] for p in procs]
+    wall = time.perf_counter() - t0
+    steps, count = 0.0, 0
+    for o in outs:
+        for ln in o.strip().splitlines():
+            if ln.startswith("{"):
+                d = json.loads(ln)
+                steps += d["steps"]
+                count += d["trajectories"]
+    return {"cores": cores, "trajectories": count, "window_s": window, "wall_s": wall, "steps": steps,
+            "steps_per_s_all_cores": steps / wall, "extrapolated_full_sweep_wall_s": wall * 30.0 / window,
+            "kind": "port (SciPy zvode-Adams, one process per host core, trajectories dealt round-robin; includes "
+                    "interpreter start-up)"}
+
+
+def zvode_worker(spec):
+    i, cores, window = spec.split("/")
+    dets = np.linspace(0.0, 3.0 * F1A, 13)
+    jobs = [(d, v, float(window)) for d in dets for v in ("center_off", "center_on", "shell_off")][int(i)::int(cores)]
+    res = [_zvode_one(j) for j in jobs]
+    print(json.dumps({"trajectories": len(jobs), "steps": float(sum(r[0] for r in res))}), flush=True)
+
+
+def c1_leg(device, with_cpu):
+    """BASELINE config 1: ONE trajectory at the reference's own sizes, through simulate_rare.
+    (i) the sweep's N = 7 point (SW:1201-1252: 30 s, 20000 outputs); (ii) the dataclass-default N = 13 icosahedron
+    (DE:332-384 with is_spin_three_half=False: 0.02 s, 2000 outputs, QuTiP default tolerances)."""
+    from oracle import dense, solvers
+    from quantumsimulations_b200 import DipolarRareParams, compile_table, simulate_rare
+
+    out = {}
+    p7 = sweep_params(6, 50e3, t_final=30.0, steps=20000)
+    simulate_rare(sweep_params(6, 50e3, t_final=3e-3, steps=200), device=device)           # warm the context
+    t0 = time.perf_counter()
+    _, _, st = simulate_rare(p7, device=device, return_stats=True)
+    w_auto = time.perf_counter() - t0
+    # the stepped integrators on a 3 ms window of the same trajectory (the full 30 s is ~10^9 steps on ANY stepper)
+    p7w = sweep_params(6, 50e3, t_final=3e-3, steps=200)
+    legs = {}
+    for m in ("taylor", "dp5"):
+        t0 = time.perf_counter()
+        _, _, sm = simulate_rare(p7w, device=device, method=m, return_stats=True)
+        w = time.perf_counter() - t0
+        legs[m] = {"wall_s": w, "kernel_ms": sm.device_ms, "steps": sm.n_accepted + sm.n_rejected, "h_applies": sm.n_rhs,
+                   "steps_per_s": (sm.n_accepted + sm.n_rejected) / (sm.device_ms / 1e3),
+                   "h_applies_per_s": sm.n_rhs / (sm.device_ms / 1e3)}
+    out["n7_sweep_point"] = {
+        "workload": "C1 (i): N=7, delta=50 kHz, rare ON, t_final=30 s, 20000 outputs, atol 1e-10 / rtol 1e-9 (SW:1201-1252)",
+        "wall_s": w_auto, "kernel_ms": st.device_ms, "path": st.path, "column_h_applies": st.n_rhs,
+        "method": "auto (propagator: not an ODE step rate)", "stepped_3ms_window": legs}
+    p13 = DipolarRareParams(is_spin_three_half=False)
+    t0 = time.perf_counter()
+    _, _, s13 = simulate_rare(p13, device=device, return_stats=True)
+    w13 = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    _, _, s13d = simulate_rare(p13, device=device, method="dp5", return_stats=True)
+    w13d = time.perf_counter() - t0
+    out["n13_dataclass_default"] = {
+        "workload": "C1 (ii): DipolarRareParams(is_spin_three_half=False): N=13 icosahedron, 0.02 s, 2000 outputs, "
+                    "options None (QuTiP defaults atol 1e-8 / rtol 1e-6)",
+        "wall_s": w13, "kernel_ms": s13.device_ms, "path": s13.path, "steps": s13.n_accepted + s13.n_rejected,
+        "h_applies": s13.n_rhs, "steps_per_s": (s13.n_accepted + s13.n_rejected) / w13, "h_applies_per_s": s13.n_rhs / w13,
+        "dp5": {"wall_s": w13d, "steps": s13d.n_accepted + s13d.n_rejected, "h_applies": s13d.n_rhs,
+                "steps_per_s": (s13d.n_accepted + s13d.n_rejected) / w13d}}
+    if with_cpu:
+        table = compile_table(p13)
+        bm = table.bit_major()
+        H = dense.csr_from_table(bm["h"], bm["J"])
+        psi0 = np.zeros(table.dim, complex)
+        psi0[table.psi0_index] = 1.0
+        t = np.linspace(0, p13.t_final, p13.steps)
+        t0 = time.perf_counter()
+        _, _, _, zs = solvers.evolve_csr(H, psi0, t, [], backend="zvode", atol=1e-8, rtol=1e-6, nsteps=2500, max_step=0.0)
+        wz = time.perf_counter() - t0
+        out["n13_dataclass_default"]["cpu_zvode_1core"] = {"wall_s": wz, "steps": zs["n_steps"], "rhs": zs["n_rhs"],
+                                                          "steps_per_s": zs["n_steps"] / wz}
+        out["n7_sweep_point"]["cpu_zvode_1core"] = cpu_zvode_rate()
+    return out
+
+
 # --------------------------------------------------------------------------------------------------------
 def workload_text(n, method):
     """config.workload shared by both arms (the driver compares the two lines on the same config)."""
@@ -181,22 +302,39 @@ def workload_text(n, method):
             f"delta=50 kHz + 12.5 kHz*rank, rare drive ON), {method} step attempts")
 
 
+def bench_config(n, method, world):
+    """config shared VERBATIM by both arms (the driver compares the two lines on the same config)."""
+    return {"workload": workload_text(n, method), "n_qubits": n, "state_bytes": 16.0 * (1 << n), "method": method,
+            "atol": 1e-10, "rtol": 1e-9, "l2": "inputs larger than L2 (4.3 GB vectors vs 126 MB)",
+            "parallelism": f"independent sweep points x{world}"}
+
+
 def run_reference(args, rank, world):
+    """The reference arm: the CPU port of the CSR row product on all host cores, K timed samples after W warm-ups,
+    sized so that the whole run stays within ~2.5 minutes (a complete H-apply per step when that fits)."""
     if rank != 0:
         return
-    n_sea = args.n_qubits - 1
-    base = cpu_port_step_rate(n_sea, 50e3, budget_s=max(5.0, 20.0 * args.steps), samples=max(1, args.steps))
-    ms = 1e3 / base["value"]
+    port = CpuPort(args.n_qubits - 1, 50e3)
+    rows = port.rows_for(150.0 / max(1, args.steps))
+    for _ in range(args.warmup):
+        port.seconds(0, min(rows, 1 << 22))
+    secs = [port.seconds((s * rows) % (1 << port.n), rows) for s in range(args.steps)]
+    step_s = [6.0 * dt * (1 << port.n) / rows for dt in secs]        # 6 H-applies per DP5 step attempt
+    value = len(step_s) / sum(step_s)
+    base = {"value": value, "unit": "ODE steps/s", "cores": port.cores, "kind": "port",
+            "sample": port.sample_text(rows, secs), "extrapolated": rows != 1 << port.n, "rows_timed": rows,
+            "seconds_per_sample": secs}
     line = {
-        "impl": "reference", "metric": "ODE steps/s", "value": base["value"], "unit": "ODE steps/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "impl": "reference", "metric": "ODE steps/s", "value": value, "unit": "ODE steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / value,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_text(args.n_qubits, args.method), "n_qubits": args.n_qubits,
-                   "state_bytes": 16.0 * (1 << args.n_qubits), "method": args.method, "atol": 1e-10, "rtol": 1e-9,
-                   "arm": "CPU port of the reference's CSR row product (oracle/c), all host threads",
-                   "timing": "bounded row sample of one H-apply per step, scaled to 6 H-applies per step attempt"},
+        "config": bench_config(args.n_qubits, args.method, world),
+        "arm": "CPU port of the reference's CSR row product (oracle/c), all host threads; QuTiP itself cannot hold the "
+               "1.2 TB CSR of this operator (SURVEY 6.3)",
+        "timing": "wall clock of the sampled rows, scaled to 6 complete H-applies per step attempt; measured time "
+                  f"{sum(secs):.1f} s, claimed (scaled) time {sum(step_s):.1f} s",
         "cpu_baseline": base,
-        "e2e": {"value": base["value"], "unit": "ODE steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "e2e": {"value": value, "unit": "ODE steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
@@ -278,7 +416,11 @@ def run_b200(args, rank, world, local_rank):
         prof = ncu_traffic()
         roofline = {
             "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-            "traffic": (prof or {}).get("dram_bytes_per_step"), "peak_source": how,
+            "traffic": (prof or {}).get("dram_bytes_per_step"),
+            "traffic_source": ("committed ncu --set full capture (profiles/ncu_summary.json" +
+                               (f", tag {prof.get('tag')}" if prof and prof.get("tag") else "") +
+                               "), not re-measured in this run") if prof else None,
+            "peak_source": how,
             "kernel": "one DP5 step attempt = 6 H-applies (pass_first[+stage combination]/mid/centre/mid/last) + error sweep",
             "algorithmic_bytes_per_step": alg_bytes_step, "moved_bytes_per_step": moved_per_step,
             "moved_GBps": moved_per_step * args.steps / (ms / 1e3) / 1e9,
@@ -405,12 +547,13 @@ def run_b200(args, rank, world, local_rank):
         launches_per_step = 1 + n_rhs * kernels_per_apply(n) + 1 if args.method == "dp5" else n_rhs * kernels_per_apply(n) + 2
         cpu = cpu_port_step_rate(n_sea, 50e3) if world == 1 and not args.no_cpu else None
         zv = cpu_zvode_rate() if world == 1 and not args.no_cpu else None
+        zv_all = cpu_zvode_sweep_all_cores() if world == 1 and not args.no_cpu else None
+        c1 = c1_leg(local_rank, world == 1 and not args.no_cpu) if world == 1 else None
         line = {
             "metric": "ODE steps/s", "value": value, "unit": "ODE steps/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_text(n, args.method), "n_qubits": n, "state_bytes": S, "method": args.method, "atol": 1e-10, "rtol": 1e-9,
-                       "l2": "inputs larger than L2 (4.3 GB vectors vs 126 MB)", "parallelism": f"independent sweep points x{world}"},
+            "config": bench_config(n, args.method, world),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps),
             "clocks": clk.summary(),
             "accepted": st.n_accepted, "rejected": st.n_rejected, "rhs": st.n_rhs, "t_reached": t_end,
@@ -421,7 +564,7 @@ def run_b200(args, rank, world, local_rank):
                       "steps_per_s": sweep_steps / sweep_s, "total_steps": sweep_steps,
                       "wall_s_taylor": sweep_default_s,
                       "taylor": "stepping Taylor order 20, atol/rtol x 1e-3 (method='taylor')",
-                      "cpu_zvode": zv,
+                      "cpu_zvode": zv, "cpu_zvode_all_cores": zv_all,
                       "wall_s_default_method": sweep_prop_ci_s,
                       "default_method": "auto = Taylor(20) columns of exp(-iH dt/2^s), s on-chip squarings, one matvec per "
                                         "output (what simulate_rare runs when steps - 1 > 2^N)",
@@ -435,6 +578,7 @@ def run_b200(args, rank, world, local_rank):
                           "cpu_zvode_extrapolated_s_per_trajectory_1core":
                               (30.0 / zv["window_s"] * zv["n_steps"] / zv["steps_per_s_1core"]) if zv else None}},
             "grid": grid,
+            "c1": c1,
             "sharded": sharded,
         }
         print(json.dumps(line), flush=True)
@@ -443,9 +587,60 @@ def run_b200(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def _product_parity(plan, table, rank, seed, count=1 << 16):
+    """max rel. error of `count` sampled rows of H psi (product state, one H-apply through the plan's kernels) against
+    the closed form of oracle/product.py; rows are drawn from this rank's slice."""
+    from oracle import product
+
+    bm = table.bit_major()
+    phi = product.random_phi(table.n, seed)
+    rng = np.random.default_rng(1000 + rank)
+    rows = rng.integers(0, plan.local_dim, size=count, dtype=np.uint64)
+    rows[:2] = (0, plan.local_dim - 1)
+    got = plan.apply_h_product(phi, rows)
+    want = product.apply_h_rows(bm["h"], bm["J"], phi, rows + np.uint64(rank * plan.local_dim))
+    return float(np.max(np.abs(got - want)) / np.max(np.abs(want)))
+
+
+def _time_sharded(table, world, local_rank, opts, attempts, barrier, allmax, parity_seed=None, rank=0):
+    from quantumsimulations_b200 import engine, shard
+
+    plan = shard.sharded_plan_from_env(table, local_rank) if world > 1 else engine.Plan(table, local_rank)
+    out = {"local_dim": plan.local_dim}
+    plan.session_begin(opts)
+    plan.session_step(1)
+    barrier()
+    _, st0, _ = plan.session_step(0)
+    t_now, st, ms = plan.session_step(attempts)
+    barrier()
+    out["ms"] = allmax(ms)
+    out["n_rhs"] = st.n_rhs - st0.n_rhs
+    out["t_reached"] = t_now
+    out["obs"] = plan.session_observe()
+    engine.profile(True)
+    plan.session_step(1)
+    kms, kcnt = engine.profile_read()
+    engine.profile(False)
+    out["kernel_ms"] = {k: (kms[k] / kcnt[k] if kcnt[k] else None) for k in kms}
+    out["centre_ms"] = allmax(kms["pass_centre"] / max(kcnt["pass_centre"], 1))
+    local_ms = sum(kms[k] for k in kms if k != "pass_centre") / max(kcnt["pass_last"], 1)
+    out["hbm_passes_ms_per_happly"] = allmax(local_ms)
+    plan.session_end()
+    if parity_seed is not None:
+        out["parity"] = allmax(_product_parity(plan, table, rank, parity_seed))
+    plan.close()
+    barrier()
+    return out
+
+
 def sharded_leg(args, rank, world, local_rank, barrier, allmax):
     """C5: ONE trajectory whose state vector is sharded over all ranks (top log2(world) index bits = rank), Taylor
-    step attempts.  world == 1 gives the single-GPU anchor at the same per-GPU shard size.  Returns a dict on rank 0."""
+    step attempts.  world == 1 gives the single-GPU anchor at the same per-GPU shard size.  Weak scaling at
+    --shard-local-bits per GPU, a strong-scaling point at N = 30, and two parity fields: product-state rows of one
+    H-apply against the closed form at the benchmarked size, and an N = 26 trajectory against the unsharded plan.
+    Returns a dict on rank 0."""
+    import torch
+
     from quantumsimulations_b200 import compile_table, engine, shard
 
     wl = world.bit_length() - 1
@@ -453,32 +648,44 @@ def sharded_leg(args, rank, world, local_rank, barrier, allmax):
     table = compile_table(sweep_params(n - 1, 50e3))
     order = 8
     opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, max_step=1e-5, nsteps=0, method="taylor", order=order)
-    if world > 1:
-        plan = shard.sharded_plan_from_env(table, local_rank)
-    else:
-        plan = engine.Plan(table, local_rank)
-    s_loc = 16.0 * plan.local_dim
-    plan.session_begin(opts)
-    plan.session_step(1)
-    barrier()
     attempts = 2
-    _, st0, _ = plan.session_step(0)
-    t_now, st, ms = plan.session_step(attempts)
-    barrier()
-    ms = allmax(ms)
-    n_rhs = st.n_rhs - st0.n_rhs
-    obs = plan.session_observe()
-    engine.profile(True)
-    plan.session_step(1)
-    kms, kcnt = engine.profile_read()
-    engine.profile(False)
-    centre_ms = allmax(kms["pass_centre"] / max(kcnt["pass_centre"], 1))
-    plan.session_end()
-    plan.close()
-    barrier()
+    w = _time_sharded(table, world, local_rank, opts, attempts, barrier, allmax, parity_seed=n, rank=rank)
+    torch.cuda.empty_cache()
+    # strong-scaling point: N = 30 on every world size (the 1-GPU anchor is the weak leg when local bits = 30)
+    n_strong = 30
+    strong = None
+    if world > 1 and n_strong - wl >= 12 and n_strong != n:
+        st_table = compile_table(sweep_params(n_strong - 1, 50e3))
+        sres = _time_sharded(st_table, world, local_rank, opts, attempts, barrier, allmax, parity_seed=n_strong, rank=rank)
+        strong = {"n_qubits": n_strong, "ms_per_happly": sres["ms"] / sres["n_rhs"], "centre_ms": sres["centre_ms"],
+                  "hbm_passes_ms_per_happly": sres["hbm_passes_ms_per_happly"], "parity_max_rel_err": sres["parity"]}
+        torch.cuda.empty_cache()
+    elif n_strong == n:
+        strong = {"n_qubits": n_strong, "ms_per_happly": w["ms"] / w["n_rhs"], "note": "same run as the weak leg"}
+    # sharded vs unsharded trajectory at N = 26 (every rank runs the sharded one; rank 0 repeats it on one plan)
+    vs = None
+    if world > 1:
+        n_cmp = 26
+        ctable = compile_table(sweep_params(n_cmp - 1, 50e3))
+        t_out = np.linspace(0.0, 2.0e-6, 3)
+        copts = engine.SolverOptions(atol=1e-10, rtol=1e-9, max_step=1e-5, nsteps=100000, method="taylor", order=order)
+        plan = shard.sharded_plan_from_env(ctable, local_rank)
+        sobs, sst = plan.evolve(t_out, copts)
+        plan.close()
+        barrier()
+        if rank == 0:
+            with engine.Plan(ctable, local_rank) as up:
+                uobs, ust = up.evolve(t_out, copts)
+            vs = {"n_qubits": n_cmp, "outputs": len(t_out), "max_abs_diff": float(np.max(np.abs(sobs - uobs))),
+                  "accepted": [sst.n_accepted, ust.n_accepted], "rejected": [sst.n_rejected, ust.n_rejected],
+                  "what": "all 8 observable columns of qsb_evolve, sharded over the ranks vs one unsharded plan on rank 0"}
+        barrier()
+        torch.cuda.empty_cache()
     if rank != 0:
         return None
     peak, how = measured_peak()
+    s_loc = 16.0 * w["local_dim"]
+    ms, n_rhs = w["ms"], w["n_rhs"]
     out = {
         "workload": f"C5: one trajectory, N={n} spins sharded over {world} GPU(s) ({args.shard_local_bits} local index bits, "
                     f"{s_loc / 1e9:.1f} GB per vector per GPU), Taylor({order}) step attempts",
@@ -486,12 +693,17 @@ def sharded_leg(args, rank, world, local_rank, barrier, allmax):
         "steps_per_s": attempts / (ms / 1e3), "ms_per_happly": ms / n_rhs,
         "layouts": engine.tile_layouts(n, world),
         "hbm": {"algorithmic_GBps_per_gpu": (n_rhs + attempts) * 2.0 * s_loc / (ms / 1e3) / 1e9, "peak": peak, "peak_source": how},
-        "kernel_ms": {k: (kms[k] / kcnt[k] if kcnt[k] else None) for k in kms},
-        "raw_norm": float(obs[7]), "Iz_sea": float(obs[2]), "t_reached": t_now,
+        "kernel_ms": w["kernel_ms"], "hbm_passes_ms_per_happly": w["hbm_passes_ms_per_happly"],
+        "raw_norm": float(w["obs"][7]), "Iz_sea": float(w["obs"][2]), "t_reached": w["t_reached"],
+        "parity_max_rel_err": w["parity"],
+        "parity": "rows of H psi on a product state (2^16 sampled rows per rank, one H-apply through the sharded kernels) "
+                  "vs the closed form of oracle/product.py; max over ranks",
+        "vs_unsharded": vs, "strong": strong,
     }
     out["hbm"]["frac"] = out["hbm"]["algorithmic_GBps_per_gpu"] / peak
     if world > 1:
         per_dir = 4.0 * (world - 1) / world * s_loc   # x and y branch, loads by me + stores by the peers (and vice versa)
+        centre_ms = w["centre_ms"]
         out["nvlink"] = {"bytes_per_happly_per_gpu_per_direction": per_dir, "centre_ms": centre_ms,
                          "achieved_GBps_per_direction": per_dir / (centre_ms / 1e3) / 1e9, "peak": 770.0,
                          "peak_source": "B200_PROFILING.md measured peer copy, per direction",
@@ -518,7 +730,10 @@ def main():
     ap.add_argument("--no-sharded", action="store_true", help="skip the sharded-state (C5) leg")
     ap.add_argument("--no-grid", action="store_true", help="skip the 2D-grid (C3) leg")
     ap.add_argument("--shard-local-bits", type=int, default=30, help="index bits per GPU in the sharded leg (30: 17 GB vectors)")
+    ap.add_argument("--zvode-worker", default=None, help=argparse.SUPPRESS)
     args = ap.parse_args()
+    if args.zvode_worker:
+        return zvode_worker(args.zvode_worker)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

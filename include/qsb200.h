@@ -145,6 +145,12 @@ int qsb_debug_propagate_shape(int32_t n_qubits, int32_t* out /* [5] */);
 /* ---- pieces of the path, exposed for parity tests and the benchmark ---------------------------- */
 /* out = H psi on host vectors of 2^n complex128 (one H-apply through the same kernels evolve uses).  */
 int qsb_apply_h(qsb_plan* plan, const double* psi_host, double* out_host);
+/* The same H-apply at sizes no host vector reaches (BASELINE configs C4 / C5): the device fills the state with the
+ * PRODUCT state psi[x] = prod_b phi[b][bit_b(x)] (phi: [n][2] complex128, interleaved re,im), applies H through the
+ * kernels qsb_evolve uses, and returns rows `rows[i]` (indices into THIS plan's slice; collective when sharded) of
+ * H psi in out_host [n_rows] complex128.  On a product state every row of H psi has an O(n^2) closed form
+ * (oracle/product.py), which is what pins the operator of dipolar_ensemble_with_rare.py:549-568 at N = 28 .. 33.  */
+int qsb_apply_h_product(qsb_plan* plan, const double* phi, const uint64_t* rows, int64_t n_rows, double* out_host);
 /* Stepping session with the state resident in HBM (tiled path, n > QSB_SMALL_MAX_QUBITS).            */
 int qsb_session_begin(qsb_plan* plan, uint64_t psi0_index, const double* psi0_host, double t0,
                       const qsb_solver_opts* opts);

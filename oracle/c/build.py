@@ -26,6 +26,7 @@ def load():
         lib = C.CDLL(LIB)
         dp, vp = C.POINTER(C.c_double), C.c_void_p
         lib.oc_max_threads.restype = C.c_int
+        lib.oc_set_threads.argtypes = [C.c_int]
         lib.oc_diagonal.argtypes = [C.c_int, dp, dp, C.c_uint64, C.c_uint64, dp]
         lib.oc_apply_h_rows.argtypes = [C.c_int, dp, dp, dp, vp, vp, C.c_uint64, C.c_uint64]
         _lib = lib
@@ -38,6 +39,12 @@ def _dp(a):
 
 def max_threads() -> int:
     return load().oc_max_threads()
+
+
+def set_threads(n: int) -> int:
+    """Force the OpenMP team size (overrides an inherited OMP_NUM_THREADS); returns the resulting maximum."""
+    load().oc_set_threads(int(n))
+    return max_threads()
 
 
 def diagonal(h: np.ndarray, J: np.ndarray, row0: int = 0, row1: int | None = None) -> np.ndarray:

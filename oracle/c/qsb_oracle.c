@@ -25,6 +25,16 @@ int oc_max_threads(void) {
 #endif
 }
 
+/* The team size of every later parallel region (bench.py's reference arm runs under torchrun, which exports
+ * OMP_NUM_THREADS=1 to its workers; the CPU baseline is meant to use all host cores). */
+void oc_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 /* diag[x - row0] for x in [row0,row1): sum_b hz_b s_b/2 + sum_{b<c} Jzz_bc s_b s_c/4 */
 void oc_diagonal(int n, const double* h, const double* J, uint64_t row0, uint64_t row1, double* diag) {
   const double* hz = h + 2 * n;

@@ -214,4 +214,45 @@ int qsb_apply_h(qsb_plan* p, const double* psi_host, double* out_host) {
   return QSB_OK;
 }
 
+
+int qsb_apply_h_product(qsb_plan* p, const double* phi, const uint64_t* rows, int64_t n_rows, double* out_host) {
+  if (!p || !phi || !rows || !out_host || n_rows < 1) return fail(QSB_ERR_BAD_ARG, "null argument or n_rows < 1");
+  if (p->small) return fail(QSB_ERR_UNSUPPORTED, "qsb_apply_h_product is a hook of the tiled path (n_qubits > 10)");
+  if (p->ses) return fail(QSB_ERR_BAD_ARG, "qsb_apply_h_product cannot run while a session is open (shared workspace)");
+  if (p->world > 1 && !p->connected) return fail(QSB_ERR_BAD_ARG, "sharded plan is not connected to its peers (qsb_shard_connect)");
+  const uint64_t dim = 1ull << p->n_loc;
+  for (int64_t i = 0; i < n_rows; ++i)
+    if (rows[i] >= dim) return fail(QSB_ERR_BAD_ARG, "row index outside this plan's local slice");
+  QSB_CUDA(cudaSetDevice(p->device));
+  int rc = ensure_workspace(p, QSB_METHOD_TAYLOR);
+  if (rc) return rc;
+  Session s;
+  s.o = {1e-8, 1e-6, 0.0, 0, QSB_METHOD_TAYLOR, 12, 0.0};
+  carve(p, &s);
+  ProductPhi pp;
+  for (int b = 0; b < QSB_MAX_QUBITS; ++b) {  // padded spectator bits (b >= n) stay in |0>
+    pp.v[b][0] = b < p->n ? mk(phi[4 * b], phi[4 * b + 1]) : mk(1.0, 0.0);
+    pp.v[b][1] = b < p->n ? mk(phi[4 * b + 2], phi[4 * b + 3]) : mk(0.0, 0.0);
+  }
+  launch_product_state(s.y, pp, p->n_eff, p->n_loc, p->g.rank_bits, p->stream);
+  QSB_CUDA(cudaGetLastError());
+  Epilogue e = blank_epilogue(&s);
+  e.raw_h = 1;
+  e.o1 = s.ys;
+  rc = launch_happly(p->g, p->tab, s.y, s.tx, s.ty, e, 0, s.partials, p->stream, link_of(p), nullptr, &p->fu);
+  if (rc) return rc;
+  QSB_CUDA(cudaGetLastError());
+  // the running Taylor term's slot is free here: row indices and gathered values live in it
+  uint64_t* d_rows = (uint64_t*)s.k[0];
+  cplx* d_out = (cplx*)(d_rows + ((n_rows + 1) & ~(int64_t)1));  // 16-byte aligned
+  if ((size_t)(n_rows + 1) * (sizeof(uint64_t) + sizeof(cplx)) > (sizeof(cplx) << p->n_loc))
+    return fail(QSB_ERR_BAD_ARG, "too many rows for the scratch vector");
+  QSB_CUDA(cudaMemcpyAsync(d_rows, rows, sizeof(uint64_t) * n_rows, cudaMemcpyHostToDevice, p->stream));
+  launch_gather_rows(s.ys, d_rows, n_rows, d_out, p->stream);
+  QSB_CUDA(cudaGetLastError());
+  QSB_CUDA(cudaMemcpyAsync(out_host, d_out, sizeof(cplx) * n_rows, cudaMemcpyDeviceToHost, p->stream));
+  QSB_CUDA(cudaStreamSynchronize(p->stream));
+  return QSB_OK;
+}
+
 }  // extern "C"

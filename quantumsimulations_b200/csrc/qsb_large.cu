@@ -63,6 +63,26 @@ LargeGeom make_geometry(int n, int rank, int world) {
     if (ng > MAX_LAYOUTS - 1) ng = MAX_LAYOUTS - 1;
     for (int k = 0; k + 1 < ng; ++k) sizes[k] = others / (ng - 1) + (k < others % (ng - 1) ? 1 : 0);
     sizes[ng - 1] = last;
+    // experiment knob: explicit group sizes in ascending bit order, e.g. QSB200_GROUPS=10,6 (each 1..12, summing to
+    // n - 12, the last one holding all rank bits).  Groups wider than 8 bits give tiles made of runs shorter than 256
+    // bytes (lk = 12 - size pad bits); that is how the short-run passes of DESIGN.md section 10 were timed.
+    if (const char* e = std::getenv("QSB200_GROUPS")) {
+      int cand[MAX_LAYOUTS] = {0}, nc = 0, sum = 0;
+      bool ok = true;
+      for (const char* q = e; *q && ok;) {
+        char* end = nullptr;
+        long v = strtol(q, &end, 10);
+        if (end == q || v < 1 || v > TB || nc >= MAX_LAYOUTS - 1) { ok = false; break; }
+        cand[nc++] = (int)v;
+        sum += (int)v;
+        q = (*end == ',') ? end + 1 : end;
+        if (*end && *end != ',') ok = false;
+      }
+      if (ok && nc > 0 && sum == rest && cand[nc - 1] >= wl) {
+        ng = nc;
+        for (int k = 0; k < ng; ++k) sizes[k] = cand[k];
+      }
+    }
     int start = TB;
     for (int k = 0; k < ng; ++k) {
       int sz = sizes[k];

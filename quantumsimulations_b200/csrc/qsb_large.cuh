@@ -169,6 +169,11 @@ int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, c
 void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out8, cudaStream_t stream);
 // psi <- basis state (index < dim) or zero (index >= dim)
 void launch_set_basis_state(cplx* psi, uint64_t dim, uint64_t index, cudaStream_t stream);
+// Product state psi[x] = prod_b phi.v[b][bit_b(x)] over this rank's 2^n_loc amplitudes (bits >= n_loc from rank_bits),
+// and a row gather; together with one H-apply they are the closed-form parity check at sizes the oracle cannot hold.
+struct ProductPhi { cplx v[QSB_MAX_QUBITS][2]; };
+void launch_product_state(cplx* psi, const ProductPhi& phi, int n, int n_loc, uint64_t rank_bits, cudaStream_t stream);
+void launch_gather_rows(const cplx* src, const uint64_t* d_rows, int64_t n_rows, cplx* d_out, cudaStream_t stream);
 size_t happly_smem_bytes();
 
 // Per-kernel-class CUDA-event timing (bench.py's roofline leg).  Classes: 0 pass_first, 1 pass_mid, 2 pass_centre,

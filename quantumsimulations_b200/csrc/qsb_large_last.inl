@@ -168,6 +168,27 @@ __global__ void reduce_partials_kernel(const double* __restrict__ partials, int6
   }
 }
 
+// psi[x] = prod_b phi[b][bit_b(x | rank_bits)]: a state whose H-image has a closed form on every row (parity hook
+// for sizes no host vector reaches).  Thread i owns x = i mod 2^12 .. in strides; the product over the bits above 12
+// is shared by a whole 4096-amplitude block, so it is formed once per block.
+__global__ void product_state_kernel(cplx* __restrict__ psi, ProductPhi phi, int n, uint64_t rank_bits) {
+  const uint64_t base = (uint64_t)blockIdx.x << TB;
+  cplx hi = mk(1.0, 0.0);
+  for (int b = TB; b < n; ++b) hi = cmul(hi, phi.v[b][((base | rank_bits) >> b) & 1]);
+  for (int i = threadIdx.x; i < TILE; i += blockDim.x) {
+    cplx a = hi;
+#pragma unroll
+    for (int b = 0; b < TB; ++b) a = cmul(a, phi.v[b][(i >> b) & 1]);
+    psi[base | (uint64_t)i] = a;
+  }
+}
+
+__global__ void gather_rows_kernel(const cplx* __restrict__ src, const uint64_t* __restrict__ rows, int64_t n_rows,
+                                   cplx* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_rows) out[i] = src[rows[i]];
+}
+
 __global__ void set_basis_kernel(cplx* psi, uint64_t dim, uint64_t index) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -523,6 +544,14 @@ void launch_error_sums(const LargeGeom& g, const ErrSpec& es, double* partials, 
 
 void launch_reduce_partials(const double* partials, int64_t n_tiles, double* out8, cudaStream_t stream) {
   reduce_partials_kernel<<<1, 1024, 0, stream>>>(partials, n_tiles, out8);
+}
+
+void launch_product_state(cplx* psi, const ProductPhi& phi, int n, int n_loc, uint64_t rank_bits, cudaStream_t stream) {
+  product_state_kernel<<<1u << (n_loc - TB), 256, 0, stream>>>(psi, phi, n, rank_bits);
+}
+
+void launch_gather_rows(const cplx* src, const uint64_t* d_rows, int64_t n_rows, cplx* d_out, cudaStream_t stream) {
+  gather_rows_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, stream>>>(src, d_rows, n_rows, d_out);
 }
 
 void launch_set_basis_state(cplx* psi, uint64_t dim, uint64_t index, cudaStream_t stream) {

@@ -215,3 +215,37 @@ def test_exact_oracle_matches_full_size_reference_sweep_samples():
             got = exact_traces(compile_table(p), t[s["index"]])
             assert np.max(np.abs(got["Iz_sea"] - np.array(s["Iz_sea"]))) < 1e-7, (delta, tag)
             assert np.max(np.abs(got["Iz_R"] - np.array(s["Iz_R"]))) < 1e-7, (delta, tag)
+
+
+@pytest.mark.parametrize("name", ["n7_d050k_center_on", "n7_d100k_shell_off", "n9_cube"])
+def test_product_state_closed_form_matches_reference_built_hamiltonians(name, golden_cases, golden_hams):
+    """oracle.product (the O(n^2)-per-row closed form used at N = 28 .. 33) vs the reference-built CSR acting on the
+    same product state, and vs the C row product (oracle/c) on a random table."""
+    from oracle import product
+    from quantumsimulations_b200 import compile_table
+
+    meta, _ = golden_cases
+    t = compile_table(params_from_meta(meta[name]))
+    bm = t.bit_major()
+    phi = product.random_phi(t.n, 11)
+    psi = product.full_state(phi)
+    G = _golden_csr(golden_hams, name)
+    want = G @ psi
+    got = product.apply_h_rows(bm["h"], bm["J"], phi, np.arange(t.dim))
+    assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-13
+
+
+def test_product_state_closed_form_matches_c_port_n20():
+    from conftest import random_table
+    from oracle import product
+    from oracle.c import build as oc
+
+    n = 20
+    t = random_table(n, 91)
+    bm = t.bit_major()
+    phi = product.random_phi(n, 3)
+    psi = product.full_state(phi)
+    row0, row1 = 777 << 8, (777 << 8) + 4096
+    want = oc.apply_h(bm["h"], bm["J"], psi, row0, row1)
+    got = product.apply_h_rows(bm["h"], bm["J"], phi, np.arange(row0, row1))
+    assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-13
