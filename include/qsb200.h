@@ -191,6 +191,9 @@ int qsb_shard_plan_create(const qsb_table* table, int device, int32_t rank, int3
 int qsb_shard_export(qsb_plan* plan, void* blob);
 /* blobs: [world][QSB_SHARD_BLOB_BYTES], rank-ordered, as gathered from every rank's qsb_shard_export.          */
 int qsb_shard_connect(qsb_plan* plan, const void* blobs, qsb_allgather_fn allgather, void* ctx);
+/* The plan's own all-gather hook, for host-side agreement between the ranks (checkpoint / resume: every rank must
+ * pick the trajectory up at the same output time).  recv: [world][count]; count = 0 is a barrier.              */
+int qsb_shard_allgather(qsb_plan* plan, const double* send, int32_t count, double* recv);
 /* Host-only (no device needed): the tile layouts the tiled path uses for n index bits split over `world` ranks.
  * out[k] = {lk, gs, ge} for k < *n_layouts (<= 6): tile-local bits [0,lk) are index bits [0,lk), tile-local bits
  * [lk,12) are index bits [gs,ge).  Layout 0 is the contiguous one; the last one is the centre and must contain all

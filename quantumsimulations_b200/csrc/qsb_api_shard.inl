@@ -197,6 +197,13 @@ int qsb_shard_connect(qsb_plan* p, const void* blobs, qsb_allgather_fn allgather
   return QSB_OK;
 }
 
+int qsb_shard_allgather(qsb_plan* p, const double* send, int32_t count, double* recv) {
+  if (!p || count < 0 || (count > 0 && (!send || !recv))) return fail(QSB_ERR_BAD_ARG, "null argument");
+  if (p->world < 2 || !p->connected) return fail(QSB_ERR_BAD_ARG, "not a connected sharded plan");
+  if (p->allgather(p->allgather_ctx, send, count, recv)) return fail(QSB_ERR_CUDA, "all-gather hook failed");
+  return QSB_OK;
+}
+
 int qsb_local_group_create(int32_t world, qsb_local_group** group) {
   if (!group || world < 1 || world > MAX_WORLD) return fail(QSB_ERR_BAD_ARG, "bad local group arguments");
   qsb_local_group* g = new qsb_local_group;

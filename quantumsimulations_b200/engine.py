@@ -59,7 +59,7 @@ EXPORTS = (
     "qsb_plan_workspace_bytes", "qsb_plan_set_workspace", "qsb_evolve", "qsb_evolve_batch", "qsb_apply_h",
     "qsb_apply_h_product",
     "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
-    "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
+    "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather",
     "qsb_propagate_batch", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
 )
@@ -110,6 +110,7 @@ def load_library() -> C.CDLL:
     lib.qsb_shard_plan_create.argtypes = [C.POINTER(_Table), C.c_int, C.c_int32, C.c_int32, C.POINTER(vp)]
     lib.qsb_shard_export.argtypes = [vp, vp]
     lib.qsb_shard_connect.argtypes = [vp, vp, vp, vp]
+    lib.qsb_shard_allgather.argtypes = [vp, dp, C.c_int32, dp]
     lib.qsb_plan_local_dim.argtypes = [vp, C.POINTER(C.c_uint64)]
     lib.qsb_debug_layouts.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     lib.qsb_local_group_create.argtypes = [C.c_int32, C.POINTER(vp)]
@@ -381,6 +382,13 @@ class ShardedPlan(Plan):
         self._hook = allgather  # keep the ctypes callback alive as long as the plan
         fn = C.cast(allgather, C.c_void_p)
         _check(self.lib.qsb_shard_connect(self._h, joined, fn, C.c_void_p(ctx) if ctx is not None else None))
+
+    def allgather(self, values) -> np.ndarray:
+        """[world][len(values)] doubles gathered over the plan's own hook (collective; host-side agreement only)."""
+        send = np.ascontiguousarray(values, dtype=np.float64).ravel()
+        recv = np.empty((self.world, send.size), dtype=np.float64)
+        _check(self.lib.qsb_shard_allgather(self._h, _dptr(send), send.size, _dptr(recv)))
+        return recv
 
     def local_slice(self) -> slice:
         return slice(self.rank * self.local_dim, (self.rank + 1) * self.local_dim)

@@ -200,6 +200,57 @@ def test_replay_shim_batches_an_unchanged_script(tmp_path):
     assert float(open(os.path.join(out, "out.txt")).read()) == pytest.approx(1e-3 * 10)
 
 
+def _check_sweep_dir_against_golden(base, rel_slope=1e-7):
+    with open(os.path.join(GOLDEN, "sweep_small.json")) as f:
+        gold = json.load(f)
+    with open(os.path.join(base, "summary.json")) as f:
+        mine = json.load(f)
+    gp = gold["summary"]["global_params"]
+    assert list(mine["global_params"].keys()) == list(gp.keys())
+    for k, v in gp.items():
+        assert mine["global_params"][k] == v, k
+    assert len(mine["sweep_results"]) == len(gold["summary"]["sweep_results"]) == 13
+    for got, want in zip(mine["sweep_results"], gold["summary"]["sweep_results"]):
+        assert list(got.keys()) == list(want.keys())
+        for k in want:
+            if k.startswith("t_") or k.startswith("R_"):
+                assert got[k] == pytest.approx(want[k], rel=max(1e-6, 10 * rel_slope)), k
+            elif k.startswith("contrast"):
+                # discontinuous at |t| = 1 (SW:308-315): only compared when both t-values are away from the gate
+                continue
+            else:
+                assert got[k] == pytest.approx(want[k], rel=rel_slope, abs=1e-12), k
+    written = sorted(os.path.relpath(os.path.join(d, fn), base) for d, _, fns in os.walk(base) for fn in fns)
+    # the reference run that made the golden had the same inert plotting stubs: identical listing, PDFs/PNGs included
+    assert written == sorted(gold["files"])
+    return mine, gold
+
+
+def test_unchanged_reference_sweep_script_runs_on_the_dropin(tmp_path):
+    """Row (b) of SURVEY 8: the reference's sweep_sea_detuning.py, UNMODIFIED, imported with the drop-in directory
+    first on sys.path, binds the engine's names (SW:103-109) and, run through the record -> batch -> replay shim at
+    its function-default grid (SW:356-376, 13 detunings x 3 variants), makes exactly ONE batch call of 39 trajectories
+    and writes the summary / file set the reference itself wrote (tests/golden/sweep_small.json).  The batch solver
+    here is the exact CPU oracle (no GPU in this suite); tests/test_gpu_evolve.py repeats it on the engine."""
+    import subprocess
+
+    from oracle import ref_loader
+
+    if not ref_loader.reference_available():
+        pytest.skip("reference checkout not present")
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "run_reference_sweep_on_dropin.py"), str(tmp_path), "oracle"],
+                         capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    info = json.loads([ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1])
+    assert info["calls"] == [39]
+    assert info["bound"] == {"simulate_rare": True, "params": True, "freqs": True, "model_module_is_dropin": True,
+                             "qutip_imported": False}
+    mine, gold = _check_sweep_dir_against_golden(info["base"])
+    for got, want in zip(mine["sweep_results"], gold["summary"]["sweep_results"]):
+        for k in ("contrast_rare_center", "contrast_sea_center"):
+            assert got[k] == pytest.approx(want[k], rel=1e-6, abs=1e-12), k
+
+
 # ---- C ABI -------------------------------------------------------------------------------------------------------
 def test_library_exports_every_declared_symbol():
     from quantumsimulations_b200 import engine
@@ -434,6 +485,17 @@ def test_trajectory_cache_serves_repeated_and_interrupted_sweeps(tmp_path):
     p = DipolarRareParams(n_sea=6, is_spin_three_half=False)
     assert trajectory_key(p) != trajectory_key(dataclasses.replace(p, gamma_sea=np.nextafter(p.gamma_sea, np.inf)))
     assert trajectory_key(p, method="dp5") != trajectory_key(p, method="taylor")
+    # ... and the RESOLVED numerics: environment overrides, explicit tol_scale, numpy scalars in the record
+    base_key = trajectory_key(p)
+    os.environ["QSB200_TOL_SCALE"] = "1e-4"
+    try:
+        assert trajectory_key(p) != base_key
+    finally:
+        del os.environ["QSB200_TOL_SCALE"]
+    assert trajectory_key(p, tol_scale=1e-2) != base_key
+    assert trajectory_key(p, method="auto") == base_key                                   # auto is the default
+    assert trajectory_key(dataclasses.replace(p, steps=5)) != trajectory_key(dataclasses.replace(p, steps=5), method="propagator")
+    assert trajectory_key(dataclasses.replace(p, n_sea=np.int64(6))) == base_key
 
 
 # ---- the reference's consumers, unchanged, on the engine's output files -------------------------------------------

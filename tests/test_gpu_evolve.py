@@ -228,3 +228,59 @@ def test_checkpointed_trajectory_resumes_bitwise(tmp_path, method):
     with pytest.raises(ValueError):
         with engine.Plan(table) as plan:
             evolve_checkpointed(plan, t_out[:5], opts, path)
+
+
+def test_checkpoint_refuses_another_trajectory(tmp_path):
+    """A checkpoint is tied to the Hamiltonian table, the initial state and max_step / nsteps, not only to the time
+    grid: resuming it with another detuning (same grid, same tolerances) must raise instead of silently continuing the
+    old state under a different H."""
+    import dataclasses
+
+    from bench import sweep_params
+    from quantumsimulations_b200 import compile_table, engine
+    from quantumsimulations_b200.checkpoint import evolve_checkpointed
+
+    t_out = np.linspace(0.0, 2.0e-5, 5)
+    opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, max_step=1e-5, nsteps=100000, method="taylor", order=12)
+    path = str(tmp_path / "traj.npz")
+    with engine.Plan(compile_table(sweep_params(13, 50e3))) as plan:
+        _, _, done = evolve_checkpointed(plan, t_out, opts, path, stop_after=2)
+    assert not done
+    with pytest.raises(ValueError, match="different trajectory"):
+        with engine.Plan(compile_table(sweep_params(13, 62.5e3))) as plan:          # another detuning
+            evolve_checkpointed(plan, t_out, opts, path)
+    with pytest.raises(ValueError, match="different trajectory"):
+        with engine.Plan(compile_table(sweep_params(13, 50e3))) as plan:            # another max_step
+            evolve_checkpointed(plan, t_out, dataclasses.replace(opts, max_step=2e-5), path)
+    with engine.Plan(compile_table(sweep_params(13, 50e3))) as plan:                # the right one still resumes
+        _, _, done = evolve_checkpointed(plan, t_out, opts, path)
+    assert done
+
+
+def test_sharded_checkpoint_ranks_must_agree(tmp_path):
+    """Sharded resume: every rank writes its own file; ranks whose files were taken at different output times (a crash
+    between two ranks' writes) must refuse to resume instead of starting at different times."""
+    import shutil
+
+    from bench import sweep_params
+    from quantumsimulations_b200 import compile_table, engine, shard
+    from quantumsimulations_b200.checkpoint import evolve_checkpointed
+
+    table = compile_table(sweep_params(13, 50e3))
+    t_out = np.linspace(0.0, 2.0e-5, 6)
+    opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, max_step=1e-5, nsteps=100000, method="taylor", order=12)
+    with engine.Plan(table) as plan:
+        want, _ = plan.evolve(t_out, opts)
+    paths = [str(tmp_path / f"r{r}.npz") for r in range(2)]
+    with shard.LocalShardGroup(table, 2) as grp:
+        grp.run(lambda plan, r: evolve_checkpointed(plan, t_out, opts, paths[r], stop_after=2))
+        shutil.copy(paths[1], str(tmp_path / "r1_at2.npz"))
+        grp.run(lambda plan, r: evolve_checkpointed(plan, t_out, opts, paths[r], stop_after=1))
+        good = [str(tmp_path / f"good{r}.npz") for r in range(2)]
+        for r in range(2):
+            shutil.copy(paths[r], good[r])
+        shutil.copy(str(tmp_path / "r1_at2.npz"), paths[1])              # rank 1 is one output time behind
+        with pytest.raises(ValueError, match="different output times"):
+            grp.run(lambda plan, r: evolve_checkpointed(plan, t_out, opts, paths[r]))
+        res = grp.run(lambda plan, r: evolve_checkpointed(plan, t_out, opts, good[r]))
+    assert res[0][2] and np.max(np.abs(res[0][0] - want)) < 1e-11
