@@ -191,6 +191,16 @@ int qsb_shard_plan_create(const qsb_table* table, int device, int32_t rank, int3
 int qsb_shard_export(qsb_plan* plan, void* blob);
 /* blobs: [world][QSB_SHARD_BLOB_BYTES], rank-ordered, as gathered from every rank's qsb_shard_export.          */
 int qsb_shard_connect(qsb_plan* plan, const void* blobs, qsb_allgather_fn allgather, void* ctx);
+/* Optional, one process per GPU only: a rank barrier that is QUEUED ON A CUDA STREAM instead of blocking the host -
+ * `stream` is a cudaStream_t; work queued on it after the call must not start before every rank's work queued on its
+ * counterpart stream before ITS call is complete (e.g. a one-element NCCL all-reduce issued on that stream).  With it
+ * the H-apply runs its two branches as a pipeline: the NVLink-bound centre pass of one branch on a second,
+ * low-priority stream under the HBM-bound passes of the other; every rank queues the barriers in the same order.
+ * Without it (fn = NULL, the default) the passes are serialised around host-side barriers through the all-gather
+ * hook, which is what ranks that share a GPU (threads, tests) must use: kernels that wait on one another as separate
+ * launches on one GPU may never be co-resident.                                                                 */
+typedef int (*qsb_stream_barrier_fn)(void* ctx, void* stream);
+int qsb_shard_set_stream_barrier(qsb_plan* plan, qsb_stream_barrier_fn fn, void* ctx);
 /* The plan's own all-gather hook, for host-side agreement between the ranks (checkpoint / resume: every rank must
  * pick the trajectory up at the same output time).  recv: [world][count]; count = 0 is a barrier.              */
 int qsb_shard_allgather(qsb_plan* plan, const double* send, int32_t count, double* recv);

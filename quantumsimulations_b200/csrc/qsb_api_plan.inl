@@ -101,7 +101,13 @@ static int plan_create(const qsb_table* table, int device, int rank, int world, 
   p->J.assign(table->J, table->J + 3 * (size_t)n * n);
   p->sea_mask = table->sea_mask;
   p->rare_mask = table->rare_mask;
-  QSB_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+  if (world > 1) {  // sharded: the plan's stream outranks the centre stream of the overlapped mode (qsb_shard_set_stream_barrier)
+    int least = 0, greatest = 0;
+    QSB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    QSB_CUDA(cudaStreamCreateWithPriority(&p->stream, cudaStreamNonBlocking, greatest));
+  } else {
+    QSB_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+  }
   if (!p->small) {
     const int ne = std::max(n, TB);
     p->n_eff = ne;
@@ -190,6 +196,11 @@ int qsb_plan_destroy(qsb_plan* p) {
   if (p->stream) cudaStreamSynchronize(p->stream);
   for (int r = 0; r < MAX_WORLD; ++r)
     if (p->ipc_opened[r]) cudaIpcCloseMemHandle(p->ipc_opened[r]);
+  if (p->link.centre_stream) {
+    cudaStreamSynchronize(p->link.centre_stream);
+    for (int b = 0; b < 2; ++b) { cudaEventDestroy(p->link.ev_fwd[b]); cudaEventDestroy(p->link.ev_centre[b]); }
+    cudaStreamDestroy(p->link.centre_stream);
+  }
   if (p->xbuf) cudaFree(p->xbuf);
   if (p->ws && p->ws_owned) cudaFree(p->ws);
   if (p->d_tables) cudaFree(p->d_tables);

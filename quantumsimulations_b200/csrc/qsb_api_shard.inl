@@ -197,6 +197,25 @@ int qsb_shard_connect(qsb_plan* p, const void* blobs, qsb_allgather_fn allgather
   return QSB_OK;
 }
 
+int qsb_shard_set_stream_barrier(qsb_plan* p, qsb_stream_barrier_fn fn, void* ctx) {
+  if (!p) return fail(QSB_ERR_BAD_ARG, "null plan");
+  if (p->world < 2) return fail(QSB_ERR_BAD_ARG, "not a sharded plan");
+  if (p->ses) return fail(QSB_ERR_BAD_ARG, "cannot change the barrier while a session is open");
+  QSB_CUDA(cudaSetDevice(p->device));
+  if (fn && !p->link.centre_stream) {
+    int least = 0, greatest = 0;
+    QSB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    QSB_CUDA(cudaStreamCreateWithPriority(&p->link.centre_stream, cudaStreamNonBlocking, least));
+    for (int b = 0; b < 2; ++b) {
+      QSB_CUDA(cudaEventCreateWithFlags(&p->link.ev_fwd[b], cudaEventDisableTiming));
+      QSB_CUDA(cudaEventCreateWithFlags(&p->link.ev_centre[b], cudaEventDisableTiming));
+    }
+  }
+  p->link.stream_barrier = (int (*)(void*, cudaStream_t))fn;
+  p->link.barrier_ctx = ctx;
+  return QSB_OK;
+}
+
 int qsb_shard_allgather(qsb_plan* p, const double* send, int32_t count, double* recv) {
   if (!p || count < 0 || (count > 0 && (!send || !recv))) return fail(QSB_ERR_BAD_ARG, "null argument");
   if (p->world < 2 || !p->connected) return fail(QSB_ERR_BAD_ARG, "not a connected sharded plan");

@@ -98,6 +98,15 @@ struct ShardLink {
   cplx* ty[MAX_WORLD];
   int (*sync)(void* ctx);
   void* ctx;
+  // Overlapped mode (one process per GPU): `stream_barrier` enqueues a rank barrier ON a stream (an NCCL collective:
+  // work queued on that stream afterwards starts only when every rank's earlier work on its counterpart stream is
+  // complete) without blocking the host.  The two branches then run as a pipeline: the NVLink-bound centre pass of
+  // one branch on `centre_stream` (low priority) under the HBM-bound mid passes of the other on the plan's stream.
+  // Null: the serialised path with the host-side `sync` (ranks that are threads sharing GPUs; nothing may spin there).
+  int (*stream_barrier)(void* ctx, cudaStream_t stream);
+  void* barrier_ctx;
+  cudaStream_t centre_stream;
+  cudaEvent_t ev_fwd[2], ev_centre[2];  // per branch: mids forward done (plan stream) / centre + barrier done (centre stream)
   // TMA descriptors of the peers' scratch vectors for the ring version of the centre pass, [branch][peer]; built on
   // first use after the link is connected (host cache)
   CUtensorMap ring_maps[2][MAX_WORLD];

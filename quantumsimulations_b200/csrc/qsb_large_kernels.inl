@@ -24,6 +24,7 @@ struct TileMap {
   unsigned cbase;
   int lb, cbits;
   unsigned zero;  // always 0; see opaque()
+  int branch0;    // branch of blockIdx.y == 0 (a launch with gridDim.y == 1 covers ONE branch: sharded overlap)
   __device__ __forceinline__ uint64_t tile(unsigned bx) const {
     return (uint64_t)cbase + (bx & ((1u << lb) - 1)) + ((uint64_t)(bx >> lb) << cbits);
   }
@@ -122,7 +123,7 @@ __global__ void __launch_bounds__(TPT, 2)
 pass_mid(Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
-  cplx* t = blockIdx.y ? ty : tx;
+  cplx* t = (tm.branch0 + blockIdx.y) ? ty : tx;
   const int tt = threadIdx.x;
   const uint64_t base = tile_base(L, tm.tile(blockIdx.x));
   cplx r[16];
@@ -196,7 +197,7 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
   __shared__ double red[2 * 32 + 2];
-  const int branch = blockIdx.y;  // 0: x, 1: y
+  const int branch = tm.branch0 + blockIdx.y;  // 0: x, 1: y
   cplx* t = branch ? ty : tx;
   const double (&ww)[16] = branch ? a.tab.Wy : a.tab.Wx;
   const uint64_t v = tm.tile(blockIdx.x);

@@ -241,25 +241,26 @@ static void set_centre_attrs(int sm) {
 // Shared memory of a strided pass: the padded buffer only if the layout transforms window [0,4).
 static size_t strided_smem(bool pad) { return (size_t)(pad ? TILE_PHYS : TILE) * sizeof(cplx); }
 
-static void launch_mid(const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, unsigned n_tiles, cudaStream_t stream) {
-  if (L.m0) pass_mid<true><<<dim3(n_tiles, 2), TPT, strided_smem(true), stream>>>(L, tm, tx, ty);
-  else pass_mid<false><<<dim3(n_tiles, 2), TPT, strided_smem(false), stream>>>(L, tm, tx, ty);
+// nb: branches per launch - 2 (both, blockIdx.y) or 1 (only tm.branch0)
+static void launch_mid(const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, unsigned n_tiles, cudaStream_t stream, int nb = 2) {
+  if (L.m0) pass_mid<true><<<dim3(n_tiles, nb), TPT, strided_smem(true), stream>>>(L, tm, tx, ty);
+  else pass_mid<false><<<dim3(n_tiles, nb), TPT, strided_smem(false), stream>>>(L, tm, tx, ty);
 }
 
 template <bool SHARDED, int W>
 static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, const PeerPtrs& pp,
-                          int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream) {
+                          int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream, int nb) {
   sm = W == 8 ? 0 : strided_smem(W == 0);  // W == 8: the whole group sits in one register window, no staging at all
-  if (collect_obs) pass_centre<SHARDED, true, W><<<dim3(n_tiles, 2), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
-  else pass_centre<SHARDED, false, W><<<dim3(n_tiles, 2), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
+  if (collect_obs) pass_centre<SHARDED, true, W><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
+  else pass_centre<SHARDED, false, W><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
 }
 template <bool SHARDED>
 static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, const PeerPtrs& pp,
-                          int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream) {
+                          int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream, int nb = 2) {
   switch (centre_window(L)) {
-    case 8: launch_centre<SHARDED, 8>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream); break;
-    case 4: launch_centre<SHARDED, 4>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream); break;
-    default: launch_centre<SHARDED, 0>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream); break;
+    case 8: launch_centre<SHARDED, 8>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream, nb); break;
+    case 4: launch_centre<SHARDED, 4>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream, nb); break;
+    default: launch_centre<SHARDED, 0>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream, nb); break;
   }
 }
 
@@ -444,7 +445,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
   const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx);
   const unsigned n_tiles = 1u << (g.n_loc - TB);
   const int centre = g.n_layouts - 1;
-  const TileMap all = {0u, 0, 0, 0u};
+  const TileMap all = {0u, 0, 0, 0u, 0};
   const double S = (double)(sizeof(cplx) << g.n_loc);  // bytes of one local vector
   if (fu && fu->on && g.world == 1 && centre_window(g.lay[centre]) != 0 && ensure_tile_maps(g, *fu, tx, ty)) {
     // layouts before f stay full-grid launches; f .. centre .. f is one persistent launch
@@ -466,18 +467,47 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
     launch_centre<false>(a, g.lay[centre], all, tx, ty, none, collect_obs, partials, n_tiles, sm1, stream);
   } else {
     if (!link) { set_error("sharded plan is not connected to its peers (qsb_shard_connect)"); return QSB_ERR_BAD_ARG; }
+    PeerPtrs pp = {};
+    for (int r = 0; r < g.world; ++r) { pp.t[0][r] = link->tx[r]; pp.t[1][r] = link->ty[r]; }
+    const int w = centre_window(g.lay[centre]);
+    if (link->stream_barrier && !(shard_ring_enabled() && w != 0)) {
+      // Overlapped: branch by branch.  Plan stream S: mids forward x, barrier, mids forward y, barrier, then (after the
+      // centre stream's events) mids back x, mids back y.  Centre stream C (low priority, so that the short HBM-bound
+      // launches of S take the SM slots the long NVLink-bound centre CTAs free): centre x, barrier, centre y, barrier.
+      // Every barrier is a collective queued on a stream - the host never waits - and all ranks queue them in the
+      // same order (x forward, x centre, y forward, y centre).  The centre pass of x thus runs under the forward mids
+      // of y, and the centre pass of y under the backward mids of x.
+      cudaStream_t C = link->centre_stream;
+      for (int br = 0; br < 2; ++br) {
+        const TileMap one = {0u, 0, 0, 0u, br};
+        for (int k = 1; k < centre; ++k) { Timed t(1, stream, 2 * S); launch_mid(g.lay[k], one, tx, ty, n_tiles, stream, 1); }
+        if (link->stream_barrier(link->barrier_ctx, stream)) { set_error("rank barrier (stream hook) failed"); return QSB_ERR_CUDA; }
+        cudaEventRecord(link->ev_fwd[br], stream);
+        cudaStreamWaitEvent(C, link->ev_fwd[br], 0);
+        {
+          Timed t(2, C, 2 * S);
+          const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u, br};
+          launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, C, 1);
+        }
+        if (link->stream_barrier(link->barrier_ctx, C)) { set_error("rank barrier (stream hook) failed"); return QSB_ERR_CUDA; }
+        cudaEventRecord(link->ev_centre[br], C);
+      }
+      for (int br = 0; br < 2; ++br) {
+        const TileMap one = {0u, 0, 0, 0u, br};
+        cudaStreamWaitEvent(stream, link->ev_centre[br], 0);
+        for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream, 2 * S); launch_mid(g.lay[k], one, tx, ty, n_tiles, stream, 1); }
+      }
+      return QSB_OK;
+    }
     int rc = link->sync(link->ctx);
     if (rc) return rc;
     {
       Timed t(2, stream, 4 * S);
-      const int w = centre_window(g.lay[centre]);
       if (shard_ring_enabled() && w != 0 && ensure_ring_maps(g, *link)) {
         if (w == 8) launch_centre_ring<8>(a, g, *link, collect_obs, partials, n_tiles, stream);
         else launch_centre_ring<4>(a, g, *link, collect_obs, partials, n_tiles, stream);
       } else {
-        PeerPtrs pp = {};
-        for (int r = 0; r < g.world; ++r) { pp.t[0][r] = link->tx[r]; pp.t[1][r] = link->ty[r]; }
-        const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u};
+        const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u, 0};
         launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, stream);
       }
     }

@@ -59,7 +59,7 @@ EXPORTS = (
     "qsb_plan_workspace_bytes", "qsb_plan_set_workspace", "qsb_evolve", "qsb_evolve_batch", "qsb_apply_h",
     "qsb_apply_h_product",
     "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
-    "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
+    "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_shard_set_stream_barrier", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather",
     "qsb_propagate_batch", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
 )
@@ -67,6 +67,8 @@ EXPORTS = (
 SHARD_BLOB_BYTES = 96
 # int (*qsb_allgather_fn)(void* ctx, const double* send, int32_t count, double* recv)
 ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(C.c_double), C.c_int32, C.POINTER(C.c_double))
+# int (*qsb_stream_barrier_fn)(void* ctx, void* cuda_stream)
+STREAM_BARRIER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p)
 
 _lib = None
 
@@ -111,6 +113,7 @@ def load_library() -> C.CDLL:
     lib.qsb_shard_export.argtypes = [vp, vp]
     lib.qsb_shard_connect.argtypes = [vp, vp, vp, vp]
     lib.qsb_shard_allgather.argtypes = [vp, dp, C.c_int32, dp]
+    lib.qsb_shard_set_stream_barrier.argtypes = [vp, vp, vp]
     lib.qsb_plan_local_dim.argtypes = [vp, C.POINTER(C.c_uint64)]
     lib.qsb_debug_layouts.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     lib.qsb_local_group_create.argtypes = [C.c_int32, C.POINTER(vp)]
@@ -360,7 +363,9 @@ class ShardedPlan(Plan):
 
     def __init__(self, table: SpinTable, rank: int, world: int, device: int = 0):
         self.rank, self.world = int(rank), int(world)
+        self.device_index = int(device)
         self._hook = None
+        self._stream_hook = None
         super().__init__(table, device)
         d = C.c_uint64(0)
         _check(self.lib.qsb_plan_local_dim(self._h, C.byref(d)))
@@ -382,6 +387,14 @@ class ShardedPlan(Plan):
         self._hook = allgather  # keep the ctypes callback alive as long as the plan
         fn = C.cast(allgather, C.c_void_p)
         _check(self.lib.qsb_shard_connect(self._h, joined, fn, C.c_void_p(ctx) if ctx is not None else None))
+
+    def set_stream_barrier(self, hook) -> None:
+        """Install (or, with None, remove) a stream-ordered rank barrier: a STREAM_BARRIER_FN instance.  With one, the
+        H-apply overlaps the NVLink-bound centre pass of one branch with the HBM-bound passes of the other
+        (qsb_shard_set_stream_barrier); only for ranks that each own their GPU."""
+        self._stream_hook = hook   # keep the ctypes callback alive
+        fn = C.cast(hook, C.c_void_p) if hook is not None else None
+        _check(self.lib.qsb_shard_set_stream_barrier(self._h, fn, None))
 
     def allgather(self, values) -> np.ndarray:
         """[world][len(values)] doubles gathered over the plan's own hook (collective; host-side agreement only)."""

@@ -75,8 +75,38 @@ def make_torch_allgather(world: int, device=None):
     return engine.ALLGATHER_FN(hook)
 
 
-def connect_torch_distributed(plan: "engine.ShardedPlan") -> None:
-    """Exchange the exchange-scratch descriptors over torch.distributed and map the peers (collective)."""
+def make_torch_stream_barrier(device=None):
+    """A STREAM_BARRIER_FN over the default (NCCL) group: a one-element all-reduce issued with the given CUDA stream
+    as torch's current stream.  ProcessGroupNCCL orders the collective after that stream's earlier work and makes the
+    stream wait for it; the host does not block.  All ranks must issue their barriers in the same order."""
+    import torch
+    import torch.distributed as dist
+
+    dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
+    token = torch.zeros(1, dtype=torch.float32, device=dev)
+    streams = {}
+
+    def hook(_ctx, stream_ptr):
+        try:
+            s = streams.get(stream_ptr)
+            if s is None:
+                s = streams[stream_ptr] = torch.cuda.ExternalStream(stream_ptr, device=dev)
+            with torch.cuda.stream(s):
+                dist.all_reduce(token)
+            return 0
+        except Exception as exc:  # never let an exception cross the C boundary
+            print(f"[qsb200] stream-barrier hook failed: {exc!r}", flush=True)
+            return 1
+
+    return engine.STREAM_BARRIER_FN(hook)
+
+
+def connect_torch_distributed(plan: "engine.ShardedPlan", overlap: Optional[bool] = None) -> None:
+    """Exchange the exchange-scratch descriptors over torch.distributed and map the peers (collective).
+    ``overlap`` (default: on with the NCCL backend, QSB200_SHARD_OVERLAP=0 turns it off): install the stream-ordered
+    barrier, i.e. run the centre pass of one branch under the HBM passes of the other."""
+    import os
+
     import torch.distributed as dist
 
     if not dist.is_initialized():
@@ -86,6 +116,10 @@ def connect_torch_distributed(plan: "engine.ShardedPlan") -> None:
     blobs: List[Optional[bytes]] = [None] * plan.world
     dist.all_gather_object(blobs, plan.export_blob())
     plan.connect(blobs, make_torch_allgather(plan.world))
+    if overlap is None:
+        overlap = os.environ.get("QSB200_SHARD_OVERLAP", "1") != "0"
+    if overlap and "nccl" in str(dist.get_backend()):
+        plan.set_stream_barrier(make_torch_stream_barrier(plan.device_index))
 
 
 def sharded_plan_from_env(table: SpinTable, device: Optional[int] = None) -> "engine.ShardedPlan":

@@ -43,7 +43,8 @@ for bits in [int(a) for a in sys.argv[1:]] or [30]:
     args = argparse.Namespace(shard_local_bits=bits)
     out = bench.sharded_leg(args, rank, world, local, barrier, allmax)
     if rank == 0:
-        keep = {k: out[k] for k in ("n_qubits", "world", "ms_per_happly", "layouts", "kernel_ms")}
+        keep = {k: out[k] for k in ("n_qubits", "world", "ms_per_happly", "layouts", "kernel_ms", "hbm_passes_ms_per_happly",
+                                    "overlap", "parity_max_rel_err", "vs_unsharded", "strong")}
         keep["nvlink"] = {k: out["nvlink"][k] for k in ("centre_ms", "achieved_GBps_per_direction", "frac")} if world > 1 else None
         print(json.dumps(keep), flush=True)
     torch.cuda.empty_cache()
