@@ -107,23 +107,40 @@ static int session_prime(qsb_plan* p, Session* s) {
 
 // One step attempt of size hu.  Returns the weighted RMS error in *err; obs sums of the candidate in cand_sums.
 // Every stage input y + hu sum_j a_sj k_j is formed inside pass_first of the apply that consumes it (Combine), the
-// applies end in the plain k-producing pass_last, and the embedded error estimate is one streaming sweep at the end:
-// no stage vector is read by a latency-bound epilogue.
+// applies end in the plain k-producing pass_last, and the embedded error estimate rides on the last stage (below).
+static bool dp5_error_sweep() {  // A/B knob: the embedded error estimate as its own 8 S streaming sweep (the round-1 form)
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("QSB200_DP5_ERR_SWEEP"); on = (e && *e == '1') ? 1 : 0; }
+  return on == 1;
+}
+
 static int attempt_dp5(qsb_plan* p, Session* s, double hu, double* err, double* cand_sums) {
   static const DP5 T = dp5_tableau();
+  const bool sweep = dp5_error_sweep();
   for (int st = 0; st <= 5; ++st) {  // apply #st: src = ys = y + hu sum_j a[st][j] k_j, produces k_{st+1} (0-based k[st+1])
     Combine cb = {};
-    cb.vin[0] = s->y; cb.c[0] = 1.0; cb.n_in = 1;
+    cb.vin[0] = s->y; cb.c[0] = 1.0; cb.e[0] = 0.0; cb.n_in = 1;
     for (int j = 0; j <= st; ++j)
-      if (T.a[st][j] != 0.0) { cb.vin[cb.n_in] = s->k[j]; cb.c[cb.n_in] = hu * T.a[st][j]; ++cb.n_in; }
+      if (T.a[st][j] != 0.0) { cb.vin[cb.n_in] = s->k[j]; cb.c[cb.n_in] = hu * T.a[st][j]; cb.e[cb.n_in] = hu * T.e[j]; ++cb.n_in; }
     cb.out = s->ys;
     Epilogue e = blank_epilogue(s);
     e.o1 = s->k[st + 1];
+    if (st == 5 && !sweep) {
+      // The embedded error estimate rides on the last stage: its pass_first reads y, k_1, k_3 .. k_6 anyway (the
+      // tableau's zero pattern, a_72 = e_2 = 0, is the same for both rows) and also forms Q = hu sum_{j<=6} e_j k_j,
+      // parked in k_7's own storage; its pass_last then reads Q (in place) and y and reduces
+      // |Q + hu e_7 k_7|^2 / sc^2 with sc = atol + rtol max(|y|, |y_new|): 3 S of traffic instead of an 8 S sweep.
+      cb.eout = s->k[6];
+      e.vin[0] = s->k[6]; e.c[0] = 0.0; e.e[0] = 1.0;
+      e.vin[1] = s->y;    e.c[1] = 0.0; e.e[1] = 0.0;
+      e.n_in = 2;
+      e.want_err = 1; e.ek = hu * T.e[6]; e.sc_i0 = 1; e.sc_i1 = -2;
+    }
     // the last apply acts on y_new (FSAL): its pass_first / pass_centre also collect y_new's observable sums
     int rc = launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, st == 5 ? 1 : 0, s->partials, p->stream, link_of(p), &cb, &p->fu);
     if (rc) return rc;
   }
-  {
+  if (sweep) {
     ErrSpec es = {};
     es.vin[0] = s->y; es.vin[1] = s->ys; es.n_in = 2;
     for (int j = 0; j < 7; ++j)

@@ -51,7 +51,7 @@ struct Epilogue {
   cplx* o2;
   int n_in;
   int want_err;          // accumulate |err|^2 / sc^2 into partials
-  int sc_i0, sc_i1;      // sc = atol + rtol max(|vin[sc_i0]|, sc_i1 < 0 ? |o2| : |vin[sc_i1]|)
+  int sc_i0, sc_i1;      // sc = atol + rtol max(|vin[sc_i0]|, sc_i1 >= 0 ? |vin[sc_i1]| : sc_i1 == -1 ? |o2| : |v|)
   int raw_h;             // 1: k = H v (no -i), for qsb_apply_h
   double atol, rtol;
 };
@@ -62,10 +62,15 @@ constexpr int MAX_WORLD = 8;
 //     v = sum_q c_q vin_q      (e.g. the DP5 stage input y + h sum_j a_sj k_j),
 // written once to `out` (pass_last needs it for the Dz term) and transformed in the same pass.  n_in = 0: no
 // combination, pass_first just reads its src.
+// Optionally the same loads also form a second combination, eout = sum_q e_q vin_q: the embedded pair's error
+// estimate over the stages that exist so far (DP5: h sum_{j<=6} e_j k_j while pass_first of the last stage holds
+// k_1..k_6 anyway); the last stage's pass_last adds its own k and takes the norm (Epilogue, sc_i1 = -2).
 struct Combine {
   const cplx* vin[MAX_VEC_IN];
   double c[MAX_VEC_IN];
+  double e[MAX_VEC_IN];
   cplx* out;
+  cplx* eout;
   int n_in;
 };
 

@@ -36,7 +36,9 @@ struct TileMap {
 // ---------------------------------------------------------------------------------------------------
 // COMB: psi is formed here as sum_q c_q vin_q (Combine) and written to cb.out on the way; the loads go in two
 // half-bursts of 8 per input vector so that accumulators + in-flight values fit the register file.
-template <bool COMB>
+// ERR (with COMB): the loads also accumulate cb.eout = sum_q e_q vin_q, in quarter-bursts of 4 so that the second
+// accumulator fits the register file.
+template <bool COMB, bool ERR = false>
 __global__ void __launch_bounds__(TPT, 2)
 pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx* __restrict__ ty, Combine cb,
            int collect_obs, double* __restrict__ partials) {
@@ -49,6 +51,36 @@ pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx
   if (!COMB) {
 #pragma unroll
     for (int j = 0; j < 16; ++j) r[j] = psi[base | (uint64_t)elem<8>(tt, j)];
+  } else if (ERR) {
+    const uint64_t i0 = base | (uint64_t)tt;  // elem<8>(tt, j) = tt + 256 j
+#pragma unroll
+    for (int q4 = 0; q4 < 16; q4 += 4) {
+      cplx er[4];
+      {
+        const cplx* v0 = cb.vin[0];
+        const double c0 = cb.c[0], e0 = cb.e[0];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const cplx w = v0[i0 + 256u * (q4 + j)];
+          r[q4 + j] = c0 * w;
+          er[j] = e0 * w;
+        }
+      }
+      for (int q = 1; q < cb.n_in; ++q) {
+        const cplx* vq = cb.vin[q];
+        const double cq = cb.c[q], eq = cb.e[q];
+        cplx w[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) w[j] = vq[i0 + 256u * (q4 + j)];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { axpy(r[q4 + j], cq, w[j]); axpy(er[j], eq, w[j]); }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        cb.out[i0 + 256u * (q4 + j)] = r[q4 + j];
+        cb.eout[i0 + 256u * (q4 + j)] = er[j];
+      }
+    }
   } else {
     const uint64_t i0 = base | (uint64_t)tt;  // elem<8>(tt, j) = tt + 256 j
 #pragma unroll

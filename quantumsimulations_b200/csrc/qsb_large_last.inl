@@ -134,7 +134,8 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
       for (int jj = 0; jj < B; ++jj) {
         if (EPI & 1) ep.o2[idx0 + 256u * (j0 + jj)] = o2[jj];
         if (EPI & 2) {
-          if (ep.sc_i1 < 0) m1[jj] = (EPI & 1) ? norm2(o2[jj]) : 0.0;
+          if (ep.sc_i1 == -2) m1[jj] = norm2(v[jj]);
+          else if (ep.sc_i1 < 0) m1[jj] = (EPI & 1) ? norm2(o2[jj]) : 0.0;
           double sc = ep.atol + ep.rtol * sqrt(fmax(m0[jj], m1[jj]));
           err_acc += norm2(er[jj]) / (sc * sc);
           aux_acc += m0[jj] / (sc * sc);
@@ -325,6 +326,7 @@ void prepare_device() {
   const int sm = (int)((size_t)TILE_PHYS * sizeof(cplx));
   tile_kernel_attrs(pass_first<false>, sm);
   tile_kernel_attrs(pass_first<true>, sm);
+  tile_kernel_attrs(pass_first<true, true>, sm);
   tile_kernel_attrs(pass_last<0, 8, 0>, sm);
   tile_kernel_attrs(pass_last<1, 4, 2>, sm);
   tile_kernel_attrs(pass_last<2, 4, 2>, sm);
@@ -460,7 +462,10 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
     for (int k = f - 1; k >= 1; --k) { Timed t(1, stream, 4 * S); launch_mid(g.lay[k], all, tx, ty, n_tiles, stream); }
     return QSB_OK;
   }
-  for (int k = 1; k < centre; ++k) { Timed t(1, stream, 4 * S); launch_mid(g.lay[k], all, tx, ty, n_tiles, stream); }
+  const bool overlapped = g.world > 1 && link && link->stream_barrier &&
+                          !(shard_ring_enabled() && centre_window(g.lay[centre]) != 0);
+  if (!overlapped)
+    for (int k = 1; k < centre; ++k) { Timed t(1, stream, 4 * S); launch_mid(g.lay[k], all, tx, ty, n_tiles, stream); }
   if (g.world == 1) {
     Timed t(2, stream, 4 * S);
     PeerPtrs none = {};
@@ -470,7 +475,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
     PeerPtrs pp = {};
     for (int r = 0; r < g.world; ++r) { pp.t[0][r] = link->tx[r]; pp.t[1][r] = link->ty[r]; }
     const int w = centre_window(g.lay[centre]);
-    if (link->stream_barrier && !(shard_ring_enabled() && w != 0)) {
+    if (overlapped) {
       // Overlapped: branch by branch.  Plan stream S: mids forward x, barrier, mids forward y, barrier, then (after the
       // centre stream's events) mids back x, mids back y.  Centre stream C (low priority, so that the short HBM-bound
       // launches of S take the SM slots the long NVLink-bound centre CTAs free): centre x, barrier, centre y, barrier.
@@ -530,10 +535,11 @@ int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cp
   const double S = (double)(sizeof(cplx) << g.n_loc);
   {
     const bool cmb = comb && comb->n_in > 0;
-    Timed t(cmb ? 4 : 0, stream, cmb ? (comb->n_in + 3) * S : 3 * S);
+    Timed t(cmb ? 4 : 0, stream, cmb ? (comb->n_in + 3 + (comb->eout ? 1 : 0)) * S : 3 * S);
     if (comb && comb->n_in > 0) {
       if (comb->out != src) { set_error("internal: Combine::out must be the vector the apply acts on"); return QSB_ERR_BAD_ARG; }
-      pass_first<true><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, *comb, collect_obs, partials);
+      if (comb->eout) pass_first<true, true><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, *comb, collect_obs, partials);
+      else pass_first<true><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, *comb, collect_obs, partials);
     } else {
       Combine none = {};
       pass_first<false><<<n_tiles, TPT, sm2, stream>>>(a, src, tx, ty, none, collect_obs, partials);

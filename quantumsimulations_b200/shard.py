@@ -75,24 +75,34 @@ def make_torch_allgather(world: int, device=None):
     return engine.ALLGATHER_FN(hook)
 
 
-def make_torch_stream_barrier(device=None):
-    """A STREAM_BARRIER_FN over the default (NCCL) group: a one-element all-reduce issued with the given CUDA stream
-    as torch's current stream.  ProcessGroupNCCL orders the collective after that stream's earlier work and makes the
-    stream wait for it; the host does not block.  All ranks must issue their barriers in the same order."""
+def make_torch_stream_barrier(device=None, n_streams: int = 2):
+    """A STREAM_BARRIER_FN over NCCL: a one-element all-reduce issued with the given CUDA stream as torch's current
+    stream, so the collective is ordered after that stream's earlier work and the stream waits for it; the host does
+    not block.  Every distinct stream gets its OWN process group (communicator): collectives of one communicator must
+    not be in flight on two streams at once - their kernels could pair up across ranks in different orders, and a
+    barrier that pairs with the wrong peer call is no barrier (measured: wrong amplitudes at N >= 24).  Collective:
+    all ranks must call this (it creates the groups) and later issue their barriers in the same order per stream."""
     import torch
     import torch.distributed as dist
 
     dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
-    token = torch.zeros(1, dtype=torch.float32, device=dev)
-    streams = {}
+    groups = [dist.new_group(backend="nccl") for _ in range(n_streams)]
+    tokens = [torch.zeros(1, dtype=torch.float32, device=dev) for _ in range(n_streams)]
+    for g, tok in zip(groups, tokens):          # build the communicators now, not inside the first H-apply
+        dist.all_reduce(tok, group=g)
+    torch.cuda.synchronize(dev)
+    slots = {}
 
     def hook(_ctx, stream_ptr):
         try:
-            s = streams.get(stream_ptr)
-            if s is None:
-                s = streams[stream_ptr] = torch.cuda.ExternalStream(stream_ptr, device=dev)
+            slot = slots.get(stream_ptr)
+            if slot is None:
+                if len(slots) >= n_streams:
+                    raise RuntimeError("more streams than barrier groups")
+                slot = slots[stream_ptr] = (len(slots), torch.cuda.ExternalStream(stream_ptr, device=dev))
+            k, s = slot
             with torch.cuda.stream(s):
-                dist.all_reduce(token)
+                dist.all_reduce(tokens[k], group=groups[k])
             return 0
         except Exception as exc:  # never let an exception cross the C boundary
             print(f"[qsb200] stream-barrier hook failed: {exc!r}", flush=True)

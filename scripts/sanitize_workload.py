@@ -1,0 +1,99 @@
+#!/usr/bin/env python
+"""CI-sized pass over every kernel family, meant to run under compute-sanitizer:
+
+    compute-sanitizer --tool memcheck  python scripts/sanitize_workload.py
+    compute-sanitizer --tool racecheck python scripts/sanitize_workload.py
+
+Covers: on-chip row product + trajectory kernel (N <= 10, DP5 and Taylor), the propagator path with time-split
+chains, the tiled H-apply with one, two and three strided layouts (incl. the padded window-[0,4) code of groups wider
+than 8 bits), both tiled integrators with the fused epilogues / stage combination / error sweep, the product-state
+hook, and the sharded path with 4 ranks as threads (P2P centre pass on one device).  Every result is also checked
+against the oracle, so a sanitizer-clean run that computes garbage still fails.
+"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+import numpy as np  # noqa: E402
+
+from bench import sweep_params  # noqa: E402
+from conftest import random_table  # noqa: E402
+from oracle import dense, product  # noqa: E402
+from quantumsimulations_b200 import compile_table, engine, shard, simulate_rare, simulate_rare_batch  # noqa: E402
+
+which = set(sys.argv[1:]) or {"small", "prop", "tiled", "steps", "shard"}
+
+
+def rand_state(n, seed):
+    rng = np.random.default_rng(seed)
+    v = rng.normal(size=1 << n) + 1j * rng.normal(size=1 << n)
+    return v / np.linalg.norm(v)
+
+
+def check_apply(table, seed):
+    bm = table.bit_major()
+    psi = rand_state(table.n, seed)
+    want = dense.apply_h(bm["h"], bm["J"], psi)
+    with engine.Plan(table) as plan:
+        got = plan.apply_h(psi)
+    err = np.max(np.abs(got - want)) / np.max(np.abs(want))
+    assert err < 1e-12, (table.n, err)
+
+
+if "small" in which:
+    for n in (3, 7, 8, 10):
+        check_apply(random_table(n, 40 + n), n)
+    for m in ("dp5", "taylor"):
+        t, out, st = simulate_rare(sweep_params(6, 50e3, t_final=2e-5, steps=9), method=m, return_stats=True)
+        assert st.n_accepted > 0 and abs(out["Iz_sea"][0] + 3.0) < 1e-12
+    simulate_rare_batch([sweep_params(6, d, v, t_final=1e-5, steps=5) for d in (0.0, 75e3) for v in ("center_on", "shell_off")],
+                        method="taylor")
+    print("small ok", flush=True)
+if "prop" in which:
+    t, out, st = simulate_rare(sweep_params(6, 50e3, t_final=3e-3, steps=600), return_stats=True)   # time-split chain
+    assert st.path == 2 and abs(out["Iz_sea"][0] + 3.0) < 1e-12
+    t, out, st = simulate_rare(sweep_params(3, 25e3, t_final=1e-3, steps=40), method="propagator", return_stats=True)
+    assert st.path == 2
+    print("prop ok", flush=True)
+if "tiled" in which:
+    for n, env in ((12, {}), (14, {}), (16, {"QSB200_MAX_GROUP": "2"}), (17, {"QSB200_MAX_GROUP": "3"}), (21, {"QSB200_GROUPS": "9"}),
+                   (22, {"QSB200_GROUPS": "10"})):
+        os.environ.update(env)
+        tb = random_table(n, 60 + n, dense_pairs=False)
+        if n <= 17:
+            check_apply(tb, n)
+        bm = tb.bit_major()
+        phi = product.random_phi(n, n)
+        rows = np.random.default_rng(n).integers(0, 1 << n, size=512, dtype=np.uint64)
+        with engine.Plan(tb) as plan:
+            got = plan.apply_h_product(phi, rows)
+        want = product.apply_h_rows(bm["h"], bm["J"], phi, rows)
+        assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-12, n
+        for k in env:
+            del os.environ[k]
+    print("tiled ok", flush=True)
+if "steps" in which:
+    table = compile_table(sweep_params(13, 50e3))
+    for m, order in (("dp5", 0), ("taylor", 7), ("taylor", 8)):
+        opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, max_step=1e-5, nsteps=0, method=m, order=order)
+        with engine.Plan(table) as plan:
+            plan.session_begin(opts)
+            _, st, _ = plan.session_step(3)
+            obs = plan.session_observe()
+            plan.session_end()
+        assert abs(obs[7] - 1.0) < 1e-6 and st.n_accepted >= 1
+    print("steps ok", flush=True)
+if "shard" in which:
+    n, world = 14, 4
+    tb = random_table(n, 77)
+    bm = tb.bit_major()
+    psi = rand_state(n, 5)
+    want = dense.apply_h(bm["h"], bm["J"], psi)
+    with shard.LocalShardGroup(tb, world) as grp:
+        got = grp.apply_h(psi)
+        opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, method="taylor", order=8)
+        grp.evolve(np.linspace(0.0, 1e-3, 3), opts, psi)
+    assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-12
+    print("shard ok", flush=True)
+print("sanitize_workload: all ok", flush=True)
