@@ -211,6 +211,12 @@ int qsb_shard_set_stream_barrier(qsb_plan* p, qsb_stream_barrier_fn fn, void* ct
       QSB_CUDA(cudaEventCreateWithFlags(&p->link.ev_centre[b], cudaEventDisableTiming));
     }
   }
+  {
+    int n_sms = 0;
+    QSB_CUDA(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, p->device));
+    p->link.centre_ctas = std::max(1, n_sms);
+    if (const char* e = getenv("QSB200_CENTRE_CTAS")) p->link.centre_ctas = std::max(1, atoi(e));
+  }
   p->link.stream_barrier = (int (*)(void*, cudaStream_t))fn;
   p->link.barrier_ctx = ctx;
   return QSB_OK;

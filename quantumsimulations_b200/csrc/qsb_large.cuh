@@ -111,6 +111,7 @@ struct ShardLink {
   int (*stream_barrier)(void* ctx, cudaStream_t stream);
   void* barrier_ctx;
   cudaStream_t centre_stream;
+  int centre_ctas;                      // CTAs of the persistent centre launch (QSB200_CENTRE_CTAS; default = SM count)
   cudaEvent_t ev_fwd[2], ev_centre[2];  // per branch: mids forward done (plan stream) / centre + barrier done (centre stream)
   // TMA descriptors of the peers' scratch vectors for the ring version of the centre pass, [branch][peer]; built on
   // first use after the link is connected (host cache)

@@ -25,6 +25,7 @@ struct TileMap {
   int lb, cbits;
   unsigned zero;  // always 0; see opaque()
   int branch0;    // branch of blockIdx.y == 0 (a launch with gridDim.y == 1 covers ONE branch: sharded overlap)
+  unsigned count; // pass_centre<PERSIST> only: the gridDim.x CTAs walk tiles 0 .. count-1 of the map
   __device__ __forceinline__ uint64_t tile(unsigned bx) const {
     return (uint64_t)cbase + (bx & ((1u << lb) - 1)) + ((uint64_t)(bx >> lb) << cbits);
   }
@@ -222,8 +223,10 @@ struct PeerPtrs {
 // SHARDED: the group's top bits are the rank, so tile rows come from (and go back to) the peers' scratch vectors
 // through P2P loads/stores; this rank owns tiles tm.cbase .. of the centre layout and the diagonal rows / partial
 // sums are numbered locally (blockIdx.x).
-template <bool SHARDED, bool COLLECT, int W>
-__global__ void __launch_bounds__(TPT, 2)
+// OCC: CTAs per SM the kernel is compiled for (2: 128 registers; 3: 80 registers, which the W = 4 / 8 bodies fit
+// without spilling - a third resident tile to cover the other two's butterfly phases; A/B knob QSB200_CENTRE_OCC).
+template <bool SHARDED, bool COLLECT, int W, int OCC = 2, bool PERSIST = false>
+__global__ void __launch_bounds__(TPT, OCC)
 pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty, PeerPtrs peers,
             double* __restrict__ partials) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -232,67 +235,77 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
   const int branch = tm.branch0 + blockIdx.y;  // 0: x, 1: y
   cplx* t = branch ? ty : tx;
   const double (&ww)[16] = branch ? a.tab.Wy : a.tab.Wx;
-  const uint64_t v = tm.tile(blockIdx.x);
   const int tt = threadIdx.x;
-  TileDiag<W> td;
-  td.load((branch ? a.tab.Ty : a.tab.Tx) + (size_t)blockIdx.x * TD_STRIDE, branch ? a.tab.Iy : a.tab.Ix, tt);
-  const uint64_t base = tile_base(L, v);
   const uint64_t lmask = (1ull << a.g.n_loc) - 1;
-  cplx r[16];
-  double s[2] = {0.0, 0.0};
-  {
-    WinOff wo;
-    wo.init<8>(L, 0);
-    const uint64_t idx0 = gidx(L, base, elem<8>(tt, 0));
+  // PERSIST: gridDim.x CTAs walk the tm.count tiles of this rank.  The overlapped sharded mode launches one CTA per
+  // SM, so that the HBM-bound passes of the other branch keep the SMs' second CTA slot while this NVLink-bound pass
+  // is in flight (two full-occupancy kernels would only take turns).  (A compile-time switch: the loop costs the
+  // one-tile-per-CTA kernels of the unsharded hot path registers they do not have.)
+  unsigned bx = blockIdx.x;
+  do {
+    const uint64_t v = tm.tile(bx);
+    TileDiag<W> td;
+    td.load((branch ? a.tab.Ty : a.tab.Tx) + (size_t)bx * TD_STRIDE, branch ? a.tab.Iy : a.tab.Ix, tt);
+    const uint64_t base = tile_base(L, v);
+    cplx r[16];
+    double s[2] = {0.0, 0.0};
+    {
+      WinOff wo;
+      wo.init<8>(L, 0);
+      const uint64_t idx0 = gidx(L, base, elem<8>(tt, 0));
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      const uint64_t idx = idx0 + wo.at(j);
-      r[j] = SHARDED ? peers.t[branch][idx >> a.g.n_loc][idx & lmask] : t[idx];
+      for (int j = 0; j < 16; ++j) {
+        const uint64_t idx = idx0 + wo.at(j);
+        r[j] = SHARDED ? peers.t[branch][idx >> a.g.n_loc][idx & lmask] : t[idx];
+      }
     }
-  }
-  if constexpr (W == 8) {
-    centre_core<8, COLLECT>(r, tt, L.m8, td, ww, L, base, a.g, s);
-  } else {
-    constexpr bool PAD = W == 0;  // only window [0,4) needs the padded buffer
-    bfly16<0>(r, L.m8);
-    any_store16<8, PAD>(sm, tt, r);
-    __syncthreads();
-    if constexpr (W == 4) {
-      tile_load16<4>(sm, tt, r);
-      centre_core<4, COLLECT>(r, tt, L.m4, td, ww, L, base, a.g, s);
-      tile_store16<4>(sm, tt, r);
+    if constexpr (W == 8) {
+      centre_core<8, COLLECT>(r, tt, L.m8, td, ww, L, base, a.g, s);
     } else {
-      smem_round<4, 0>(sm, tt, L.m4);
+      constexpr bool PAD = W == 0;  // only window [0,4) needs the padded buffer
+      bfly16<0>(r, L.m8);
+      any_store16<8, PAD>(sm, tt, r);
       __syncthreads();
-      smem_load16<0>(sm, tt, r);
-      centre_core<0, COLLECT>(r, tt, L.m0, td, ww, L, base, a.g, s);
-      smem_store16<0>(sm, tt, r);
+      if constexpr (W == 4) {
+        tile_load16<4>(sm, tt, r);
+        centre_core<4, COLLECT>(r, tt, L.m4, td, ww, L, base, a.g, s);
+        tile_store16<4>(sm, tt, r);
+      } else {
+        smem_round<4, 0>(sm, tt, L.m4);
+        __syncthreads();
+        smem_load16<0>(sm, tt, r);
+        centre_core<0, COLLECT>(r, tt, L.m0, td, ww, L, base, a.g, s);
+        smem_store16<0>(sm, tt, r);
+        __syncthreads();
+        smem_round<4, 0>(sm, tt, L.m4);
+      }
       __syncthreads();
-      smem_round<4, 0>(sm, tt, L.m4);
+      any_load16<8, PAD>(sm, tt, r);
+      bfly16<0>(r, L.m8);
     }
-    __syncthreads();
-    any_load16<8, PAD>(sm, tt, r);
-    bfly16<0>(r, L.m8);
-  }
-  {
-    const unsigned late0 = tm.zero & (unsigned)__double2loint(r[0].x);  // 0, but only known once the data is final
-    WinOff wo;
-    wo.init<8>(L, late0);
-    const uint64_t idx0 = gidx(L, base | late0, elem<8>(tt, 0));
+    {
+      const unsigned late0 = tm.zero & (unsigned)__double2loint(r[0].x);  // 0, but only known once the data is final
+      WinOff wo;
+      wo.init<8>(L, late0);
+      const uint64_t idx0 = gidx(L, base | late0, elem<8>(tt, 0));
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      const uint64_t idx = idx0 + wo.at(j);
-      if (SHARDED) peers.t[branch][idx >> a.g.n_loc][idx & lmask] = r[j];
-      else t[idx] = r[j];
+      for (int j = 0; j < 16; ++j) {
+        const uint64_t idx = idx0 + wo.at(j);
+        if (SHARDED) peers.t[branch][idx >> a.g.n_loc][idx & lmask] = r[j];
+        else t[idx] = r[j];
+      }
     }
-  }
-  if (COLLECT) {
-    block_reduce<2>(s, red);
-    if (threadIdx.x == 0) {
-      double* p = partials + (size_t)blockIdx.x * PSTRIDE + 3 + 2 * branch;
-      p[0] = s[0]; p[1] = s[1];
+    if (COLLECT) {
+      block_reduce<2>(s, red);
+      if (threadIdx.x == 0) {
+        double* p = partials + (size_t)bx * PSTRIDE + 3 + 2 * branch;
+        p[0] = s[0]; p[1] = s[1];
+      }
     }
-  }
+    if constexpr (!PERSIST) break;
+    __syncthreads();  // the next tile's first store must not overtake this tile's last shared-memory reads
+    bx += gridDim.x;
+  } while (bx < tm.count);
 }
 
 // ---------------------------------------------------------------------------------------------------

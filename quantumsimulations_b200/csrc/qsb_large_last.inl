@@ -237,6 +237,15 @@ static void set_centre_attrs(int sm) {
   tile_kernel_attrs(pass_centre<false, true, W>, sm);
   tile_kernel_attrs(pass_centre<true, false, W>, sm);
   tile_kernel_attrs(pass_centre<true, true, W>, sm);
+  tile_kernel_attrs(pass_centre<true, false, W, 2, true>, sm);
+  tile_kernel_attrs(pass_centre<true, true, W, 2, true>, sm);
+  if constexpr (W != 0) {
+    tile_kernel_attrs(pass_centre<false, false, W, 3>, sm);
+    tile_kernel_attrs(pass_centre<false, true, W, 3>, sm);
+    // three 64 KB tiles only fit with the large carve-out
+    cudaFuncSetAttribute(pass_centre<false, false, W, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(pass_centre<false, true, W, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  }
 }
 
 // Shared memory of a strided pass: the padded buffer only if the layout transforms window [0,4).
@@ -248,10 +257,30 @@ static void launch_mid(const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, u
   else pass_mid<false><<<dim3(n_tiles, nb), TPT, strided_smem(false), stream>>>(L, tm, tx, ty);
 }
 
+static int centre_occupancy() {
+  static int occ = -1;
+  if (occ < 0) { const char* e = std::getenv("QSB200_CENTRE_OCC"); occ = (e && atoi(e) == 3) ? 3 : 2; }
+  return occ;
+}
+
 template <bool SHARDED, int W>
 static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, const PeerPtrs& pp,
                           int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream, int nb) {
   sm = W == 8 ? 0 : strided_smem(W == 0);  // W == 8: the whole group sits in one register window, no staging at all
+  if constexpr (!SHARDED && W != 0) {
+    if (centre_occupancy() == 3) {
+      if (collect_obs) pass_centre<false, true, W, 3><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
+      else pass_centre<false, false, W, 3><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
+      return;
+    }
+  }
+  if constexpr (SHARDED) {
+    if (tm.count) {  // persistent walk (overlapped sharded mode)
+      if (collect_obs) pass_centre<true, true, W, 2, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
+      else pass_centre<true, false, W, 2, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
+      return;
+    }
+  }
   if (collect_obs) pass_centre<SHARDED, true, W><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
   else pass_centre<SHARDED, false, W><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
 }
@@ -447,7 +476,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
   const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx);
   const unsigned n_tiles = 1u << (g.n_loc - TB);
   const int centre = g.n_layouts - 1;
-  const TileMap all = {0u, 0, 0, 0u, 0};
+  const TileMap all = {0u, 0, 0, 0u, 0, 0u};
   const double S = (double)(sizeof(cplx) << g.n_loc);  // bytes of one local vector
   if (fu && fu->on && g.world == 1 && centre_window(g.lay[centre]) != 0 && ensure_tile_maps(g, *fu, tx, ty)) {
     // layouts before f stay full-grid launches; f .. centre .. f is one persistent launch
@@ -484,21 +513,23 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
       // of y, and the centre pass of y under the backward mids of x.
       cudaStream_t C = link->centre_stream;
       for (int br = 0; br < 2; ++br) {
-        const TileMap one = {0u, 0, 0, 0u, br};
+        const TileMap one = {0u, 0, 0, 0u, br, 0u};
         for (int k = 1; k < centre; ++k) { Timed t(1, stream, 2 * S); launch_mid(g.lay[k], one, tx, ty, n_tiles, stream, 1); }
         if (link->stream_barrier(link->barrier_ctx, stream)) { set_error("rank barrier (stream hook) failed"); return QSB_ERR_CUDA; }
         cudaEventRecord(link->ev_fwd[br], stream);
         cudaStreamWaitEvent(C, link->ev_fwd[br], 0);
         {
           Timed t(2, C, 2 * S);
-          const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u, br};
-          launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, C, 1);
+          // persistent: centre_ctas CTAs (default one per SM) walk this rank's n_tiles centre tiles
+          const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u, br, n_tiles};
+          launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials,
+                              std::min<unsigned>(n_tiles, (unsigned)link->centre_ctas), sm1, C, 1);
         }
         if (link->stream_barrier(link->barrier_ctx, C)) { set_error("rank barrier (stream hook) failed"); return QSB_ERR_CUDA; }
         cudaEventRecord(link->ev_centre[br], C);
       }
       for (int br = 0; br < 2; ++br) {
-        const TileMap one = {0u, 0, 0, 0u, br};
+        const TileMap one = {0u, 0, 0, 0u, br, 0u};
         cudaStreamWaitEvent(stream, link->ev_centre[br], 0);
         for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream, 2 * S); launch_mid(g.lay[k], one, tx, ty, n_tiles, stream, 1); }
       }
@@ -512,7 +543,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
         if (w == 8) launch_centre_ring<8>(a, g, *link, collect_obs, partials, n_tiles, stream);
         else launch_centre_ring<4>(a, g, *link, collect_obs, partials, n_tiles, stream);
       } else {
-        const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u, 0};
+        const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u, 0, 0u};
         launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, stream);
       }
     }
