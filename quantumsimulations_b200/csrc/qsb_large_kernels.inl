@@ -223,10 +223,11 @@ struct PeerPtrs {
 // SHARDED: the group's top bits are the rank, so tile rows come from (and go back to) the peers' scratch vectors
 // through P2P loads/stores; this rank owns tiles tm.cbase .. of the centre layout and the diagonal rows / partial
 // sums are numbered locally (blockIdx.x).
-// OCC: CTAs per SM the kernel is compiled for (2: 128 registers; 3: 80 registers, which the W = 4 / 8 bodies fit
-// without spilling - a third resident tile to cover the other two's butterfly phases; A/B knob QSB200_CENTRE_OCC).
-template <bool SHARDED, bool COLLECT, int W, int OCC = 2, bool PERSIST = false>
-__global__ void __launch_bounds__(TPT, OCC)
+// (Three CTAs per SM - 80 registers, which the W = 4 body fits without spilling, and the large carve-out - were
+// measured at N = 28: 3.99 ms against 3.28 ms, profiles/r2_centre_occ3.json; L1 capacity, not a third tile, is what
+// the loads in flight need.)
+template <bool SHARDED, bool COLLECT, int W, bool PERSIST = false>
+__global__ void __launch_bounds__(TPT, 2)
 pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty, PeerPtrs peers,
             double* __restrict__ partials) {
   extern __shared__ __align__(16) unsigned char smem_raw[];

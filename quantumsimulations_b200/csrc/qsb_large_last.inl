@@ -237,15 +237,8 @@ static void set_centre_attrs(int sm) {
   tile_kernel_attrs(pass_centre<false, true, W>, sm);
   tile_kernel_attrs(pass_centre<true, false, W>, sm);
   tile_kernel_attrs(pass_centre<true, true, W>, sm);
-  tile_kernel_attrs(pass_centre<true, false, W, 2, true>, sm);
-  tile_kernel_attrs(pass_centre<true, true, W, 2, true>, sm);
-  if constexpr (W != 0) {
-    tile_kernel_attrs(pass_centre<false, false, W, 3>, sm);
-    tile_kernel_attrs(pass_centre<false, true, W, 3>, sm);
-    // three 64 KB tiles only fit with the large carve-out
-    cudaFuncSetAttribute(pass_centre<false, false, W, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    cudaFuncSetAttribute(pass_centre<false, true, W, 3>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-  }
+  tile_kernel_attrs(pass_centre<true, false, W, true>, sm);
+  tile_kernel_attrs(pass_centre<true, true, W, true>, sm);
 }
 
 // Shared memory of a strided pass: the padded buffer only if the layout transforms window [0,4).
@@ -257,27 +250,14 @@ static void launch_mid(const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, u
   else pass_mid<false><<<dim3(n_tiles, nb), TPT, strided_smem(false), stream>>>(L, tm, tx, ty);
 }
 
-static int centre_occupancy() {
-  static int occ = -1;
-  if (occ < 0) { const char* e = std::getenv("QSB200_CENTRE_OCC"); occ = (e && atoi(e) == 3) ? 3 : 2; }
-  return occ;
-}
-
 template <bool SHARDED, int W>
 static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, const PeerPtrs& pp,
                           int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream, int nb) {
   sm = W == 8 ? 0 : strided_smem(W == 0);  // W == 8: the whole group sits in one register window, no staging at all
-  if constexpr (!SHARDED && W != 0) {
-    if (centre_occupancy() == 3) {
-      if (collect_obs) pass_centre<false, true, W, 3><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
-      else pass_centre<false, false, W, 3><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
-      return;
-    }
-  }
   if constexpr (SHARDED) {
     if (tm.count) {  // persistent walk (overlapped sharded mode)
-      if (collect_obs) pass_centre<true, true, W, 2, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
-      else pass_centre<true, false, W, 2, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
+      if (collect_obs) pass_centre<true, true, W, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
+      else pass_centre<true, false, W, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
       return;
     }
   }
