@@ -145,6 +145,18 @@ int qsb_debug_propagate_shape(int32_t n_qubits, int32_t* out /* [5] */);
 /* ---- pieces of the path, exposed for parity tests and the benchmark ---------------------------- */
 /* out = H psi on host vectors of 2^n complex128 (one H-apply through the same kernels evolve uses).  */
 int qsb_apply_h(qsb_plan* plan, const double* psi_host, double* out_host);
+/* qsb_apply_h WITHOUT any device allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same inputs, outputs and arithmetic as qsb_apply_h on an n_qubits <= QSB_STATIC_MAX_QUBITS plan (host
+ * vectors of 2^n complex128), but the descriptor / input / output device buffers that qsb_apply_h cudaMallocs per call
+ * live in ONE file-scope `static __device__` array of QSB_STATIC_SCRATCH_BYTES (36 KB, held by every GPU that loads the
+ * library until exit).  It calls no cudaMalloc, cudaFree or allocating library routine.  Larger plans are rejected with
+ * QSB_ERR_UNSUPPORTED.  Every call on a device shares that array, which keeps the previous call's contents (the
+ * output slot is cleared at the start of each call): the call blocks until its result is on the host, but calls that
+ * overlap on one GPU (several host threads, several plans) RACE on it - serialise them.                          */
+#define QSB_STATIC_MAX_QUBITS 10
+#define QSB_STATIC_SCRATCH_BYTES (4096 + 2 * 16 * 1024)
+int qsb_apply_h_static(qsb_plan* plan, const double* psi_host, double* out_host);
 /* The same H-apply at sizes no host vector reaches (BASELINE configs C4 / C5): the device fills the state with the
  * PRODUCT state psi[x] = prod_b phi[b][bit_b(x)] (phi: [n][2] complex128, interleaved re,im), applies H through the
  * kernels qsb_evolve uses, and returns rows `rows[i]` (indices into THIS plan's slice; collective when sharded) of

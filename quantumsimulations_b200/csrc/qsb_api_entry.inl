@@ -255,4 +255,22 @@ int qsb_apply_h_product(qsb_plan* p, const double* phi, const uint64_t* rows, in
   return QSB_OK;
 }
 
+
+int qsb_apply_h_static(qsb_plan* p, const double* psi_host, double* out_host) {
+  if (!p || !psi_host || !out_host) return fail(QSB_ERR_BAD_ARG, "null argument");
+  if (!p->small || p->n > QSB_STATIC_MAX_QUBITS)
+    return fail(QSB_ERR_UNSUPPORTED, "qsb_apply_h_static: the static scratch holds at most 2^" + std::to_string(QSB_STATIC_MAX_QUBITS) +
+                                         " amplitudes (n_qubits <= " + std::to_string(QSB_STATIC_MAX_QUBITS) + "); this plan has n_qubits = " +
+                                         std::to_string(p->n) + " - use qsb_apply_h");
+  QSB_CUDA(cudaSetDevice(p->device));
+  qsb_table t;
+  t.n_qubits = p->n; t.h = p->h.data(); t.J = p->J.data(); t.sea_mask = p->sea_mask; t.rare_mask = p->rare_mask;
+  qsb_solver_opts o = {1e-8, 1e-6, 0.0, 0, QSB_METHOD_DP5, 0, 0.0};
+  SmallDesc d;
+  compile_small(&t, 0, &o, 0, &d);
+  // no cudaMalloc / cudaFree on this path: descriptor, input and output go through the library's static device scratch
+  QSB_CUDA(launch_small_apply_static(&d, p->n, (const cplx*)psi_host, (cplx*)out_host, p->stream));
+  return QSB_OK;
+}
+
 }  // extern "C"

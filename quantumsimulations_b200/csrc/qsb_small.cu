@@ -13,6 +13,7 @@
 #include "qsb_small.cuh"
 
 #include <cstdlib>
+#include <mutex>
 
 namespace qsb {
 namespace {

@@ -67,4 +67,9 @@ void small_propagate_shape(int n, int* threads, int* split, int* n_cache, int* r
 // out = H in for one n <= 10 table (test hook: same RHS routine the trajectory kernel uses).
 void launch_small_apply(const SmallDesc* d_desc, int n, const cplx* d_in, cplx* d_out, cudaStream_t stream);
 
+// The same H-apply without any device allocation (host vectors in and out, scratch in a file-scope device array of
+// small_apply_static_bytes() bytes; see qsb_apply_h_static).  The target device must be current.
+cudaError_t launch_small_apply_static(const SmallDesc* h_desc, int n, const cplx* h_in, cplx* h_out, cudaStream_t stream);
+size_t small_apply_static_bytes();
+
 }  // namespace qsb

@@ -505,6 +505,95 @@ void launch_small_apply(const SmallDesc* d_desc, int n, const cplx* d_in, cplx* 
   small_apply_kernel<<<1, threads, smem, stream>>>(d_desc, d_in, d_out, use_reg);
 }
 
+// ---- allocation-free H-apply (qsb_apply_h_static) ------------------------------------------------------------------
+// Scratch of the variant below: [0, 4096) the compiled descriptor, then 2^10 input amplitudes, then 2^10 output
+// amplitudes.  File-scope device memory: every GPU that loads the library holds these 36 KB until exit, every call
+// shares them (calls that overlap on the GPU race), and they keep the last call's contents.
+constexpr size_t STATIC_DESC_BYTES = 4096;
+constexpr size_t STATIC_VEC_BYTES = sizeof(cplx) << SMALL_MAXQ;
+constexpr size_t STATIC_SCRATCH_BYTES = STATIC_DESC_BYTES + 2 * STATIC_VEC_BYTES;
+static_assert(sizeof(SmallDesc) <= STATIC_DESC_BYTES, "descriptor slot of the static scratch is too small");
+static_assert(STATIC_SCRATCH_BYTES == QSB_STATIC_SCRATCH_BYTES && SMALL_MAXQ == QSB_STATIC_MAX_QUBITS, "header and scratch disagree");
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+namespace {
+// small_apply_kernel with its three device buffers inside ONE scratch block (the address comes from the host, which
+// obtained it with cudaGetSymbolAddress: in host code the array's name is not a device address).
+__global__ void small_apply_static_kernel(unsigned char* __restrict__ scratch, int use_reg) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  SmallShared& sh = *reinterpret_cast<SmallShared*>(smem_raw);
+  cplx* buf = reinterpret_cast<cplx*>(smem_raw + ((sizeof(SmallShared) + 15) & ~size_t(15)));
+  const cplx* in = reinterpret_cast<const cplx*>(scratch + STATIC_DESC_BYTES);
+  cplx* out = reinterpret_cast<cplx*>(scratch + STATIC_DESC_BYTES + STATIC_VEC_BYTES);
+  {
+    const int* src = reinterpret_cast<const int*>(scratch);
+    int* dst = reinterpret_cast<int*>(&sh.d);
+    for (int i = threadIdx.x; i < (int)(sizeof(SmallDesc) / 4); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  const SmallDesc& d = sh.d;
+  const uint32_t x = threadIdx.x;
+  const bool live = x < (1u << d.n);
+  const uint32_t xs = live ? x : 0;
+  buf[x] = live ? in[x] : mk(0, 0);
+  __syncthreads();
+  cplx k;
+  if (use_reg && d.n == 7) { RhsReg<7> r; r.setup(d, xs); k = r(buf); }
+  else if (use_reg && d.n == 8) { RhsReg<8> r; r.setup(d, xs); k = r(buf); }
+  else if (use_reg && d.n == 5) { RhsReg<5> r; r.setup(d, xs); k = r(buf); }
+  else if (use_reg && d.n == 3) { RhsReg<3> r; r.setup(d, xs); k = r(buf); }
+  else { RhsGeneric r; r.setup(d, xs); k = r(buf); }
+  if (live) out[x] = mk(-k.y, k.x);  // i * k = H psi
+}
+}  // namespace
+
+// Device address of the scratch on the CURRENT device, resolved once per device (cudaGetSymbolAddress answers for the
+// device that is current when it is called).
+static cudaError_t static_scratch_ptr(unsigned char** out) {
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static unsigned char* ptrs[MAX_DEV] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= MAX_DEV) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[dev]) {
+    unsigned char* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_static_scratch);
+    if (e != cudaSuccess) return e;
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return cudaSuccess;
+}
+
+size_t small_apply_static_bytes() { return STATIC_SCRATCH_BYTES; }
+
+// out_host = H in_host for one n <= SMALL_MAXQ table, with NO device allocation: descriptor, input and output live in
+// g_static_scratch.  The device must be current; blocks until the result is on the host.
+cudaError_t launch_small_apply_static(const SmallDesc* h_desc, int n, const cplx* h_in, cplx* h_out, cudaStream_t stream) {
+  unsigned char* scratch = nullptr;
+  cudaError_t e = static_scratch_ptr(&scratch);
+  if (e != cudaSuccess) return e;
+  const size_t bytes = sizeof(cplx) << n;
+  e = cudaMemcpyAsync(scratch, h_desc, sizeof(SmallDesc), cudaMemcpyHostToDevice, stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(scratch + STATIC_DESC_BYTES, h_in, bytes, cudaMemcpyHostToDevice, stream);
+  // the array keeps the previous call's output: start from zero
+  if (e == cudaSuccess) e = cudaMemsetAsync(scratch + STATIC_DESC_BYTES + STATIC_VEC_BYTES, 0, STATIC_VEC_BYTES, stream);
+  if (e != cudaSuccess) return e;
+  int threads = 1 << n;
+  if (threads < 32) threads = 32;
+  const size_t smem = ((sizeof(SmallShared) + 15) & ~size_t(15)) + sizeof(cplx) * threads;
+  const int use_reg = getenv("QSB200_SMALL_GENERIC") ? 0 : 1;
+  small_apply_static_kernel<<<1, threads, smem, stream>>>(scratch, use_reg);
+  e = cudaGetLastError();
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(h_out, scratch + STATIC_DESC_BYTES + STATIC_VEC_BYTES, bytes, cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  return e;
+}
+
 template <bool COL>
 static void launch_evolve_any(const SmallDesc* d_desc, int n_ctas, int max_n, int uniform_n, const double* d_t_out,
                               int64_t n_out, double* d_obs, SmallStats* d_stats, cplx* d_columns, cudaStream_t stream) {

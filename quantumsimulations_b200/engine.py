@@ -57,7 +57,7 @@ class _Stats(C.Structure):
 EXPORTS = (
     "qsb_version", "qsb_last_error", "qsb_device_count", "qsb_plan_create", "qsb_plan_destroy",
     "qsb_plan_workspace_bytes", "qsb_plan_set_workspace", "qsb_evolve", "qsb_evolve_batch", "qsb_apply_h",
-    "qsb_apply_h_product",
+    "qsb_apply_h_product", "qsb_apply_h_static",
     "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_shard_set_stream_barrier", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather",
@@ -102,6 +102,7 @@ def load_library() -> C.CDLL:
     lib.qsb_debug_squarings.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(C.c_int32)]
     lib.qsb_debug_propagate_shape.argtypes = [C.c_int32, C.POINTER(C.c_int32)]
     lib.qsb_apply_h.argtypes = [vp, dp, dp]
+    lib.qsb_apply_h_static.argtypes = [vp, dp, dp]
     lib.qsb_apply_h_product.argtypes = [vp, dp, C.POINTER(C.c_uint64), C.c_int64, dp]
     lib.qsb_session_begin.argtypes = [vp, C.c_uint64, dp, C.c_double, C.POINTER(_Opts)]
     lib.qsb_session_step.argtypes = [vp, C.c_int64, dp, C.POINTER(_Stats), dp]
@@ -297,6 +298,16 @@ class Plan:
             raise ValueError("psi must have 2^n amplitudes (the rank's own slice for a sharded plan)")
         out = np.empty_like(psi)
         _check(self.lib.qsb_apply_h(self._h, _dptr(psi.view(np.float64)), _dptr(out.view(np.float64))))
+        return out
+
+    def apply_h_static(self, psi: np.ndarray) -> np.ndarray:
+        """``apply_h`` through qsb_apply_h_static: no device allocation (scratch in a static device array of
+        36 KB, n_qubits <= 10); calls that overlap on one GPU race on that array."""
+        psi = np.ascontiguousarray(psi, dtype=np.complex128)
+        if psi.shape != (self.local_dim,):
+            raise ValueError("psi must have 2^n amplitudes")
+        out = np.empty_like(psi)
+        _check(self.lib.qsb_apply_h_static(self._h, _dptr(psi.view(np.float64)), _dptr(out.view(np.float64))))
         return out
 
     def apply_h_product(self, phi: np.ndarray, rows: np.ndarray) -> np.ndarray:
