@@ -92,6 +92,17 @@ LargeGeom make_geometry(int n, int rank, int world) {
       set_masks(L);
       start += sz;
     }
+    // Unsharded plans may apply the diagonal on ANY group (only the rank bits tie a sharded centre to the top one).
+    // QSB200_CENTRE_LOW=1 makes the lowest strided group the centre, so that the far-strided top group is served by
+    // the lighter pass_mid (experiment knob).
+    if (world == 1 && g.n_layouts > 2) {
+      const char* e = std::getenv("QSB200_CENTRE_LOW");
+      if (e && *e == '1') {
+        const Layout low = g.lay[1];
+        for (int k = 1; k + 1 < g.n_layouts; ++k) g.lay[k] = g.lay[k + 1];
+        g.lay[g.n_layouts - 1] = low;
+      }
+    }
   } else {
     // n == 12: the centre pass is layout 0 with nothing left to transform (diagonal multiply only)
     Layout& L = g.lay[g.n_layouts++];

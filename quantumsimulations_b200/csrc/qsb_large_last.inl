@@ -477,8 +477,23 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
     for (int k = 1; k < centre; ++k) { Timed t(1, stream, 4 * S); launch_mid(g.lay[k], all, tx, ty, n_tiles, stream); }
   if (g.world == 1) {
     Timed t(2, stream, 4 * S);
-    PeerPtrs none = {};
-    launch_centre<false>(a, g.lay[centre], all, tx, ty, none, collect_obs, partials, n_tiles, sm1, stream);
+    // experiment knob: the TMA-ring centre kernel (one persistent CTA per SM, three tile buffers) on an unsharded plan
+    static const bool ring1 = [] { const char* e = std::getenv("QSB200_CENTRE_RING"); return e && *e == '1'; }();
+    const int w = centre_window(g.lay[centre]);
+    const bool top = g.lay[centre].ge == g.n_loc;  // the ring's box coordinates assume the group reaches the top bit
+    if (ring1 && w != 0 && top && fu && encode_tile_map(&fu->maps[0][0], g.lay[centre], g.n_loc, tx) &&
+        encode_tile_map(&fu->maps[1][0], g.lay[centre], g.n_loc, ty)) {
+      ShardLink self = {};
+      self.ring_maps[0][0] = fu->maps[0][0];
+      self.ring_maps[1][0] = fu->maps[1][0];
+      LargeGeom g1 = g;
+      g1.rank = 0;
+      if (w == 8) launch_centre_ring<8>(a, g1, self, collect_obs, partials, n_tiles, stream);
+      else launch_centre_ring<4>(a, g1, self, collect_obs, partials, n_tiles, stream);
+    } else {
+      PeerPtrs none = {};
+      launch_centre<false>(a, g.lay[centre], all, tx, ty, none, collect_obs, partials, n_tiles, sm1, stream);
+    }
   } else {
     if (!link) { set_error("sharded plan is not connected to its peers (qsb_shard_connect)"); return QSB_ERR_BAD_ARG; }
     PeerPtrs pp = {};
