@@ -198,7 +198,7 @@ int qsb_plan_destroy(qsb_plan* p) {
     if (p->ipc_opened[r]) cudaIpcCloseMemHandle(p->ipc_opened[r]);
   if (p->link.centre_stream) {
     cudaStreamSynchronize(p->link.centre_stream);
-    for (int b = 0; b < 2; ++b) { cudaEventDestroy(p->link.ev_fwd[b]); cudaEventDestroy(p->link.ev_centre[b]); }
+    for (int b = 0; b < MAX_PIPE; ++b) { cudaEventDestroy(p->link.ev_fwd[b]); cudaEventDestroy(p->link.ev_centre[b]); }
     cudaStreamDestroy(p->link.centre_stream);
   }
   if (p->xbuf) cudaFree(p->xbuf);

@@ -206,7 +206,7 @@ int qsb_shard_set_stream_barrier(qsb_plan* p, qsb_stream_barrier_fn fn, void* ct
     int least = 0, greatest = 0;
     QSB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
     QSB_CUDA(cudaStreamCreateWithPriority(&p->link.centre_stream, cudaStreamNonBlocking, least));
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < MAX_PIPE; ++b) {
       QSB_CUDA(cudaEventCreateWithFlags(&p->link.ev_fwd[b], cudaEventDisableTiming));
       QSB_CUDA(cudaEventCreateWithFlags(&p->link.ev_centre[b], cudaEventDisableTiming));
     }
@@ -216,6 +216,8 @@ int qsb_shard_set_stream_barrier(qsb_plan* p, qsb_stream_barrier_fn fn, void* ct
     QSB_CUDA(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, p->device));
     p->link.centre_ctas = std::max(1, n_sms);
     if (const char* e = getenv("QSB200_CENTRE_CTAS")) p->link.centre_ctas = std::max(1, atoi(e));
+    p->link.pipe_lb = 3;  // measured on 2 x B200 at N = 31: 118 / 107 / 102 / 98 ms per H-apply for 1 / 2 / 4 / 8 groups
+    if (const char* e = getenv("QSB200_SHARD_PIPE")) p->link.pipe_lb = std::max(0, std::min(4, atoi(e)));
   }
   p->link.stream_barrier = (int (*)(void*, cudaStream_t))fn;
   p->link.barrier_ctx = ctx;

@@ -57,6 +57,7 @@ struct Epilogue {
 };
 
 constexpr int MAX_WORLD = 8;
+constexpr int MAX_PIPE = 16;            // chunk groups of the overlapped sharded pipeline
 
 // Stage combination fused into the load phase of pass_first: the vector the H-apply acts on is FORMED there,
 //     v = sum_q c_q vin_q      (e.g. the DP5 stage input y + h sum_j a_sj k_j),
@@ -112,7 +113,8 @@ struct ShardLink {
   void* barrier_ctx;
   cudaStream_t centre_stream;
   int centre_ctas;                      // CTAs of the persistent centre launch (QSB200_CENTRE_CTAS; default = SM count)
-  cudaEvent_t ev_fwd[2], ev_centre[2];  // per branch: mids forward done (plan stream) / centre + barrier done (centre stream)
+  cudaEvent_t ev_fwd[MAX_PIPE], ev_centre[MAX_PIPE];  // per chunk group: mids forward + barrier done (plan stream) / centre + barrier done (centre stream)
+  int pipe_lb;                          // log2 of the chunk groups the strided passes are pipelined over (QSB200_SHARD_PIPE; default 3)
   // TMA descriptors of the peers' scratch vectors for the ring version of the centre pass, [branch][peer]; built on
   // first use after the link is connected (host cache)
   CUtensorMap ring_maps[2][MAX_WORLD];

@@ -16,18 +16,23 @@ struct PassArgs {
 constexpr double M_SCALE = -64.0 / (double)TILE;
 
 // Which tiles a launch of a strided-layout pass covers.  Tile v of a layout is numbered by its outer bits in
-// ascending order, so for layouts sharing lk the low (12 - lk) bits of v are index bits [lk, 12): a "chunk".
-// A launch covers 2^lb consecutive chunks starting at cbase: v = cbase + (bx mod 2^lb) + (bx >> lb) << cbits.
-// All tiles of every strided layout inside one chunk touch the same 2^(n - cbits) amplitudes, which is what lets
-// consecutive passes over a chunk batch find their data in L2.  {0, cbits, cbits} is the identity map.
+// ascending order, so index bit b in [lk, 12) - a pad bit that NO strided layout transforms once b >= the largest lk -
+// is bit (b - lk) of v.  Those bits select a "chunk": all strided passes of one chunk touch the same amplitudes and
+// nothing of any other chunk, which is what lets the sharded mode pipeline chunk c's NVLink-bound centre pass under
+// the HBM-bound passes of chunks c - 1 and c + 1.  A launch covers chunks c0 .. c0 + 2^lb - 1 of a cw-bit chunk field
+// that starts at bit `shift` of v:
+//     bx = [low: shift bits][chunk - c0: lb bits][high]   ->   v = vbase + low + (chunk << shift) + (high << (shift + cw)).
+// {vbase, 0, 0, 0, 0} is v = vbase + bx.  vbase: first tile of this rank's slice of the centre layout (sharded), else 0.
 struct TileMap {
-  unsigned cbase;
-  int lb, cbits;
+  unsigned vbase;
+  int shift, cw, lb;
+  unsigned c0;
   unsigned zero;  // always 0; see opaque()
   int branch0;    // branch of blockIdx.y == 0 (a launch with gridDim.y == 1 covers ONE branch: sharded overlap)
-  unsigned count; // pass_centre<PERSIST> only: the gridDim.x CTAs walk tiles 0 .. count-1 of the map
+  unsigned count; // pass_centre<PERSIST> only: the gridDim.x CTAs walk bx = 0 .. count-1
   __device__ __forceinline__ uint64_t tile(unsigned bx) const {
-    return (uint64_t)cbase + (bx & ((1u << lb) - 1)) + ((uint64_t)(bx >> lb) << cbits);
+    const unsigned low = bx & ((1u << shift) - 1), cl = (bx >> shift) & ((1u << lb) - 1), hi = bx >> (shift + lb);
+    return (uint64_t)vbase + low + ((uint64_t)(c0 + cl) << shift) + ((uint64_t)hi << (shift + cw));
   }
 };
 
@@ -221,7 +226,7 @@ struct PeerPtrs {
 // short groups with lk > 8 land here).  The diagonal coefficients (10 registers) are fetched FIRST so that their
 // latency hides behind the tile loads and nothing but the data is live across the butterflies.
 // SHARDED: the group's top bits are the rank, so tile rows come from (and go back to) the peers' scratch vectors
-// through P2P loads/stores; this rank owns tiles tm.cbase .. of the centre layout and the diagonal rows / partial
+// through P2P loads/stores; this rank owns tiles tm.vbase .. of the centre layout and the diagonal rows / partial
 // sums are numbered locally (blockIdx.x).
 // (Three CTAs per SM - 80 registers, which the W = 4 body fits without spilling, and the large carve-out - were
 // measured at N = 28: 3.99 ms against 3.28 ms, profiles/r2_centre_occ3.json; L1 capacity, not a third tile, is what
@@ -245,8 +250,9 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
   unsigned bx = blockIdx.x;
   do {
     const uint64_t v = tm.tile(bx);
+    const size_t slot = (size_t)(v - tm.vbase);  // this rank's number for the tile (diagonal rows, partial sums)
     TileDiag<W> td;
-    td.load((branch ? a.tab.Ty : a.tab.Tx) + (size_t)bx * TD_STRIDE, branch ? a.tab.Iy : a.tab.Ix, tt);
+    td.load((branch ? a.tab.Ty : a.tab.Tx) + slot * TD_STRIDE, branch ? a.tab.Iy : a.tab.Ix, tt);
     const uint64_t base = tile_base(L, v);
     cplx r[16];
     double s[2] = {0.0, 0.0};
@@ -299,7 +305,7 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
     if (COLLECT) {
       block_reduce<2>(s, red);
       if (threadIdx.x == 0) {
-        double* p = partials + (size_t)bx * PSTRIDE + 3 + 2 * branch;
+        double* p = partials + slot * PSTRIDE + 3 + 2 * branch;
         p[0] = s[0]; p[1] = s[1];
       }
     }

@@ -456,7 +456,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
   const size_t sm1 = (size_t)TILE_PHYS * sizeof(cplx);
   const unsigned n_tiles = 1u << (g.n_loc - TB);
   const int centre = g.n_layouts - 1;
-  const TileMap all = {0u, 0, 0, 0u, 0, 0u};
+  const TileMap all = {0u, 0, 0, 0, 0u, 0u, 0, 0u};
   const double S = (double)(sizeof(cplx) << g.n_loc);  // bytes of one local vector
   if (fu && fu->on && g.world == 1 && centre_window(g.lay[centre]) != 0 && ensure_tile_maps(g, *fu, tx, ty)) {
     // layouts before f stay full-grid launches; f .. centre .. f is one persistent launch
@@ -500,34 +500,58 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
     for (int r = 0; r < g.world; ++r) { pp.t[0][r] = link->tx[r]; pp.t[1][r] = link->ty[r]; }
     const int w = centre_window(g.lay[centre]);
     if (overlapped) {
-      // Overlapped: branch by branch.  Plan stream S: mids forward x, barrier, mids forward y, barrier, then (after the
-      // centre stream's events) mids back x, mids back y.  Centre stream C (low priority, so that the short HBM-bound
-      // launches of S take the SM slots the long NVLink-bound centre CTAs free): centre x, barrier, centre y, barrier.
-      // Every barrier is a collective queued on a stream - the host never waits - and all ranks queue them in the
-      // same order (x forward, x centre, y forward, y centre).  The centre pass of x thus runs under the forward mids
-      // of y, and the centre pass of y under the backward mids of x.
+      // Overlapped: a software pipeline over chunk groups.  Index bits [lmax, 12) - pad bits of every strided tile, lmax
+      // the largest lk - are transformed by no strided pass, so they cut the vectors into 2^(12 - lmax) chunks whose
+      // strided passes are independent; K = 2^pipe_lb groups of chunks are pipelined:
+      //   plan stream S (high priority):  fwd 0, B, fwd 1, B, [cen 0] back 0, fwd 2, B, [cen 1] back 1, ... [cen K-1] back K-1
+      //   centre stream C (low priority): [fwd c] centre x c, centre y c, B       for c = 0 .. K-1
+      // (fwd / back: the mid passes of both branches on one group; B: a rank barrier queued on the stream - an NCCL
+      // collective, the host never waits; [..]: an event wait).  The centre pass is NVLink-bound and persistent, one
+      // CTA per SM, so the HBM-bound launches of S keep the second CTA slot of every SM; with K >= 3 the links stay
+      // busy from the end of fwd 0 to the start of back K-1.  Every rank queues the same barriers in the same order
+      // on each stream (one communicator per stream).
       cudaStream_t C = link->centre_stream;
-      for (int br = 0; br < 2; ++br) {
-        const TileMap one = {0u, 0, 0, 0u, br, 0u};
-        for (int k = 1; k < centre; ++k) { Timed t(1, stream, 2 * S); launch_mid(g.lay[k], one, tx, ty, n_tiles, stream, 1); }
+      int lmax = 0;
+      for (int k = 1; k <= centre; ++k) lmax = std::max(lmax, g.lay[k].lk);
+      const int cw = TB - lmax;                                  // chunk field width
+      const int plb = std::max(0, std::min(std::min(link->pipe_lb, cw), 4));
+      const int K = 1 << plb, lb = cw - plb;                     // groups, log2 chunks per group
+      const unsigned per_group = n_tiles >> plb;                 // tiles of one layout in one group
+      auto group_map = [&](const Layout& L, int c, unsigned vbase, int br, unsigned count) {
+        TileMap m = {vbase, lmax - L.lk, cw, lb, (unsigned)c << lb, 0u, br, count};
+        return m;
+      };
+      auto fwd = [&](int c) -> int {
+        for (int k = 1; k < centre; ++k) {
+          Timed t(1, stream, 4 * S / K);
+          launch_mid(g.lay[k], group_map(g.lay[k], c, 0u, 0, 0u), tx, ty, per_group, stream);
+        }
         if (link->stream_barrier(link->barrier_ctx, stream)) { set_error("rank barrier (stream hook) failed"); return QSB_ERR_CUDA; }
-        cudaEventRecord(link->ev_fwd[br], stream);
-        cudaStreamWaitEvent(C, link->ev_fwd[br], 0);
-        {
-          Timed t(2, C, 2 * S);
-          // persistent: centre_ctas CTAs (default one per SM) walk this rank's n_tiles centre tiles
-          const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u, br, n_tiles};
-          launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials,
-                              std::min<unsigned>(n_tiles, (unsigned)link->centre_ctas), sm1, C, 1);
+        cudaEventRecord(link->ev_fwd[c], stream);
+        cudaStreamWaitEvent(C, link->ev_fwd[c], 0);
+        for (int br = 0; br < 2; ++br) {
+          Timed t(2, C, 2 * S / K);
+          launch_centre<true>(a, g.lay[centre], group_map(g.lay[centre], c, (unsigned)g.rank * n_tiles, br, per_group), tx, ty,
+                              pp, collect_obs, partials, std::min<unsigned>(per_group, (unsigned)link->centre_ctas), sm1, C, 1);
         }
         if (link->stream_barrier(link->barrier_ctx, C)) { set_error("rank barrier (stream hook) failed"); return QSB_ERR_CUDA; }
-        cudaEventRecord(link->ev_centre[br], C);
+        cudaEventRecord(link->ev_centre[c], C);
+        return QSB_OK;
+      };
+      auto back = [&](int c) {
+        cudaStreamWaitEvent(stream, link->ev_centre[c], 0);
+        for (int k = centre - 1; k >= 1; --k) {
+          Timed t(1, stream, 4 * S / K);
+          launch_mid(g.lay[k], group_map(g.lay[k], c, 0u, 0, 0u), tx, ty, per_group, stream);
+        }
+      };
+      int rc = fwd(0);
+      for (int c = 1; c < K && !rc; ++c) {
+        rc = fwd(c);
+        back(c - 1);
       }
-      for (int br = 0; br < 2; ++br) {
-        const TileMap one = {0u, 0, 0, 0u, br, 0u};
-        cudaStreamWaitEvent(stream, link->ev_centre[br], 0);
-        for (int k = centre - 1; k >= 1; --k) { Timed t(1, stream, 2 * S); launch_mid(g.lay[k], one, tx, ty, n_tiles, stream, 1); }
-      }
+      if (rc) return rc;
+      back(K - 1);
       return QSB_OK;
     }
     int rc = link->sync(link->ctx);
@@ -538,7 +562,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
         if (w == 8) launch_centre_ring<8>(a, g, *link, collect_obs, partials, n_tiles, stream);
         else launch_centre_ring<4>(a, g, *link, collect_obs, partials, n_tiles, stream);
       } else {
-        const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0u, 0, 0u};
+        const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0, 0u, 0u, 0, 0u};
         launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, stream);
       }
     }
