@@ -28,6 +28,7 @@ extern "C" {
 #define QSB_MAX_QUBITS 34
 #define QSB_SMALL_MAX_QUBITS 10 /* whole trajectory on-chip (one CTA) up to here */
 #define QSB_NOBS 8
+#define QSB_MAX_TAYLOR_ORDER 30
 
 typedef enum {
   QSB_OK = 0,
@@ -65,7 +66,7 @@ typedef struct {
   double max_step;  /* hard cap on h; 0 = none                                                      */
   int64_t nsteps;   /* max internal steps per output interval (zvode MXSTEP semantics); 0 = no cap  */
   int32_t method;   /* qsb_method                                                                   */
-  int32_t order;    /* Taylor order p (4..30); ignored for DP5; 0 = default 20                      */
+  int32_t order;    /* Taylor order p (4..QSB_MAX_TAYLOR_ORDER); ignored for DP5; 0 = default 20    */
   double first_step;/* 0 = automatic                                                                */
 } qsb_solver_opts;
 

@@ -58,7 +58,7 @@ static int check_opts(const qsb_solver_opts* o) {
   if (o->max_step < 0.0 || o->first_step < 0.0 || o->nsteps < 0)
     return fail(QSB_ERR_BAD_ARG, "max_step, first_step and nsteps must be >= 0");
   if (o->method != QSB_METHOD_DP5 && o->method != QSB_METHOD_TAYLOR) return fail(QSB_ERR_BAD_ARG, "unknown method");
-  if (o->method == QSB_METHOD_TAYLOR && o->order != 0 && (o->order < 4 || o->order > 30))
+  if (o->method == QSB_METHOD_TAYLOR && o->order != 0 && (o->order < 4 || o->order > QSB_MAX_TAYLOR_ORDER))
     return fail(QSB_ERR_BAD_ARG, "Taylor order must be 0 (default) or 4..30");
   return QSB_OK;
 }

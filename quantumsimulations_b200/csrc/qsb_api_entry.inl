@@ -131,10 +131,20 @@ int qsb_evolve(qsb_plan* p, uint64_t psi0_index, const double* psi0_host, int64_
   if (!rc) {
     Session* s = p->ses;
     rc = session_observe(p, s, out_obs);
-    for (int64_t k = 1; k < n_out && !rc; ++k) {
+    const bool dense = dense_setup(p, s);
+    int64_t in_interval = 0;
+    for (int64_t k = 1; k < n_out && !rc;) {
+      const double hmax = s->o.max_step > 0.0 ? std::min(s->h, s->o.max_step) : s->h;
+      if (dense && hmax > (t_out[k] - s->t) * (1.0 + 1e-9)) {
+        // the grid is finer than the step the controller wants: one unclipped step serves all outputs inside it
+        rc = dense_step(p, s, t_out, n_out, &k, out_obs, &in_interval);
+        continue;
+      }
       int64_t done = 0;
       rc = session_advance(p, s, t_out[k], INT64_MAX, opts->nsteps, &done);
       if (!rc) rc = session_observe(p, s, out_obs + k * QSB_NOBS);
+      ++k;
+      in_interval = 0;
     }
     cudaEventRecord(e1, p->stream);
     cudaEventSynchronize(e1);

@@ -24,6 +24,8 @@ struct qsb_plan {
   double* d_red = nullptr;      // [PSTRIDE] reduced sums
   double* h_red = nullptr;      // pinned mirror
   Session* ses = nullptr;
+  void* dense_buf = nullptr;    // `order` vectors of kept Taylor terms (dense output, qsb_evolve); grown on demand
+  size_t dense_bytes = 0;
   StridedFusion fu;             // L2-resident fusion of the strided passes (unsharded plans); fu.ctrl is owned here
   // sharded state (world > 1): exchange scratch (tx, ty) the peers map, and the peers' mappings
   void* xbuf = nullptr;
@@ -201,6 +203,7 @@ int qsb_plan_destroy(qsb_plan* p) {
     for (int b = 0; b < MAX_PIPE; ++b) { cudaEventDestroy(p->link.ev_fwd[b]); cudaEventDestroy(p->link.ev_centre[b]); }
     cudaStreamDestroy(p->link.centre_stream);
   }
+  if (p->dense_buf) cudaFree(p->dense_buf);
   if (p->xbuf) cudaFree(p->xbuf);
   if (p->ws && p->ws_owned) cudaFree(p->ws);
   if (p->d_tables) cudaFree(p->d_tables);

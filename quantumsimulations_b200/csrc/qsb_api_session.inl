@@ -18,6 +18,12 @@ struct Session {
   int64_t n_tiles = 0;
   double obs_sums[PSTRIDE] = {};  // sums belonging to the current y (when valid)
   bool obs_valid = false;
+  // Dense output (Taylor, constant H): when the output grid is finer than the controller's step, ONE natural step is
+  // taken with every term kept (dense[m] = term_m = (hu^m / m!) (-iH)^m y, m = 1 .. order), and every output time
+  // inside it is read off the same polynomial, psi(t + s hu) = y + sum_m s^m term_m - one combination + one
+  // observation per output instead of `order` H-applies per output.  Owned by the plan (qsb_plan::dense_buf).
+  cplx* dense[QSB_MAX_TAYLOR_ORDER + 1] = {};
+  bool dense_on = false;
 };
 
 static void carve(qsb_plan* p, Session* s) {
@@ -157,7 +163,7 @@ static int attempt_dp5(qsb_plan* p, Session* s, double hu, double* err, double* 
   return QSB_OK;
 }
 
-static int attempt_taylor(qsb_plan* p, Session* s, double hu, double* err, double* cand_sums) {
+static int attempt_taylor(qsb_plan* p, Session* s, double hu, double* err, double* cand_sums, bool keep_terms = false) {
   // k[0] holds the running term, term_{m+1} = hu/(m+1) * f(term_m), term_0 = y; ys becomes y + sum of terms.
   // The vector an apply acts on (term_m) is in pass_last's registers anyway, so ys is only touched by every second
   // apply, which adds BOTH term_m and term_{m+1}:  m = 1: ys = y + term_1 + term_2;  m = 3, 5, ..: ys += term_m +
@@ -167,7 +173,7 @@ static int attempt_taylor(qsb_plan* p, Session* s, double hu, double* err, doubl
     const bool last = m == s->order - 1;
     Epilogue e = blank_epilogue(s);
     e.alpha = hu / (double)(m + 1);
-    e.o1 = s->k[0];
+    e.o1 = keep_terms ? s->dense[m + 1] : s->k[0];
     if ((m & 1) || last) {
       e.o2 = s->ys;
       e.vin[0] = m <= 1 ? s->y : s->ys; e.c[0] = 1.0; e.n_in = 1;
@@ -179,7 +185,8 @@ static int attempt_taylor(qsb_plan* p, Session* s, double hu, double* err, doubl
       e.want_err = 1; e.ek = e.alpha; e.sc_i0 = e.n_in; e.sc_i1 = -1;
       ++e.n_in;
     }
-    int rc = launch_happly(p->g, p->tab, m == 0 ? s->y : s->k[0], s->tx, s->ty, e, 0, s->partials, p->stream, link_of(p), nullptr, &p->fu);
+    const cplx* src = m == 0 ? s->y : (keep_terms ? s->dense[m] : s->k[0]);
+    int rc = launch_happly(p->g, p->tab, src, s->tx, s->ty, e, 0, s->partials, p->stream, link_of(p), nullptr, &p->fu);
     if (rc) return rc;
   }
   QSB_CUDA(cudaGetLastError());
@@ -251,6 +258,91 @@ static int session_observe(qsb_plan* p, Session* s, double* obs) {
     s->obs_valid = true;
   }
   obs_from_sums(p, s->obs_sums, obs);
+  return QSB_OK;
+}
+
+// Observables of an arbitrary local vector (tx / ty are clobbered).
+static int observe_vec(qsb_plan* p, Session* s, const cplx* vec, double* obs) {
+  int rc = launch_observe(p->g, p->tab, vec, s->tx, s->ty, s->partials, p->stream, link_of(p), &p->fu);
+  if (rc) return rc;
+  QSB_CUDA(cudaGetLastError());
+  double sums[PSTRIDE];
+  rc = fetch_sums(p, s, sums);
+  if (rc) return rc;
+  obs_from_sums(p, sums, obs);
+  return QSB_OK;
+}
+
+// Dense output is offered when the kept terms fit a modest extra allocation: Taylor sessions of plans with at most
+// 2^22 local amplitudes (64 MB per vector; QSB200_DENSE_OUTPUT=0 turns it off, =1 lifts the size limit).
+static bool dense_setup(qsb_plan* p, Session* s) {
+  s->dense_on = false;
+  if (s->o.method != QSB_METHOD_TAYLOR) return false;
+  const char* e = getenv("QSB200_DENSE_OUTPUT");
+  if (e && *e == '0') return false;
+  if (p->n_loc > 22 && !(e && *e == '1')) return false;
+  const size_t vec = sizeof(cplx) << p->n_loc, need = vec * (size_t)s->order;
+  if (p->dense_bytes < need) {
+    if (p->dense_buf) cudaFree(p->dense_buf);
+    p->dense_buf = nullptr; p->dense_bytes = 0;
+    if (cudaMalloc(&p->dense_buf, need) != cudaSuccess) { cudaGetLastError(); p->dense_buf = nullptr; return false; }
+    p->dense_bytes = need;
+  }
+  for (int m = 1; m <= s->order; ++m) s->dense[m] = (cplx*)((char*)p->dense_buf + vec * (size_t)(m - 1));
+  s->dense_on = true;
+  return true;
+}
+
+// One natural step from s->t that is NOT clipped to the next output time; every output time it covers is evaluated
+// from the step's own Taylor polynomial.  *k: next output index (advanced past the outputs served).  Returns with the
+// step accepted (state advanced) or rejected (h reduced); the caller loops.  *in_interval counts attempts since the
+// last served output (zvode's nsteps cap applies per output interval).
+static int dense_step(qsb_plan* p, Session* s, const double* t_out, int64_t n_out, int64_t* k, double* out_obs,
+                      int64_t* in_interval) {
+  if (s->o.nsteps > 0 && *in_interval >= s->o.nsteps)
+    return fail(QSB_ERR_NSTEPS, "more than nsteps internal steps inside one output interval (excess work)");
+  const double t_final = t_out[n_out - 1];
+  const double hmax = s->o.max_step > 0.0 ? std::min(s->h, s->o.max_step) : s->h;
+  double hu = hmax;
+  bool hit = false;
+  const double remaining = t_final - s->t;
+  if (hu >= remaining * (1.0 - 1e-12)) { hu = remaining; hit = true; }
+  if (hu <= 16.0 * 2.220446049250313e-16 * std::fabs(s->t)) return fail(QSB_ERR_STEP_UNDERFLOW, "step size underflow");
+  double err = 0.0, cand[PSTRIDE];
+  int rc = attempt_taylor(p, s, hu, &err, cand, true);
+  if (rc) return rc;
+  ++*in_interval;
+  if (!(err == err)) return fail(QSB_ERR_CUDA, "non-finite error estimate (state blew up)");
+  if (err > 1.0) {
+    ++s->n_rej;
+    s->h = hu * Controller::factor(err, s->inv_q, true);
+    s->after_reject = true;
+    return QSB_OK;
+  }
+  const double t_new = hit ? t_final : s->t + hu;
+  while (*k < n_out && (t_out[*k] <= t_new || (hit && *k == n_out - 1))) {
+    const double frac = (hit && *k == n_out - 1) ? 1.0 : (t_out[*k] - s->t) / hu;
+    const cplx* vec = s->ys;                       // the full step
+    if (frac < 1.0 - 1e-13) {
+      DenseSpec d = {};
+      d.y = s->y; d.out = s->k[0]; d.n = s->order;
+      double pw = 1.0;
+      for (int m = 0; m < s->order; ++m) { pw *= frac; d.term[m] = s->dense[m + 1]; d.c[m] = pw; }
+      launch_dense_eval(d, 1ull << p->n_loc, p->stream);
+      vec = s->k[0];
+    }
+    rc = observe_vec(p, s, vec, out_obs + *k * QSB_NOBS);
+    if (rc) return rc;
+    ++*k;
+    *in_interval = 0;
+  }
+  std::swap(s->y, s->ys);
+  s->obs_valid = false;
+  s->t = t_new;
+  ++s->n_acc;
+  const double hn = hu * Controller::factor(err, s->inv_q, s->after_reject);
+  s->h = (hu < hmax) ? std::max(hn, s->h) : hn;
+  s->after_reject = false;
   return QSB_OK;
 }
 

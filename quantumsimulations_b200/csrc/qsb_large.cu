@@ -43,6 +43,13 @@ LargeGeom make_geometry(int n, int rank, int world) {
     // group sizes, ascending bit order; the LAST group must contain all wl rank bits (it becomes the centre, the
     // only pass that reaches the peers), so it is sized first and the other bits are balanced over the rest
     int sizes[MAX_LAYOUTS] = {0};
+    // Unsharded plans take 9-bit groups (tiles of 128-byte runs: pass_mid 6.1 instead of 6.7 TB/s,
+    // profiles/r2_short_run_pass.json) where that saves a whole layout, i.e. two more HBM passes: N = 29 and 30
+    // become 12 | 9 | 8 and 12 | 9 | 9 (19 S per H-apply) instead of four layouts (27 S).
+    // (Not with the opt-in L2-fused strided pass, QSB200_FUSE_LB, which is written for groups of at most 8 bits.)
+    if (world == 1 && gmax == 8 && !std::getenv("QSB200_MAX_GROUP") && !std::getenv("QSB200_FUSE_LB") &&
+        (rest + 8) / 9 < (rest + 7) / 8)
+      gmax = 9;
     int ng = (rest + gmax - 1) / gmax;
     if (ng > MAX_LAYOUTS - 1) ng = MAX_LAYOUTS - 1;
     int last = std::max(wl, (rest + ng - 1) / ng);
@@ -63,6 +70,12 @@ LargeGeom make_geometry(int n, int rank, int world) {
     if (ng > MAX_LAYOUTS - 1) ng = MAX_LAYOUTS - 1;
     for (int k = 0; k + 1 < ng; ++k) sizes[k] = others / (ng - 1) + (k < others % (ng - 1) ? 1 : 0);
     sizes[ng - 1] = last;
+    if (world == 1 && ng > 1) {  // the centre (last) is the heavier kernel: give it the smallest group, the mids the wide ones
+      int lo = 0;
+      for (int k = 1; k < ng; ++k)
+        if (sizes[k] < sizes[lo]) lo = k;
+      std::swap(sizes[lo], sizes[ng - 1]);
+    }
     // experiment knob: explicit group sizes in ascending bit order, e.g. QSB200_GROUPS=10,6 (each 1..12, summing to
     // n - 12, the last one holding all rank bits).  Groups wider than 8 bits give tiles made of runs shorter than 256
     // bytes (lk = 12 - size pad bits); that is how the short-run passes of DESIGN.md section 10 were timed.

@@ -191,6 +191,15 @@ void launch_set_basis_state(cplx* psi, uint64_t dim, uint64_t index, cudaStream_
 struct ProductPhi { cplx v[QSB_MAX_QUBITS][2]; };
 void launch_product_state(cplx* psi, const ProductPhi& phi, int n, int n_loc, uint64_t rank_bits, cudaStream_t stream);
 void launch_gather_rows(const cplx* src, const uint64_t* d_rows, int64_t n_rows, cplx* d_out, cudaStream_t stream);
+// Dense output of a Taylor step: out = y + sum_{m < n} c[m] term[m]  (c[m] = s^(m+1), s = fraction of the step).
+struct DenseSpec {
+  const cplx* y;
+  const cplx* term[QSB_MAX_TAYLOR_ORDER];
+  double c[QSB_MAX_TAYLOR_ORDER];
+  cplx* out;
+  int n;
+};
+void launch_dense_eval(const DenseSpec& d, uint64_t dim, cudaStream_t stream);
 size_t happly_smem_bytes();
 
 // Per-kernel-class CUDA-event timing (bench.py's roofline leg).  Classes: 0 pass_first, 1 pass_mid, 2 pass_centre,

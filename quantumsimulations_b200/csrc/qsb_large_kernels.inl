@@ -316,6 +316,94 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
 }
 
 // ---------------------------------------------------------------------------------------------------
+// pass_centre_pipe: the sharded centre pass as a persistent, double-buffered kernel (one CTA per SM).  The NVLink
+// round trip of a tile is several microseconds; pass_centre exposes it once per tile (load -> transform -> store with
+// nothing in flight during the transform).  Here tile i + 1 is already on its way - cp.async copies straight from the
+// peers' scratch into the OTHER 64 KB shared-memory buffer - while tile i is transformed in place in this one, so the
+// links always have 64 KB per SM in flight.  Same arithmetic per tile as pass_centre (bitwise).  W = 8 or 4 only
+// (window [0,4) would need the padded buffer).
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+
+template <bool COLLECT, int W>
+__global__ void __launch_bounds__(TPT, 2)
+pass_centre_pipe(PassArgs a, Layout L, TileMap tm, PeerPtrs peers, double* __restrict__ partials) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* bufs = reinterpret_cast<cplx*>(smem_raw);  // [2][TILE], unpadded
+  __shared__ double red[2 * 32 + 2];
+  const int branch = tm.branch0 + blockIdx.y;
+  const double (&ww)[16] = branch ? a.tab.Wy : a.tab.Wx;
+  const int tt = threadIdx.x;
+  const uint64_t lmask = (1ull << a.g.n_loc) - 1;
+  auto issue = [&](unsigned bx, cplx* dst) {
+    const uint64_t base = tile_base(L, tm.tile(bx));
+    WinOff wo;
+    wo.init<8>(L, 0);
+    const uint64_t idx0 = gidx(L, base, elem<8>(tt, 0));
+    cplx* d = dst + elem<8>(tt, 0);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const uint64_t idx = idx0 + wo.at(j);
+      cp_async16(d + (j << 8), &peers.t[branch][idx >> a.g.n_loc][idx & lmask]);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  unsigned bx = blockIdx.x;
+  int cur = 0;
+  if (bx < tm.count) issue(bx, bufs);
+  while (bx < tm.count) {
+    const unsigned next = bx + gridDim.x;
+    cplx* sm = bufs + (size_t)cur * TILE;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();  // tile bx has landed for every thread, and nobody still reads the other buffer (tile bx - stride)
+    if (next < tm.count) issue(next, bufs + (size_t)(cur ^ 1) * TILE);
+    const uint64_t v = tm.tile(bx);
+    const size_t slot = (size_t)(v - tm.vbase);
+    TileDiag<W> td;
+    td.load((branch ? a.tab.Ty : a.tab.Tx) + slot * TD_STRIDE, branch ? a.tab.Iy : a.tab.Ix, tt);
+    const uint64_t base = tile_base(L, v);
+    cplx r[16];
+    double s[2] = {0.0, 0.0};
+    tile_load16<8>(sm, tt, r);
+    if constexpr (W == 8) {
+      centre_core<8, COLLECT>(r, tt, L.m8, td, ww, L, base, a.g, s);
+    } else {
+      bfly16<0>(r, L.m8);
+      tile_store16<8>(sm, tt, r);
+      __syncthreads();
+      tile_load16<4>(sm, tt, r);
+      centre_core<4, COLLECT>(r, tt, L.m4, td, ww, L, base, a.g, s);
+      tile_store16<4>(sm, tt, r);
+      __syncthreads();
+      tile_load16<8>(sm, tt, r);
+      bfly16<0>(r, L.m8);
+    }
+    {
+      const unsigned late0 = tm.zero & (unsigned)__double2loint(r[0].x);
+      WinOff wo;
+      wo.init<8>(L, late0);
+      const uint64_t idx0 = gidx(L, base | late0, elem<8>(tt, 0));
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const uint64_t idx = idx0 + wo.at(j);
+        peers.t[branch][idx >> a.g.n_loc][idx & lmask] = r[j];
+      }
+    }
+    if (COLLECT) {
+      block_reduce<2>(s, red);
+      if (threadIdx.x == 0) {
+        double* p = partials + slot * PSTRIDE + 3 + 2 * branch;
+        p[0] = s[0]; p[1] = s[1];
+      }
+    }
+    bx = next;
+    cur ^= 1;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
 // error_sums: the embedded-pair error norm as one streaming sweep; CTA b covers amplitudes [4096 b, 4096 (b+1)),
 // so its partial sums land in the same per-tile slots (7: error, 8: |vin[sc_i0]|^2 / sc^2) the fused epilogues use.
 // ---------------------------------------------------------------------------------------------------

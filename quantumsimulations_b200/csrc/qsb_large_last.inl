@@ -190,6 +190,17 @@ __global__ void gather_rows_kernel(const cplx* __restrict__ src, const uint64_t*
   if (i < n_rows) out[i] = src[rows[i]];
 }
 
+// out[i] = y[i] + sum_m c[m] term[m][i]: the Taylor polynomial of one step read off at an interior time.
+__global__ void __launch_bounds__(256)
+dense_eval_kernel(DenseSpec d, uint64_t dim) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < dim; i += stride) {
+    cplx acc = d.y[i];
+    for (int m = 0; m < d.n; ++m) axpy(acc, d.c[m], d.term[m][i]);
+    d.out[i] = acc;
+  }
+}
+
 __global__ void set_basis_kernel(cplx* psi, uint64_t dim, uint64_t index) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -239,6 +250,11 @@ static void set_centre_attrs(int sm) {
   tile_kernel_attrs(pass_centre<true, true, W>, sm);
   tile_kernel_attrs(pass_centre<true, false, W, true>, sm);
   tile_kernel_attrs(pass_centre<true, true, W, true>, sm);
+  if constexpr (W != 0) {
+    const int sm2 = 2 * TILE * (int)sizeof(cplx);
+    tile_kernel_attrs(pass_centre_pipe<false, W>, sm2);
+    tile_kernel_attrs(pass_centre_pipe<true, W>, sm2);
+  }
 }
 
 // Shared memory of a strided pass: the padded buffer only if the layout transforms window [0,4).
@@ -250,10 +266,25 @@ static void launch_mid(const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, u
   else pass_mid<false><<<dim3(n_tiles, nb), TPT, strided_smem(false), stream>>>(L, tm, tx, ty);
 }
 
+static int centre_pipe_mode() {  // read per launch: tests switch it inside one process
+  const char* e = std::getenv("QSB200_CENTRE_PIPE");
+  return e ? atoi(e) : 1;
+}
+
 template <bool SHARDED, int W>
 static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, const PeerPtrs& pp,
                           int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream, int nb) {
   sm = W == 8 ? 0 : strided_smem(W == 0);  // W == 8: the whole group sits in one register window, no staging at all
+  if constexpr (SHARDED && W != 0) {
+    // persistent + double-buffered (cp.async prefetch of the next tile from the peers); QSB200_CENTRE_PIPE=0: off,
+    // =2: also in the serialised sharded path (how a one-GPU box tests the kernel)
+    if (tm.count && centre_pipe_mode() != 0) {
+      const size_t sm2 = 2 * (size_t)TILE * sizeof(cplx);
+      if (collect_obs) pass_centre_pipe<true, W><<<dim3(n_tiles, nb), TPT, sm2, stream>>>(a, L, tm, pp, partials);
+      else pass_centre_pipe<false, W><<<dim3(n_tiles, nb), TPT, sm2, stream>>>(a, L, tm, pp, partials);
+      return;
+    }
+  }
   if constexpr (SHARDED) {
     if (tm.count) {  // persistent walk (overlapped sharded mode)
       if (collect_obs) pass_centre<true, true, W, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials);
@@ -562,8 +593,17 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
         if (w == 8) launch_centre_ring<8>(a, g, *link, collect_obs, partials, n_tiles, stream);
         else launch_centre_ring<4>(a, g, *link, collect_obs, partials, n_tiles, stream);
       } else {
-        const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0, 0u, 0u, 0, 0u};
-        launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, stream);
+        if (centre_pipe_mode() == 2 && w != 0) {
+          int dev = 0, n_sms = 148;
+          cudaGetDevice(&dev);
+          cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+          const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0, 0u, 0u, 0, n_tiles};
+          launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials,
+                              std::min<unsigned>(n_tiles, (unsigned)n_sms), sm1, stream);
+        } else {
+          const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0, 0u, 0u, 0, 0u};
+          launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, stream);
+        }
       }
     }
     rc = link->sync(link->ctx);
@@ -638,6 +678,11 @@ void launch_product_state(cplx* psi, const ProductPhi& phi, int n, int n_loc, ui
 
 void launch_gather_rows(const cplx* src, const uint64_t* d_rows, int64_t n_rows, cplx* d_out, cudaStream_t stream) {
   gather_rows_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, stream>>>(src, d_rows, n_rows, d_out);
+}
+
+void launch_dense_eval(const DenseSpec& d, uint64_t dim, cudaStream_t stream) {
+  const int blocks = (int)std::min<uint64_t>((dim + 255) / 256, 148 * 8);
+  dense_eval_kernel<<<blocks, 256, 0, stream>>>(d, dim);
 }
 
 void launch_set_basis_state(cplx* psi, uint64_t dim, uint64_t index, cudaStream_t stream) {

@@ -27,9 +27,14 @@ def test_layouts_cover_all_bits_and_centre_holds_rank_bits(world, monkeypatch):
             lay = engine.tile_layouts(n, world)
             assert lay[0] == (12, 12, 12)
             covered = 12
+            # groups of at most 8 bits (256-byte runs); unsharded plans may take 9 where that saves a layout
+            widest = 9 if (world == 1 and gmax is None) else 8
             for lk, gs, ge in lay[1:]:
-                assert gs == covered and 1 <= ge - gs <= 8 and lk == 12 - (ge - gs)
+                assert gs == covered and 1 <= ge - gs <= widest and lk == 12 - (ge - gs)
                 covered = ge
+            if world == 1 and gmax is None:
+                assert len(lay) - 1 == max(1, -(-(n - 12) // 9)) or n - 12 <= 16 and len(lay) - 1 == max(1, -(-(n - 12) // 8))
+                assert (lay[-1][2] - lay[-1][1]) == min(ge - gs for _, gs, ge in lay[1:])   # the centre is the smallest group
             assert covered == n
             assert lay[-1][1] <= n - wl            # every rank bit is inside the centre group
             assert all(ge <= n - wl for _, _, ge in lay[1:-1])  # mid passes are local
@@ -44,7 +49,10 @@ def test_flagship_layouts():
     assert engine.tile_layouts(33, 8) == [(12, 12, 12), (4, 12, 20), (4, 20, 28), (7, 28, 33)]
     assert engine.tile_layouts(31, 2) == [(12, 12, 12), (5, 12, 19), (5, 19, 26), (7, 26, 31)]
     assert engine.tile_layouts(28, 2) == [(12, 12, 12), (4, 12, 20), (4, 20, 28)]      # 5 bits would add a layout
-    assert engine.tile_layouts(30, 1) == [(12, 12, 12), (6, 12, 18), (6, 18, 24), (6, 24, 30)]  # unsharded: balanced
+    # unsharded: 9-bit groups where they save a layout (two HBM passes), the centre on the smallest group
+    assert engine.tile_layouts(30, 1) == [(12, 12, 12), (3, 12, 21), (3, 21, 30)]
+    assert engine.tile_layouts(29, 1) == [(12, 12, 12), (3, 12, 21), (4, 21, 29)]
+    assert engine.tile_layouts(27, 1) == [(12, 12, 12), (4, 12, 20), (5, 20, 27)]
     with pytest.raises(ValueError):
         engine.tile_layouts(14, 8)
     with pytest.raises(ValueError):

@@ -284,3 +284,27 @@ def test_sharded_checkpoint_ranks_must_agree(tmp_path):
             grp.run(lambda plan, r: evolve_checkpointed(plan, t_out, opts, paths[r]))
         res = grp.run(lambda plan, r: evolve_checkpointed(plan, t_out, opts, good[r]))
     assert res[0][2] and np.max(np.abs(res[0][0] - want)) < 1e-11
+
+
+def test_dense_output_of_taylor_steps(golden_cases, monkeypatch):
+    """Tiled path, output grid finer than the controller's step (C1 (ii): N = 13, 2000 outputs over 0.02 s): ONE
+    unclipped Taylor step serves every output time inside it from its own polynomial.  Same traces as stepping onto
+    every output (and as exact diagonalisation, on the golden's coarser grid), for a fraction of the H-applies."""
+    import dataclasses
+    from quantumsimulations_b200 import simulate_rare
+
+    meta, arrs = golden_cases
+    name = "n13_dataclass_default"
+    base = params_from_meta(meta[name])
+    assert base.steps == 201
+    p = dataclasses.replace(base, steps=2001, solver_atol=1e-11, solver_rtol=1e-10, solver_nsteps=100000)
+    t, dense, sd = simulate_rare(p, method="taylor", return_stats=True)
+    monkeypatch.setenv("QSB200_DENSE_OUTPUT", "0")
+    _, stepped, ss = simulate_rare(p, method="taylor", return_stats=True)
+    assert sd.path == 1 and ss.path == 1
+    assert ss.n_accepted >= 2000                       # stepping lands on every output time
+    assert sd.n_accepted + sd.n_rejected <= ss.n_accepted // 3, (sd, ss)
+    for k in KEYS:
+        assert np.max(np.abs(dense[k] - stepped[k])) < 1e-8, k
+        assert np.max(np.abs(dense[k][::10] - arrs[f"{name}/{k}"])) < TOL, k
+    assert np.max(np.abs(dense["state_norm"] - 1.0)) < 1e-12

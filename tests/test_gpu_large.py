@@ -176,3 +176,22 @@ def test_explicit_group_layouts(n, groups, monkeypatch):
     with engine.Plan(table) as plan:
         got = plan.apply_h_product(phi, rows)
     assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-12
+
+
+@pytest.mark.parametrize("n", [21, 29])
+def test_nine_bit_group_layouts_product_rows(n):
+    """Unsharded plans take a 9-bit group where that saves a layout (N = 21: one strided layout; N = 29: 12 | 9 | 8
+    instead of four layouts).  Product-state rows against the closed form at those sizes (N = 29: 8.6 GB vectors)."""
+    from oracle import product
+    from quantumsimulations_b200 import engine
+
+    lays = engine.tile_layouts(n)
+    assert len(lays) == (2 if n == 21 else 3) and max(ge - gs for _, gs, ge in lays[1:]) == 9
+    table = _c4_table(n)
+    bm = table.bit_major()
+    phi = product.random_phi(n, n)
+    rows = _sample_rows(1 << n, 1 << 14, n)
+    want = product.apply_h_rows(bm["h"], bm["J"], phi, rows)
+    with engine.Plan(table) as plan:
+        got = plan.apply_h_product(phi, rows)
+    assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-12

@@ -164,3 +164,34 @@ def test_ring_centre_pass_is_bitwise_the_register_staged_one(n, world):
         outs.append(json.loads(res.stdout.strip().splitlines()[-1]))
     assert outs[0]["ring"] == "0" and outs[1]["ring"] == "1"
     assert outs[0]["obs"] == outs[1]["obs"] and outs[0]["rhs"] == outs[1]["rhs"]
+
+
+@pytest.mark.parametrize("n,world,gmax", [(14, 2, None), (16, 4, None), (18, 8, None), (19, 2, 4), (19, 8, 3), (21, 4, None)])
+def test_pipelined_centre_kernel(n, world, gmax, monkeypatch):
+    """pass_centre_pipe - the persistent, double-buffered (cp.async) centre pass the overlapped multi-GPU mode runs -
+    forced into the serialised path (QSB200_CENTRE_PIPE=2) so that a one-GPU box exercises it: H-apply against the
+    numpy oracle, and the observable sums it collects against the default kernel's, bit for bit."""
+    from oracle import dense
+    from quantumsimulations_b200 import engine, shard
+
+    if gmax is not None:
+        monkeypatch.setenv("QSB200_MAX_GROUP", str(gmax))
+    table = random_table(n, 800 + n + world, dense_pairs=False)
+    bm = table.bit_major()
+    psi = _rand_state(n, 7 * n + world)
+    opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, method="taylor", order=6)
+
+    def run():
+        with shard.LocalShardGroup(table, world) as grp:
+            got = grp.apply_h(psi)
+            obs, st = grp.evolve(np.linspace(0.0, 1e-3, 3), opts, psi)
+        return got, obs, st
+
+    monkeypatch.setenv("QSB200_CENTRE_PIPE", "0")
+    ref_h, ref_obs, ref_st = run()
+    monkeypatch.setenv("QSB200_CENTRE_PIPE", "2")
+    got_h, got_obs, got_st = run()
+    want = dense.apply_h(bm["h"], bm["J"], psi)
+    assert np.max(np.abs(got_h - want)) / np.max(np.abs(want)) < 2e-13
+    assert np.array_equal(got_h, ref_h) and np.array_equal(got_obs, ref_obs)
+    assert (got_st.n_accepted, got_st.n_rejected) == (ref_st.n_accepted, ref_st.n_rejected)
