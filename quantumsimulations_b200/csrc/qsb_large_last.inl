@@ -266,9 +266,12 @@ static void launch_mid(const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, u
   else pass_mid<false><<<dim3(n_tiles, nb), TPT, strided_smem(false), stream>>>(L, tm, tx, ty);
 }
 
+// Opt-in.  Measured on 2 x B200 at N = 31 (profiles/r2k_centre_pipe_2gpu.jsonl): the centre pass alone gains 3 %
+// (49.9 vs 51.5 ms per H-apply) but the overlapped H-apply LOSES, 115.7 vs 98.2 ms - its 128 KB of shared memory shrink
+// the L1 of the co-resident HBM passes, whose loads in flight are bounded by L1 capacity.
 static int centre_pipe_mode() {  // read per launch: tests switch it inside one process
   const char* e = std::getenv("QSB200_CENTRE_PIPE");
-  return e ? atoi(e) : 1;
+  return e ? atoi(e) : 0;
 }
 
 template <bool SHARDED, int W>
@@ -276,7 +279,7 @@ static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm,
                           int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream, int nb) {
   sm = W == 8 ? 0 : strided_smem(W == 0);  // W == 8: the whole group sits in one register window, no staging at all
   if constexpr (SHARDED && W != 0) {
-    // persistent + double-buffered (cp.async prefetch of the next tile from the peers); QSB200_CENTRE_PIPE=0: off,
+    // persistent + double-buffered (cp.async prefetch of the next tile from the peers); QSB200_CENTRE_PIPE=1: on,
     // =2: also in the serialised sharded path (how a one-GPU box tests the kernel)
     if (tm.count && centre_pipe_mode() != 0) {
       const size_t sm2 = 2 * (size_t)TILE * sizeof(cplx);
