@@ -134,6 +134,9 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
 int qsb_propagate_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
                         const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
                         int32_t obs_by_column, double* out_obs, qsb_stats* stats, int device);
+/* qsb_propagate_batch keeps its stream and device buffers (up to a few GiB) per device between calls; this frees
+ * them (device < 0: on every device).  Safe to call at any time; the next call re-allocates.                        */
+int qsb_release_caches(int device);
 /* Step 1 alone, for parity tests: u_host[(j * 2^n + x) * 2 + {0,1}] = re, im of <x| exp(-i H dt) |j>.              */
 int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opts* opts, int32_t max_squarings,
                          double* u_host, qsb_stats* stats, int device);

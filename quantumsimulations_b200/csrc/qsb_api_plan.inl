@@ -329,6 +329,64 @@ static int auto_squarings(const qsb_table* t, double dt) {
   return s;
 }
 
+// Per-device context of the propagator path, kept between calls: a sweep driver calls qsb_propagate_batch once per
+// sweep (or once per grid), and stream / event creation plus 7-10 cudaMalloc + cudaFree pairs per call were a third
+// of the full-size C2 sweep's wall time (40 ms for 17 ms of kernels).  Buffers only grow; qsb_release_caches() frees
+// them.  One call at a time per device (the mutex is held for the whole call).
+struct PropCtx {
+  static constexpr int NBUF = 10;
+  std::mutex mu;
+  cudaStream_t st = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  void* buf[NBUF] = {};
+  size_t cap[NBUF] = {};
+  int ensure_stream() {
+    if (st) return QSB_OK;
+    QSB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    QSB_CUDA(cudaEventCreate(&e0));
+    QSB_CUDA(cudaEventCreate(&e1));
+    return QSB_OK;
+  }
+  int get(int slot, size_t bytes, void** out) {
+    if (cap[slot] < bytes) {
+      if (buf[slot]) { cudaFree(buf[slot]); buf[slot] = nullptr; cap[slot] = 0; }
+      cudaError_t e = cudaMalloc(&buf[slot], bytes);
+      if (e != cudaSuccess) {
+        buf[slot] = nullptr;
+        cudaGetLastError();
+        return fail(QSB_ERR_OOM, "cudaMalloc of " + std::to_string(bytes) + " bytes for the propagator path failed: " + cudaGetErrorString(e));
+      }
+      cap[slot] = bytes;
+    }
+    *out = buf[slot];
+    return QSB_OK;
+  }
+  void release() {
+    if (st) cudaStreamSynchronize(st);
+    for (int i = 0; i < NBUF; ++i) { if (buf[i]) cudaFree(buf[i]); buf[i] = nullptr; cap[i] = 0; }
+  }
+};
+static PropCtx& prop_ctx(int device) {
+  static PropCtx ctxs[64];
+  return ctxs[device & 63];
+}
+
+// First touch of a large pageable host buffer costs ~0.35 s per GB on one thread (page faults); done here by a few
+// threads WHILE the kernels that will fill it are running, it costs nothing.
+static void prefault_async(std::vector<std::thread>& pool, void* ptr, size_t bytes) {
+  if (bytes < ((size_t)64 << 20)) return;
+  unsigned nt = std::min(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
+  const size_t page = 4096, per = ((bytes / nt) + page - 1) & ~(page - 1);
+  for (unsigned t = 0; t < nt; ++t) {
+    const size_t lo = (size_t)t * per, hi = std::min(bytes, lo + per);
+    if (lo >= hi) break;
+    pool.emplace_back([=] {
+      volatile char* p = (volatile char*)ptr;
+      for (size_t o = lo; o < hi; o += page) p[o] = 0;
+    });
+  }
+}
+
 static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
                           const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
                           int32_t obs_by_column, double* out_obs, qsb_stats* stats, double* u_host, int device) {
@@ -357,23 +415,22 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
     chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)chunk, ((size_t)2 << 30) / per_traj));
   }
 
+  PropCtx& ctx = prop_ctx(device);
+  std::lock_guard<std::mutex> ctx_lock(ctx.mu);
+  rc = ctx.ensure_stream();
+  if (rc) return rc;
+  cudaStream_t st = ctx.st;
+  cudaEvent_t e0 = ctx.e0, e1 = ctx.e1;
   SmallDesc* d_desc = nullptr;
   double *d_t = nullptr, *d_obs = nullptr;
   SmallStats* d_stats = nullptr;
   cplx *d_u = nullptr, *d_tmp = nullptr;
   int32_t* d_sq = nullptr;
-  cudaStream_t st = nullptr;
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
-  struct Cleanup {
-    SmallDesc*& a; double*& b; double*& c; SmallStats*& d; cplx*& e; cplx*& f; int32_t*& g; cudaStream_t& s;
-    cudaEvent_t &x, &y;
-    ~Cleanup() {
-      cudaFree(a); cudaFree(b); cudaFree(c); cudaFree(d); cudaFree(e); cudaFree(f); cudaFree(g);
-      if (x) cudaEventDestroy(x);
-      if (y) cudaEventDestroy(y);
-      if (s) cudaStreamDestroy(s);
-    }
-  } cleanup{d_desc, d_t, d_obs, d_stats, d_u, d_tmp, d_sq, st, e0, e1};
+  struct Drain {  // an early return must not leave work of this call running on the shared stream
+    cudaStream_t s;
+    std::vector<std::thread> pool;
+    ~Drain() { cudaStreamSynchronize(s); for (auto& t : pool) t.join(); }
+  } drain{st, {}};
   std::vector<int32_t> n_sq(n_traj, 0);
   bool any_sq = false;
   for (int i = 0; i < n_traj; ++i) {
@@ -382,18 +439,15 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
     n_sq[i] = s;
     any_sq = any_sq || s > 0;
   }
-  QSB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
-  QSB_CUDA(cudaEventCreate(&e0));
-  QSB_CUDA(cudaEventCreate(&e1));
-  QSB_CUDA(cudaMalloc(&d_desc, sizeof(SmallDesc) * chunk));
-  QSB_CUDA(cudaMalloc(&d_t, sizeof(double) * 2 * chunk));
-  QSB_CUDA(cudaMalloc(&d_stats, sizeof(SmallStats) * chunk * dim));
-  QSB_CUDA(cudaMalloc(&d_u, u_bytes * chunk));
+  if ((rc = ctx.get(0, sizeof(SmallDesc) * chunk, (void**)&d_desc))) return rc;
+  if ((rc = ctx.get(1, sizeof(double) * 2 * chunk, (void**)&d_t))) return rc;
+  if ((rc = ctx.get(2, sizeof(SmallStats) * chunk * dim, (void**)&d_stats))) return rc;
+  if ((rc = ctx.get(3, u_bytes * chunk, (void**)&d_u))) return rc;
   if (any_sq) {
-    QSB_CUDA(cudaMalloc(&d_tmp, u_bytes * chunk));
-    QSB_CUDA(cudaMalloc(&d_sq, sizeof(int32_t) * chunk));
+    if ((rc = ctx.get(4, u_bytes * chunk, (void**)&d_tmp))) return rc;
+    if ((rc = ctx.get(5, sizeof(int32_t) * chunk, (void**)&d_sq))) return rc;
   }
-  if (n_out > 0) QSB_CUDA(cudaMalloc(&d_obs, sizeof(double) * chunk * n_out * QSB_NOBS));
+  if (n_out > 0 && (rc = ctx.get(6, sizeof(double) * chunk * n_out * QSB_NOBS, (void**)&d_obs))) return rc;
 
   // Time-split chains: a trajectory's outputs are cut into segments of 2^seg_lb outputs that run as separate CTAs, each
   // from its own seed psi_{c 2^seg_lb} = (U^(2^seg_lb))^c psi_0 (seg_lb more squarings of a copy of U, then a chain of
@@ -412,18 +466,14 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
       seg_lb = 0;
     }
   }
-  struct FreeList { std::vector<void*> p; ~FreeList() { for (void* q : p) cudaFree(q); } } extra;
   cplx *d_v = nullptr, *d_seeds = nullptr;
   int32_t* d_seg_sq = nullptr;
   std::vector<int32_t> seg_sq(chunk, seg_lb);
   if (n_seg > 1) {
-    QSB_CUDA(cudaMalloc(&d_v, u_bytes * chunk));
-    extra.p.push_back(d_v);
-    QSB_CUDA(cudaMalloc(&d_seeds, sizeof(cplx) * dim * (size_t)n_seg * chunk));
-    extra.p.push_back(d_seeds);
-    QSB_CUDA(cudaMalloc(&d_seg_sq, sizeof(int32_t) * chunk));
-    extra.p.push_back(d_seg_sq);
-    if (!d_tmp) QSB_CUDA(cudaMalloc(&d_tmp, u_bytes * chunk));  // freed by `cleanup`
+    if ((rc = ctx.get(7, u_bytes * chunk, (void**)&d_v))) return rc;
+    if ((rc = ctx.get(8, sizeof(cplx) * dim * (size_t)n_seg * chunk, (void**)&d_seeds))) return rc;
+    if ((rc = ctx.get(9, sizeof(int32_t) * chunk, (void**)&d_seg_sq))) return rc;
+    if (!d_tmp && (rc = ctx.get(4, u_bytes * chunk, (void**)&d_tmp))) return rc;
     QSB_CUDA(cudaMemcpyAsync(d_seg_sq, seg_sq.data(), sizeof(int32_t) * chunk, cudaMemcpyHostToDevice, st));
   }
 
@@ -462,6 +512,9 @@ static int propagate_impl(int32_t n_traj, const qsb_table* tables, const uint64_
       if (rc) return rc;
     }
     QSB_CUDA(cudaEventRecord(e1, st));
+    if (n_out > 0 && base == 0)  // the kernels are running: fault the caller's output pages in meanwhile
+      prefault_async(drain.pool, out_obs, sizeof(double) * (size_t)n_traj * n_out * QSB_NOBS);
+    if (base == 0) { for (auto& t : drain.pool) t.join(); drain.pool.clear(); }
     QSB_CUDA(cudaMemcpyAsync(hs.data(), d_stats, sizeof(SmallStats) * m * dim, cudaMemcpyDeviceToHost, st));
     if (n_out > 0)
       QSB_CUDA(cudaMemcpyAsync(out_obs + (size_t)base * n_out * QSB_NOBS, d_obs, sizeof(double) * m * n_out * QSB_NOBS,
@@ -506,6 +559,20 @@ int qsb_build_propagator(const qsb_table* table, double dt, const qsb_solver_opt
                          double* u_host, qsb_stats* stats, int device) {
   if (!table || !opts || !u_host) return fail(QSB_ERR_BAD_ARG, "qsb_build_propagator: null argument");
   return propagate_impl(1, table, nullptr, 0, &dt, 0, opts, max_squarings, 0, nullptr, stats, u_host, device);
+}
+
+int qsb_release_caches(int device) {
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess) { cudaGetLastError(); return QSB_OK; }
+  for (int dev = 0; dev < count && dev < 64; ++dev) {
+    if (device >= 0 && dev != device) continue;
+    PropCtx& c = prop_ctx(dev);
+    std::lock_guard<std::mutex> lk(c.mu);
+    if (!c.st) continue;
+    if (cudaSetDevice(dev) != cudaSuccess) { cudaGetLastError(); continue; }
+    c.release();
+  }
+  return QSB_OK;
 }
 
 int qsb_debug_squarings(const qsb_table* table, double dt, int32_t* n_squarings) {

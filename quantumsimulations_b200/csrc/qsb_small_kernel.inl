@@ -416,6 +416,128 @@ small_propagate_kernel_n7(const SmallDesc* __restrict__ descs, const cplx* __res
   }
 }
 
+// M segments of ONE trajectory per CTA (time-split chains only): the M states advance together, so every element of U
+// that a thread loads from shared memory (or holds in registers) feeds M complex multiply-adds instead of one - the
+// one-segment kernel spends 1630 of its 2970 shared-memory wavefronts per output re-reading U
+// (profiles/r1zz_ncu_propagator_summary.json).  CTA b works on segments [M g, M g + M) of trajectory b / n_grp,
+// g = b % n_grp, n_grp = ceil(n_seg / M).  Thread mapping, column cache and register columns are those of
+// small_propagate_kernel_n7; each (row, segment) has ONE accumulator (2 rows x M segments = 2 M independent chains),
+// summed over j = q, q + 8, .. in order and then over q by the fixed xor-shuffle tree, so a segment's numbers do not
+// depend on which other segments share its CTA.  The ring holds `ring` states per segment.
+template <int M>
+__global__ void __launch_bounds__(P2_THREADS, 1)
+small_propagate_kernel_n7m(const SmallDesc* __restrict__ descs, const cplx* __restrict__ ut_all, int64_t n_out,
+                           double* __restrict__ obs_all, int n_cache, int ring, int by_column,
+                           const cplx* __restrict__ seeds, int n_seg, int64_t seg_len) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  SmallShared& sh = *reinterpret_cast<SmallShared*>(smem_raw);
+  const int n_grp = (n_seg + M - 1) / M;
+  const int traj = blockIdx.x / n_grp, seg0 = (blockIdx.x - traj * n_grp) * M;
+  {
+    const int* src = reinterpret_cast<const int*>(descs + traj);
+    int* dst = reinterpret_cast<int*>(&sh.d);
+    for (int i = threadIdx.x; i < (int)(sizeof(SmallDesc) / 4); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  const SmallDesc& d = sh.d;
+  constexpr int dim = P2_DIM;
+  cplx* states = reinterpret_cast<cplx*>(smem_raw + ((sizeof(SmallShared) + 15) & ~size_t(15)));  // [M][ring][dim]
+  cplx* us = states + (size_t)M * ring * dim;                                                     // [n_cache][P2_CS]
+  const cplx* __restrict__ ut = ut_all + (size_t)traj * dim * dim;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = P2_THREADS / 32;
+  const int q = lane >> 2;
+  const int x = 4 * warp + (lane & 3);  // second row: x + 64
+  double* obs = obs_all + (size_t)traj * n_out * QSB_NOBS;
+  // outputs of segment seg0 + s: [o0, o0 + n_mine); segments past n_seg are idle copies (never observed)
+  auto first_output = [&](int s) { return (int64_t)(seg0 + s) * seg_len; };
+  auto outputs_of = [&](int s) -> int64_t {
+    if (seg0 + s >= n_seg) return 0;
+    const int64_t left = n_out - first_output(s);
+    return left < seg_len ? (left > 0 ? left : 0) : seg_len;
+  };
+  const int64_t n_max = outputs_of(0);  // segments are full except the trajectory's last one
+
+  for (int i = threadIdx.x; i < n_cache * dim; i += blockDim.x) us[(i >> 7) * P2_CS + (i & (dim - 1))] = ut[i];
+  for (int i = threadIdx.x; i < M * dim; i += blockDim.x) {
+    const int s = i >> 7, xi = i & (dim - 1);
+    states[(size_t)s * ring * dim + xi] =
+        seg0 + s < n_seg ? seeds[((size_t)traj * n_seg + seg0 + s) * dim + xi] : mk(0.0, 0.0);
+  }
+  int j_tail = q;
+  while (j_tail < n_cache) j_tail += P2_SPLIT;
+  cplx ur0[P2_NREG], ur1[P2_NREG];
+#pragma unroll
+  for (int r = 0; r < P2_NREG; ++r) {
+    const int j = j_tail + r * P2_SPLIT;
+    ur0[r] = j < dim ? ut[(size_t)j * dim + x] : mk(0, 0);
+    ur1[r] = j < dim ? ut[(size_t)j * dim + x + 64] : mk(0, 0);
+  }
+  __syncthreads();
+
+  for (int64_t base = 0; base < n_max; base += ring) {
+    const int count = (int)((n_max - base < ring) ? n_max - base : ring);
+    for (int r = (base == 0 ? 1 : 0); r < count; ++r) {
+      const cplx* cur = states + (size_t)(r == 0 ? ring - 1 : r - 1) * dim;  // segment s: + s * ring * dim
+      cplx a[M], b[M];
+#pragma unroll
+      for (int s = 0; s < M; ++s) { a[s] = mk(0, 0); b[s] = mk(0, 0); }
+      int j = q;
+      for (; j < n_cache; j += P2_SPLIT) {
+        const cplx u0 = us[j * P2_CS + x], u1 = us[j * P2_CS + x + 64];
+#pragma unroll
+        for (int s = 0; s < M; ++s) {
+          const cplx p0 = cur[(size_t)s * ring * dim + j];
+          caxpy(a[s], u0, p0);
+          caxpy(b[s], u1, p0);
+        }
+      }
+#pragma unroll
+      for (int rr = 0; rr < P2_NREG; ++rr) {
+        if (j < dim) {
+#pragma unroll
+          for (int s = 0; s < M; ++s) {
+            const cplx p0 = cur[(size_t)s * ring * dim + j];
+            caxpy(a[s], ur0[rr], p0);
+            caxpy(b[s], ur1[rr], p0);
+          }
+        }
+        j += P2_SPLIT;
+      }
+      for (; j < dim; j += P2_SPLIT) {  // only if fewer columns are cached than the launcher normally arranges
+        const cplx u0 = __ldg(ut + (size_t)j * dim + x), u1 = __ldg(ut + (size_t)j * dim + x + 64);
+#pragma unroll
+        for (int s = 0; s < M; ++s) {
+          const cplx p0 = cur[(size_t)s * ring * dim + j];
+          caxpy(a[s], u0, p0);
+          caxpy(b[s], u1, p0);
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < M; ++s) {
+#pragma unroll
+        for (int off = 4; off < 32; off <<= 1) {  // the 8 partial sums of a row: lanes differing in q
+          a[s].x += __shfl_xor_sync(0xffffffffu, a[s].x, off);
+          a[s].y += __shfl_xor_sync(0xffffffffu, a[s].y, off);
+          b[s].x += __shfl_xor_sync(0xffffffffu, b[s].x, off);
+          b[s].y += __shfl_xor_sync(0xffffffffu, b[s].y, off);
+        }
+        if (q == 0) {
+          states[((size_t)s * ring + r) * dim + x] = a[s];
+          states[((size_t)s * ring + r) * dim + x + 64] = b[s];
+        }
+      }
+      __syncthreads();
+    }
+    for (int idx = warp; idx < M * count; idx += nwarp) {
+      const int s = idx / count, r = idx - s * count;
+      if (base + r < outputs_of(s))
+        warp_observe(states + ((size_t)s * ring + r) * dim, dim, d,
+                     obs + (first_output(s) + base + r) * (by_column ? 1 : QSB_NOBS), by_column ? n_out : 1);
+    }
+    __syncthreads();
+  }
+}
+
 // U <- U^(2^s): s = n_sq[traj] in-place squarings of one column-major propagator per CTA (scaling and squaring: the
 // columns were integrated over dt / 2^s only).  C[x][j] = sum_k A[x][k] A[k][j]; thread (x, q) owns row x of the
 // columns j = 4 (q + split i) .. +3, so the A[x][k] load is coalesced over x and shared by four accumulators while
@@ -668,6 +790,23 @@ int launch_small_propagate(const SmallDesc* d_desc, int n_traj, int n, const cpl
   if (n_seg < 1) n_seg = 1;
   if (seg_len < 1) seg_len = n_out;
   const unsigned grid = (unsigned)n_traj * (unsigned)n_seg;
+  // n = 7 time-split chains: PROP_M segments of a trajectory per CTA share every U element they load.  (QSB200_PROP_M=1:
+  // the one-segment kernel; seeds / state-storing chains always use it.)
+  constexpr int PROP_M = 4;
+  const char* pm = getenv("QSB200_PROP_M");
+  if (n == 7 && d_seeds && !d_states_out && n_seg >= 2 && !(pm && atoi(pm) == 1) && !getenv("QSB200_PROP_ONE_ROW")) {
+    const int ring_m = 2;  // states per segment between two rounds of observable reductions (M x 2 x 2 KB = 16 KB)
+    const size_t fixed = ((sizeof(SmallShared) + 15) & ~size_t(15)) + (size_t)PROP_M * ring_m * P2_DIM * sizeof(cplx);
+    int nc = (int)((PROPAGATE_SMEM_MAX - fixed) / ((size_t)P2_CS * sizeof(cplx)));
+    if (nc > P2_DIM) nc = P2_DIM;
+    const size_t smem2 = fixed + (size_t)nc * P2_CS * sizeof(cplx);
+    const unsigned grid_m = (unsigned)n_traj * (unsigned)((n_seg + PROP_M - 1) / PROP_M);
+    QSB_CUDA(cudaFuncSetAttribute(small_propagate_kernel_n7m<PROP_M>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    small_propagate_kernel_n7m<PROP_M><<<grid_m, P2_THREADS, smem2, stream>>>(d_desc, d_columns, n_out, d_obs, nc, ring_m,
+                                                                               by_column, d_seeds, n_seg, seg_len);
+    QSB_CUDA(cudaGetLastError());
+    return QSB_OK;
+  }
   if (n == 7 && !getenv("QSB200_PROP_ONE_ROW")) {  // two rows per thread, padded column stride
     const size_t fixed = ((sizeof(SmallShared) + 15) & ~size_t(15)) + (size_t)ring * P2_DIM * sizeof(cplx);
     int nc = (int)((PROPAGATE_SMEM_MAX - fixed) / ((size_t)P2_CS * sizeof(cplx)));

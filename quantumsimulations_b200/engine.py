@@ -61,7 +61,7 @@ EXPORTS = (
     "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_shard_set_stream_barrier", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather",
-    "qsb_propagate_batch", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
+    "qsb_propagate_batch", "qsb_release_caches", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
 )
 
 SHARD_BLOB_BYTES = 96
@@ -178,6 +178,13 @@ def strided_fusion(n_qubits: int, n_sms: int = 148):
         return None
     return {"f": out[1], "m": out[2], "fbits": out[3], "tiles_lb": out[4], "lag": out[5], "vmask": out[6],
             "fixed_vmask": [out[7 + k] for k in range(6)]}
+
+
+def release_caches(device: int = -1) -> None:
+    """Free the device buffers the propagator path keeps between calls (qsb_release_caches)."""
+    lib = load_library()
+    lib.qsb_release_caches.argtypes = [C.c_int]
+    _check(lib.qsb_release_caches(int(device)))
 
 
 def device_count() -> int:

@@ -21,6 +21,8 @@ is bit N-1-k of the amplitude index; bit value 0 <-> Iz = +1/2.
 """
 from __future__ import annotations
 
+import functools
+
 from dataclasses import dataclass, field
 from typing import Dict, List
 
@@ -114,6 +116,20 @@ def initial_basis_index(params: DipolarRareParams) -> int:
     return idx
 
 
+@functools.lru_cache(maxsize=256)
+def _couplings(n_shell: int, shell_scale: float, dipolar_scale: float, gamma_sea: float, gamma_centre: float) -> np.ndarray:
+    """b_ij of DE:533-545 for one geometry.  A sweep compiles hundreds of tables that differ only in drive fields and
+    detunings (SW:631-668), so the geometry + couplings (the reference's own functions, bit-exact) are computed once
+    per distinct argument tuple; the returned array is read-only."""
+    n = n_shell + 1
+    pos = shell_positions_with_rare_center(n_sea=n_shell, radius=shell_scale)
+    if pos.shape != (n, 3):
+        raise RuntimeError("Shell geometry returned unexpected number of sites.")
+    b = dipolar_couplings_from_positions(pos, dipolar_scale, gamma_sea, gamma_centre)
+    b.setflags(write=False)
+    return b
+
+
 def compile_table(params: DipolarRareParams) -> SpinTable:
     """Compile the reference's Hamiltonian/observable/initial-state recipe (DE:483-606) into a SpinTable."""
     if params.is_spin_three_half:
@@ -147,27 +163,13 @@ def compile_table(params: DipolarRareParams) -> SpinTable:
         hx[rare] += w1r * np.cos(params.phi_rare)
         hy[rare] += w1r * np.sin(params.phi_rare)
 
-    pos = shell_positions_with_rare_center(n_sea=n_shell, radius=params.shell_scale)
-    if pos.shape != (n, 3):
-        raise RuntimeError("Shell geometry returned unexpected number of sites.")
-    b = dipolar_couplings_from_positions(
-        pos,
-        params.dipolar_scale,
-        params.gamma_sea,
-        params.gamma_rare if centre_is_rare else params.gamma_sea,
-    )
+    b = _couplings(n_shell, float(params.shell_scale), float(params.dipolar_scale), float(params.gamma_sea),
+                   float(params.gamma_rare if centre_is_rare else params.gamma_sea))
 
-    jxx = np.zeros((n, n))
+    jzz = np.triu(b, 1)                      # every pair has the Ising term (sea-rare pairs ONLY that one)
     jyy = np.zeros((n, n))
-    jzz = np.zeros((n, n))
-    for i in range(n):
-        for j in range(i + 1, n):
-            if i < n_like_sea and j < n_like_sea:
-                jzz[i, j] = b[i, j]
-                jxx[i, j] = -(0.25 * b[i, j])
-                jyy[i, j] = 0.25 * b[i, j]
-            else:
-                jzz[i, j] = b[i, j]          # one of them is the rare site: Ising only
+    jyy[:n_like_sea, :n_like_sea] = 0.25 * jzz[:n_like_sea, :n_like_sea]
+    jxx = -jyy
 
     return SpinTable(
         n=n,
