@@ -44,6 +44,11 @@ def check_apply(table, seed):
 if "small" in which:
     for n in (3, 7, 8, 10):
         check_apply(random_table(n, 40 + n), n)
+        tb = random_table(n, 40 + n)
+        with engine.Plan(tb) as plan:                      # the static-scratch variant, two calls in a row
+            for seed in (1, 2):
+                psi = rand_state(n, seed)
+                assert np.array_equal(plan.apply_h_static(psi), plan.apply_h(psi))
     for m in ("dp5", "taylor"):
         t, out, st = simulate_rare(sweep_params(6, 50e3, t_final=2e-5, steps=9), method=m, return_stats=True)
         assert st.n_accepted > 0 and abs(out["Iz_sea"][0] + 3.0) < 1e-12
@@ -83,6 +88,16 @@ if "steps" in which:
             obs = plan.session_observe()
             plan.session_end()
         assert abs(obs[7] - 1.0) < 1e-6 and st.n_accepted >= 1
+    # dense output: output grid finer than the controller's step (kept Taylor terms + dense_eval_kernel)
+    t = np.linspace(0.0, 2e-4, 41)
+    opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, nsteps=100000, method="taylor", order=12)
+    with engine.Plan(table) as plan:
+        dense_obs, sd = plan.evolve(t, opts)
+    os.environ["QSB200_DENSE_OUTPUT"] = "0"
+    with engine.Plan(table) as plan:
+        step_obs, ss = plan.evolve(t, opts)
+    del os.environ["QSB200_DENSE_OUTPUT"]
+    assert np.max(np.abs(dense_obs - step_obs)) < 1e-8 and sd.n_rhs < ss.n_rhs
     print("steps ok", flush=True)
 if "shard" in which:
     n, world = 14, 4
@@ -95,5 +110,11 @@ if "shard" in which:
         opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, method="taylor", order=8)
         grp.evolve(np.linspace(0.0, 1e-3, 3), opts, psi)
     assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-12
+    os.environ["QSB200_CENTRE_PIPE"] = "2"            # the double-buffered cp.async centre kernel
+    with shard.LocalShardGroup(tb, world) as grp:
+        got2 = grp.apply_h(psi)
+        grp.evolve(np.linspace(0.0, 1e-3, 3), opts, psi)
+    del os.environ["QSB200_CENTRE_PIPE"]
+    assert np.array_equal(got2, got)
     print("shard ok", flush=True)
 print("sanitize_workload: all ok", flush=True)
