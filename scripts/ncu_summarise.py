@@ -4,9 +4,9 @@ profiles/ncu_summary.json (what bench.py's roofline.traffic reads).
 
     python scripts/ncu_summarise.py r1o gpurun_out/r1o_dp5_apply_raw.csv gpurun_out/r1o_error_sums_raw.csv
 
-The captures hold ONE H-apply of a DP5 step attempt (pass_first<comb>, pass_mid, pass_centre, pass_mid, pass_last,
-and the next stage's pass_first<comb>) and the error sweep; a step attempt is 6 applies + 1 error sweep, so
-dram_bytes_per_step = 6 * (mean first_comb + 2 mid + centre + last) + error_sums.
+Round 2 captures hold ALL 30 launches of one DP5 step attempt (6 x [pass_first<comb>, pass_mid, pass_centre, pass_mid,
+pass_last]; the embedded error estimate rides on the last stage): dram_bytes_per_step is their sum.  Round-1 style
+captures (one H-apply + the error sweep) are scaled: 6 * (mean first_comb + 2 mid + centre + last) + error_sums.
 """
 import csv
 import json
@@ -81,11 +81,21 @@ def main():
     err = mean([dram(d) for d in by.get("error_sums_kernel", [])]) if by.get("error_sums_kernel") else 0.0
     ms_apply = (mean([d["gpu__time_duration.sum"] for d in by["pass_first"]]) + 2 * mean([d["gpu__time_duration.sum"] for d in by["pass_mid"]])
                 + mean([d["gpu__time_duration.sum"] for d in by["pass_centre"]]) + mean([d["gpu__time_duration.sum"] for d in by["pass_last"]]))
+    whole_step = len(by["pass_last"]) == 6 and len(by["pass_first"]) == 6
+    per_step = sum(dram(d) for d in launches) if whole_step else 6 * per_apply + err
+    ms_step = sum(d["gpu__time_duration.sum"] for d in launches) if whole_step else None
+    shares = {}
+    if whole_step:
+        for key, ds in by.items():
+            shares[key] = {"launches": len(ds), "ncu_ms": sum(d["gpu__time_duration.sum"] for d in ds),
+                           "share_of_step": sum(d["gpu__time_duration.sum"] for d in ds) / ms_step,
+                           "dram_bytes": sum(dram(d) for d in ds)}
     summary = {
         "tag": tag,
         "source": "ncu --set full --clock-control none, python bench.py --steps 1 --warmup 3 --no-cpu --no-sharded (N=28, DP5); "
-                  "one H-apply of the timed step attempt + the next stage's pass_first + the error sweep",
-        "dram_bytes_per_step": 6 * per_apply + err,
+                  "round 2: all 30 launches of the timed step attempt",
+        "dram_bytes_per_step": per_step,
+        "whole_step_capture": whole_step, "ncu_ms_per_step": ms_step, "kernel_shares": shares,
         "dram_bytes_per_happly": per_apply,
         "dram_bytes_error_sweep": err,
         "ncu_ms_per_happly": ms_apply,

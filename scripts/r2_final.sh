@@ -1,0 +1,19 @@
+#!/bin/bash
+# Round-2 evidence pass on one GPU: full GPU test suite, smoke, default bench line, ncu launch list, ncu --set full of the
+# 30 launches of one DP5 step attempt at N = 28.   usage: scripts/r2_final.sh TAG [notest]
+TAG=${1:-r2z}
+mkdir -p gpurun_out
+if [ "$2" != "notest" ]; then
+  timeout -s KILL 1200 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest_gpu.log 2>&1; tail -3 gpurun_out/${TAG}_pytest_gpu.log
+  timeout -s KILL 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -4 gpurun_out/${TAG}_smoke.log
+fi
+timeout -s KILL 300 python scripts/sanitize_workload.py > gpurun_out/${TAG}_selfcheck_workload.log 2>&1; tail -3 gpurun_out/${TAG}_selfcheck_workload.log
+timeout -s KILL 900 python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err || tail -5 gpurun_out/${TAG}_bench.err
+cut -c1-300 gpurun_out/${TAG}_bench.json
+timeout -s KILL 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_reference.json 2> gpurun_out/${TAG}_bench_reference.err; cut -c1-200 gpurun_out/${TAG}_bench_reference.json
+B="python bench.py --steps 1 --warmup 3 --no-cpu --no-sharded --no-grid"
+timeout -s KILL 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches_bench_steps1.csv $B > gpurun_out/${TAG}_ncu_list.log 2>&1
+# pass_* launches: prime 5, warm-up 3 x 30, then the timed step's 30
+timeout -s KILL 1500 ncu --set full --clock-control none --import-source on -k regex:'pass_' -s 95 -c 30 -f -o gpurun_out/${TAG}_dp5_step $B > gpurun_out/${TAG}_ncu_full.log 2>&1
+ncu -i gpurun_out/${TAG}_dp5_step.ncu-rep --page raw --csv > gpurun_out/${TAG}_dp5_step_raw.csv 2>/dev/null
+ls -la gpurun_out/${TAG}_* | awk '{print $5, $9}'

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""CI-sized pass over every kernel family, meant to run under compute-sanitizer:
+"""CI-sized, self-checking pass over every kernel family.  Written to run under compute-sanitizer:
 
     compute-sanitizer --tool memcheck  python scripts/sanitize_workload.py
     compute-sanitizer --tool racecheck python scripts/sanitize_workload.py
@@ -9,6 +9,10 @@ chains, the tiled H-apply with one, two and three strided layouts (incl. the pad
 than 8 bits), both tiled integrators with the fused epilogues / stage combination / error sweep, the product-state
 hook, and the sharded path with 4 ranks as threads (P2P centre pass on one device).  Every result is also checked
 against the oracle, so a sanitizer-clean run that computes garbage still fails.
+
+Round 2: compute-sanitizer is CLOSED on this GPU pool by its operators (every invocation returns rc 86, "runs under it
+have left GPUs needing a reset", profiles/r2_sanitizer_closed.log), so the script is run plain: what it pins is that
+every kernel family reproduces the oracle on small cases, including twice in a row on reused buffers.
 """
 import os
 import sys
@@ -89,7 +93,7 @@ if "steps" in which:
             plan.session_end()
         assert abs(obs[7] - 1.0) < 1e-6 and st.n_accepted >= 1
     # dense output: output grid finer than the controller's step (kept Taylor terms + dense_eval_kernel)
-    t = np.linspace(0.0, 2e-4, 41)
+    t = np.linspace(0.0, 2e-5, 201)
     opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, nsteps=100000, method="taylor", order=12)
     with engine.Plan(table) as plan:
         dense_obs, sd = plan.evolve(t, opts)
@@ -97,7 +101,10 @@ if "steps" in which:
     with engine.Plan(table) as plan:
         step_obs, ss = plan.evolve(t, opts)
     del os.environ["QSB200_DENSE_OUTPUT"]
-    assert np.max(np.abs(dense_obs - step_obs)) < 1e-8 and sd.n_rhs < ss.n_rhs
+    dev = float(np.max(np.abs(dense_obs - step_obs)))
+    print(f"dense output: max dev {dev:.2e}, H-applies {sd.n_rhs} vs {ss.n_rhs} stepping", flush=True)
+    assert dev < 1e-8, dev
+    assert sd.n_rhs < ss.n_rhs, (sd.n_rhs, ss.n_rhs)
     print("steps ok", flush=True)
 if "shard" in which:
     n, world = 14, 4
