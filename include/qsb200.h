@@ -240,6 +240,10 @@ int qsb_local_group_create(int32_t world, qsb_local_group** group);
 int qsb_local_group_destroy(qsb_local_group* group);
 void* qsb_local_group_member(qsb_local_group* group, int32_t rank); /* the ctx to pass with qsb_local_allgather */
 int qsb_local_allgather(void* member_ctx, const double* send, int32_t count, double* recv);
+/* A qsb_stream_barrier_fn for such ranks: drains the stream and joins the thread barrier ON THE HOST (no kernel waits
+ * on another, so the ranks may share a GPU).  It serialises what an NCCL barrier overlaps; it exists so that the
+ * pipelined H-apply of qsb_shard_set_stream_barrier can be tested on a one-GPU box.                              */
+int qsb_local_stream_barrier(void* member_ctx, void* stream);
 
 /* Benchmark aid: when enabled, every launch of the tiled path is bracketed by CUDA events on its stream (this
  * serialises host and device; never enable it inside a timed throughput run).  Classes: 0 pass_first, 1 pass_mid,

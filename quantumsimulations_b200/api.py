@@ -193,6 +193,11 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
     "taylor", "dp5", or "propagator" / "propagator-dp5" (N <= 10: one propagator per trajectory, then one matvec per
     output time; see PROPAGATOR).  ``tol_scale`` multiplies solver_atol/solver_rtol before
     they reach the integrator (default 1e-3 for taylor, 1 for dp5; see DEFAULT_TOL_SCALE).
+    Deviation from the reference's error behaviour: on the propagator path (what "auto" picks for N <= 10 and
+    steps - 1 > 2^N) ``solver_nsteps`` / ``solver_max_step`` apply to the column integrations over dt / 2^s only, so a
+    long output interval never exhausts ``nsteps`` there, where QuTiP raises IntegratorException ("Excess work") and the
+    stepped integrators (``method="taylor"`` / ``"dp5"``) raise ``IntegratorError``.  The traces are the same (<= 1e-6
+    from exact); ask for a stepped method if the exception itself matters.
     ``raw_norm=True`` adds the integrator's own norm under an extra key (QuTiP discards it).
     ``checkpoint``: file the tiled path (N >= 11) writes its state to every ``checkpoint_every`` output times and
     resumes from if it exists (``checkpoint.evolve_checkpointed``); the on-chip path is one launch per trajectory

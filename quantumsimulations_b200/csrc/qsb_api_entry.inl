@@ -192,6 +192,10 @@ int qsb_apply_h(qsb_plan* p, const double* psi_host, double* out_host) {
     compile_small(&t, 0, &o, 0, &d);
     SmallDesc* dd = nullptr;
     cplx *din = nullptr, *dout = nullptr;
+    struct Guard {  // early returns free what has been allocated
+      SmallDesc*& a; cplx*& b; cplx*& c; cudaStream_t s;
+      ~Guard() { cudaStreamSynchronize(s); cudaFree(a); cudaFree(b); cudaFree(c); }
+    } guard{dd, din, dout, p->stream};
     QSB_CUDA(cudaMalloc(&dd, sizeof d));
     QSB_CUDA(cudaMalloc(&din, ubytes));
     QSB_CUDA(cudaMalloc(&dout, ubytes));
@@ -201,7 +205,6 @@ int qsb_apply_h(qsb_plan* p, const double* psi_host, double* out_host) {
     QSB_CUDA(cudaGetLastError());
     QSB_CUDA(cudaMemcpyAsync(out_host, dout, ubytes, cudaMemcpyDeviceToHost, p->stream));
     QSB_CUDA(cudaStreamSynchronize(p->stream));
-    cudaFree(dd); cudaFree(din); cudaFree(dout);
     return QSB_OK;
   }
   if (p->ses) return fail(QSB_ERR_BAD_ARG, "qsb_apply_h cannot run while a session is open (shared workspace)");

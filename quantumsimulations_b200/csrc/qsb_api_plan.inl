@@ -265,8 +265,18 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
   SmallStats* d_stats = nullptr;
   const size_t nt = (size_t)n_out * (t_out_per_traj ? n_traj : 1);
   const size_t nobs = (size_t)n_traj * n_out * QSB_NOBS;
-  cudaStream_t st;
-  cudaEvent_t e0, e1;
+  cudaStream_t st = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  struct Guard {  // every early return (QSB_CUDA) releases what has been created so far
+    SmallDesc*& a; double*& b; double*& c; SmallStats*& d; cudaStream_t& s; cudaEvent_t &x, &y;
+    ~Guard() {
+      if (s) cudaStreamSynchronize(s);
+      cudaFree(a); cudaFree(b); cudaFree(c); cudaFree(d);
+      if (x) cudaEventDestroy(x);
+      if (y) cudaEventDestroy(y);
+      if (s) cudaStreamDestroy(s);
+    }
+  } guard{d_desc, d_t, d_obs, d_stats, st, e0, e1};
   QSB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
   QSB_CUDA(cudaEventCreate(&e0));
   QSB_CUDA(cudaEventCreate(&e1));
@@ -286,9 +296,7 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
   QSB_CUDA(cudaStreamSynchronize(st));
   float ms = 0.f;
   cudaEventElapsedTime(&ms, e0, e1);
-  cudaFree(d_desc); cudaFree(d_t); cudaFree(d_obs); cudaFree(d_stats);
-  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st);
-  int worst = QSB_OK;
+  int worst = QSB_OK;  // (buffers, events and the stream are released by `guard`)
   for (int i = 0; i < n_traj; ++i) {
     if (stats) {
       stats[i].n_accepted = hs[i].n_accepted; stats[i].n_rejected = hs[i].n_rejected; stats[i].n_rhs = hs[i].n_rhs;

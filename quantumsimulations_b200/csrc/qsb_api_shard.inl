@@ -253,6 +253,20 @@ void* qsb_local_group_member(qsb_local_group* g, int32_t rank) {
   return &g->members[rank];
 }
 
+// A qsb_stream_barrier_fn for ranks that are threads of one process: it BLOCKS the host (drain the stream, then the
+// thread barrier), which satisfies the hook's contract - work queued after the call starts only when every rank's
+// earlier work on its counterpart stream is complete - without any kernel waiting on another (ranks may share a GPU).
+// It serialises what the NCCL version overlaps; its purpose is to run the pipelined code path (chunk maps, persistent
+// centre pass, event wiring) on a one-GPU box.
+int qsb_local_stream_barrier(void* member_ctx, void* stream) {
+  auto* m = (qsb_local_group::Member*)member_ctx;
+  if (!m) return 1;
+  const cudaError_t e = cudaStreamSynchronize((cudaStream_t)stream);
+  const bool ok = m->g->barrier();
+  if (e != cudaSuccess) { cudaGetLastError(); return 1; }
+  return ok ? 0 : 1;
+}
+
 int qsb_local_allgather(void* member_ctx, const double* send, int32_t count, double* recv) {
   auto* m = (qsb_local_group::Member*)member_ctx;
   if (!m) return 1;

@@ -547,7 +547,11 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
       cudaStream_t C = link->centre_stream;
       int lmax = 0;
       for (int k = 1; k <= centre; ++k) lmax = std::max(lmax, g.lay[k].lk);
-      const int cw = TB - lmax;                                  // chunk field width
+      // chunk field = index bits [lmax, lmax + cw): below 12, and below the bits of the centre layout's tile number
+      // that say which rank owns the tile (its top log2(world) bits = index bits [gs - wl, gs)); tiny shards only
+      int wl = 0;
+      while ((1 << wl) < g.world) ++wl;
+      const int cw = std::max(0, std::min(TB, g.lay[centre].gs - wl) - lmax);
       const int plb = std::max(0, std::min(std::min(link->pipe_lb, cw), 4));
       const int K = 1 << plb, lb = cw - plb;                     // groups, log2 chunks per group
       const unsigned per_group = n_tiles >> plb;                 // tiles of one layout in one group

@@ -60,7 +60,7 @@ EXPORTS = (
     "qsb_apply_h_product", "qsb_apply_h_static",
     "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_shard_set_stream_barrier", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
-    "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather",
+    "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather", "qsb_local_stream_barrier",
     "qsb_propagate_batch", "qsb_release_caches", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
 )
 
@@ -258,7 +258,11 @@ class Plan:
             self._h = C.c_void_p()
             self._ws = None
 
-    __del__ = close
+    def __del__(self):
+        try:                       # interpreter teardown: the library object may already be gone
+            self.close()
+        except Exception:
+            pass
 
     def __enter__(self):
         return self
@@ -406,13 +410,13 @@ class ShardedPlan(Plan):
         fn = C.cast(allgather, C.c_void_p)
         _check(self.lib.qsb_shard_connect(self._h, joined, fn, C.c_void_p(ctx) if ctx is not None else None))
 
-    def set_stream_barrier(self, hook) -> None:
+    def set_stream_barrier(self, hook, ctx=None) -> None:
         """Install (or, with None, remove) a stream-ordered rank barrier: a STREAM_BARRIER_FN instance.  With one, the
         H-apply overlaps the NVLink-bound centre pass of one branch with the HBM-bound passes of the other
         (qsb_shard_set_stream_barrier); only for ranks that each own their GPU."""
         self._stream_hook = hook   # keep the ctypes callback alive
         fn = C.cast(hook, C.c_void_p) if hook is not None else None
-        _check(self.lib.qsb_shard_set_stream_barrier(self._h, fn, None))
+        _check(self.lib.qsb_shard_set_stream_barrier(self._h, fn, C.c_void_p(ctx) if ctx is not None else None))
 
     def allgather(self, values) -> np.ndarray:
         """[world][len(values)] doubles gathered over the plan's own hook (collective; host-side agreement only)."""

@@ -149,7 +149,10 @@ class LocalShardGroup:
     """``world`` ranks as threads of this process.  ``run(fn)`` calls ``fn(plan, rank)`` on every rank concurrently
     (the engine's calls are collective, so they must overlap in time) and returns the per-rank results."""
 
-    def __init__(self, table: SpinTable, world: int, devices: Optional[Sequence[int]] = None):
+    def __init__(self, table: SpinTable, world: int, devices: Optional[Sequence[int]] = None, pipeline: bool = False):
+        """``pipeline``: install the host-blocking stream barrier (qsb_local_stream_barrier), i.e. run the chunk-pipelined
+        H-apply of the multi-process mode - serialised, since these ranks may share a GPU - instead of the plain
+        serialised passes."""
         shard_geometry(table.n, world)
         self.lib = engine.load_library()
         self.world = world
@@ -161,6 +164,10 @@ class LocalShardGroup:
         blobs = [p.export_blob() for p in self.plans]
         fn = C.cast(self.lib.qsb_local_allgather, C.c_void_p).value
         self.run(lambda plan, r: plan.connect(blobs, fn, self.lib.qsb_local_group_member(self._group, r)))
+        if pipeline:
+            sb = C.cast(self.lib.qsb_local_stream_barrier, C.c_void_p).value
+            for r, plan in enumerate(self.plans):
+                plan.set_stream_barrier(sb, self.lib.qsb_local_group_member(self._group, r))
 
     def run(self, fn: Callable) -> List:
         out: List = [None] * self.world

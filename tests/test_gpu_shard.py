@@ -195,3 +195,33 @@ def test_pipelined_centre_kernel(n, world, gmax, monkeypatch):
     assert np.max(np.abs(got_h - want)) / np.max(np.abs(want)) < 2e-13
     assert np.array_equal(got_h, ref_h) and np.array_equal(got_obs, ref_obs)
     assert (got_st.n_accepted, got_st.n_rejected) == (ref_st.n_accepted, ref_st.n_rejected)
+
+
+@pytest.mark.parametrize("n,world,gmax,pipe", [(14, 4, None, 3), (16, 2, None, 3), (18, 8, None, 2), (19, 2, 4, 3), (20, 4, 3, 4),
+                                               (21, 8, None, 1), (22, 2, None, 3)])
+def test_pipelined_strided_passes(n, world, gmax, pipe, monkeypatch):
+    """The chunk-pipelined H-apply of the one-process-per-GPU mode (qsb_shard_set_stream_barrier: chunk-group tile maps,
+    persistent centre pass, two streams + events) with ranks as threads and the HOST-blocking barrier
+    qsb_local_stream_barrier, so that a one-GPU box runs that code path: H psi against the numpy oracle and, bit for
+    bit, against the serialised passes; trajectories (observable sums collected by the chunked centre passes) too."""
+    from oracle import dense
+    from quantumsimulations_b200 import engine, shard
+
+    if gmax is not None:
+        monkeypatch.setenv("QSB200_MAX_GROUP", str(gmax))
+    monkeypatch.setenv("QSB200_SHARD_PIPE", str(pipe))
+    table = random_table(n, 880 + n + world, dense_pairs=False)
+    bm = table.bit_major()
+    psi = _rand_state(n, 11 * n + world)
+    opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, method="dp5")
+    t = np.linspace(0.0, 1e-3, 3)
+    with shard.LocalShardGroup(table, world) as grp:
+        ref_h = grp.apply_h(psi)
+        ref_obs, ref_st = grp.evolve(t, opts, psi)
+    with shard.LocalShardGroup(table, world, pipeline=True) as grp:
+        got_h = grp.apply_h(psi)
+        got_obs, got_st = grp.evolve(t, opts, psi)
+    want = dense.apply_h(bm["h"], bm["J"], psi)
+    assert np.max(np.abs(got_h - want)) / np.max(np.abs(want)) < 2e-13
+    assert np.array_equal(got_h, ref_h) and np.array_equal(got_obs, ref_obs)
+    assert (got_st.n_accepted, got_st.n_rejected) == (ref_st.n_accepted, ref_st.n_rejected)
