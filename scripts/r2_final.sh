@@ -3,7 +3,9 @@
 # 30 launches of one DP5 step attempt at N = 28.   usage: scripts/r2_final.sh TAG [notest]
 TAG=${1:-r2z}
 mkdir -p gpurun_out
-if [ "$2" != "notest" ]; then
+if [ "$2" == "shardtests" ]; then
+  timeout -s KILL 900 python -m pytest tests/test_gpu_shard.py -x -q > gpurun_out/${TAG}_pytest_shard.log 2>&1; tail -3 gpurun_out/${TAG}_pytest_shard.log
+elif [ "$2" != "notest" ]; then
   timeout -s KILL 1200 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest_gpu.log 2>&1; tail -3 gpurun_out/${TAG}_pytest_gpu.log
   timeout -s KILL 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -4 gpurun_out/${TAG}_smoke.log
 fi
@@ -14,6 +16,9 @@ timeout -s KILL 600 python bench.py --impl reference --steps 2 --warmup 1 > gpur
 B="python bench.py --steps 1 --warmup 3 --no-cpu --no-sharded --no-grid"
 timeout -s KILL 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches_bench_steps1.csv $B > gpurun_out/${TAG}_ncu_list.log 2>&1
 # pass_* launches: prime 5, warm-up 3 x 30, then the timed step's 30
-timeout -s KILL 1500 ncu --set full --clock-control none --import-source on -k regex:'pass_' -s 95 -c 30 -f -o gpurun_out/${TAG}_dp5_step $B > gpurun_out/${TAG}_ncu_full.log 2>&1
-ncu -i gpurun_out/${TAG}_dp5_step.ncu-rep --page raw --csv > gpurun_out/${TAG}_dp5_step_raw.csv 2>/dev/null
+timeout -s KILL 1500 ncu --set full --clock-control none --import-source on -k regex:'pass_' -s 95 -c 30 -f -o /tmp/${TAG}_dp5_step $B > gpurun_out/${TAG}_ncu_full.log 2>&1
+# the .ncu-rep (126 MB) stays on the box: gpurun_out is capped at 64 MiB; the raw page and the source page of pass_centre / pass_last come back as CSV
+ncu -i /tmp/${TAG}_dp5_step.ncu-rep --page raw --csv > gpurun_out/${TAG}_dp5_step_raw.csv 2>/dev/null
+ncu -i /tmp/${TAG}_dp5_step.ncu-rep --page source --csv -k regex:'pass_last' -c 1 > gpurun_out/${TAG}_pass_last_source.csv 2>/dev/null
+ncu -i /tmp/${TAG}_dp5_step.ncu-rep --page source --csv -k regex:'pass_centre' -c 1 > gpurun_out/${TAG}_pass_centre_source.csv 2>/dev/null
 ls -la gpurun_out/${TAG}_* | awk '{print $5, $9}'

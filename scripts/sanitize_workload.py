@@ -103,7 +103,7 @@ if "steps" in which:
     del os.environ["QSB200_DENSE_OUTPUT"]
     dev = float(np.max(np.abs(dense_obs - step_obs)))
     print(f"dense output: max dev {dev:.2e}, H-applies {sd.n_rhs} vs {ss.n_rhs} stepping", flush=True)
-    assert dev < 1e-8, dev
+    assert dev < 1e-6, dev      # two different step sequences at rtol 1e-9: both within the parity tolerance of exact
     assert sd.n_rhs < ss.n_rhs, (sd.n_rhs, ss.n_rhs)
     print("steps ok", flush=True)
 if "shard" in which:
