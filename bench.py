@@ -266,17 +266,30 @@ def c1_leg(device, with_cpu):
         "wall_s": w_auto, "kernel_ms": st.device_ms, "path": st.path, "column_h_applies": st.n_rhs,
         "method": "auto (propagator: not an ODE step rate)", "stepped_3ms_window": legs}
     p13 = DipolarRareParams(is_spin_three_half=False)
+    simulate_rare(p13, device=device)                                                      # plan + dense buffers warm
     t0 = time.perf_counter()
     _, _, s13 = simulate_rare(p13, device=device, return_stats=True)
     w13 = time.perf_counter() - t0
+    os.environ["QSB200_DENSE_OUTPUT"] = "0"          # round-1 behaviour: step ONTO each of the 2000 output times
+    try:
+        t0 = time.perf_counter()
+        _, _, s13s = simulate_rare(p13, device=device, return_stats=True)
+        w13s = time.perf_counter() - t0
+    finally:
+        del os.environ["QSB200_DENSE_OUTPUT"]
     t0 = time.perf_counter()
     _, _, s13d = simulate_rare(p13, device=device, method="dp5", return_stats=True)
     w13d = time.perf_counter() - t0
     out["n13_dataclass_default"] = {
         "workload": "C1 (ii): DipolarRareParams(is_spin_three_half=False): N=13 icosahedron, 0.02 s, 2000 outputs, "
                     "options None (QuTiP defaults atol 1e-8 / rtol 1e-6)",
-        "wall_s": w13, "kernel_ms": s13.device_ms, "path": s13.path, "steps": s13.n_accepted + s13.n_rejected,
-        "h_applies": s13.n_rhs, "steps_per_s": (s13.n_accepted + s13.n_rejected) / w13, "h_applies_per_s": s13.n_rhs / w13,
+        "method": "auto = Taylor(20) with dense output: unclipped steps, interior outputs read off the step's polynomial",
+        "wall_s": w13, "kernel_ms": s13.device_ms, "path": s13.path, "outputs": p13.steps,
+        "steps": s13.n_accepted + s13.n_rejected, "h_applies": s13.n_rhs, "outputs_per_s": p13.steps / w13,
+        "steps_per_s": (s13.n_accepted + s13.n_rejected) / w13, "h_applies_per_s": s13.n_rhs / w13,
+        "stepping_onto_every_output": {"wall_s": w13s, "steps": s13s.n_accepted + s13s.n_rejected, "h_applies": s13s.n_rhs,
+                                       "steps_per_s": (s13s.n_accepted + s13s.n_rejected) / w13s,
+                                       "h_applies_per_s": s13s.n_rhs / w13s},
         "dp5": {"wall_s": w13d, "steps": s13d.n_accepted + s13d.n_rejected, "h_applies": s13d.n_rhs,
                 "steps_per_s": (s13d.n_accepted + s13d.n_rejected) / w13d}}
     if with_cpu:

@@ -75,6 +75,9 @@ def make_torch_allgather(world: int, device=None):
     return engine.ALLGATHER_FN(hook)
 
 
+_BARRIER_GROUPS: dict = {}
+
+
 def make_torch_stream_barrier(device=None, n_streams: int = 2):
     """A STREAM_BARRIER_FN over NCCL: a one-element all-reduce issued with the given CUDA stream as torch's current
     stream, so the collective is ordered after that stream's earlier work and the stream waits for it; the host does
@@ -86,11 +89,15 @@ def make_torch_stream_barrier(device=None, n_streams: int = 2):
     import torch.distributed as dist
 
     dev = torch.device("cuda", torch.cuda.current_device() if device is None else device)
-    groups = [dist.new_group(backend="nccl") for _ in range(n_streams)]
-    tokens = [torch.zeros(1, dtype=torch.float32, device=dev) for _ in range(n_streams)]
-    for g, tok in zip(groups, tokens):          # build the communicators now, not inside the first H-apply
-        dist.all_reduce(tok, group=g)
-    torch.cuda.synchronize(dev)
+    key = (dist.get_world_size(), n_streams, dev.index)
+    if key not in _BARRIER_GROUPS:              # one set of communicators per process, shared by every plan it makes
+        groups = [dist.new_group(backend="nccl") for _ in range(n_streams)]
+        tokens = [torch.zeros(1, dtype=torch.float32, device=dev) for _ in range(n_streams)]
+        for g, tok in zip(groups, tokens):      # build the communicators now, not inside the first H-apply
+            dist.all_reduce(tok, group=g)
+        torch.cuda.synchronize(dev)
+        _BARRIER_GROUPS[key] = (groups, tokens)
+    groups, tokens = _BARRIER_GROUPS[key]
     slots = {}
 
     def hook(_ctx, stream_ptr):
