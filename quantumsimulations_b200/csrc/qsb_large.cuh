@@ -53,6 +53,8 @@ struct Epilogue {
   int want_err;          // accumulate |err|^2 / sc^2 into partials
   int sc_i0, sc_i1;      // sc = atol + rtol max(|vin[sc_i0]|, sc_i1 >= 0 ? |vin[sc_i1]| : sc_i1 == -1 ? |o2| : |v|)
   int raw_h;             // 1: k = H v (no -i), for qsb_apply_h
+  int pf;                // prefetch policy of pass_last (experiment knob QSB200_LAST_PF): bit 0 = tX to L1 instead of L2,
+                         // bit 1 = do not prefetch the epilogue's input vectors
   double atol, rtol;
 };
 

@@ -28,12 +28,17 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
   {  // pull the tiles needed later (tX in three rounds, the epilogue inputs after six) towards L2
     const size_t off = (size_t)tt * 256;
     const char* p = reinterpret_cast<const char*>(tx + base) + off;
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128));
+    if (ep.pf & 1) {
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(p + 128));
+    } else {
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128));
+    }
     p = reinterpret_cast<const char*>(src + base) + off;
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
     asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128));
-    if (EPI) {
+    if (EPI && !(ep.pf & 2)) {
       for (int q = 0; q < ep.n_in; ++q) {
         p = reinterpret_cast<const char*>(ep.vin[q] + base) + off;
         asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
@@ -645,6 +650,10 @@ int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cp
   int rc = launch_strided_passes(g, a, tx, ty, collect_obs, partials, stream, link, fu);
   if (rc) return rc;
   {
+    static const int last_pf = [] { const char* e = std::getenv("QSB200_LAST_PF"); return e ? atoi(e) : 0; }();
+    Epilogue epx = ep;
+    epx.pf = last_pf;
+    const Epilogue& ep = epx;
     const int epi = (ep.o2 ? 1 : 0) | (ep.want_err ? 2 : 0);
     Timed t(3, stream, (3 + ep.n_in + (ep.o1 ? 1 : 0) + (ep.o2 ? 1 : 0)) * S);
     switch (epi) {
