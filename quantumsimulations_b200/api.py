@@ -121,13 +121,26 @@ PROPAGATOR = "propagator"
 PROPAGATOR_TOL_SCALE = {"taylor": 1e-5, "dp5": 1.0}
 
 
-def split_method(method: Optional[str], n_qubits: Optional[int] = None, steps: Optional[int] = None) -> Tuple[str, bool]:
+# "auto" for 11 <= N <= 13: the HBM-resident propagator (engine.propagate_hbm) costs a few seconds per trajectory
+# whatever the trajectory; stepping costs ~3 H-applies per unit of ||H|| t at ~25 us each at these sizes.  The
+# propagator is picked when the cheap bound ||H|| t_final (SpinTable.spectral_bound) says stepping would take longer.
+AUTO_HBM_NORM_T = 2.0e5
+
+
+def split_method(method: Optional[str], n_qubits: Optional[int] = None, steps: Optional[int] = None,
+                 norm_t: Optional[float] = None) -> Tuple[str, bool]:
     """(integrator, use_propagator) from a method string: "auto", "taylor", "dp5", "propagator", "propagator-dp5".
-    "auto" needs the trajectory's size (``n_qubits``, ``steps``) to choose; without it, it means stepping."""
+    "auto" needs the trajectory's size (``n_qubits``, ``steps``; for 11 <= N <= 13 also ``norm_t`` = bound on
+    ||H|| t_final) to choose; without it, it means stepping."""
     m = method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)
     if m == "auto":
-        fits = n_qubits is not None and steps is not None and n_qubits <= engine.SMALL_MAX_QUBITS
-        return "taylor", bool(fits and steps - 1 > (1 << n_qubits))
+        if n_qubits is None or steps is None:
+            return "taylor", False
+        if n_qubits <= engine.SMALL_MAX_QUBITS:
+            return "taylor", bool(steps - 1 > (1 << n_qubits))
+        if n_qubits <= engine.HBM_PROPAGATOR_MAX_QUBITS:
+            return "taylor", bool(norm_t is not None and norm_t > AUTO_HBM_NORM_T and steps >= 3)
+        return "taylor", False
     if m.startswith(PROPAGATOR):
         rest = m[len(PROPAGATOR):].lstrip("-")
         m, prop = (rest or "taylor"), True
@@ -138,6 +151,16 @@ def split_method(method: Optional[str], n_qubits: Optional[int] = None, steps: O
     return m, prop
 
 
+def resolve_method(params: DipolarRareParams, method: Optional[str]) -> Tuple[str, bool]:
+    """``split_method`` for one parameter record (computes the ||H|| t_final bound only where "auto" needs it)."""
+    n, steps = _size_of(params)
+    norm_t = None
+    m = method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)
+    if m == "auto" and engine.SMALL_MAX_QUBITS < n <= engine.HBM_PROPAGATOR_MAX_QUBITS and not params.is_spin_three_half:
+        norm_t = compile_table(params).spectral_bound() * float(params.t_final)
+    return split_method(method, n, steps, norm_t)
+
+
 def _size_of(params: DipolarRareParams) -> Tuple[int, int]:
     return params.n_sea + 1, params.steps
 
@@ -145,7 +168,7 @@ def _size_of(params: DipolarRareParams) -> Tuple[int, int]:
 def _options_from(params: DipolarRareParams, method: Optional[str], tol_scale: Optional[float] = None
                   ) -> Tuple[engine.SolverOptions, bool]:
     """Map the reference's solver_* fields (DE:629-651); returns (options, any_override)."""
-    integrator, propagate = split_method(method, *_size_of(params))
+    integrator, propagate = resolve_method(params, method)
     knobs = (params.solver_atol, params.solver_rtol, params.solver_nsteps, params.solver_max_step)
     override = any(v is not None for v in knobs)
     o = engine.SolverOptions()
@@ -206,7 +229,7 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
     t = _check_grid(params)
     table = compile_table(params)
     opts, override = _options_from(params, method, tol_scale)
-    if split_method(method, table.n, len(t))[1]:
+    if resolve_method(params, method)[1]:
         obs, stats = _propagate([table], [t], [opts], device)
         out = _pack(obs[0], override, raw_norm, by_column=True)
         return (t, out, stats[0]) if return_stats else (t, out)
@@ -224,25 +247,29 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
 
 
 def _propagate(tables, grids, opts, device):
-    """Propagator path for trajectories of equal N and equal number of outputs (their dt may differ)."""
-    if tables[0].n > engine.SMALL_MAX_QUBITS:
-        raise ValueError(f"method 'propagator' holds a dense 2^N x 2^N matrix on chip: N <= {engine.SMALL_MAX_QUBITS}")
+    """Propagator path for trajectories of equal N and equal number of outputs (their dt may differ): the on-chip one
+    (N <= 10, one batched call) or the HBM-resident one (11 <= N <= 13, one call per trajectory)."""
+    if tables[0].n > engine.HBM_PROPAGATOR_MAX_QUBITS:
+        raise ValueError(f"method 'propagator' holds a dense 2^N x 2^N matrix: N <= {engine.HBM_PROPAGATOR_MAX_QUBITS}")
     seen: Dict[Tuple[float, float, int], Optional[float]] = {}   # sweeps share one grid: check each distinct one once
     dts = []
     for g in grids:
         key = (float(g[0]), float(g[-1]), len(g))
         if key not in seen:
             seen[key] = engine.uniform_step(g)
+        if seen[key] is None:
+            raise ValueError("method 'propagator' needs a uniform output grid (np.linspace, DE:626)")
         dts.append(seen[key])
-    if any(d is None for d in dts):
-        raise ValueError("method 'propagator' needs a uniform output grid")
-    return engine.propagate_batch(tables, len(grids[0]), np.array(dts) if len(dts) > 1 else dts[0], opts, device,
-                                  by_column=True)
+    if tables[0].n > engine.SMALL_MAX_QUBITS:
+        res = [engine.propagate_hbm(tb, len(g), dt, o, device, by_column=True) for tb, g, dt, o in zip(tables, grids, dts, opts)]
+        return np.stack([r[0] for r in res]), [r[1] for r in res]
+    return engine.propagate_batch(tables, len(grids[0]), dts, opts, device, by_column=True)
 
 
 def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int = 0, method: Optional[str] = None,
                         tol_scale: Optional[float] = None, raw_norm: bool = False):
-    """Independent trajectories; those with N <= 10 share ONE kernel launch (one CTA each)."""
+    """Independent trajectories; those with N <= 10 share ONE kernel launch (one CTA each), 11 <= N <= 13 on a uniform
+    grid may go through the HBM-resident propagator (``resolve_method``), the rest is stepped on the tiled path."""
     n = len(params_list)
     results: List = [None] * n
     base_grids: Dict[Tuple[float, int], np.ndarray] = {}   # a sweep's trajectories share one grid: build it once
@@ -254,8 +281,9 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
         grids.append(base_grids[key])
     tables = [compile_table(p) for p in params_list]
     om = [_options_from(p, method, tol_scale) for p in params_list]
-    if any(split_method(method, t.n, len(g))[1] and t.n > engine.SMALL_MAX_QUBITS for t, g in zip(tables, grids)):
-        raise ValueError(f"method 'propagator' holds a dense 2^N x 2^N matrix on chip: N <= {engine.SMALL_MAX_QUBITS}")
+    props = [resolve_method(p, method)[1] for p in params_list]
+    if any(pr and t.n > engine.HBM_PROPAGATOR_MAX_QUBITS for pr, t in zip(props, tables)):
+        raise ValueError(f"method 'propagator' holds a dense 2^N x 2^N matrix: N <= {engine.HBM_PROPAGATOR_MAX_QUBITS}")
     small = [i for i in range(n) if tables[i].n <= engine.SMALL_MAX_QUBITS]
     groups: Dict[int, List[int]] = {}
     for i in small:
@@ -271,6 +299,11 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
         for j, i in enumerate(idxs):
             results[i] = (grids[i].copy(), _pack(obs[j], om[i][1], raw_norm, by_column=prop))
             stats_out[i] = stats[j]
+    for i in range(n):
+        if results[i] is None and props[i]:     # 11 <= N <= 13: the HBM-resident propagator, one trajectory per call
+            obs, st = _propagate([tables[i]], [grids[i]], [om[i][0]], device)
+            results[i] = (grids[i].copy(), _pack(obs[0], om[i][1], raw_norm, by_column=True))
+            stats_out[i] = st[0]
     for i in range(n):
         if results[i] is None:
             with engine.Plan(tables[i], device) as plan:

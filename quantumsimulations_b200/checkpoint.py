@@ -66,7 +66,7 @@ def effective_solver(params: DipolarRareParams, method: Optional[str] = None, to
     library version."""
     from . import api, engine
 
-    integrator, propagate = api.split_method(method, params.n_sea + 1, params.steps)
+    integrator, propagate = api.resolve_method(params, method)
     o, _ = api._options_from(params, method, tol_scale)
     return {"integrator": integrator, "propagator": bool(propagate), "order": int(o.order), "atol": float(o.atol),
             "rtol": float(o.rtol), "qsb_version": int(engine.load_library().qsb_version())}

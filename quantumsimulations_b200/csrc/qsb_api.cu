@@ -10,6 +10,8 @@
 #include <string>
 #include <vector>
 
+#include <cublas_v2.h>
+
 #include "qsb_large.cuh"
 #include "qsb_small.cuh"
 

@@ -2,7 +2,10 @@
 
 static int upload_state(qsb_plan* p, cplx* dst, uint64_t psi0_index, const double* psi0_host) {
   const uint64_t dim = 1ull << p->n_loc, udim = p->world > 1 ? dim : (1ull << p->n);
-  if (!psi0_host) {
+  if (!psi0_host && p->identity_bits) {  // the propagator build: all basis states at once (qsb_propagate_hbm)
+    launch_set_identity(dst, p->identity_bits, p->stream);
+    QSB_CUDA(cudaGetLastError());
+  } else if (!psi0_host) {
     if (psi0_index >> p->n) return fail(QSB_ERR_BAD_ARG, "psi0_index out of range");
     // sharded: only the owner of the index sets a 1 (local index); everybody else zero-fills
     uint64_t local = psi0_index;
@@ -287,3 +290,5 @@ int qsb_apply_h_static(qsb_plan* p, const double* psi_host, double* out_host) {
 }
 
 }  // extern "C"
+
+#include "qsb_api_prophbm.inl"

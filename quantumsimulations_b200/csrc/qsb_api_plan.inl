@@ -24,6 +24,7 @@ struct qsb_plan {
   double* d_red = nullptr;      // [PSTRIDE] reduced sums
   double* h_red = nullptr;      // pinned mirror
   Session* ses = nullptr;
+  int identity_bits = 0;        // > 0: a session's default initial state is the 2^bits x 2^bits identity (qsb_propagate_hbm)
   void* dense_buf = nullptr;    // `order` vectors of kept Taylor terms (dense output, qsb_evolve); grown on demand
   size_t dense_bytes = 0;
   StridedFusion fu;             // L2-resident fusion of the strided passes (unsharded plans); fu.ctrl is owned here

@@ -202,6 +202,14 @@ struct DenseSpec {
   int n;
 };
 void launch_dense_eval(const DenseSpec& d, uint64_t dim, cudaStream_t stream);
+// ---- HBM-resident propagator (11 <= n <= 13 qubits; qsb_propagate_hbm) -------------------------------------------------
+// psi[col * 2^n + row] = (row == col): the identity as 2^n basis-state columns, i.e. the start of the integration that
+// yields ALL columns of exp(-i H t) in one go (a 2n-qubit plan whose upper n bits are decoupled spectators).
+void launch_set_identity(cplx* psi, int n, cudaStream_t stream);
+// Observables of n_cols states of 2^n amplitudes stored as columns (x[col * 2^n + row]); column c is the state at output
+// index o = c * seg_len + k and is skipped when o >= n_out.  out: [n_out][QSB_NOBS], or [QSB_NOBS][n_out] (by_column).
+void launch_observe_columns(const cplx* x, int n, int n_cols, int64_t seg_len, int64_t k, int64_t n_out, uint64_t sea_mask,
+                            uint64_t rare_mask, double* out, int by_column, cudaStream_t stream);
 size_t happly_smem_bytes();
 
 // Per-kernel-class CUDA-event timing (bench.py's roofline leg).  Classes: 0 pass_first, 1 pass_mid, 2 pass_centre,

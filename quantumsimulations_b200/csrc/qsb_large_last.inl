@@ -206,6 +206,49 @@ dense_eval_kernel(DenseSpec d, uint64_t dim) {
   }
 }
 
+__global__ void set_identity_kernel(cplx* psi, int n) {
+  const uint64_t dim2 = 1ull << (2 * n), stride = (uint64_t)gridDim.x * blockDim.x, mask = (1ull << n) - 1;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < dim2; i += stride)
+    psi[i] = mk((i & mask) == (i >> n) ? 1.0 : 0.0, 0.0);
+}
+
+// One CTA per column: the eight numbers qsb_evolve reports for a state (same sums as small_observe / warp_observe),
+// reduced in a fixed order.
+__global__ void __launch_bounds__(256)
+observe_columns_kernel(const cplx* __restrict__ x, int n, int64_t seg_len, int64_t k, int64_t n_out, uint64_t sea_mask,
+                       uint64_t rare_mask, double* __restrict__ out, int by_column) {
+  __shared__ double red[7 * 32 + 7];
+  const int64_t o = (int64_t)blockIdx.x * seg_len + k;
+  if (o >= n_out) return;  // uniform per CTA
+  const uint32_t dim = 1u << n;
+  const cplx* v = x + ((size_t)blockIdx.x << n);
+  const int n_sea = __popcll(sea_mask);
+  double s[7] = {0, 0, 0, 0, 0, 0, 0};  // nrm2, zsea, zrare, csea.re, csea.im, crare.re, crare.im
+  for (uint32_t i = threadIdx.x; i < dim; i += blockDim.x) {
+    const cplx me = v[i];
+    const double p = norm2(me);
+    s[0] += p;
+    s[1] = fma(p, (double)(n_sea - 2 * __popcll((uint64_t)i & sea_mask)), s[1]);
+    s[2] += ((uint64_t)i & rare_mask) ? -p : p;
+    for (int b = 0; b < n; ++b) {
+      const uint32_t m = 1u << b;
+      if (i & m) continue;
+      const bool is_sea = sea_mask >> b & 1, is_rare = rare_mask >> b & 1;
+      if (!is_sea && !is_rare) continue;
+      const cplx u = v[i | m];  // conj(me) * u
+      const double re = fma(me.x, u.x, me.y * u.y), im = fma(me.x, u.y, -me.y * u.x);
+      if (is_sea) { s[3] += re; s[4] += im; }
+      if (is_rare) { s[5] += re; s[6] += im; }
+    }
+  }
+  block_reduce<7>(s, red);
+  if (threadIdx.x == 0) {
+    const double inv = 1.0 / s[0];
+    const double val[QSB_NOBS] = {s[3] * inv, s[4] * inv, 0.5 * s[1] * inv, 0.5 * s[2] * inv, s[5] * inv, s[6] * inv, 1.0, sqrt(s[0])};
+    for (int j = 0; j < QSB_NOBS; ++j) out[by_column ? (size_t)j * n_out + o : (size_t)o * QSB_NOBS + j] = val[j];
+  }
+}
+
 __global__ void set_basis_kernel(cplx* psi, uint64_t dim, uint64_t index) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -699,6 +742,15 @@ void launch_gather_rows(const cplx* src, const uint64_t* d_rows, int64_t n_rows,
 void launch_dense_eval(const DenseSpec& d, uint64_t dim, cudaStream_t stream) {
   const int blocks = (int)std::min<uint64_t>((dim + 255) / 256, 148 * 8);
   dense_eval_kernel<<<blocks, 256, 0, stream>>>(d, dim);
+}
+
+void launch_set_identity(cplx* psi, int n, cudaStream_t stream) {
+  set_identity_kernel<<<148 * 8, 256, 0, stream>>>(psi, n);
+}
+
+void launch_observe_columns(const cplx* x, int n, int n_cols, int64_t seg_len, int64_t k, int64_t n_out, uint64_t sea_mask,
+                            uint64_t rare_mask, double* out, int by_column, cudaStream_t stream) {
+  observe_columns_kernel<<<n_cols, 256, 0, stream>>>(x, n, seg_len, k, n_out, sea_mask, rare_mask, out, by_column);
 }
 
 void launch_set_basis_state(cplx* psi, uint64_t dim, uint64_t index, cudaStream_t stream) {

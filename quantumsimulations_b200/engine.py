@@ -20,6 +20,7 @@ LIB_PATH = os.path.join(_PKG, "libqsb200.so")
 NOBS = 8
 OBS_COLUMNS = ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R", "state_norm", "raw_norm")
 SMALL_MAX_QUBITS = 10
+HBM_PROPAGATOR_MAX_QUBITS = 13
 METHOD_DP5, METHOD_TAYLOR = 0, 1
 _METHODS = {"dp5": METHOD_DP5, "taylor": METHOD_TAYLOR}
 
@@ -61,7 +62,7 @@ EXPORTS = (
     "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_shard_set_stream_barrier", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather", "qsb_local_stream_barrier",
-    "qsb_propagate_batch", "qsb_release_caches", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
+    "qsb_propagate_batch", "qsb_propagate_hbm", "qsb_release_caches", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
 )
 
 SHARD_BLOB_BYTES = 96
@@ -97,6 +98,8 @@ def load_library() -> C.CDLL:
                                      C.POINTER(_Opts), dp, C.POINTER(_Stats), C.c_int]
     lib.qsb_propagate_batch.argtypes = [C.c_int32, C.POINTER(_Table), C.POINTER(C.c_uint64), C.c_int64, dp, C.c_int32,
                                         C.POINTER(_Opts), C.c_int32, C.c_int32, dp, C.POINTER(_Stats), C.c_int]
+    lib.qsb_propagate_hbm.argtypes = [C.POINTER(_Table), C.c_uint64, C.c_int64, C.c_double, C.POINTER(_Opts), C.c_int32,
+                                      C.c_int32, dp, C.POINTER(_Stats), C.c_int]
     lib.qsb_build_propagator.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(_Opts), C.c_int32, dp,
                                          C.POINTER(_Stats), C.c_int]
     lib.qsb_debug_squarings.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(C.c_int32)]
@@ -491,6 +494,20 @@ def propagate_batch(tables: Sequence[SpinTable], n_out: int, dt, opts: Sequence[
     stats = [Stats.from_c(s) for s in cstats]
     _check(code)
     return obs, stats
+
+
+def propagate_hbm(table: SpinTable, n_out: int, dt: float, opts: SolverOptions, device: int = 0,
+                  max_squarings: Optional[int] = None, by_column: bool = False):
+    """Constant-H propagator path for ONE trajectory of 11 <= n <= 13 qubits, U resident in HBM (qsb_propagate_hbm):
+    output k = state after k dt.  Returns (obs [n_out, NOBS] or [NOBS, n_out] with ``by_column``, Stats)."""
+    lib = load_library()
+    holder = _TableHolder(table)
+    copts = opts.to_c()
+    st = _Stats()
+    obs = np.empty((NOBS, int(n_out)) if by_column else (int(n_out), NOBS), dtype=np.float64)
+    _check(lib.qsb_propagate_hbm(C.byref(holder.c), table.psi0_index, int(n_out), float(dt), C.byref(copts),
+                                 _max_squarings(max_squarings), 1 if by_column else 0, _dptr(obs), C.byref(st), int(device)))
+    return obs, Stats.from_c(st)
 
 
 def build_propagator(table: SpinTable, dt: float, opts: SolverOptions, device: int = 0,

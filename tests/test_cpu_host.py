@@ -251,6 +251,25 @@ def test_unchanged_reference_sweep_script_runs_on_the_dropin(tmp_path):
             assert got[k] == pytest.approx(want[k], rel=1e-6, abs=1e-12), k
 
 
+def test_auto_method_picks_the_cheaper_path_by_size():
+    """"auto": on-chip propagator for N <= 10 when there are more output intervals than basis states; for 11 <= N <= 13
+    the HBM-resident propagator only where the ||H|| t_final bound says stepping is the expensive way (the sweep's
+    parameters), not for the cheap dataclass-default trajectory; stepping beyond."""
+    import dataclasses
+
+    from bench import sweep_params
+    from quantumsimulations_b200 import DipolarRareParams, api
+
+    assert api.resolve_method(sweep_params(6, 50e3, t_final=30.0, steps=20000), None) == ("taylor", True)
+    assert api.resolve_method(sweep_params(6, 50e3, t_final=1e-3, steps=50), None) == ("taylor", False)
+    assert api.resolve_method(DipolarRareParams(is_spin_three_half=False), None) == ("taylor", False)          # N = 13, cheap
+    assert api.resolve_method(sweep_params(12, 50e3, t_final=30.0, steps=20000), None) == ("taylor", True)     # N = 13, sweep
+    assert api.resolve_method(sweep_params(10, 50e3, t_final=30.0, steps=20000), None) == ("taylor", True)     # N = 11
+    assert api.resolve_method(sweep_params(13, 50e3, t_final=30.0, steps=20000), None) == ("taylor", False)    # N = 14
+    assert api.resolve_method(sweep_params(12, 50e3, t_final=30.0, steps=20000), "dp5") == ("dp5", False)
+    assert api.resolve_method(dataclasses.replace(sweep_params(12, 50e3), t_final=30.0, steps=20000), "propagator-dp5") == ("dp5", True)
+
+
 # ---- C ABI -------------------------------------------------------------------------------------------------------
 def test_library_exports_every_declared_symbol():
     from quantumsimulations_b200 import engine
@@ -627,10 +646,10 @@ def test_propagate_kernel_launch_shapes():
 def test_propagator_needs_small_n_and_no_device_fails_loudly():
     from quantumsimulations_b200 import DipolarRareParams, engine, simulate_rare, simulate_rare_batch
 
-    big = DipolarRareParams(n_sea=12, is_spin_three_half=False)
-    with pytest.raises(ValueError, match="N <= 10"):
+    big = DipolarRareParams(n_sea=13, is_spin_three_half=False)      # N = 14: beyond the HBM-resident propagator too
+    with pytest.raises(ValueError, match="N <= 13"):
         simulate_rare(big, method="propagator")
-    with pytest.raises(ValueError, match="N <= 10"):
+    with pytest.raises(ValueError, match="N <= 13"):
         simulate_rare_batch([big], method="propagator")
     if engine.device_count() == 0:
         with pytest.raises(engine.EngineError, match="no CUDA device"):

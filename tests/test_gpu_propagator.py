@@ -253,3 +253,35 @@ def test_time_split_chain_matches_unsplit(n, monkeypatch):
         assert np.max(np.abs(other - whole)) < 1e-10
     want = exact_traces(tables[0], dt * np.arange(n_out))
     assert max(float(np.max(np.abs(a[0][:, j] - want[k]))) for j, k in enumerate(KEYS)) < 1e-8
+
+
+@pytest.mark.parametrize("n_sea,steps,variant", [(10, 600, "center_on"), (10, 40, "shell_off"), (11, 300, "center_on")])
+def test_hbm_resident_propagator_matches_exact(n_sea, steps, variant):
+    """11 <= N <= 13: U = exp(-i H dt) resident in HBM (qsb_propagate_hbm): all columns integrated at once by the tiled
+    path, cuBLAS squarings and chain.  Traces against exact diagonalisation (<= 1e-6), time-split (>= 256 outputs) and
+    single-segment chains, centre-rare and sea-centre variants; the raw norm stays at 1."""
+    from bench import sweep_params
+    from conftest import exact_traces
+    from quantumsimulations_b200 import compile_table, simulate_rare
+
+    p = sweep_params(n_sea, 50e3, variant, t_final=3.0e-2 * steps / 2000.0, steps=steps)
+    t, out, st = simulate_rare(p, method="propagator", return_stats=True, raw_norm=True)
+    assert st.path == 3 and st.n_rhs > 0
+    want = exact_traces(compile_table(p), t)
+    for k in ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R"):
+        assert np.max(np.abs(out[k] - want[k])) < 1e-6, k
+    assert np.max(np.abs(out["raw_norm"] - 1.0)) < 1e-7
+    assert np.max(np.abs(out["state_norm"] - 1.0)) < 1e-12
+
+
+def test_hbm_propagator_agrees_with_stepping_n13():
+    """N = 13 (the reference sweep function's default n_sea = 12): a short window both ways."""
+    from bench import sweep_params
+    from quantumsimulations_b200 import simulate_rare
+
+    p = sweep_params(12, 50e3, t_final=3.0e-4, steps=21)
+    _, a, sa = simulate_rare(p, method="propagator", return_stats=True)
+    _, b, sb = simulate_rare(p, method="taylor", return_stats=True)
+    assert sa.path == 3 and sb.path == 1
+    for k in ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R"):
+        assert np.max(np.abs(a[k] - b[k])) < 1e-7, k
