@@ -292,6 +292,27 @@ def c1_leg(device, with_cpu):
                                        "h_applies_per_s": s13s.n_rhs / w13s},
         "dp5": {"wall_s": w13d, "steps": s13d.n_accepted + s13d.n_rejected, "h_applies": s13d.n_rhs,
                 "steps_per_s": (s13d.n_accepted + s13d.n_rejected) / w13d}}
+    # the sweep's parameters at the reference sweep FUNCTION's default size, n_sea = 12 (SW:356-376), full length:
+    # "auto" takes the HBM-resident propagator there (stepping is ~10^9 H-applies)
+    p13s = sweep_params(12, 50e3, t_final=30.0, steps=20000)
+    t0 = time.perf_counter()
+    _, o13s, s13p = simulate_rare(p13s, device=device, return_stats=True, raw_norm=True)
+    w13p = time.perf_counter() - t0
+    p13w = sweep_params(12, 50e3, t_final=3.0e-4, steps=3)
+    t0 = time.perf_counter()
+    _, _, s13w = simulate_rare(p13w, device=device, method="taylor", return_stats=True)
+    w13w = time.perf_counter() - t0
+    out["n13_sweep_point_full_size"] = {
+        "workload": "N=13 (n_sea=12, the default of run_sweep_sea_detuning), delta=50 kHz, rare ON, t_final=30 s, 20000 outputs, "
+                    "atol 1e-10 / rtol 1e-9",
+        "method": "auto -> HBM-resident propagator (qsb_propagate_hbm): 2^13 columns integrated at once as a 26-qubit "
+                  "tiled-path state, cuBLAS Zgemm squarings + time-split chain; not an ODE step rate",
+        "wall_s": w13p, "kernel_ms": s13p.device_ms, "path": s13p.path, "column_h_applies": s13p.n_rhs,
+        "max_raw_norm_deviation": float(np.max(np.abs(o13s["raw_norm"] - 1.0))),
+        "stepped_3e-4s_window": {"wall_s": w13w, "steps": s13w.n_accepted + s13w.n_rejected, "h_applies": s13w.n_rhs,
+                                 "steps_per_s": (s13w.n_accepted + s13w.n_rejected) / w13w,
+                                 "extrapolated_full_trajectory_s": w13w * 30.0 / 3.0e-4}}
+    del o13s
     if with_cpu:
         table = compile_table(p13)
         bm = table.bit_major()
