@@ -27,7 +27,7 @@ extern "C" {
 #define QSB_VERSION 100
 #define QSB_MAX_QUBITS 34
 #define QSB_SMALL_MAX_QUBITS 10 /* whole trajectory on-chip (one CTA) up to here */
-#define QSB_HBM_PROPAGATOR_MAX_QUBITS 13 /* dense propagator resident in HBM up to here (1 GB at 13) */
+#define QSB_HBM_PROPAGATOR_MAX_QUBITS 14 /* dense propagator resident in HBM up to here (1 GB at 13, 4 GB at 14) */
 #define QSB_NOBS 8
 #define QSB_MAX_TAYLOR_ORDER 30
 
@@ -136,7 +136,7 @@ int qsb_propagate_batch(int32_t n_traj, const qsb_table* tables, const uint64_t*
                         const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
                         int32_t obs_by_column, double* out_obs, qsb_stats* stats, int device);
 /* The same constant-H propagator path one size class up, QSB_SMALL_MAX_QUBITS < n <= QSB_HBM_PROPAGATOR_MAX_QUBITS, ONE
- * trajectory per call, U = exp(-i H dt) resident in HBM (1 GB at n = 13).  The reference's sweep function defaults to
+ * trajectory per call, U = exp(-i H dt) resident in HBM (1 GB at n = 13, 4 GB at 14).  The reference's sweep function defaults to
  * n_sea = 12, i.e. n = 13 (sweep_sea_detuning.py:356-376), where a full-size trajectory (30 s, 20000 outputs, ||H|| dt ~
  * 10^3) is hours of stepping.  All 2^n columns are integrated at once over dt / 2^s by the tiled path's adaptive
  * integrator (the matrix is the state of a 2n-qubit plan whose upper n bits are decoupled; opts as in

@@ -121,7 +121,7 @@ PROPAGATOR = "propagator"
 PROPAGATOR_TOL_SCALE = {"taylor": 1e-5, "dp5": 1.0}
 
 
-# "auto" for 11 <= N <= 13: the HBM-resident propagator (engine.propagate_hbm) costs a few seconds per trajectory
+# "auto" for 11 <= N <= 14: the HBM-resident propagator (engine.propagate_hbm) costs a few seconds per trajectory
 # whatever the trajectory; stepping costs ~3 H-applies per unit of ||H|| t at ~25 us each at these sizes.  The
 # propagator is picked when the cheap bound ||H|| t_final (SpinTable.spectral_bound) says stepping would take longer.
 AUTO_HBM_NORM_T = 2.0e5
@@ -130,7 +130,7 @@ AUTO_HBM_NORM_T = 2.0e5
 def split_method(method: Optional[str], n_qubits: Optional[int] = None, steps: Optional[int] = None,
                  norm_t: Optional[float] = None) -> Tuple[str, bool]:
     """(integrator, use_propagator) from a method string: "auto", "taylor", "dp5", "propagator", "propagator-dp5".
-    "auto" needs the trajectory's size (``n_qubits``, ``steps``; for 11 <= N <= 13 also ``norm_t`` = bound on
+    "auto" needs the trajectory's size (``n_qubits``, ``steps``; for 11 <= N <= 14 also ``norm_t`` = bound on
     ||H|| t_final) to choose; without it, it means stepping."""
     m = method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)
     if m == "auto":
@@ -248,7 +248,7 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
 
 def _propagate(tables, grids, opts, device):
     """Propagator path for trajectories of equal N and equal number of outputs (their dt may differ): the on-chip one
-    (N <= 10, one batched call) or the HBM-resident one (11 <= N <= 13, one call per trajectory)."""
+    (N <= 10, one batched call) or the HBM-resident one (11 <= N <= 14, one call per trajectory)."""
     if tables[0].n > engine.HBM_PROPAGATOR_MAX_QUBITS:
         raise ValueError(f"method 'propagator' holds a dense 2^N x 2^N matrix: N <= {engine.HBM_PROPAGATOR_MAX_QUBITS}")
     seen: Dict[Tuple[float, float, int], Optional[float]] = {}   # sweeps share one grid: check each distinct one once
@@ -268,7 +268,7 @@ def _propagate(tables, grids, opts, device):
 
 def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int = 0, method: Optional[str] = None,
                         tol_scale: Optional[float] = None, raw_norm: bool = False):
-    """Independent trajectories; those with N <= 10 share ONE kernel launch (one CTA each), 11 <= N <= 13 on a uniform
+    """Independent trajectories; those with N <= 10 share ONE kernel launch (one CTA each), 11 <= N <= 14 on a uniform
     grid may go through the HBM-resident propagator (``resolve_method``), the rest is stepped on the tiled path."""
     n = len(params_list)
     results: List = [None] * n
@@ -300,7 +300,7 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
             results[i] = (grids[i].copy(), _pack(obs[j], om[i][1], raw_norm, by_column=prop))
             stats_out[i] = stats[j]
     for i in range(n):
-        if results[i] is None and props[i]:     # 11 <= N <= 13: the HBM-resident propagator, one trajectory per call
+        if results[i] is None and props[i]:     # 11 <= N <= 14: the HBM-resident propagator, one trajectory per call
             obs, st = _propagate([tables[i]], [grids[i]], [om[i][0]], device)
             results[i] = (grids[i].copy(), _pack(obs[0], om[i][1], raw_norm, by_column=True))
             stats_out[i] = st[0]

@@ -1,4 +1,4 @@
-// HBM-resident constant-H propagator for 11 <= n <= 13 qubits (qsb_propagate_hbm); included from qsb_api_entry.inl.
+// HBM-resident constant-H propagator for 11 <= n <= 14 qubits (qsb_propagate_hbm); included from qsb_api_entry.inl.
 //
 // Same idea as the on-chip propagator path (qsb_propagate_batch) one size class up.  U = exp(-i H dt) no longer fits an
 // SM (1 GB at n = 13), but it fits HBM comfortably, and the pieces are already there:

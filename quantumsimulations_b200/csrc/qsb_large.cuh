@@ -202,7 +202,7 @@ struct DenseSpec {
   int n;
 };
 void launch_dense_eval(const DenseSpec& d, uint64_t dim, cudaStream_t stream);
-// ---- HBM-resident propagator (11 <= n <= 13 qubits; qsb_propagate_hbm) -------------------------------------------------
+// ---- HBM-resident propagator (11 <= n <= 14 qubits; qsb_propagate_hbm) -------------------------------------------------
 // psi[col * 2^n + row] = (row == col): the identity as 2^n basis-state columns, i.e. the start of the integration that
 // yields ALL columns of exp(-i H t) in one go (a 2n-qubit plan whose upper n bits are decoupled spectators).
 void launch_set_identity(cplx* psi, int n, cudaStream_t stream);

@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_PKG, "libqsb200.so")
 NOBS = 8
 OBS_COLUMNS = ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R", "state_norm", "raw_norm")
 SMALL_MAX_QUBITS = 10
-HBM_PROPAGATOR_MAX_QUBITS = 13
+HBM_PROPAGATOR_MAX_QUBITS = 14
 METHOD_DP5, METHOD_TAYLOR = 0, 1
 _METHODS = {"dp5": METHOD_DP5, "taylor": METHOD_TAYLOR}
 
@@ -498,7 +498,7 @@ def propagate_batch(tables: Sequence[SpinTable], n_out: int, dt, opts: Sequence[
 
 def propagate_hbm(table: SpinTable, n_out: int, dt: float, opts: SolverOptions, device: int = 0,
                   max_squarings: Optional[int] = None, by_column: bool = False):
-    """Constant-H propagator path for ONE trajectory of 11 <= n <= 13 qubits, U resident in HBM (qsb_propagate_hbm):
+    """Constant-H propagator path for ONE trajectory of 11 <= n <= 14 qubits, U resident in HBM (qsb_propagate_hbm):
     output k = state after k dt.  Returns (obs [n_out, NOBS] or [NOBS, n_out] with ``by_column``, Stats)."""
     lib = load_library()
     holder = _TableHolder(table)

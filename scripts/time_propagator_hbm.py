@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Wall / device time of the HBM-resident propagator path (11 <= N <= 13) on full-size sweep trajectories
+"""Wall / device time of the HBM-resident propagator path (11 <= N <= 14) on full-size sweep trajectories
 (t_final = 30 s, 20000 outputs, the sweep's tolerances), next to the stepped Taylor path on a short window of the same
 trajectory (extrapolated to the full length).
 

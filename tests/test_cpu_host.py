@@ -265,7 +265,8 @@ def test_auto_method_picks_the_cheaper_path_by_size():
     assert api.resolve_method(DipolarRareParams(is_spin_three_half=False), None) == ("taylor", False)          # N = 13, cheap
     assert api.resolve_method(sweep_params(12, 50e3, t_final=30.0, steps=20000), None) == ("taylor", True)     # N = 13, sweep
     assert api.resolve_method(sweep_params(10, 50e3, t_final=30.0, steps=20000), None) == ("taylor", True)     # N = 11
-    assert api.resolve_method(sweep_params(13, 50e3, t_final=30.0, steps=20000), None) == ("taylor", False)    # N = 14
+    assert api.resolve_method(sweep_params(13, 50e3, t_final=30.0, steps=20000), None) == ("taylor", True)     # N = 14
+    assert api.resolve_method(sweep_params(14, 50e3, t_final=30.0, steps=20000), None) == ("taylor", False)    # N = 15
     assert api.resolve_method(sweep_params(12, 50e3, t_final=30.0, steps=20000), "dp5") == ("dp5", False)
     assert api.resolve_method(dataclasses.replace(sweep_params(12, 50e3), t_final=30.0, steps=20000), "propagator-dp5") == ("dp5", True)
 
@@ -646,10 +647,10 @@ def test_propagate_kernel_launch_shapes():
 def test_propagator_needs_small_n_and_no_device_fails_loudly():
     from quantumsimulations_b200 import DipolarRareParams, engine, simulate_rare, simulate_rare_batch
 
-    big = DipolarRareParams(n_sea=13, is_spin_three_half=False)      # N = 14: beyond the HBM-resident propagator too
-    with pytest.raises(ValueError, match="N <= 13"):
+    big = DipolarRareParams(n_sea=14, is_spin_three_half=False)      # N = 15: beyond the HBM-resident propagator too
+    with pytest.raises(ValueError, match="N <= 14"):
         simulate_rare(big, method="propagator")
-    with pytest.raises(ValueError, match="N <= 13"):
+    with pytest.raises(ValueError, match="N <= 14"):
         simulate_rare_batch([big], method="propagator")
     if engine.device_count() == 0:
         with pytest.raises(engine.EngineError, match="no CUDA device"):

@@ -257,7 +257,7 @@ def test_time_split_chain_matches_unsplit(n, monkeypatch):
 
 @pytest.mark.parametrize("n_sea,steps,variant", [(10, 600, "center_on"), (10, 40, "shell_off"), (11, 300, "center_on")])
 def test_hbm_resident_propagator_matches_exact(n_sea, steps, variant):
-    """11 <= N <= 13: U = exp(-i H dt) resident in HBM (qsb_propagate_hbm): all columns integrated at once by the tiled
+    """11 <= N <= 14: U = exp(-i H dt) resident in HBM (qsb_propagate_hbm): all columns integrated at once by the tiled
     path, cuBLAS squarings and chain.  Traces against exact diagonalisation (<= 1e-6), time-split (>= 256 outputs) and
     single-segment chains, centre-rare and sea-centre variants; the raw norm stays at 1."""
     from bench import sweep_params
@@ -274,12 +274,13 @@ def test_hbm_resident_propagator_matches_exact(n_sea, steps, variant):
     assert np.max(np.abs(out["state_norm"] - 1.0)) < 1e-12
 
 
-def test_hbm_propagator_agrees_with_stepping_n13():
-    """N = 13 (the reference sweep function's default n_sea = 12): a short window both ways."""
+@pytest.mark.parametrize("n_sea", [12, 13])
+def test_hbm_propagator_agrees_with_stepping_n13_n14(n_sea):
+    """N = 13 (the reference sweep function's default n_sea = 12) and N = 14 (the path's limit): a short window both ways."""
     from bench import sweep_params
     from quantumsimulations_b200 import simulate_rare
 
-    p = sweep_params(12, 50e3, t_final=3.0e-4, steps=21)
+    p = sweep_params(n_sea, 50e3, t_final=3.0e-4, steps=21)
     _, a, sa = simulate_rare(p, method="propagator", return_stats=True)
     _, b, sb = simulate_rare(p, method="taylor", return_stats=True)
     assert sa.path == 3 and sb.path == 1
