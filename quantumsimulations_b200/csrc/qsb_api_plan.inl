@@ -383,7 +383,7 @@ static PropCtx& prop_ctx(int device) {
 // First touch of a large pageable host buffer costs ~0.35 s per GB on one thread (page faults); done here by a few
 // threads WHILE the kernels that will fill it are running, it costs nothing.
 static void prefault_async(std::vector<std::thread>& pool, void* ptr, size_t bytes) {
-  if (bytes < ((size_t)64 << 20)) return;
+  if (bytes < ((size_t)8 << 20)) return;
   unsigned nt = std::min(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
   const size_t page = 4096, per = ((bytes / nt) + page - 1) & ~(page - 1);
   for (unsigned t = 0; t < nt; ++t) {
