@@ -455,8 +455,9 @@ def run_b200(args, rank, world, local_rank):
                                (f", tag {prof.get('tag')}" if prof and prof.get("tag") else "") +
                                "), not re-measured in this run") if prof else None,
             "peak_source": how,
-            "kernel": "one DP5 step attempt = 6 H-applies (pass_first[+stage combination]/mid/centre/mid/last), the embedded "
-                      "error estimate folded into the last stage's pass_first / pass_last",
+            "kernel": "one DP5 step attempt = 6 H-applies (pass_first[+stage combination]/mid/centre/mid/last; stages 1-4 "
+                      "end in pass_last_first, which also begins the next stage), the embedded error estimate folded "
+                      "into the last stage's pass_first / pass_last",
             "algorithmic_bytes_per_step": alg_bytes_step, "moved_bytes_per_step": moved_per_step,
             "moved_GBps": moved_per_step * args.steps / (ms / 1e3) / 1e9,
             "moved_frac_of_peak": moved_per_step * args.steps / (ms / 1e3) / 1e9 / peak,
@@ -579,7 +580,8 @@ def run_b200(args, rank, world, local_rank):
         sharded = sharded_leg(args, rank, world, local_rank, barrier, allmax)
 
     if rank == 0:
-        launches_per_step = n_rhs * kernels_per_apply(n) + 1 if args.method == "dp5" else n_rhs * kernels_per_apply(n) + 2
+        # launches of one step attempt, counted in the profiled pass (2 attempts) + the partial-sum reduction kernel
+        launches_per_step = sum(kcnt.values()) / 2.0 + 1
         cpu = cpu_port_step_rate(n_sea, 50e3) if world == 1 and not args.no_cpu else None
         zv = cpu_zvode_rate() if world == 1 and not args.no_cpu else None
         zv_all = cpu_zvode_sweep_all_cores() if world == 1 and not args.no_cpu else None

@@ -259,9 +259,9 @@ int qsb_local_stream_barrier(void* member_ctx, void* stream);
 /* Benchmark aid: when enabled, every launch of the tiled path is bracketed by CUDA events on its stream (this
  * serialises host and device; never enable it inside a timed throughput run).  Classes: 0 pass_first, 1 pass_mid,
  * 2 pass_centre, 3 pass_last, 4 pass_first with a fused stage combination, 5 error_sums, 6 strided_fused (mid .. centre
- * .. mid as one L2-resident persistent launch).  ms / count / bytes: summed
+ * .. mid as one L2-resident persistent launch), 7 pass_last_first (a DP5 stage's pass_last fused with the next stage's pass_first).  ms / count / bytes: summed
  * milliseconds, launches and bytes moved by design (vectors read + written) per class since the last enable.        */
-#define QSB_N_PROFILE 7
+#define QSB_N_PROFILE 8
 int qsb_profile(int enable);
 int qsb_profile_read(double* ms, int64_t* count, double* bytes, int32_t n);
 

@@ -123,12 +123,23 @@ static bool dp5_error_sweep() {  // A/B knob: the embedded error estimate as its
 static int attempt_dp5(qsb_plan* p, Session* s, double hu, double* err, double* cand_sums) {
   static const DP5 T = dp5_tableau();
   const bool sweep = dp5_error_sweep();
-  for (int st = 0; st <= 5; ++st) {  // apply #st: src = ys = y + hu sum_j a[st][j] k_j, produces k_{st+1} (0-based k[st+1])
+  // Stages 0 .. 3 end in pass_last_first: the kernel that finishes apply #st also forms the input of apply #st + 1 from
+  // the k it has just produced (still in registers) and the older stage vectors, and starts its transform; the next
+  // apply then skips its pass_first.  (QSB200_DP5_FUSE=0: every stage is pass_first .. pass_last, the round-1 form.)
+  static const bool fuse_stages = [] { const char* e = getenv("QSB200_DP5_FUSE"); return !(e && *e == '0'); }();
+  auto combination = [&](int st, bool skip_fresh) {  // y + hu sum_j a[st][j] k_j, optionally without the newest k
     Combine cb = {};
     cb.vin[0] = s->y; cb.c[0] = 1.0; cb.e[0] = 0.0; cb.n_in = 1;
-    for (int j = 0; j <= st; ++j)
+    for (int j = 0; j <= st; ++j) {
+      if (skip_fresh && j == st) continue;
       if (T.a[st][j] != 0.0) { cb.vin[cb.n_in] = s->k[j]; cb.c[cb.n_in] = hu * T.a[st][j]; cb.e[cb.n_in] = hu * T.e[j]; ++cb.n_in; }
+    }
     cb.out = s->ys;
+    return cb;
+  };
+  bool fused_in = false;  // the previous apply's last kernel has already begun this one
+  for (int st = 0; st <= 5; ++st) {  // apply #st: src = ys = y + hu sum_j a[st][j] k_j, produces k_{st+1} (0-based k[st+1])
+    Combine cb = combination(st, false);
     Epilogue e = blank_epilogue(s);
     e.o1 = s->k[st + 1];
     if (st == 5 && !sweep) {
@@ -142,9 +153,17 @@ static int attempt_dp5(qsb_plan* p, Session* s, double hu, double* err, double* 
       e.n_in = 2;
       e.want_err = 1; e.ek = hu * T.e[6]; e.sc_i0 = 1; e.sc_i1 = -2;
     }
+    FuseNext fn = {};
+    const bool fuse_out = fuse_stages && st <= 3 && T.a[st + 1][st + 1] != 0.0;
+    if (fuse_out) {
+      fn.cb = combination(st + 1, true);
+      fn.c_fresh = hu * T.a[st + 1][st + 1];
+    }
     // the last apply acts on y_new (FSAL): its pass_first / pass_centre also collect y_new's observable sums
-    int rc = launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, st == 5 ? 1 : 0, s->partials, p->stream, link_of(p), &cb, &p->fu);
+    int rc = launch_happly(p->g, p->tab, s->ys, s->tx, s->ty, e, st == 5 ? 1 : 0, s->partials, p->stream, link_of(p), &cb, &p->fu,
+                           fuse_out ? &fn : nullptr, fused_in);
     if (rc) return rc;
+    fused_in = fuse_out;
   }
   if (sweep) {
     ErrSpec es = {};

@@ -176,9 +176,17 @@ int centre_window(const Layout& L);
 // link: null when unsharded.  Returns a qsb_status (only the rank barrier can fail).
 // comb: optional stage combination; when comb->n_in > 0 the apply acts on sum_q c_q vin_q, which is also written
 // to comb->out, and `src` must equal comb->out.  Epilogues take at most 2 input vectors.
+// next: when given, the apply ends in pass_last_first instead of pass_last - it writes k = -i H v to ep.o1 AND begins
+// the next apply (forms next->cb + c_fresh k into next->cb.out, which must be `src`, and its tX / tY); the next call
+// then passes skip_first.  Plain k-producing epilogues only (no o2, no error sums, alpha = 1).
+struct FuseNext {
+  Combine cb;      // the next stage's combination WITHOUT the fresh k
+  double c_fresh;  // weight of the fresh k in it
+};
 int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
                   const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream,
-                  ShardLink* link = nullptr, const Combine* comb = nullptr, StridedFusion* fu = nullptr);
+                  ShardLink* link = nullptr, const Combine* comb = nullptr, StridedFusion* fu = nullptr,
+                  const FuseNext* next = nullptr, bool skip_first = false);
 void launch_error_sums(const LargeGeom& g, const ErrSpec& es, double* partials, cudaStream_t stream);
 // Observables only (pass_first + mids + pass_centre), filling partial slots 0..6.
 int launch_observe(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
@@ -213,9 +221,9 @@ void launch_observe_columns(const cplx* x, int n, int n_cols, int64_t seg_len, i
 size_t happly_smem_bytes();
 
 // Per-kernel-class CUDA-event timing (bench.py's roofline leg).  Classes: 0 pass_first, 1 pass_mid, 2 pass_centre,
-// 3 pass_last, 4 pass_first with a fused stage combination, 5 error_sums, 6 the fused strided passes.  bytes = what the launch moves by design
+// 3 pass_last, 4 pass_first with a fused stage combination, 5 error_sums, 6 the fused strided passes, 7 pass_last_first.  bytes = what the launch moves by design
 // (vectors read + written, in bytes), so ms and bytes of a class give its achieved GB/s.
-constexpr int N_PROFILE = 7;
+constexpr int N_PROFILE = 8;
 struct Profile {
   bool on = false;
   double ms[N_PROFILE] = {};

@@ -158,6 +158,103 @@ pass_last(PassArgs a, const cplx* src, const cplx* __restrict__ tx, const cplx* 
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// pass_last_first: pass_last of one DP5 stage fused with pass_first<COMB> of the NEXT stage.  Both work on the same
+// layout-0 tile, so the fresh k never leaves the registers between them: the next stage's combination
+//     v' = sum_q c_q vin_q + c_fresh k        (vin: y and the OLDER stage vectors)
+// takes it from there instead of re-reading it (1 S less traffic per stage, one launch less), and v' replaces v in
+// `ys` - the same addresses this thread has just read for the Dz term.  tX / tY are rewritten in place, tile by tile,
+// with the mappings they were read with.  The arithmetic of the two halves is that of pass_last<0, 8, 0> and
+// pass_first<true>; only the order of the combination's summands differs (the fresh k first).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TPT, 2)
+pass_last_first(PassArgs a, cplx* ys, cplx* tx, cplx* ty, cplx* __restrict__ kout, Combine cb, double c_fresh) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  cplx* sm = reinterpret_cast<cplx*>(smem_raw);
+  const int tt = threadIdx.x;
+  const uint64_t base = (uint64_t)blockIdx.x << TB;
+  cplx r[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) r[j] = ty[base | (uint64_t)elem<8>(tt, j)];
+  {
+    const size_t off = (size_t)tt * 256;
+    const char* p = reinterpret_cast<const char*>(tx + base) + off;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128));
+    p = reinterpret_cast<const char*>(ys + base) + off;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 128));
+  }
+  bfly16<1>(r, 0xF);
+  smem_store16<8>(sm, tt, r);
+  __syncthreads();
+  smem_round<0, 1>(sm, tt, 0xF);
+  __syncthreads();
+  smem_load16<4>(sm, tt, r);
+  bfly16<1>(r, 0xF);
+  const int pv = __popcll(base | a.g.rank_bits);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) r[j] = mul_pi_pow(M_SCALE * r[j], pv) + tx[base | (uint64_t)elem<4>(tt, j)];
+  bfly16<0>(r, 0xF);
+  smem_store16<4>(sm, tt, r);
+  __syncthreads();
+  smem_round<0, 0>(sm, tt, 0xF);
+  __syncthreads();
+  smem_load16<8>(sm, tt, r);
+  bfly16<0>(r, 0xF);
+  const uint64_t idx0 = base | (uint64_t)tt;  // element j of this thread is idx0 + 256 j
+  {
+    TileDiag<8> td;
+    td.load(a.tab.Tz + (size_t)blockIdx.x * TD_STRIDE, a.tab.Iz, tt);
+#pragma unroll
+    for (int j0 = 0; j0 < 16; j0 += 8) {
+      cplx v[8];
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) v[jj] = ys[idx0 + 256u * (j0 + jj)];
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) r[j0 + jj] = mul_mi(td.at(a.tab.Wz, j0 + jj) * v[jj] + r[j0 + jj]);  // k = -i (Dz v + ..)
+#pragma unroll
+      for (int jj = 0; jj < 8; ++jj) kout[idx0 + 256u * (j0 + jj)] = r[j0 + jj];
+    }
+  }
+  // ---- the next stage's pass_first<COMB>, with k already in r ------------------------------------------------------
+#pragma unroll
+  for (int half = 0; half < 16; half += 8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r[half + j] = c_fresh * r[half + j];
+    for (int q = 0; q < cb.n_in; ++q) {
+      const cplx* vq = cb.vin[q];
+      const double cq = cb.c[q];
+      cplx w[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = vq[idx0 + 256u * (half + j)];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) axpy(r[half + j], cq, w[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ys[idx0 + 256u * (half + j)] = r[half + j];
+  }
+  bfly16<0>(r, 0xF);
+  __syncthreads();  // every thread is past its smem_load16<8> above before the tile buffer is written again
+  smem_store16<8>(sm, tt, r);
+  __syncthreads();
+  smem_round<0, 0>(sm, tt, 0xF);
+  __syncthreads();
+  smem_load16<4>(sm, tt, r);
+  bfly16<0>(r, 0xF);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) tx[base | (uint64_t)elem<4>(tt, j)] = r[j];
+  bfly16<2>(r, 0xF);
+  smem_store16<4>(sm, tt, r);
+  __syncthreads();
+  smem_round<0, 2>(sm, tt, 0xF);
+  __syncthreads();
+  smem_load16<8>(sm, tt, r);
+  bfly16<2>(r, 0xF);
+#pragma unroll
+  for (int j = 0; j < 16; ++j) ty[base | (uint64_t)elem<8>(tt, j)] = mul_mi_pow(M_SCALE * r[j], pv);
+}
+
 __global__ void reduce_partials_kernel(const double* __restrict__ partials, int64_t n_tiles, double* __restrict__ out8) {
   __shared__ double red[PSTRIDE * 32 + PSTRIDE];
   double s[PSTRIDE];
@@ -419,6 +516,7 @@ void prepare_device() {
   tile_kernel_attrs(pass_first<true>, sm);
   tile_kernel_attrs(pass_first<true, true>, sm);
   tile_kernel_attrs(pass_last<0, 8, 0>, sm);
+  tile_kernel_attrs(pass_last_first, sm);
   tile_kernel_attrs(pass_last<1, 4, 2>, sm);
   tile_kernel_attrs(pass_last<2, 4, 2>, sm);
   tile_kernel_attrs(pass_last<3, 4, 2>, sm);
@@ -670,7 +768,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
 
 int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cplx* tx, cplx* ty,
                   const Epilogue& ep, int collect_obs, double* partials, cudaStream_t stream, ShardLink* link,
-                  const Combine* comb, StridedFusion* fu) {
+                  const Combine* comb, StridedFusion* fu, const FuseNext* next, bool skip_first) {
   const size_t sm2 = (size_t)TILE_PHYS * sizeof(cplx);
   PassArgs a;
   a.g = g;
@@ -678,7 +776,7 @@ int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cp
   const unsigned n_tiles = 1u << (g.n_loc - TB);
   if (ep.n_in > 2) { set_error("internal: fused epilogues take at most 2 input vectors"); return QSB_ERR_BAD_ARG; }
   const double S = (double)(sizeof(cplx) << g.n_loc);
-  {
+  if (!skip_first) {
     const bool cmb = comb && comb->n_in > 0;
     Timed t(cmb ? 4 : 0, stream, cmb ? (comb->n_in + 3 + (comb->eout ? 1 : 0)) * S : 3 * S);
     if (comb && comb->n_in > 0) {
@@ -692,6 +790,15 @@ int launch_happly(const LargeGeom& g, const DiagTables& tab, const cplx* src, cp
   }
   int rc = launch_strided_passes(g, a, tx, ty, collect_obs, partials, stream, link, fu);
   if (rc) return rc;
+  if (next) {
+    if (ep.o2 || ep.want_err || ep.raw_h || ep.alpha != 1.0 || !ep.o1 || next->cb.out != src) {
+      set_error("internal: pass_last_first needs a plain k-producing epilogue and next->cb.out == src");
+      return QSB_ERR_BAD_ARG;
+    }
+    Timed t(7, stream, (3 + 1 + next->cb.n_in + 3) * S);
+    pass_last_first<<<n_tiles, TPT, sm2, stream>>>(a, const_cast<cplx*>(src), tx, ty, ep.o1, next->cb, next->c_fresh);
+    return QSB_OK;
+  }
   {
     static const int last_pf = [] { const char* e = std::getenv("QSB200_LAST_PF"); return e ? atoi(e) : 0; }();
     Epilogue epx = ep;

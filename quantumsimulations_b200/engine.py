@@ -147,7 +147,7 @@ def profile(enable: bool) -> None:
 
 
 PROFILE_CLASSES = ("pass_first", "pass_mid", "pass_centre", "pass_last", "pass_first_comb", "error_sums",
-                   "strided_fused")
+                   "strided_fused", "pass_last_first")
 
 
 def profile_read(with_bytes: bool = False):

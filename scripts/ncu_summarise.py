@@ -4,8 +4,8 @@ profiles/ncu_summary.json (what bench.py's roofline.traffic reads).
 
     python scripts/ncu_summarise.py r1o gpurun_out/r1o_dp5_apply_raw.csv gpurun_out/r1o_error_sums_raw.csv
 
-Round 2 captures hold ALL 30 launches of one DP5 step attempt (6 x [pass_first<comb>, pass_mid, pass_centre, pass_mid,
-pass_last]; the embedded error estimate rides on the last stage): dram_bytes_per_step is their sum.  Round-1 style
+Round 2 captures hold ALL launches of one DP5 step attempt (6 x [pass_first<comb>, pass_mid, pass_centre, pass_mid,
+pass_last], four of the last/first pairs fused into pass_last_first; the embedded error estimate rides on the last stage): dram_bytes_per_step is their sum.  Round-1 style
 captures (one H-apply + the error sweep) are scaled: 6 * (mean first_comb + 2 mid + centre + last) + error_sums.
 """
 import csv
@@ -81,7 +81,8 @@ def main():
     err = mean([dram(d) for d in by.get("error_sums_kernel", [])]) if by.get("error_sums_kernel") else 0.0
     ms_apply = (mean([d["gpu__time_duration.sum"] for d in by["pass_first"]]) + 2 * mean([d["gpu__time_duration.sum"] for d in by["pass_mid"]])
                 + mean([d["gpu__time_duration.sum"] for d in by["pass_centre"]]) + mean([d["gpu__time_duration.sum"] for d in by["pass_last"]]))
-    whole_step = len(by["pass_last"]) == 6 and len(by["pass_first"]) == 6
+    n_fused = len(by.get("pass_last_first", []))   # a stage's pass_last fused with the next stage's pass_first
+    whole_step = len(by["pass_last"]) + n_fused == 6 and len(by["pass_first"]) + n_fused == 6
     per_step = sum(dram(d) for d in launches) if whole_step else 6 * per_apply + err
     ms_step = sum(d["gpu__time_duration.sum"] for d in launches) if whole_step else None
     shares = {}
@@ -93,7 +94,7 @@ def main():
     summary = {
         "tag": tag,
         "source": "ncu --set full --clock-control none, python bench.py --steps 1 --warmup 3 --no-cpu --no-sharded (N=28, DP5); "
-                  "round 2: all 30 launches of the timed step attempt",
+                  "round 2: all launches of the timed step attempt",
         "dram_bytes_per_step": per_step,
         "whole_step_capture": whole_step, "ncu_ms_per_step": ms_step, "kernel_shares": shares,
         "dram_bytes_per_happly": per_apply,

@@ -1,6 +1,6 @@
 #!/bin/bash
 # Round-2 evidence pass on one GPU: full GPU test suite, smoke, default bench line, ncu launch list, ncu --set full of the
-# 30 launches of one DP5 step attempt at N = 28.   usage: scripts/r2_final.sh TAG [notest]
+# 26 launches of one DP5 step attempt at N = 28.   usage: scripts/r2_final.sh TAG [notest]
 TAG=${1:-r2z}
 mkdir -p gpurun_out
 if [ "$2" == "shardtests" ]; then
@@ -15,8 +15,8 @@ cut -c1-300 gpurun_out/${TAG}_bench.json
 timeout -s KILL 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_reference.json 2> gpurun_out/${TAG}_bench_reference.err; cut -c1-200 gpurun_out/${TAG}_bench_reference.json
 B="python bench.py --steps 1 --warmup 3 --no-cpu --no-sharded --no-grid"
 timeout -s KILL 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches_bench_steps1.csv $B > gpurun_out/${TAG}_ncu_list.log 2>&1
-# pass_* launches: prime 5, warm-up 3 x 30, then the timed step's 30
-timeout -s KILL 1500 ncu --set full --clock-control none --import-source on -k regex:'pass_' -s 95 -c 30 -f -o /tmp/${TAG}_dp5_step $B > gpurun_out/${TAG}_ncu_full.log 2>&1
+# pass_* launches: prime 5, warm-up 3 x 26, then the timed step's 26 (four stage pairs are fused: pass_last_first)
+timeout -s KILL 1500 ncu --set full --clock-control none --import-source on -k regex:'pass_' -s 83 -c 26 -f -o /tmp/${TAG}_dp5_step $B > gpurun_out/${TAG}_ncu_full.log 2>&1
 # the .ncu-rep (126 MB) stays on the box: gpurun_out is capped at 64 MiB; the raw page and the source page of pass_centre / pass_last come back as CSV
 ncu -i /tmp/${TAG}_dp5_step.ncu-rep --page raw --csv > gpurun_out/${TAG}_dp5_step_raw.csv 2>/dev/null
 ncu -i /tmp/${TAG}_dp5_step.ncu-rep --page source --csv -k regex:'pass_last' -c 1 > gpurun_out/${TAG}_pass_last_source.csv 2>/dev/null

@@ -181,8 +181,10 @@ def test_errors():
     with pytest.raises(IntegratorError):
         engine.propagate_batch([random_table(6, 3)], 5, 50.0, [SolverOptions(atol=1e-12, rtol=1e-11, nsteps=3)],
                                max_squarings=0)
-    with pytest.raises(ValueError, match="N <= 10"):
-        simulate_rare(DipolarRareParams(n_sea=12, is_spin_three_half=False), method="propagator")
+    with pytest.raises(ValueError, match="N <= 14"):   # beyond the HBM-resident propagator (11 <= N <= 14) as well
+        simulate_rare(DipolarRareParams(n_sea=14, is_spin_three_half=False), method="propagator")
+    with pytest.raises(engine.EngineError):            # the C entry point refuses sizes outside its range itself
+        engine.propagate_hbm(random_table(10, 4), 5, 0.1, _tight())
 
 
 def test_full_size_sweep_reproduces_reference_metrics(tmp_path):
