@@ -469,10 +469,12 @@ def run_b200(args, rank, world, local_rank):
         stages = 48 + 4 * (n - 12)
         flops_apply = (2.0 * stages + 40.0) * (1 << n)
         fp64_rate = n_rhs * flops_apply * args.steps / (ms / 1e3) / 1e12
-        roofline["fp64"] = {"flops_per_step": n_rhs * flops_apply, "achieved_TFLOPs": fp64_rate, "peak_TFLOPs": 40.0,
-                            "peak_source": "nominal B200 FP64 (datasheet; not measured on this box)",
-                            "frac": fp64_rate / 40.0,
-                            "binding": "hbm" if roofline["moved_frac_of_peak"] > fp64_rate / 40.0 else "fp64"}
+        fp64_peak = engine.fp64_peak_tflops(local_rank)
+        roofline["fp64"] = {"flops_per_step": n_rhs * flops_apply, "achieved_TFLOPs": fp64_rate, "peak_TFLOPs": fp64_peak,
+                            "peak_source": "measured in this run (qsb_debug_fp64_peak: DFMA chains on all SMs, under the "
+                                           "same power cap); nominal B200 FP64 is 40",
+                            "frac": fp64_rate / fp64_peak,
+                            "binding": "hbm" if roofline["moved_frac_of_peak"] > fp64_rate / fp64_peak else "fp64"}
     plan.session_end()
     plan.close()
 

@@ -261,6 +261,9 @@ int qsb_local_stream_barrier(void* member_ctx, void* stream);
  * 2 pass_centre, 3 pass_last, 4 pass_first with a fused stage combination, 5 error_sums, 6 strided_fused (mid .. centre
  * .. mid as one L2-resident persistent launch), 7 pass_last_first (a DP5 stage's pass_last fused with the next stage's pass_first).  ms / count / bytes: summed
  * milliseconds, launches and bytes moved by design (vectors read + written) per class since the last enable.        */
+/* Benchmark aid: measured FP64 FMA rate of `device` in TFLOP/s (DFMA-chain microbenchmark over all SMs) - the
+ * denominator of the FP64 co-bound bench.py reports next to the HBM roofline.                                       */
+int qsb_debug_fp64_peak(int device, double* tflops);
 #define QSB_N_PROFILE 8
 int qsb_profile(int enable);
 int qsb_profile_read(double* ms, int64_t* count, double* bytes, int32_t n);

@@ -165,6 +165,15 @@ int qsb_evolve(qsb_plan* p, uint64_t psi0_index, const double* psi0_host, int64_
   return rc;
 }
 
+int qsb_debug_fp64_peak(int device, double* tflops) {
+  if (!tflops) return fail(QSB_ERR_BAD_ARG, "null argument");
+  int rc = pick_device(device);
+  if (rc) return rc;
+  *tflops = measure_fp64_peak_tflops(nullptr);
+  QSB_CUDA(cudaGetLastError());
+  return QSB_OK;
+}
+
 int qsb_profile(int enable) {
   Profile& pr = profile();
   pr.on = enable != 0;

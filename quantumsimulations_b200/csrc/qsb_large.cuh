@@ -218,6 +218,8 @@ void launch_set_identity(cplx* psi, int n, cudaStream_t stream);
 // index o = c * seg_len + k and is skipped when o >= n_out.  out: [n_out][QSB_NOBS], or [QSB_NOBS][n_out] (by_column).
 void launch_observe_columns(const cplx* x, int n, int n_cols, int64_t seg_len, int64_t k, int64_t n_out, uint64_t sea_mask,
                             uint64_t rare_mask, double* out, int by_column, cudaStream_t stream);
+// Measured FP64 FMA rate of the current device in TFLOP/s (8 independent DFMA chains per thread, all SMs, best of 3).
+double measure_fp64_peak_tflops(cudaStream_t stream);
 size_t happly_smem_bytes();
 
 // Per-kernel-class CUDA-event timing (bench.py's roofline leg).  Classes: 0 pass_first, 1 pass_mid, 2 pass_centre,

@@ -303,6 +303,22 @@ dense_eval_kernel(DenseSpec d, uint64_t dim) {
   }
 }
 
+// FP64 issue-rate microbenchmark (the denominator of bench.py's FP64 co-bound): 8 independent DFMA chains per thread.
+__global__ void __launch_bounds__(256)
+fp64_peak_kernel(double* out, int iters, double a, double b) {
+  double x[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) x[k] = (double)(threadIdx.x + k);
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x[k] = fma(x[k], a, b);
+  }
+  double s = 0.0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += x[k];
+  if (s == 123.456) out[0] = s;  // keeps the chains alive without a store in practice
+}
+
 __global__ void set_identity_kernel(cplx* psi, int n) {
   const uint64_t dim2 = 1ull << (2 * n), stride = (uint64_t)gridDim.x * blockDim.x, mask = (1ull << n) - 1;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < dim2; i += stride)
@@ -849,6 +865,32 @@ void launch_gather_rows(const cplx* src, const uint64_t* d_rows, int64_t n_rows,
 void launch_dense_eval(const DenseSpec& d, uint64_t dim, cudaStream_t stream) {
   const int blocks = (int)std::min<uint64_t>((dim + 255) / 256, 148 * 8);
   dense_eval_kernel<<<blocks, 256, 0, stream>>>(d, dim);
+}
+
+double measure_fp64_peak_tflops(cudaStream_t stream) {
+  double* d = nullptr;
+  if (cudaMalloc(&d, sizeof(double)) != cudaSuccess) { cudaGetLastError(); return 0.0; }
+  int dev = 0, n_sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+  const int blocks = n_sms * 8, iters = 1 << 15;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0); cudaEventCreate(&e1);
+  fp64_peak_kernel<<<blocks, 256, 0, stream>>>(d, 1 << 10, 0.999999, 1e-9);  // warm-up
+  double best = 0.0;
+  for (int rep = 0; rep < 3; ++rep) {
+    cudaEventRecord(e0, stream);
+    fp64_peak_kernel<<<blocks, 256, 0, stream>>>(d, iters, 0.999999, 1e-9);
+    cudaEventRecord(e1, stream);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double tf = 2.0 * 8.0 * 256.0 * blocks * (double)iters / (ms * 1e-3) / 1e12;
+    if (tf > best) best = tf;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  cudaFree(d);
+  return best;
 }
 
 void launch_set_identity(cplx* psi, int n, cudaStream_t stream) {

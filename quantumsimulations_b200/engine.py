@@ -59,7 +59,7 @@ EXPORTS = (
     "qsb_version", "qsb_last_error", "qsb_device_count", "qsb_plan_create", "qsb_plan_destroy",
     "qsb_plan_workspace_bytes", "qsb_plan_set_workspace", "qsb_evolve", "qsb_evolve_batch", "qsb_apply_h",
     "qsb_apply_h_product", "qsb_apply_h_static",
-    "qsb_profile", "qsb_profile_read", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
+    "qsb_profile", "qsb_profile_read", "qsb_debug_fp64_peak", "qsb_session_begin", "qsb_session_step", "qsb_session_advance", "qsb_session_observe", "qsb_session_state", "qsb_session_end",
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_shard_set_stream_barrier", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather", "qsb_local_stream_barrier",
     "qsb_propagate_batch", "qsb_propagate_hbm", "qsb_release_caches", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
@@ -181,6 +181,15 @@ def strided_fusion(n_qubits: int, n_sms: int = 148):
         return None
     return {"f": out[1], "m": out[2], "fbits": out[3], "tiles_lb": out[4], "lag": out[5], "vmask": out[6],
             "fixed_vmask": [out[7 + k] for k in range(6)]}
+
+
+def fp64_peak_tflops(device: int = 0) -> float:
+    """Measured FP64 FMA rate of the device (qsb_debug_fp64_peak)."""
+    lib = load_library()
+    lib.qsb_debug_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
+    v = C.c_double(0.0)
+    _check(lib.qsb_debug_fp64_peak(int(device), C.byref(v)))
+    return v.value
 
 
 def release_caches(device: int = -1) -> None:
