@@ -12,6 +12,7 @@
 // (||H|| dt_out ~ 10^3 .. 10^4 H-applies per output interval).
 struct CublasCtx {
   std::mutex mu;
+  std::mutex busy[64];   // one qsb_propagate_hbm at a time per device: the handle and its stream binding are shared
   cublasHandle_t h[64] = {};
 };
 static CublasCtx& cublas_ctx() {
@@ -68,6 +69,7 @@ extern "C" int qsb_propagate_hbm(const qsb_table* table, uint64_t psi0_index, in
   if (rc) return rc;
   struct PlanGuard { qsb_plan* p; ~PlanGuard() { qsb_plan_destroy(p); } } guard{bp};
   bp->identity_bits = n;
+  std::lock_guard<std::mutex> one_at_a_time(cublas_ctx().busy[device & 63]);
   cublasHandle_t cb = nullptr;
   rc = cublas_for(device, &cb);
   if (rc) return rc;
