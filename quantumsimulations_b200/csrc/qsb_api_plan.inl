@@ -268,6 +268,7 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
   const size_t nobs = (size_t)n_traj * n_out * QSB_NOBS;
   cudaStream_t st = nullptr;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
+  std::vector<SmallStats> hs(n_traj);  // declared before the guard: it must outlive the guard's stream drain
   struct Guard {  // every early return (QSB_CUDA) releases what has been created so far
     SmallDesc*& a; double*& b; double*& c; SmallStats*& d; cudaStream_t& s; cudaEvent_t &x, &y;
     ~Guard() {
@@ -291,7 +292,6 @@ int qsb_evolve_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* ps
   launch_small_evolve(d_desc, n_traj, max_n, min_n == max_n, d_t, n_out, d_obs, d_stats, st);
   QSB_CUDA(cudaGetLastError());
   QSB_CUDA(cudaEventRecord(e1, st));
-  std::vector<SmallStats> hs(n_traj);
   QSB_CUDA(cudaMemcpyAsync(out_obs, d_obs, sizeof(double) * nobs, cudaMemcpyDeviceToHost, st));
   QSB_CUDA(cudaMemcpyAsync(hs.data(), d_stats, sizeof(SmallStats) * n_traj, cudaMemcpyDeviceToHost, st));
   QSB_CUDA(cudaStreamSynchronize(st));
