@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define QSB_VERSION 100
+#define QSB_VERSION 200
 #define QSB_MAX_QUBITS 34
 #define QSB_SMALL_MAX_QUBITS 10 /* whole trajectory on-chip (one CTA) up to here */
 #define QSB_HBM_PROPAGATOR_MAX_QUBITS 14 /* dense propagator resident in HBM up to here (1 GB at 13, 4 GB at 14) */

@@ -282,7 +282,7 @@ def test_library_exports_every_declared_symbol():
     for sym in declared:
         assert hasattr(lib, sym), sym
     assert declared == set(engine.EXPORTS)
-    assert lib.qsb_version() == 100
+    assert lib.qsb_version() == 200
 
 
 def test_no_silent_cpu_fallback():
