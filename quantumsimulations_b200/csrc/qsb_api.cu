@@ -10,7 +10,8 @@
 #include <string>
 #include <vector>
 
-#include <cublas_v2.h>
+#include <cublas_v2.h>  // types only: the library itself is dlopen-ed on first use (qsb_api_prophbm.inl)
+#include <dlfcn.h>
 
 #include "qsb_large.cuh"
 #include "qsb_small.cuh"

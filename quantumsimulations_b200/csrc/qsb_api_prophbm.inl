@@ -10,10 +10,25 @@
 //   * the observables of every state of every segment come from observe_columns_kernel.
 // A 20000-output trajectory at the sweep's tolerances then costs seconds instead of the hours the stepped path needs
 // (||H|| dt_out ~ 10^3 .. 10^4 H-applies per output interval).
+// cuBLAS is loaded on first use (dlopen), not linked: only this path needs it, and a box without libcublas on the loader
+// path must still be able to load the engine.
+typedef cublasStatus_t (*CublasCreateFn)(cublasHandle_t*);
+typedef cublasStatus_t (*CublasSetStreamFn)(cublasHandle_t, cudaStream_t);
+typedef cublasStatus_t (*CublasZgemmFn)(cublasHandle_t, cublasOperation_t, cublasOperation_t, int, int, int, const cuDoubleComplex*,
+                                        const cuDoubleComplex*, int, const cuDoubleComplex*, int, const cuDoubleComplex*,
+                                        cuDoubleComplex*, int);
+typedef cublasStatus_t (*CublasZgemvFn)(cublasHandle_t, cublasOperation_t, int, int, const cuDoubleComplex*, const cuDoubleComplex*, int,
+                                        const cuDoubleComplex*, int, const cuDoubleComplex*, cuDoubleComplex*, int);
 struct CublasCtx {
   std::mutex mu;
   std::mutex busy[64];   // one qsb_propagate_hbm at a time per device: the handle and its stream binding are shared
   cublasHandle_t h[64] = {};
+  void* lib = nullptr;
+  bool tried = false;
+  CublasCreateFn create = nullptr;
+  CublasSetStreamFn set_stream = nullptr;
+  CublasZgemmFn zgemm = nullptr;
+  CublasZgemvFn zgemv = nullptr;
 };
 static CublasCtx& cublas_ctx() {
   static CublasCtx c;
@@ -22,7 +37,22 @@ static CublasCtx& cublas_ctx() {
 static int cublas_for(int device, cublasHandle_t* out) {
   CublasCtx& c = cublas_ctx();
   std::lock_guard<std::mutex> lk(c.mu);
-  if (!c.h[device & 63] && cublasCreate(&c.h[device & 63]) != CUBLAS_STATUS_SUCCESS) {
+  if (!c.tried) {
+    c.tried = true;
+    for (const char* name : {"libcublas.so.12", "libcublas.so"}) {
+      c.lib = dlopen(name, RTLD_NOW | RTLD_LOCAL);
+      if (c.lib) break;
+    }
+    if (c.lib) {
+      c.create = (CublasCreateFn)dlsym(c.lib, "cublasCreate_v2");
+      c.set_stream = (CublasSetStreamFn)dlsym(c.lib, "cublasSetStream_v2");
+      c.zgemm = (CublasZgemmFn)dlsym(c.lib, "cublasZgemm_v2");
+      c.zgemv = (CublasZgemvFn)dlsym(c.lib, "cublasZgemv_v2");
+    }
+  }
+  if (!c.lib || !c.create || !c.set_stream || !c.zgemm || !c.zgemv)
+    return fail(QSB_ERR_UNSUPPORTED, "qsb_propagate_hbm needs cuBLAS (libcublas.so.12 could not be loaded)");
+  if (!c.h[device & 63] && c.create(&c.h[device & 63]) != CUBLAS_STATUS_SUCCESS) {
     c.h[device & 63] = nullptr;
     return fail(QSB_ERR_CUDA, "cublasCreate failed");
   }
@@ -73,7 +103,7 @@ extern "C" int qsb_propagate_hbm(const qsb_table* table, uint64_t psi0_index, in
   cublasHandle_t cb = nullptr;
   rc = cublas_for(device, &cb);
   if (rc) return rc;
-  if (cublasSetStream(cb, bp->stream) != CUBLAS_STATUS_SUCCESS) return fail(QSB_ERR_CUDA, "cublasSetStream failed");
+  if (cublas_ctx().set_stream(cb, bp->stream) != CUBLAS_STATUS_SUCCESS) return fail(QSB_ERR_CUDA, "cublasSetStream failed");
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   QSB_CUDA(cudaEventCreate(&e0));
   QSB_CUDA(cudaEventCreate(&e1));
@@ -95,7 +125,7 @@ extern "C" int qsb_propagate_hbm(const qsb_table* table, uint64_t psi0_index, in
   char* misc = (char*)s->ty;
   const cuDoubleComplex one = make_cuDoubleComplex(1.0, 0.0), zero = make_cuDoubleComplex(0.0, 0.0);
   auto gemm = [&](const cuDoubleComplex* A, const cuDoubleComplex* B, cuDoubleComplex* C, int cols) -> int {
-    if (cublasZgemm(cb, CUBLAS_OP_N, CUBLAS_OP_N, (int)dim, cols, (int)dim, &one, A, (int)dim, B, (int)dim, &zero, C, (int)dim) !=
+    if (cublas_ctx().zgemm(cb, CUBLAS_OP_N, CUBLAS_OP_N, (int)dim, cols, (int)dim, &one, A, (int)dim, B, (int)dim, &zero, C, (int)dim) !=
         CUBLAS_STATUS_SUCCESS)
       return fail(QSB_ERR_CUDA, "cublasZgemm failed");
     return QSB_OK;
@@ -130,7 +160,7 @@ extern "C" int qsb_propagate_hbm(const qsb_table* table, uint64_t psi0_index, in
       std::swap(V, Vt);
     }
     for (int c = 1; c < n_seg; ++c)  // seeds: column c = V column c-1
-      if (cublasZgemv(cb, CUBLAS_OP_N, (int)dim, (int)dim, &one, V, (int)dim, X0 + (size_t)(c - 1) * dim, 1, &zero,
+      if (cublas_ctx().zgemv(cb, CUBLAS_OP_N, (int)dim, (int)dim, &one, V, (int)dim, X0 + (size_t)(c - 1) * dim, 1, &zero,
                       X0 + (size_t)c * dim, 1) != CUBLAS_STATUS_SUCCESS)
         return fail(QSB_ERR_CUDA, "cublasZgemv failed");
   }
