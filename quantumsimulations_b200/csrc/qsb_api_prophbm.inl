@@ -76,11 +76,12 @@ extern "C" int qsb_propagate_hbm(const qsb_table* table, uint64_t psi0_index, in
   if (!(dt > 0.0) || !std::isfinite(dt)) return fail(QSB_ERR_BAD_ARG, "dt must be finite and > 0");
   const size_t dim = (size_t)1 << n;
 
-  // squarings: integrate over dt / 2^s with ||H|| dt / 2^s <= ~32 (a squaring is a 2^(3n+3)-flop GEMM, 0.12 s at n = 13;
-  // a unit of ||H|| t costs ~3 H-applies of the 2^(2n) matrix, ~12 ms)
+  // squarings: integrate over dt / 2^s with ||H|| dt / 2^s <= ~8 (table_norm_bound overestimates ||H||).  Measured at
+  // n = 13: a squaring is a 2^(3n+3)-flop GEMM, 0.13 s; integrating over dt / 256 takes 0.88 s and halves with every
+  // further squaring, so the total is smallest two squarings beyond the <= 32 rule used first (1.5 s against 1.9 s)
   int s_sq = 0;
   if (max_squarings != 0) {
-    const double x = table_norm_bound(table) * dt / 32.0;
+    const double x = table_norm_bound(table) * dt / 8.0;
     while (s_sq < 40 && std::ldexp(1.0, s_sq) < x) ++s_sq;
     if (max_squarings > 0 && s_sq > max_squarings) s_sq = max_squarings;
   }
