@@ -30,6 +30,7 @@ struct qsb_plan {
   StridedFusion fu;             // L2-resident fusion of the strided passes (unsharded plans); fu.ctrl is owned here
   // sharded state (world > 1): exchange scratch (tx, ty) the peers map, and the peers' mappings
   void* xbuf = nullptr;
+  int xvecs = 2;                // vectors in xbuf: tx, ty [, rx, ry]
   ShardLink link = {};
   bool connected = false;
   void* ipc_opened[MAX_WORLD] = {};
@@ -172,7 +173,10 @@ static int plan_create(const qsb_table* table, int device, int rank, int world, 
       if (p->fu.on) QSB_CUDA(cudaMalloc(&p->fu.ctrl, p->fu.ctrl_bytes));
     }
     if (world > 1) {
-      cudaError_t e = cudaMalloc(&p->xbuf, 2 * (sizeof(cplx) << p->n_loc));
+      // exchange allocation the peers map: tx, ty and - for the push-only exchange - the receive buffers rx, ry
+      const char* pe = getenv("QSB200_SHARD_PUSH");
+      p->xvecs = (pe && *pe == '1') ? 4 : 2;
+      cudaError_t e = cudaMalloc(&p->xbuf, p->xvecs * (sizeof(cplx) << p->n_loc));
       if (e != cudaSuccess) {
         cudaGetLastError();
         p->xbuf = nullptr;

@@ -144,7 +144,7 @@ int qsb_shard_export(qsb_plan* p, void* blob) {
   b.device = p->device;
   b.rank = p->rank;
   b.ptr = (uint64_t)(uintptr_t)p->xbuf;
-  b.bytes = 2 * (sizeof(cplx) << p->n_loc);
+  b.bytes = (uint64_t)p->xvecs * (sizeof(cplx) << p->n_loc);
   QSB_CUDA(cudaIpcGetMemHandle(&b.handle, p->xbuf));
   memcpy(blob, &b, sizeof b);
   return QSB_OK;
@@ -159,7 +159,7 @@ int qsb_shard_connect(qsb_plan* p, const void* blobs, qsb_allgather_fn allgather
   for (int r = 0; r < p->world; ++r) {
     ShardBlob b;
     memcpy(&b, (const char*)blobs + (size_t)r * sizeof b, sizeof b);
-    if (b.rank != r || b.bytes != 2 * vec)
+    if (b.rank != r || b.bytes != (uint64_t)p->xvecs * vec)
       return fail(QSB_ERR_BAD_ARG, "blob " + std::to_string(r) + " does not describe rank " + std::to_string(r) +
                                        " of a plan with this shard size");
     char* base = nullptr;
@@ -184,9 +184,12 @@ int qsb_shard_connect(qsb_plan* p, const void* blobs, qsb_allgather_fn allgather
     }
     p->link.tx[r] = (cplx*)base;
     p->link.ty[r] = (cplx*)(base + vec);
+    p->link.rx[r] = p->xvecs == 4 ? (cplx*)(base + 2 * vec) : nullptr;
+    p->link.ry[r] = p->xvecs == 4 ? (cplx*)(base + 3 * vec) : nullptr;
   }
   p->allgather = allgather;
   p->allgather_ctx = ctx;
+  p->link.push = p->xvecs == 4;
   p->link.ring_ready = false;  // the peers' pointers changed: the TMA descriptors are rebuilt on first use
   p->link.sync = shard_sync;
   p->link.ctx = p;

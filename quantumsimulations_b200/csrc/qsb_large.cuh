@@ -104,6 +104,12 @@ struct LargeGeom {
 struct ShardLink {
   cplx* tx[MAX_WORLD];
   cplx* ty[MAX_WORLD];
+  // Push-only exchange (QSB200_SHARD_PUSH=1 at plan creation): receive buffers of every rank, [n_tiles_loc][4096] in
+  // centre-tile order.  The last forward mid pass stores each amplitude straight into the buffer of the rank that owns
+  // its centre tile (posted NVLink writes), so the centre pass loads locally and only its stores are remote.
+  cplx* rx[MAX_WORLD];
+  cplx* ry[MAX_WORLD];
+  bool push;
   int (*sync)(void* ctx);
   void* ctx;
   // Overlapped mode (one process per GPU): `stream_barrier` enqueues a rank barrier ON a stream (an NCCL collective:

@@ -151,17 +151,39 @@ pass_first(PassArgs a, const cplx* __restrict__ psi, cplx* __restrict__ tx, cplx
   }
 }
 
+// Peer bases of both branches for the sharded centre pass: element idx lives on rank idx >> n_loc.
+struct PeerPtrs {
+  cplx* t[2][MAX_WORLD];
+};
+
+// Push-only exchange: where the last forward mid pass delivers its output.  The amplitude at local index i of this
+// rank belongs to centre tile v = index bits [lk_c, gs_c) (owner = the top bits of v, v >> tl), tile-local position
+// u = pad bits [0, lk_c) | centre-group bits (local ones [gs_c, n_loc), then the rank) << lk_c.
+struct PushSpec {
+  cplx* r[2][MAX_WORLD];  // receive buffers [branch][owner]
+  int lk_c, gs_c, tl;     // centre layout's pad bits / group start; log2 of the centre tiles per rank
+  uint64_t rank_hi;       // rank << (n_loc - gs_c): this rank's bits in the centre group
+  int on;
+  __device__ __forceinline__ cplx* dest(int branch, uint64_t i) const {
+    const uint64_t v = (i & ((1ull << gs_c) - 1)) >> lk_c;
+    const uint64_t u = (i & ((1ull << lk_c) - 1)) | (((i >> gs_c) | rank_hi) << lk_c);
+    return r[branch][v >> tl] + (((v & ((1ull << tl) - 1)) << TB) | u);
+  }
+};
+
 // ---------------------------------------------------------------------------------------------------
 // pass_mid: in-place Hadamard on one group's bits (layout k, 0 < k < centre).  blockIdx.y = branch.
 // ---------------------------------------------------------------------------------------------------
 // PAD: the tile buffer has the bank-conflict pad (needed only if the layout transforms window [0,4), which no layout
 // built by make_geometry does: groups have at most 8 bits)
-template <bool PAD>
+// PUSH: the stores go to the owners' receive buffers (PushSpec) instead of back in place.
+template <bool PAD, bool PUSH = false>
 __global__ void __launch_bounds__(TPT, 2)
-pass_mid(Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty) {
+pass_mid(Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty, PushSpec ps) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
-  cplx* t = (tm.branch0 + blockIdx.y) ? ty : tx;
+  const int branch = tm.branch0 + blockIdx.y;
+  cplx* t = branch ? ty : tx;
   const int tt = threadIdx.x;
   const uint64_t base = tile_base(L, tm.tile(blockIdx.x));
   cplx r[16];
@@ -187,9 +209,15 @@ pass_mid(Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty) {
     const unsigned late0 = tm.zero & (unsigned)__double2loint(r[0].x);  // 0, but only known once the data is final
     WinOff wo;
     wo.init<4>(L, late0);
-    cplx* p = t + gidx(L, base | late0, elem<4>(tt, 0));
+    if constexpr (PUSH) {
+      const uint64_t i0 = gidx(L, base | late0, elem<4>(tt, 0));
 #pragma unroll
-    for (int j = 0; j < 16; ++j) p[wo.at(j)] = r[j];
+      for (int j = 0; j < 16; ++j) *ps.dest(branch, i0 + wo.at(j)) = r[j];
+    } else {
+      cplx* p = t + gidx(L, base | late0, elem<4>(tt, 0));
+#pragma unroll
+      for (int j = 0; j < 16; ++j) p[wo.at(j)] = r[j];
+    }
   }
 }
 
@@ -216,11 +244,6 @@ __device__ __forceinline__ void centre_core(cplx (&r)[16], int tt, int mask, con
   bfly16<0>(r, mask);
 }
 
-// Peer bases of both branches for the sharded centre pass: element idx lives on rank idx >> n_loc.
-struct PeerPtrs {
-  cplx* t[2][MAX_WORLD];
-};
-
 // W = centre_window(L): the register window the diagonal is evaluated in (8: the group fits window [8,12) and never
 // touches shared memory; 4: N = 28; 0: groups wider than 8 bits do not exist, but layout 0 as centre (n = 12) and
 // short groups with lk > 8 land here).  The diagonal coefficients (10 registers) are fetched FIRST so that their
@@ -231,10 +254,12 @@ struct PeerPtrs {
 // (Three CTAs per SM - 80 registers, which the W = 4 body fits without spilling, and the large carve-out - were
 // measured at N = 28: 3.99 ms against 3.28 ms, profiles/r2_centre_occ3.json; L1 capacity, not a third tile, is what
 // the loads in flight need.)
-template <bool SHARDED, bool COLLECT, int W, bool PERSIST = false>
+// PUSHED (sharded): the tile was delivered by the peers' last forward mid pass into this rank's receive buffer
+// (rbuf[branch], [slot][4096] in tile-local order): the loads are local and contiguous, only the stores are remote.
+template <bool SHARDED, bool COLLECT, int W, bool PERSIST = false, bool PUSHED = false>
 __global__ void __launch_bounds__(TPT, 2)
 pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __restrict__ ty, PeerPtrs peers,
-            double* __restrict__ partials) {
+            double* __restrict__ partials, const cplx* __restrict__ rbuf_x = nullptr, const cplx* __restrict__ rbuf_y = nullptr) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   cplx* sm = reinterpret_cast<cplx*>(smem_raw);
   __shared__ double red[2 * 32 + 2];
@@ -256,7 +281,11 @@ pass_centre(PassArgs a, Layout L, TileMap tm, cplx* __restrict__ tx, cplx* __res
     const uint64_t base = tile_base(L, v);
     cplx r[16];
     double s[2] = {0.0, 0.0};
-    {
+    if constexpr (PUSHED) {
+      const cplx* rb = (branch ? rbuf_y : rbuf_x) + (slot << TB) + elem<8>(tt, 0);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) r[j] = rb[j << 8];
+    } else {
       WinOff wo;
       wo.init<8>(L, 0);
       const uint64_t idx0 = gidx(L, base, elem<8>(tt, 0));

@@ -411,6 +411,10 @@ static void set_centre_attrs(int sm) {
   tile_kernel_attrs(pass_centre<true, true, W>, sm);
   tile_kernel_attrs(pass_centre<true, false, W, true>, sm);
   tile_kernel_attrs(pass_centre<true, true, W, true>, sm);
+  tile_kernel_attrs(pass_centre<true, false, W, true, true>, sm);
+  tile_kernel_attrs(pass_centre<true, true, W, true, true>, sm);
+  tile_kernel_attrs(pass_centre<true, false, W, false, true>, sm);
+  tile_kernel_attrs(pass_centre<true, true, W, false, true>, sm);
   if constexpr (W != 0) {
     const int sm2 = 2 * TILE * (int)sizeof(cplx);
     tile_kernel_attrs(pass_centre_pipe<false, W>, sm2);
@@ -422,9 +426,17 @@ static void set_centre_attrs(int sm) {
 static size_t strided_smem(bool pad) { return (size_t)(pad ? TILE_PHYS : TILE) * sizeof(cplx); }
 
 // nb: branches per launch - 2 (both, blockIdx.y) or 1 (only tm.branch0)
-static void launch_mid(const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, unsigned n_tiles, cudaStream_t stream, int nb = 2) {
-  if (L.m0) pass_mid<true><<<dim3(n_tiles, nb), TPT, strided_smem(true), stream>>>(L, tm, tx, ty);
-  else pass_mid<false><<<dim3(n_tiles, nb), TPT, strided_smem(false), stream>>>(L, tm, tx, ty);
+// push: non-null for the LAST forward mid pass of a push-only sharded exchange (its output goes to the owners' buffers)
+static void launch_mid(const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, unsigned n_tiles, cudaStream_t stream, int nb = 2,
+                       const PushSpec* push = nullptr) {
+  PushSpec none = {};
+  if (push) {
+    if (L.m0) pass_mid<true, true><<<dim3(n_tiles, nb), TPT, strided_smem(true), stream>>>(L, tm, tx, ty, *push);
+    else pass_mid<false, true><<<dim3(n_tiles, nb), TPT, strided_smem(false), stream>>>(L, tm, tx, ty, *push);
+    return;
+  }
+  if (L.m0) pass_mid<true><<<dim3(n_tiles, nb), TPT, strided_smem(true), stream>>>(L, tm, tx, ty, none);
+  else pass_mid<false><<<dim3(n_tiles, nb), TPT, strided_smem(false), stream>>>(L, tm, tx, ty, none);
 }
 
 // Opt-in.  Measured on 2 x B200 at N = 31 (profiles/r2k_centre_pipe_2gpu.jsonl): the centre pass alone gains 3 %
@@ -437,8 +449,21 @@ static int centre_pipe_mode() {  // read per launch: tests switch it inside one 
 
 template <bool SHARDED, int W>
 static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, const PeerPtrs& pp,
-                          int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream, int nb) {
+                          int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream, int nb,
+                          const cplx* rbx = nullptr, const cplx* rby = nullptr) {
   sm = W == 8 ? 0 : strided_smem(W == 0);  // W == 8: the whole group sits in one register window, no staging at all
+  if constexpr (SHARDED) {
+    if (rbx) {  // push-only exchange: local loads from the receive buffers
+      if (tm.count) {
+        if (collect_obs) pass_centre<true, true, W, true, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials, rbx, rby);
+        else pass_centre<true, false, W, true, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials, rbx, rby);
+      } else {
+        if (collect_obs) pass_centre<true, true, W, false, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials, rbx, rby);
+        else pass_centre<true, false, W, false, true><<<dim3(n_tiles, nb), TPT, sm, stream>>>(a, L, tm, tx, ty, pp, partials, rbx, rby);
+      }
+      return;
+    }
+  }
   if constexpr (SHARDED && W != 0) {
     // persistent + double-buffered (cp.async prefetch of the next tile from the peers); QSB200_CENTRE_PIPE=1: on,
     // =2: also in the serialised sharded path (how a one-GPU box tests the kernel)
@@ -461,11 +486,12 @@ static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm,
 }
 template <bool SHARDED>
 static void launch_centre(const PassArgs& a, const Layout& L, const TileMap& tm, cplx* tx, cplx* ty, const PeerPtrs& pp,
-                          int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream, int nb = 2) {
+                          int collect_obs, double* partials, unsigned n_tiles, size_t sm, cudaStream_t stream, int nb = 2,
+                          const cplx* rbx = nullptr, const cplx* rby = nullptr) {
   switch (centre_window(L)) {
-    case 8: launch_centre<SHARDED, 8>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream, nb); break;
-    case 4: launch_centre<SHARDED, 4>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream, nb); break;
-    default: launch_centre<SHARDED, 0>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream, nb); break;
+    case 8: launch_centre<SHARDED, 8>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream, nb, rbx, rby); break;
+    case 4: launch_centre<SHARDED, 4>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream, nb, rbx, rby); break;
+    default: launch_centre<SHARDED, 0>(a, L, tm, tx, ty, pp, collect_obs, partials, n_tiles, sm, stream, nb, rbx, rby); break;
   }
 }
 
@@ -538,6 +564,8 @@ void prepare_device() {
   tile_kernel_attrs(pass_last<3, 4, 2>, sm);
   tile_kernel_attrs(pass_mid<true>, sm);
   tile_kernel_attrs(pass_mid<false>, sm);
+  tile_kernel_attrs(pass_mid<true, true>, sm);
+  tile_kernel_attrs(pass_mid<false, true>, sm);
   set_centre_attrs<8>(sm);
   set_centre_attrs<4>(sm);
   set_centre_attrs<0>(sm);
@@ -669,8 +697,22 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
   }
   const bool overlapped = g.world > 1 && link && link->stream_barrier &&
                           !(shard_ring_enabled() && centre_window(g.lay[centre]) != 0);
+  const bool push_serial = !overlapped && g.world > 1 && link && link->push && centre >= 2 &&
+                           !(shard_ring_enabled() && centre_window(g.lay[centre]) != 0);
+  PushSpec push_s = {};
+  if (push_serial) {
+    for (int r = 0; r < g.world; ++r) { push_s.r[0][r] = link->rx[r]; push_s.r[1][r] = link->ry[r]; }
+    push_s.lk_c = g.lay[centre].lk;
+    push_s.gs_c = g.lay[centre].gs;
+    push_s.tl = g.n_loc - TB;
+    push_s.rank_hi = (uint64_t)g.rank << (g.n_loc - g.lay[centre].gs);
+    push_s.on = 1;
+  }
   if (!overlapped)
-    for (int k = 1; k < centre; ++k) { Timed t(1, stream, 4 * S); launch_mid(g.lay[k], all, tx, ty, n_tiles, stream); }
+    for (int k = 1; k < centre; ++k) {
+      Timed t(1, stream, 4 * S);
+      launch_mid(g.lay[k], all, tx, ty, n_tiles, stream, 2, (push_serial && k == centre - 1) ? &push_s : nullptr);
+    }
   if (g.world == 1) {
     Timed t(2, stream, 4 * S);
     // experiment knob: the TMA-ring centre kernel (one persistent CTA per SM, three tile buffers) on an unsharded plan
@@ -695,6 +737,19 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
     PeerPtrs pp = {};
     for (int r = 0; r < g.world; ++r) { pp.t[0][r] = link->tx[r]; pp.t[1][r] = link->ty[r]; }
     const int w = centre_window(g.lay[centre]);
+    // push-only exchange: needs a mid pass to deliver the tiles (centre >= 2) and the peers' receive buffers
+    PushSpec push = {};
+    const bool pushing = link->push && centre >= 2 && !(shard_ring_enabled() && w != 0);
+    if (pushing) {
+      for (int r = 0; r < g.world; ++r) { push.r[0][r] = link->rx[r]; push.r[1][r] = link->ry[r]; }
+      push.lk_c = g.lay[centre].lk;
+      push.gs_c = g.lay[centre].gs;
+      push.tl = g.n_loc - TB;
+      push.rank_hi = (uint64_t)g.rank << (g.n_loc - g.lay[centre].gs);
+      push.on = 1;
+    }
+    const cplx* rbx = pushing ? link->rx[g.rank] : nullptr;
+    const cplx* rby = pushing ? link->ry[g.rank] : nullptr;
     if (overlapped) {
       // Overlapped: a software pipeline over chunk groups.  Index bits [lmax, 12) - pad bits of every strided tile, lmax
       // the largest lk - are transformed by no strided pass, so they cut the vectors into 2^(12 - lmax) chunks whose
@@ -724,7 +779,8 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
       auto fwd = [&](int c) -> int {
         for (int k = 1; k < centre; ++k) {
           Timed t(1, stream, 4 * S / K);
-          launch_mid(g.lay[k], group_map(g.lay[k], c, 0u, 0, 0u), tx, ty, per_group, stream);
+          launch_mid(g.lay[k], group_map(g.lay[k], c, 0u, 0, 0u), tx, ty, per_group, stream, 2,
+                     (pushing && k == centre - 1) ? &push : nullptr);
         }
         if (link->stream_barrier(link->barrier_ctx, stream)) { set_error("rank barrier (stream hook) failed"); return QSB_ERR_CUDA; }
         cudaEventRecord(link->ev_fwd[c], stream);
@@ -732,7 +788,8 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
         for (int br = 0; br < 2; ++br) {
           Timed t(2, C, 2 * S / K);
           launch_centre<true>(a, g.lay[centre], group_map(g.lay[centre], c, (unsigned)g.rank * n_tiles, br, per_group), tx, ty,
-                              pp, collect_obs, partials, std::min<unsigned>(per_group, (unsigned)link->centre_ctas), sm1, C, 1);
+                              pp, collect_obs, partials, std::min<unsigned>(per_group, (unsigned)link->centre_ctas), sm1, C, 1,
+                              rbx, rby);
         }
         if (link->stream_barrier(link->barrier_ctx, C)) { set_error("rank barrier (stream hook) failed"); return QSB_ERR_CUDA; }
         cudaEventRecord(link->ev_centre[c], C);
@@ -771,7 +828,7 @@ static int launch_strided_passes(const LargeGeom& g, const PassArgs& a, cplx* tx
                               std::min<unsigned>(n_tiles, (unsigned)n_sms), sm1, stream);
         } else {
           const TileMap mine = {(unsigned)g.rank * n_tiles, 0, 0, 0, 0u, 0u, 0, 0u};
-          launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, stream);
+          launch_centre<true>(a, g.lay[centre], mine, tx, ty, pp, collect_obs, partials, n_tiles, sm1, stream, 2, rbx, rby);
         }
       }
     }

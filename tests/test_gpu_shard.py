@@ -225,3 +225,35 @@ def test_pipelined_strided_passes(n, world, gmax, pipe, monkeypatch):
     assert np.max(np.abs(got_h - want)) / np.max(np.abs(want)) < 2e-13
     assert np.array_equal(got_h, ref_h) and np.array_equal(got_obs, ref_obs)
     assert (got_st.n_accepted, got_st.n_rejected) == (ref_st.n_accepted, ref_st.n_rejected)
+
+
+@pytest.mark.parametrize("n,world,gmax,pipeline", [(16, 2, 2, False), (17, 4, 3, False), (19, 8, 3, False), (19, 2, 4, True),
+                                                    (20, 4, 3, True), (21, 8, 5, True), (22, 2, None, True), (14, 4, None, False)])
+def test_push_only_exchange(n, world, gmax, pipeline, monkeypatch):
+    """QSB200_SHARD_PUSH=1: the last forward mid pass stores every amplitude into the receive buffer of the rank that
+    owns its centre tile, the centre pass loads locally (pass_mid<.., PUSH>, pass_centre<.., PUSHED>); serialised and
+    chunk-pipelined passes, ranks as threads.  H psi against the numpy oracle and, bit for bit, against the pulling
+    exchange; trajectories too.  (n = 14 x 4 has no mid pass: it must fall back to pulling.)"""
+    from oracle import dense
+    from quantumsimulations_b200 import engine, shard
+
+    if gmax is not None:
+        monkeypatch.setenv("QSB200_MAX_GROUP", str(gmax))
+    table = random_table(n, 990 + n + world, dense_pairs=False)
+    bm = table.bit_major()
+    psi = _rand_state(n, 13 * n + world)
+    opts = engine.SolverOptions(atol=1e-10, rtol=1e-9, method="taylor", order=6)
+    t = np.linspace(0.0, 1e-3, 3)
+
+    def run():
+        with shard.LocalShardGroup(table, world, pipeline=pipeline) as grp:
+            return grp.apply_h(psi), grp.evolve(t, opts, psi)
+
+    monkeypatch.setenv("QSB200_SHARD_PUSH", "0")
+    ref_h, (ref_obs, ref_st) = run()
+    monkeypatch.setenv("QSB200_SHARD_PUSH", "1")
+    got_h, (got_obs, got_st) = run()
+    want = dense.apply_h(bm["h"], bm["J"], psi)
+    assert np.max(np.abs(got_h - want)) / np.max(np.abs(want)) < 2e-13
+    assert np.array_equal(got_h, ref_h) and np.array_equal(got_obs, ref_obs)
+    assert (got_st.n_accepted, got_st.n_rejected) == (ref_st.n_accepted, ref_st.n_rejected)
