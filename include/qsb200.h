@@ -78,7 +78,8 @@ typedef struct {
   double last_h;
   double device_ms;  /* CUDA-event time of the whole evolve on its stream      */
   int32_t path;      /* 0 = on-chip small-N kernel, 1 = tiled HBM path, 2 = on-chip propagator (counters summed
-                        over the 2^n column trajectories that built U)         */
+                        over the 2^n column trajectories that built U), 3 = HBM-resident propagator, 4 = on-chip
+                        propagator + Pauli-string observables (qsb_propagate_expect) */
   int32_t status;    /* qsb_status of this trajectory (batch calls)            */
 } qsb_stats;
 
@@ -195,6 +196,38 @@ int qsb_session_observe(qsb_plan* plan, double* obs);
 /* Copy the current state to host (2^n complex128).                                                   */
 int qsb_session_state(qsb_plan* plan, double* psi_host);
 int qsb_session_end(qsb_plan* plan);
+
+/* ---- local dimension 4: the spin-3/2 rare spin on two index bits ----------------------------------- */
+/* The reference declares a J = 3/2 rare spin (4x4 _Jx, _Jy, _Jz, dipolar_ensemble_with_rare.py:22-25, used at
+ * :499-501, :523-528, :563-568, :576-578; `is_spin_three_half=True` is the dataclass default, :377), although its own
+ * builder cannot run it (:486 forces all local dimensions to 2).  Here the four-level site is the two LOWEST index bits,
+ * level m = 2 a + b with m = 0 <-> J_z = +3/2 (qt.tensor order: the rare site is the last factor):
+ *     J_z = 2 I^z_a + I^z_b,    J_x = sqrt(3) I^x_b + 2 (I^x_a I^x_b + I^y_a I^y_b),
+ *     J_y = sqrt(3) I^y_b + 2 (I^y_a I^x_b - I^x_a I^y_b).
+ * In the frame rotating about J_z by the drive phase phi_R the rare drive w1R (cos phi_R J_x + sin phi_R J_y) becomes
+ * w1R J_x, so the whole Hamiltonian fits qsb_table's same-axis form and the time evolution runs through the kernels of
+ * the spin-1/2 path.  The observables do not: <J_x>, <J_y> are two-bit (one of them mixed-axis) Pauli strings.  They are
+ * given as a list of weighted strings; output column `column` (0 .. 5 = Ix_sea, Iy_sea, Iz_sea, Iz_R, Ix_R, Iy_R)
+ * receives sum_t weight_t <psi|P_t|psi> / <psi|psi>,  P = i^popcount(x_mask & z_mask) X^x_mask Z^z_mask  (a bit in
+ * both masks carries Y = i X Z); columns 6 / 7 are state_norm / raw_norm as everywhere else.                        */
+typedef struct {
+  uint64_t x_mask;  /* bits carrying X or Y                                       */
+  uint64_t z_mask;  /* bits carrying Z or Y                                       */
+  double weight;
+  int32_t column;   /* 0 .. 5                                                     */
+  int32_t reserved; /* 0                                                          */
+} qsb_pauli_term;
+#define QSB_MAX_PAULI_TERMS 512
+/* qsb_propagate_batch for ONE trajectory with such observables, n <= QSB_SMALL_MAX_QUBITS (n_sea <= 8 with a spin-3/2
+ * rare spin): the same column integrations and on-chip squarings build U = exp(-i H dt); the matvec chain keeps every
+ * psi_k in device memory (n_out * 2^n * 16 bytes, at most 16 GiB) and one more kernel reduces the strings on all of
+ * them.  out_obs / obs_by_column / stats as in qsb_propagate_batch; stats->path = 4.                               */
+int qsb_propagate_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt, const qsb_solver_opts* opts,
+                         int32_t max_squarings, const qsb_pauli_term* terms, int32_t n_terms, int32_t obs_by_column,
+                         double* out_obs, qsb_stats* stats, int device);
+/* The same observables on the current state of an open session (tiled path, unsharded plans), [QSB_NOBS] host:
+ * qsb_session_advance to every output time + this call is the spin-3/2 trajectory for n > QSB_SMALL_MAX_QUBITS.    */
+int qsb_session_expect(qsb_plan* plan, const qsb_pauli_term* terms, int32_t n_terms, double* obs);
 
 
 /* ---- sharded state: one trajectory whose 2^n amplitudes do not fit one GPU ------------------------ */

@@ -1,7 +1,8 @@
 """K: literal Kronecker-product restatement of the reference's Hamiltonian/observable/initial-state build.
 
-TEST INFRASTRUCTURE ONLY.  Follows DE:453-606 term by term on scipy.sparse matrices (all local
-dimensions 2 - the only case the reference can run).  It takes a *duck-typed* params
+TEST INFRASTRUCTURE ONLY.  Follows DE:453-606 term by term on scipy.sparse matrices: ``build`` with all local
+dimensions 2 (the only case the reference can run as written), ``build_spin32`` with the J = 3/2 rare
+spin on a four-level last site (the reference with DE:486 repaired; pinned by tests/golden/spin32_cases.*).  It takes a *duck-typed* params
 object (anything with the DipolarRareParams attribute names) plus the geometry/frequency callables,
 so it can be driven either by the reference's own helpers (in the build container) or by the
 product's mirror of them (anywhere) without importing either.
@@ -87,6 +88,79 @@ def build(params, freqs_fn: Callable, positions_fn: Callable, couplings_fn: Call
     idx = 0
     for q in bits:
         idx = 2 * idx + q
+    psi0 = np.zeros(dim, dtype=complex)
+    psi0[idx] = 1.0
+    return H.tocsr(), obs, psi0
+
+
+# ---- local dimension 4: the J = 3/2 rare spin (DE:22-25, DE:499-501) ------------------------------------------------
+def _jmat32():
+    """Spin-3/2 matrices in the basis m = +3/2, +1/2, -1/2, -3/2 (what ``qt.jmat(1.5, ...)`` returns, DE:22-24)."""
+    m = 1.5 - np.arange(4)
+    jp = np.zeros((4, 4), dtype=complex)                 # J+ |m> = sqrt(j(j+1) - m(m+1)) |m+1>
+    for k in range(1, 4):
+        jp[k - 1, k] = np.sqrt(1.5 * 2.5 - m[k] * (m[k] + 1.0))
+    jx = 0.5 * (jp + jp.conj().T)
+    jy = -0.5j * (jp - jp.conj().T)
+    return sp.csr_matrix(jx), sp.csr_matrix(jy), sp.csr_matrix(np.diag(m).astype(complex))
+
+
+def build_spin32(params, freqs_fn: Callable, positions_fn: Callable, couplings_fn: Callable
+                 ) -> Tuple[sp.csr_matrix, Dict[str, sp.csr_matrix], np.ndarray]:
+    """(H, observables, psi0) of DE:483-606 for ``is_spin_three_half=True`` with the reference's dims repaired:
+    local dimensions [2] * n_sea + [4] (DE:28-34) instead of DE:486's all-2, rare operators the 4 x 4 J matrices
+    (DE:499-501).  LAB frame, literal Kronecker products - independent of the product's two-bit encoding, rotated frame
+    and Pauli strings.  Needs ``is_center_rare`` (the sea-centre control has no spin-3/2 site)."""
+    if not params.is_center_rare:
+        raise ValueError("spin-3/2 needs is_center_rare=True")
+    n_sea = params.n_sea
+    dim = (1 << n_sea) * 4
+    jx, jy, jz = _jmat32()
+
+    def sea_op(local, k):
+        left = sp.identity(1 << k, dtype=complex, format="csr")
+        right = sp.identity((1 << (n_sea - 1 - k)) * 4, dtype=complex, format="csr")
+        return sp.kron(sp.kron(left, local), right, format="csr")
+
+    def rare_op(local):
+        return sp.kron(sp.identity(1 << n_sea, dtype=complex, format="csr"), local, format="csr")
+
+    def sea_sum(local):
+        acc = sp.csr_matrix((dim, dim), dtype=complex)
+        for k in range(n_sea):
+            acc = acc + sea_op(local, k)
+        return acc
+
+    fr = freqs_fn(params)
+    H = sp.csr_matrix((dim, dim), dtype=complex)
+    if params.drive_sea and fr["delta_sea"] != 0.0:                                   # DE:505-508
+        H = H + fr["delta_sea"] * sea_sum(_SZ)
+    if params.drive_rare and fr["delta_rare"] != 0.0:                                 # DE:510-512
+        H = H + fr["delta_rare"] * rare_op(jz)
+    if params.drive_sea and fr["omega1_sea"] != 0.0:                                  # DE:515-519
+        H = H + fr["omega1_sea"] * (np.cos(params.phi_sea) * sea_sum(_SX) + np.sin(params.phi_sea) * sea_sum(_SY))
+    if params.drive_rare and fr["omega1_rare"] != 0.0:                                # DE:523-528
+        H = H + fr["omega1_rare"] * (np.cos(params.phi_rare) * rare_op(jx) + np.sin(params.phi_rare) * rare_op(jy))
+    pos = positions_fn(n_sea, params.shell_scale)                                     # DE:533-536
+    b = couplings_fn(pos, params.dipolar_scale, params.gamma_sea, params.gamma_rare)  # DE:540-545
+    for i, j in combinations(range(n_sea + 1), 2):                                    # DE:549-568
+        if j < n_sea:
+            zz = sea_op(_SZ, i) @ sea_op(_SZ, j)
+            xx = sea_op(_SX, i) @ sea_op(_SX, j)
+            yy = sea_op(_SY, i) @ sea_op(_SY, j)
+            H = H + b[i, j] * (zz - 0.25 * (xx - yy))
+        else:
+            H = H + b[i, j] * (sea_op(_SZ, i) @ rare_op(jz))
+    obs = {                                                                           # DE:573-587
+        "Ix_sea": sea_sum(_SX), "Iy_sea": sea_sum(_SY), "Iz_sea": sea_sum(_SZ),
+        "Iz_R": rare_op(jz), "Ix_R": rare_op(jx), "Iy_R": rare_op(jy),
+    }
+    sea_bit = 0 if params.init_x_sign >= 0 else 1                                     # DE:71, DE:599
+    level = 0 if (-params.init_x_sign) >= 0 else 3                                    # DE:99, DE:602: argmax / argmin of Jz
+    idx = 0
+    for _ in range(n_sea):
+        idx = 2 * idx + sea_bit
+    idx = 4 * idx + level
     psi0 = np.zeros(dim, dtype=complex)
     psi0[idx] = 1.0
     return H.tocsr(), obs, psi0

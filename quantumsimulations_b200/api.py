@@ -25,13 +25,17 @@ class SpinOperator:
     def __init__(self, table: SpinTable, kind: str = "H"):
         self.table = table
         self.kind = kind
-        self.dims = [[2] * table.n, [2] * table.n]
+        # a spin-3/2 rare spin is the last tensor factor, local dimension 4 (two index bits; DE:28-34)
+        local = [2] * table.n if table.pauli_terms is None else [2] * (table.n - 2) + [4]
+        self.dims = [local, list(local)]
         self.shape = (table.dim, table.dim)
 
     def _as_table(self) -> SpinTable:
         if self.kind == "H":
             return self.table
         t = self.table
+        if t.pauli_terms is not None and self.kind in ("Ix_R", "Iy_R", "Iz_R"):
+            raise NotImplementedError(f"{self.kind} of a spin-3/2 rare spin is not a one-bit operator: use to_csr()")
         n = t.n
         z = np.zeros(n)
         zz = np.zeros((n, n))
@@ -43,17 +47,44 @@ class SpinOperator:
                          t.psi0_index)
 
     def apply(self, psi: np.ndarray, device: int = 0) -> np.ndarray:
-        """H @ psi on the GPU (one H-apply through the engine's kernels)."""
+        """H @ psi on the GPU (one H-apply through the engine's kernels).  A local-dimension-4 table lives in the frame
+        rotating about J_z (table.py): H_lab psi = R H_table R^dagger psi with the diagonal R applied here."""
+        r = self.table.frame_phases() if self.kind == "H" else None
         with engine.Plan(self._as_table(), device) as plan:
-            return plan.apply_h(psi)
+            if r is None:
+                return plan.apply_h(psi)
+            return r * plan.apply_h(np.conj(r) * np.asarray(psi, dtype=np.complex128))
+
+    def _pauli_csr(self):
+        """Lab-frame observable of a local-dimension-4 table from its weighted Pauli strings (host, inspection only)."""
+        import scipy.sparse as sp
+
+        t = self.table
+        col = TRACE_KEYS.index(self.kind)
+        dim = t.dim
+        x = np.arange(dim, dtype=np.int64)
+        m = sp.csr_matrix((dim, dim), dtype=complex)
+        for xm, zm, w, c in t.pauli_terms:
+            if c != col:
+                continue
+            par = np.zeros(dim, dtype=np.int64)
+            for b in range(t.n):
+                if (zm >> b) & 1:
+                    par ^= (x >> b) & 1
+            val = w * (1j ** bin(xm & zm).count("1")) * (1.0 - 2.0 * par)       # P |x> = i^ny (-1)^popc(x & zm) |x ^ xm>
+            m = m + sp.coo_matrix((val, (x ^ xm, x)), shape=(dim, dim)).tocsr()
+        r = t.frame_phases()
+        return (sp.diags(r) @ m @ sp.diags(np.conj(r))).tocsr()
 
     def to_csr(self):
         """scipy CSR matrix (host, small N only; for inspection and tests - not used by the solver)."""
         import scipy.sparse as sp
 
-        t = self._as_table()
-        if t.n > 16:
+        if self.table.n > 16:
             raise MemoryError("refusing to materialise a 2^N x 2^N operator for N > 16")
+        if self.kind != "H" and self.table.pauli_terms is not None:
+            return self._pauli_csr()
+        t = self._as_table()
         bm = t.bit_major()
         h, J = bm["h"], bm["J"]
         n, dim = t.n, t.dim
@@ -77,6 +108,9 @@ class SpinOperator:
         cols.append(x)
         vals.append(diag.astype(complex))
         m = sp.coo_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(dim, dim)).tocsr()
+        if self.kind == "H" and t.frame_phi is not None:       # back to the lab frame (table.py)
+            r = t.frame_phases()
+            m = (sp.diags(r) @ m @ sp.diags(np.conj(r))).tocsr()
         m.eliminate_zeros()
         return m
 
@@ -152,8 +186,15 @@ def split_method(method: Optional[str], n_qubits: Optional[int] = None, steps: O
 
 
 def resolve_method(params: DipolarRareParams, method: Optional[str]) -> Tuple[str, bool]:
-    """``split_method`` for one parameter record (computes the ||H|| t_final bound only where "auto" needs it)."""
+    """``split_method`` for one parameter record (computes the ||H|| t_final bound only where "auto" needs it).
+    A spin-3/2 rare spin (local dimension 4) has two paths only: N <= 10 bits always goes through the propagator (the
+    stepped on-chip kernel cannot report its observables), N > 10 is always stepped (``_evolve_pauli``)."""
     n, steps = _size_of(params)
+    if params.is_spin_three_half:
+        integrator, asked = split_method(method)
+        if asked and n > engine.SMALL_MAX_QUBITS:
+            raise ValueError(f"method 'propagator' with a spin-3/2 rare spin needs n_sea + 2 <= {engine.SMALL_MAX_QUBITS}")
+        return integrator, n <= engine.SMALL_MAX_QUBITS
     norm_t = None
     m = method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)
     if m == "auto" and engine.SMALL_MAX_QUBITS < n <= engine.HBM_PROPAGATOR_MAX_QUBITS and not params.is_spin_three_half:
@@ -162,7 +203,8 @@ def resolve_method(params: DipolarRareParams, method: Optional[str]) -> Tuple[st
 
 
 def _size_of(params: DipolarRareParams) -> Tuple[int, int]:
-    return params.n_sea + 1, params.steps
+    """(index bits, outputs): the spin-3/2 rare spin takes two bits (table.py)."""
+    return params.n_sea + (2 if params.is_spin_three_half else 1), params.steps
 
 
 def _options_from(params: DipolarRareParams, method: Optional[str], tol_scale: Optional[float] = None
@@ -229,6 +271,12 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
     t = _check_grid(params)
     table = compile_table(params)
     opts, override = _options_from(params, method, tol_scale)
+    if table.pauli_terms is not None:
+        if checkpoint is not None:
+            raise ValueError("checkpoint= is not available with is_spin_three_half=True")
+        obs, stats = _evolve_pauli(table, t, opts, device)
+        out = _pack(obs, override, raw_norm, by_column=True)
+        return (t, out, stats) if return_stats else (t, out)
     if resolve_method(params, method)[1]:
         obs, stats = _propagate([table], [t], [opts], device)
         out = _pack(obs[0], override, raw_norm, by_column=True)
@@ -244,6 +292,30 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
     if return_stats:
         return t, out, stats
     return t, out
+
+
+def _evolve_pauli(table: SpinTable, t: np.ndarray, opts: engine.SolverOptions, device: int):
+    """One trajectory of a local-dimension-4 table (spin-3/2 rare spin on two bits, DE:22-25 / DE:499-501): the time
+    evolution runs through the spin-1/2 kernels in the rotated frame, the observables are the table's weighted Pauli
+    strings.  N <= 10 bits: the propagator path with every state kept on the device (engine.propagate_expect; the
+    reference's grid is uniform, DE:626).  Larger: a stepping session on the tiled path, advanced to every output time
+    (``nsteps`` per output interval, like the stepped integrators) and read with ``Plan.session_expect``.
+    Returns (obs [NOBS, n_out], Stats)."""
+    if table.n <= engine.SMALL_MAX_QUBITS:
+        dt = engine.uniform_step(t)
+        if dt is None:
+            raise ValueError("the spin-3/2 on-chip path needs a uniform output grid (np.linspace, DE:626)")
+        return engine.propagate_expect(table, len(t), dt, opts, device, by_column=True)
+    obs = np.empty((engine.NOBS, len(t)), dtype=np.float64)
+    with engine.Plan(table, device) as plan:
+        plan.session_begin(opts, t0=float(t[0]))
+        obs[:, 0] = plan.session_expect(table.pauli_terms)
+        stats = None
+        for k in range(1, len(t)):
+            _, stats = plan.session_advance(float(t[k]))
+            obs[:, k] = plan.session_expect(table.pauli_terms)
+        plan.session_end()
+    return obs, stats
 
 
 def _propagate(tables, grids, opts, device):
@@ -271,6 +343,20 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
     """Independent trajectories; those with N <= 10 share ONE kernel launch (one CTA each), 11 <= N <= 14 on a uniform
     grid may go through the HBM-resident propagator (``resolve_method``), the rest is stepped on the tiled path."""
     n = len(params_list)
+    special = [i for i, p in enumerate(params_list) if p.is_spin_three_half]
+    if special:   # local dimension 4: one call per trajectory (_evolve_pauli); the rest batches as usual
+        rest = [i for i in range(n) if not params_list[i].is_spin_three_half]
+        results, stats_out = [None] * n, [None] * n
+        for i in special:
+            t, out, st = simulate_rare(params_list[i], device=device, method=method, tol_scale=tol_scale,
+                                       return_stats=True, raw_norm=raw_norm)
+            results[i], stats_out[i] = (t, out), st
+        if rest:
+            r, s = simulate_rare_batch([params_list[i] for i in rest], device=device, method=method,
+                                       tol_scale=tol_scale, raw_norm=raw_norm)
+            for j, i in enumerate(rest):
+                results[i], stats_out[i] = r[j], s[j]
+        return results, stats_out
     results: List = [None] * n
     base_grids: Dict[Tuple[float, int], np.ndarray] = {}   # a sweep's trajectories share one grid: build it once
     grids = []

@@ -11,7 +11,7 @@ import sys
 PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libqsb200.so")
-SOURCES = ["qsb_api.cu", "qsb_small.cu", "qsb_large.cu"]
+SOURCES = ["qsb_api.cu", "qsb_small.cu", "qsb_large.cu", "qsb_expect.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",

@@ -13,6 +13,7 @@
 #include <cublas_v2.h>  // types only: the library itself is dlopen-ed on first use (qsb_api_prophbm.inl)
 #include <dlfcn.h>
 
+#include "qsb_expect.cuh"
 #include "qsb_large.cuh"
 #include "qsb_small.cuh"
 
@@ -126,3 +127,4 @@ static int pick_device(int device) {
 }  // namespace qsb
 
 #include "qsb_api_plan.inl"
+#include "qsb_api_expect.inl"

@@ -1,0 +1,187 @@
+// Local dimension 4 (the reference's spin-3/2 rare spin, dipolar_ensemble_with_rare.py:22-25 / :499-501) on two index
+// bits: trajectories whose observables are weighted sums of Pauli strings.  Included from qsb_api.cu.
+//
+// With m = 2 a + b the level index of the four-level site (m = 0 is J_z = +3/2), J_z = 2 I^z_a + I^z_b and
+// J_x = sqrt(3) I^x_b + 2 (I^x_a I^x_b + I^y_a I^y_b): in the frame rotating about J_z by the drive phase the whole
+// Hamiltonian stays inside the same-axis coupling table the integrator kernels take, so the time evolution runs through
+// the existing kernels unchanged.  What they cannot produce is <J_x>, <J_y> (two-bit strings, one of them mixed-axis):
+// the state-storing matvec chain of the propagator path (n <= 10) or a session's vector (n > 10) is handed to
+// launch_expect (qsb_expect.cu) instead of the fused mask-based observable sums.
+
+static int stage_terms(const qsb_pauli_term* terms, int32_t n_terms, int n_qubits, std::vector<ExpectTerm>* out,
+                       int* column_begin /* [7] */) {
+  if (!terms || n_terms < 1 || n_terms > EXPECT_MAX_TERMS)
+    return fail(QSB_ERR_BAD_ARG, "need 1 .. " + std::to_string(EXPECT_MAX_TERMS) + " Pauli terms");
+  const uint64_t all = (n_qubits >= 64) ? ~0ull : ((1ull << n_qubits) - 1);
+  for (int c = 0; c < 7; ++c) column_begin[c] = 0;
+  for (int t = 0; t < n_terms; ++t) {
+    const qsb_pauli_term& e = terms[t];
+    if ((e.x_mask | e.z_mask) & ~all) return fail(QSB_ERR_BAD_ARG, "Pauli term " + std::to_string(t) + " touches bits above n_qubits");
+    if (e.column < 0 || e.column > 5) return fail(QSB_ERR_BAD_ARG, "Pauli term " + std::to_string(t) + ": column must be 0 .. 5");
+    if (!std::isfinite(e.weight)) return fail(QSB_ERR_BAD_ARG, "Pauli term " + std::to_string(t) + ": non-finite weight");
+    ++column_begin[e.column + 1];
+  }
+  for (int c = 0; c < 6; ++c) column_begin[c + 1] += column_begin[c];
+  out->resize((size_t)n_terms);
+  int fill[6];
+  for (int c = 0; c < 6; ++c) fill[c] = column_begin[c];
+  for (int t = 0; t < n_terms; ++t) {  // counting sort by column: terms of one column keep the caller's order
+    const qsb_pauli_term& e = terms[t];
+    ExpectTerm& d = (*out)[(size_t)fill[e.column]++];
+    d.x_mask = e.x_mask; d.z_mask = e.z_mask; d.weight = e.weight; d.column = e.column;
+    d.ny = __builtin_popcountll(e.x_mask & e.z_mask) & 3;
+  }
+  return QSB_OK;
+}
+
+namespace {
+struct ExpectScratch {  // device buffers, events and the stream of one qsb_propagate_expect call
+  cudaStream_t st = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  std::vector<void*> bufs;
+  int get(size_t bytes, void** out) {
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return fail(QSB_ERR_OOM, "cudaMalloc of " + std::to_string(bytes) + " bytes failed: " + cudaGetErrorString(e));
+    }
+    bufs.push_back(p);
+    *out = p;
+    return QSB_OK;
+  }
+  ~ExpectScratch() {
+    if (st) cudaStreamSynchronize(st);
+    for (void* p : bufs) cudaFree(p);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (st) cudaStreamDestroy(st);
+  }
+};
+}  // namespace
+
+extern "C" {
+
+int qsb_propagate_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt, const qsb_solver_opts* opts,
+                         int32_t max_squarings, const qsb_pauli_term* terms, int32_t n_terms, int32_t obs_by_column,
+                         double* out_obs, qsb_stats* stats, int device) {
+  if (!table || !opts || !out_obs || n_out < 1) return fail(QSB_ERR_BAD_ARG, "qsb_propagate_expect: null argument or n_out < 1");
+  int rc = check_table(table);
+  if (rc) return rc;
+  rc = check_opts(opts);
+  if (rc) return rc;
+  const int n = table->n_qubits;
+  if (n > QSB_SMALL_MAX_QUBITS)
+    return fail(QSB_ERR_UNSUPPORTED, "qsb_propagate_expect handles n_qubits <= " + std::to_string(QSB_SMALL_MAX_QUBITS) +
+                                         " (larger: a session with qsb_session_expect)");
+  if (psi0_index >> n) return fail(QSB_ERR_BAD_ARG, "psi0_index out of range");
+  if (!(dt > 0.0) || !std::isfinite(dt)) return fail(QSB_ERR_BAD_ARG, "dt must be finite and > 0");
+  std::vector<ExpectTerm> staged;
+  int column_begin[7];
+  rc = stage_terms(terms, n_terms, n, &staged, column_begin);
+  if (rc) return rc;
+  const size_t dim = (size_t)1 << n;
+  const int nb = expect_blocks(dim);
+  if ((double)n_out * (double)dim * sizeof(cplx) > 16.0 * 1073741824.0 || (double)n_out * nb > 2.0e9)
+    return fail(QSB_ERR_UNSUPPORTED, "qsb_propagate_expect keeps every output state in device memory: n_out * 2^n * 16 bytes must stay below 16 GiB");
+  rc = pick_device(device);
+  if (rc) return rc;
+
+  std::vector<SmallStats> hs(dim);  // declared before `sc`: its destructor drains the stream that copies into it
+  ExpectScratch sc;
+  QSB_CUDA(cudaStreamCreateWithFlags(&sc.st, cudaStreamNonBlocking));
+  QSB_CUDA(cudaEventCreate(&sc.e0));
+  QSB_CUDA(cudaEventCreate(&sc.e1));
+  cudaStream_t st = sc.st;
+  const size_t u_bytes = sizeof(cplx) * dim * dim;
+  SmallDesc* d_desc = nullptr;
+  double *d_t = nullptr, *d_partials = nullptr, *d_obs = nullptr;
+  SmallStats* d_stats = nullptr;
+  cplx *d_u = nullptr, *d_tmp = nullptr, *d_states = nullptr;
+  int32_t* d_sq = nullptr;
+  ExpectTerm* d_terms = nullptr;
+  int32_t s = max_squarings == 0 ? 0 : auto_squarings(table, dt);
+  if (max_squarings > 0 && s > max_squarings) s = max_squarings;
+  if ((rc = sc.get(sizeof(SmallDesc), (void**)&d_desc))) return rc;
+  if ((rc = sc.get(sizeof(double) * 2, (void**)&d_t))) return rc;
+  if ((rc = sc.get(sizeof(SmallStats) * dim, (void**)&d_stats))) return rc;
+  if ((rc = sc.get(u_bytes, (void**)&d_u))) return rc;
+  if (s > 0) {
+    if ((rc = sc.get(u_bytes, (void**)&d_tmp))) return rc;
+    if ((rc = sc.get(sizeof(int32_t), (void**)&d_sq))) return rc;
+  }
+  if ((rc = sc.get(sizeof(cplx) * dim * (size_t)n_out, (void**)&d_states))) return rc;
+  if ((rc = sc.get(sizeof(ExpectTerm) * staged.size(), (void**)&d_terms))) return rc;
+  if ((rc = sc.get(sizeof(double) * 8 * (size_t)nb * (size_t)n_out, (void**)&d_partials))) return rc;
+  if ((rc = sc.get(sizeof(double) * QSB_NOBS * (size_t)n_out, (void**)&d_obs))) return rc;
+
+  SmallDesc desc;
+  compile_small(table, psi0_index, opts, 1, &desc);
+  const double tp[2] = {0.0, std::ldexp(dt, -s)};
+  QSB_CUDA(cudaMemcpyAsync(d_desc, &desc, sizeof desc, cudaMemcpyHostToDevice, st));
+  QSB_CUDA(cudaMemcpyAsync(d_t, tp, sizeof tp, cudaMemcpyHostToDevice, st));
+  QSB_CUDA(cudaMemcpyAsync(d_terms, staged.data(), sizeof(ExpectTerm) * staged.size(), cudaMemcpyHostToDevice, st));
+  if (s > 0) QSB_CUDA(cudaMemcpyAsync(d_sq, &s, sizeof s, cudaMemcpyHostToDevice, st));
+  QSB_CUDA(cudaEventRecord(sc.e0, st));
+  launch_small_columns(d_desc, 1, n, d_t, d_stats, d_u, st);  // U^(1 / 2^s), one CTA per column
+  QSB_CUDA(cudaGetLastError());
+  if (s > 0) {
+    launch_small_square(d_u, d_tmp, d_sq, 1, n, st);
+    QSB_CUDA(cudaGetLastError());
+  }
+  rc = launch_small_propagate(d_desc, 1, n, d_u, n_out, nullptr, 0, st, nullptr, 1, n_out, d_states);  // psi_k = U psi_{k-1}, kept
+  if (rc) return rc;
+  if (obs_by_column) launch_expect(d_states, n_out, dim, d_terms, (int)staged.size(), column_begin, d_partials, d_obs, 1, n_out, st);
+  else launch_expect(d_states, n_out, dim, d_terms, (int)staged.size(), column_begin, d_partials, d_obs, QSB_NOBS, 1, st);
+  QSB_CUDA(cudaGetLastError());
+  QSB_CUDA(cudaEventRecord(sc.e1, st));
+  QSB_CUDA(cudaMemcpyAsync(hs.data(), d_stats, sizeof(SmallStats) * dim, cudaMemcpyDeviceToHost, st));
+  QSB_CUDA(cudaMemcpyAsync(out_obs, d_obs, sizeof(double) * QSB_NOBS * (size_t)n_out, cudaMemcpyDeviceToHost, st));
+  QSB_CUDA(cudaStreamSynchronize(st));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, sc.e0, sc.e1);
+  qsb_stats acc = {0, 0, 0, 0.0, (double)ms, 4, QSB_OK};
+  for (size_t c = 0; c < dim; ++c) {
+    acc.n_accepted += hs[c].n_accepted; acc.n_rejected += hs[c].n_rejected; acc.n_rhs += hs[c].n_rhs;
+    acc.last_h = hs[c].last_h;
+    if (hs[c].status != QSB_OK && acc.status == QSB_OK) acc.status = hs[c].status;
+  }
+  if (stats) *stats = acc;
+  if (acc.status != QSB_OK)
+    return fail(acc.status, acc.status == QSB_ERR_NSTEPS
+                                ? "propagator column: more than nsteps internal steps inside one output interval (excess work)"
+                                : "propagator column: step size underflow");
+  return QSB_OK;
+}
+
+int qsb_session_expect(qsb_plan* p, const qsb_pauli_term* terms, int32_t n_terms, double* obs) {
+  if (!p || !p->ses || !obs) return fail(QSB_ERR_BAD_ARG, "no open session or null obs");
+  if (p->world > 1) return fail(QSB_ERR_UNSUPPORTED, "qsb_session_expect: not available on sharded plans");
+  std::vector<ExpectTerm> staged;
+  int column_begin[7];
+  int rc = stage_terms(terms, n_terms, p->n, &staged, column_begin);
+  if (rc) return rc;
+  QSB_CUDA(cudaSetDevice(p->device));
+  const uint64_t dim = 1ull << p->n;  // amplitudes above 2^n (spectator padding of plans below 12 qubits) are zero
+  const int nb = expect_blocks(dim);
+  const size_t terms_bytes = (sizeof(ExpectTerm) * staged.size() + 255) & ~size_t(255);
+  const size_t part_bytes = sizeof(double) * 8 * (size_t)nb;
+  char* d_all = nullptr;
+  cudaError_t e = cudaMalloc((void**)&d_all, terms_bytes + part_bytes + sizeof(double) * QSB_NOBS);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(QSB_ERR_OOM, std::string("qsb_session_expect: cudaMalloc failed: ") + cudaGetErrorString(e));
+  }
+  struct Free { char* p; cudaStream_t s; ~Free() { cudaStreamSynchronize(s); cudaFree(p); } } guard{d_all, p->stream};
+  ExpectTerm* d_terms = (ExpectTerm*)d_all;
+  double* d_partials = (double*)(d_all + terms_bytes);
+  double* d_out = (double*)(d_all + terms_bytes + part_bytes);
+  QSB_CUDA(cudaMemcpyAsync(d_terms, staged.data(), sizeof(ExpectTerm) * staged.size(), cudaMemcpyHostToDevice, p->stream));
+  launch_expect(p->ses->y, 1, dim, d_terms, (int)staged.size(), column_begin, d_partials, d_out, QSB_NOBS, 1, p->stream);
+  QSB_CUDA(cudaGetLastError());
+  QSB_CUDA(cudaMemcpyAsync(obs, d_out, sizeof(double) * QSB_NOBS, cudaMemcpyDeviceToHost, p->stream));
+  QSB_CUDA(cudaStreamSynchronize(p->stream));
+  return QSB_OK;
+}
+
+}  // extern "C"

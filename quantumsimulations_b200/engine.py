@@ -55,6 +55,13 @@ class _Stats(C.Structure):
                 ("device_ms", C.c_double), ("path", C.c_int32), ("status", C.c_int32)]
 
 
+class _PauliTerm(C.Structure):
+    _fields_ = [("x_mask", C.c_uint64), ("z_mask", C.c_uint64), ("weight", C.c_double), ("column", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
+MAX_PAULI_TERMS = 512
+
 EXPORTS = (
     "qsb_version", "qsb_last_error", "qsb_device_count", "qsb_plan_create", "qsb_plan_destroy",
     "qsb_plan_workspace_bytes", "qsb_plan_set_workspace", "qsb_evolve", "qsb_evolve_batch", "qsb_apply_h",
@@ -63,6 +70,7 @@ EXPORTS = (
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_shard_set_stream_barrier", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather", "qsb_local_stream_barrier",
     "qsb_propagate_batch", "qsb_propagate_hbm", "qsb_release_caches", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
+    "qsb_propagate_expect", "qsb_session_expect",
 )
 
 SHARD_BLOB_BYTES = 96
@@ -103,6 +111,9 @@ def load_library() -> C.CDLL:
     lib.qsb_build_propagator.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(_Opts), C.c_int32, dp,
                                          C.POINTER(_Stats), C.c_int]
     lib.qsb_debug_squarings.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(C.c_int32)]
+    lib.qsb_propagate_expect.argtypes = [C.POINTER(_Table), C.c_uint64, C.c_int64, C.c_double, C.POINTER(_Opts), C.c_int32,
+                                         C.POINTER(_PauliTerm), C.c_int32, C.c_int32, dp, C.POINTER(_Stats), C.c_int]
+    lib.qsb_session_expect.argtypes = [vp, C.POINTER(_PauliTerm), C.c_int32, dp]
     lib.qsb_debug_propagate_shape.argtypes = [C.c_int32, C.POINTER(C.c_int32)]
     lib.qsb_apply_h.argtypes = [vp, dp, dp]
     lib.qsb_apply_h_static.argtypes = [vp, dp, dp]
@@ -377,6 +388,15 @@ class Plan:
         _check(self.lib.qsb_session_observe(self._h, _dptr(obs)))
         return obs
 
+    def session_expect(self, terms) -> np.ndarray:
+        """The NOBS columns of the session's current state with the six observables given as weighted Pauli strings
+        ``(x_mask, z_mask, weight, column)`` (qsb_session_expect; what a local-dimension-4 table's trajectory reads
+        instead of ``session_observe``)."""
+        cterms = _pauli_terms(terms)
+        obs = np.empty(NOBS, dtype=np.float64)
+        _check(self.lib.qsb_session_expect(self._h, cterms, len(cterms), _dptr(obs)))
+        return obs
+
     def session_state(self) -> np.ndarray:
         out = np.empty(self.local_dim, dtype=np.complex128)
         _check(self.lib.qsb_session_state(self._h, _dptr(out.view(np.float64))))
@@ -516,6 +536,35 @@ def propagate_hbm(table: SpinTable, n_out: int, dt: float, opts: SolverOptions, 
     obs = np.empty((NOBS, int(n_out)) if by_column else (int(n_out), NOBS), dtype=np.float64)
     _check(lib.qsb_propagate_hbm(C.byref(holder.c), table.psi0_index, int(n_out), float(dt), C.byref(copts),
                                  _max_squarings(max_squarings), 1 if by_column else 0, _dptr(obs), C.byref(st), int(device)))
+    return obs, Stats.from_c(st)
+
+
+def _pauli_terms(terms):
+    """ctypes array of qsb_pauli_term from (x_mask, z_mask, weight, column) tuples."""
+    terms = list(terms)
+    if not 1 <= len(terms) <= MAX_PAULI_TERMS:
+        raise ValueError(f"need 1 .. {MAX_PAULI_TERMS} Pauli terms")
+    return (_PauliTerm * len(terms))(*[_PauliTerm(int(xm), int(zm), float(w), int(col), 0) for xm, zm, w, col in terms])
+
+
+def propagate_expect(table: SpinTable, n_out: int, dt: float, opts: SolverOptions, device: int = 0,
+                     max_squarings: Optional[int] = None, by_column: bool = False, terms=None):
+    """``propagate_batch`` for ONE trajectory whose six observables are weighted Pauli strings (``terms``, default
+    ``table.pauli_terms``: a local-dimension-4 table, n <= 10 bits) - qsb_propagate_expect: U built as usual, the chain
+    keeps every state on the device, one kernel reduces the strings.  Returns (obs [n_out, NOBS] or [NOBS, n_out] with
+    ``by_column``, Stats)."""
+    lib = load_library()
+    terms = table.pauli_terms if terms is None else terms
+    if terms is None:
+        raise ValueError("the table carries no Pauli-string observables")
+    cterms = _pauli_terms(terms)
+    holder = _TableHolder(table)
+    copts = opts.to_c()
+    st = _Stats()
+    obs = np.empty((NOBS, int(n_out)) if by_column else (int(n_out), NOBS), dtype=np.float64)
+    _check(lib.qsb_propagate_expect(C.byref(holder.c), table.psi0_index, int(n_out), float(dt), C.byref(copts),
+                                    _max_squarings(max_squarings), cterms, len(cterms), 1 if by_column else 0, _dptr(obs),
+                                    C.byref(st), int(device)))
     return obs, Stats.from_c(st)
 
 

@@ -18,13 +18,28 @@ so the table is three length-N field vectors and three strictly-upper-triangular
 
 Index convention (DE:43-45, appendix A.1): site 0 is the most significant tensor factor, i.e. site k
 is bit N-1-k of the amplitude index; bit value 0 <-> Iz = +1/2.
+
+Local dimension 4 (``is_spin_three_half=True``: the J = 3/2 rare spin of DE:22-25, DE:499-501).  The reference's builder
+cannot run it (DE:486 forces every local dimension to 2 while DE:499-501 pick the 4 x 4 operators); what is
+compiled here is that builder with DE:486 repaired to ``dims_with_rare(n_sea, is_spin_three_half)`` - the reading its
+own ``initial_state_rare`` (DE:602-603) and ``dims_with_rare`` docstring (DE:28-34) imply.  The four-level site is the
+LAST tensor factor, i.e. the two lowest index bits a = bit 1, b = bit 0 with level m = 2a + b, m = 0 <-> J_z = +3/2:
+
+    J_z = 2 Iz_a + Iz_b      J_x = sqrt(3) Ix_b + 2 (Ix_a Ix_b + Iy_a Iy_b)      J_y = sqrt(3) Iy_b + 2 (Iy_a Ix_b - Ix_a Iy_b)
+
+J_y is a mixed-axis pair term, outside the table's form; but exp(-i phi_R J_z) commutes with every other term of H, so in
+the frame rotating about J_z by the drive phase, H' = R^dagger H R with R = exp(-i phi_R J_z) (diagonal in the index
+basis), the rare drive w1R (cos phi_R J_x + sin phi_R J_y) (DE:523-528) is w1R J_x and H' is an ordinary SpinTable on
+n_sea + 2 bits.  psi(t) = R exp(-i H' t) R^dagger psi0, and psi0 is a basis state (DE:599-603), which R^dagger only
+multiplies by a phase.  The observables of the lab frame become weighted Pauli strings in the rotated one
+(``SpinTable.pauli_terms``): R^dagger J_x R = cos phi_R J_x - sin phi_R J_y, R^dagger J_y R = sin phi_R J_x + cos phi_R J_y.
 """
 from __future__ import annotations
 
 import functools
 
 from dataclasses import dataclass, field
-from typing import Dict, List
+from typing import Dict, List, Optional, Tuple
 
 import numpy as np
 
@@ -50,6 +65,11 @@ class SpinTable:
     sea_sites: List[int] = field(default_factory=list)   # sites summed into the *_sea observables
     rare_site: int = 0                                   # site of the *_R observables
     psi0_index: int = 0                                  # computational-basis index of psi(0)
+    # Local dimension 4 (module docstring): the six observables as weighted Pauli strings (x_mask, z_mask, weight,
+    # column) in the table's own (rotated) frame - taken instead of the mask-based sums when present - and the drive
+    # phase phi_R of the frame, lab = R table R^dagger with R[x] = exp(-i phi_R (3/2 - (x & 3))).
+    pauli_terms: Optional[List[Tuple[int, int, float, int]]] = None
+    frame_phi: Optional[float] = None
 
     # ---- helpers shared by host code and tests ------------------------------------------------
     def bit_of_site(self, k: int) -> int:
@@ -91,6 +111,13 @@ class SpinTable:
             J[a] = full[np.ix_(perm, perm)]
         return {"h": np.ascontiguousarray(h), "J": np.ascontiguousarray(J)}
 
+    def frame_phases(self) -> Optional[np.ndarray]:
+        """Diagonal of R = exp(-i phi_R J_z) for a local-dimension-4 table (None otherwise): H_lab = R H_table R^dagger."""
+        if self.frame_phi is None:
+            return None
+        x = np.arange(self.dim)
+        return np.exp(-1j * self.frame_phi * (1.5 - (x & 3)))
+
     def spectral_bound(self) -> float:
         """Cheap upper bound on ||H||_2 (sum of term norms); used for step-size sanity checks only."""
         s = 0.5 * float(np.sum(np.sqrt(self.hx**2 + self.hy**2)) + np.sum(np.abs(self.hz)))
@@ -130,15 +157,78 @@ def _couplings(n_shell: int, shell_scale: float, dipolar_scale: float, gamma_sea
     return b
 
 
+def spin32_observable_terms(n_sea: int, phi_rare: float) -> List[Tuple[int, int, float, int]]:
+    """The six observables of DE:573-587 for n_sea spin-1/2 sites + one four-level site on bits (1, 0), as weighted Pauli
+    strings (x_mask, z_mask, weight, column) in the frame rotating about J_z by phi_rare (module docstring).  A bit in
+    both masks carries Y; <I^a_k> = <sigma^a_k> / 2; columns 0 .. 5 = Ix_sea, Iy_sea, Iz_sea, Iz_R, Ix_R, Iy_R."""
+    n = n_sea + 2
+    terms: List[Tuple[int, int, float, int]] = []
+    for k in range(n_sea):
+        bit = 1 << (n - 1 - k)
+        terms += [(bit, 0, 0.5, 0), (bit, bit, 0.5, 1), (0, bit, 0.5, 2)]
+    a, b = 2, 1
+    terms += [(0, a, 1.0, 3), (0, b, 0.5, 3)]                                  # J_z = 2 Iz_a + Iz_b
+    r3 = 0.5 * np.sqrt(3.0)
+    jx = [(b, 0, r3), (a | b, 0, 0.5), (a | b, a | b, 0.5)]                    # sqrt(3) Ix_b + 2 (Ix_a Ix_b + Iy_a Iy_b)
+    jy = [(b, b, r3), (a | b, a, 0.5), (a | b, b, -0.5)]                       # sqrt(3) Iy_b + 2 (Iy_a Ix_b - Ix_a Iy_b)
+    c, s = float(np.cos(phi_rare)), float(np.sin(phi_rare))
+    terms += [(xm, zm, w * c, 4) for xm, zm, w in jx] + [(xm, zm, -w * s, 4) for xm, zm, w in jy]
+    terms += [(xm, zm, w * s, 5) for xm, zm, w in jx] + [(xm, zm, w * c, 5) for xm, zm, w in jy]
+    return terms
+
+
+def _compile_spin32(params: DipolarRareParams) -> SpinTable:
+    """``compile_table`` for the J = 3/2 rare spin: n_sea + 2 bits, rotated frame (module docstring)."""
+    if not params.is_center_rare:
+        # DE:486 gives the centre local dimension 4 exactly when it is NOT the rare spin, and DE:507 / DE:552-557 then
+        # embed 2 x 2 sea operators there: no reading of that combination is a spin model.
+        raise NotImplementedError(
+            "is_spin_three_half=True needs is_center_rare=True (the sea-centre control has no spin-3/2 site; "
+            "the reference's own dims for it are inconsistent, DE:486 vs DE:507)"
+        )
+    n_sea = params.n_sea
+    n = n_sea + 2
+    sa, sb = n_sea, n_sea + 1                      # sites of the two bits of the four-level site: a = bit 1, b = bit 0
+    fr = get_derived_frequencies(params)
+    w1a, w1r = fr["omega1_sea"], fr["omega1_rare"]
+    da, dr = fr["delta_sea"], fr["delta_rare"]
+    hx, hy, hz = np.zeros(n), np.zeros(n), np.zeros(n)
+    jxx, jyy = np.zeros((n, n)), np.zeros((n, n))
+    if params.drive_sea and da != 0.0:                       # DE:505-508
+        hz[:n_sea] += da
+    if params.drive_rare and dr != 0.0:                      # DE:510-512 with J_z = 2 Iz_a + Iz_b
+        hz[sa] += 2.0 * dr
+        hz[sb] += dr
+    if params.drive_sea and w1a != 0.0:                      # DE:515-519
+        hx[:n_sea] += w1a * np.cos(params.phi_sea)
+        hy[:n_sea] += w1a * np.sin(params.phi_sea)
+    if params.drive_rare and w1r != 0.0:                     # DE:523-528 in the rotated frame: w1R J_x
+        hx[sb] += np.sqrt(3.0) * w1r
+        jxx[sa, sb] += 2.0 * w1r
+        jyy[sa, sb] += 2.0 * w1r
+    b = _couplings(n_sea, float(params.shell_scale), float(params.dipolar_scale), float(params.gamma_sea),
+                   float(params.gamma_rare))
+    jzz = np.zeros((n, n))
+    jzz[:n_sea, :n_sea] = np.triu(b[:n_sea, :n_sea], 1)      # DE:559-561
+    jyy[:n_sea, :n_sea] = 0.25 * jzz[:n_sea, :n_sea]
+    jxx[:n_sea, :n_sea] = -jyy[:n_sea, :n_sea]
+    jzz[:n_sea, sa] = 2.0 * b[:n_sea, n_sea]                 # DE:563-568: b_iR Iz_i J_z
+    jzz[:n_sea, sb] = b[:n_sea, n_sea]
+    sea_bit = 0 if params.init_x_sign >= 0 else 1            # DE:71-72, DE:599
+    level = 0 if (-params.init_x_sign) >= 0 else 3           # DE:99, DE:602: J_z = +3/2 or -3/2
+    idx = 0
+    for _ in range(n_sea):
+        idx = (idx << 1) | sea_bit
+    idx = (idx << 2) | level
+    return SpinTable(n=n, hx=hx, hy=hy, hz=hz, jxx=jxx, jyy=jyy, jzz=jzz, sea_sites=list(range(n_sea)), rare_site=sb,
+                     psi0_index=idx, pauli_terms=spin32_observable_terms(n_sea, float(params.phi_rare)),
+                     frame_phi=float(params.phi_rare))
+
+
 def compile_table(params: DipolarRareParams) -> SpinTable:
     """Compile the reference's Hamiltonian/observable/initial-state recipe (DE:483-606) into a SpinTable."""
     if params.is_spin_three_half:
-        # DE:486/DE:499-501 build operators of inconsistent dimension for spin-3/2 (SURVEY C.1): the
-        # reference itself cannot run it.  Refuse loudly instead of silently substituting spin-1/2.
-        raise NotImplementedError(
-            "is_spin_three_half=True is not runnable in the reference either (operator dimensions "
-            "disagree, DE:486 vs DE:499-501); pass is_spin_three_half=False."
-        )
+        return _compile_spin32(params)
     n_shell = params.n_sea
     n = n_shell + 1
     rare = n_shell

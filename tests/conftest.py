@@ -25,6 +25,14 @@ def golden_cases():
 
 
 @pytest.fixture(scope="session")
+def golden_spin32():
+    """Fixtures the reference's own code produced with its dims repaired (oracle/make_goldens_spin32.py)."""
+    with open(os.path.join(GOLDEN, "spin32_cases.json")) as f:
+        meta = json.load(f)
+    return meta, np.load(os.path.join(GOLDEN, "spin32_cases.npz"))
+
+
+@pytest.fixture(scope="session")
 def golden_hams():
     return np.load(os.path.join(GOLDEN, "hamiltonians.npz"))
 
@@ -60,6 +68,11 @@ def exact_traces(table, t):
     psi0[table.psi0_index] = 1.0
     states = solvers.exact_states(H, psi0, np.asarray(t))
     keys = ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R")
+    if table.pauli_terms is not None:      # local dimension 4: the observables are weighted Pauli strings
+        from oracle import pauli
+
+        cols = pauli.expect_terms(states, table.pauli_terms)
+        return {k: cols[i].copy() for i, k in enumerate(keys)}
     out = {k: np.empty(len(t)) for k in keys}
     for i in range(len(t)):
         o = dense.observable_sums(states[:, i], table.sea_mask, table.rare_mask)

@@ -49,8 +49,8 @@ def test_error_behaviour_matches_reference():
         q.simulate_rare(q.DipolarRareParams(n_sea=6, is_spin_three_half=False, steps=1))
     with pytest.raises(ValueError, match="Bad time grid"):
         q.simulate_rare(q.DipolarRareParams(n_sea=6, is_spin_three_half=False, t_final=0.0))
-    with pytest.raises(NotImplementedError):
-        q.compile_table(q.DipolarRareParams())          # spin-3/2 default cannot run in the reference either
+    with pytest.raises(NotImplementedError, match="is_center_rare"):
+        q.compile_table(q.DipolarRareParams(is_center_rare=False))   # spin-3/2 without a rare site: no spin model (DE:486 vs DE:507)
 
 
 def test_geometry_shapes_and_symmetry():
