@@ -12,6 +12,8 @@ unmodified code on top of ``oracle/fake_qutip`` (exact propagation).  The fixtur
 and the traces of the local-dimension-4 row; like every other fixture they leave the integrator half unpinned.
 
   spin32_cases.json / spin32_cases.npz   params + (t, 7 traces) per case, CSR of H + psi0 index for the small ones
+  sweep_small_spin32.json                global_params / metrics rows / file listing of one sweep through the
+                                         reference's unchanged driver with is_spin_three_half=True (see ``sweep_golden``)
 """
 from __future__ import annotations
 
@@ -19,13 +21,14 @@ import dataclasses
 import json
 import os
 import sys
+import tempfile
 
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from oracle import ref_loader  # noqa: E402
-from oracle.make_goldens import GOLD, TRACE_KEYS, sweep_point  # noqa: E402
+from oracle.make_goldens import B0_T, F1A, G_RARE, G_SEA, GOLD, TRACE_KEYS, sweep_point  # noqa: E402
 
 
 def load_repaired_reference():
@@ -69,6 +72,42 @@ def case_list(ref):
     return cases
 
 
+def sweep_golden(ref):
+    """One sweep through the reference's UNMODIFIED ``run_sweep_sea_detuning`` (SW:356-1165) at its function-default grid
+    with ``is_spin_three_half=True``.  Its two rare-centre variants run ``ref.simulate_rare`` with the dims repaired.  Its
+    sea-centre control (``is_center_rare=False``, SW:640-668) has no rare spin: the centre is one more sea spin 1/2
+    (DE:488-489), the reference's own rare observables for it mix 4 x 4 operators into all-2 dims (DE:499-501 /
+    DE:576-578) under any repair, so that variant runs the unrepaired reference with the meaningless flag off - the
+    semantics ``quantumsimulations_b200.table.local_dim4`` states.  Only ``sw.simulate_rare`` is rebound."""
+    sw = ref_loader.load_reference_sweep()
+    original = sw.simulate_rare
+
+    def simulate(params):
+        if params.is_center_rare:
+            return ref.simulate_rare(params)
+        restore_reference(ref)
+        try:
+            return ref.simulate_rare(dataclasses.replace(params, is_spin_three_half=False))
+        finally:
+            load_repaired_reference()
+
+    sw.simulate_rare = simulate
+    try:
+        with tempfile.TemporaryDirectory() as tmp:
+            base = sw.run_sweep_sea_detuning(
+                f_Az=G_SEA * B0_T / (2 * np.pi), f1A=F1A, target_sea_detuning=F1A, gamma_sea=G_SEA, gamma_rare=G_RARE,
+                sea_detunings_Hz=np.linspace(0.0, 3.0 * F1A, 13), n_sea=6, phi_sea=np.pi / 2.0, phi_rare=np.pi / 2.0,
+                out_root=tmp, is_spin_three_half=True, solver_atol=1e-10, solver_rtol=1e-9, solver_nsteps=10_000_000,
+                solver_max_step=1e-5)
+            with open(os.path.join(base, "summary.json")) as f:
+                summary = json.load(f)
+            listing = sorted(os.path.relpath(os.path.join(d, fn), base) for d, _, fns in os.walk(base) for fn in fns)
+    finally:
+        sw.simulate_rare = original
+    with open(os.path.join(GOLD, "sweep_small_spin32.json"), "w") as f:
+        json.dump({"summary": summary, "files": listing}, f, indent=1)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = load_repaired_reference()
@@ -92,6 +131,8 @@ def main():
                 for k, op in obs.items():
                     arrays[f"{name}/op_{k}"] = op.full()
         print(f"{name:28s} Iz_R[1]={out['Iz_R'][1]:+.15f} Ix_R[1]={out['Ix_R'][1]:+.15f}", flush=True)
+    if "--cases-only" not in sys.argv:
+        sweep_golden(ref)
     restore_reference(ref)
     with open(os.path.join(GOLD, "spin32_cases.json"), "w") as f:
         json.dump(meta, f, indent=1, default=float)

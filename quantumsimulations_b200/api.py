@@ -14,7 +14,7 @@ import numpy as np
 
 from . import engine
 from .model import DipolarRareParams
-from .table import SpinTable, compile_table
+from .table import SpinTable, compile_table, local_dim4
 
 TRACE_KEYS = ("Ix_sea", "Iy_sea", "Iz_sea", "Iz_R", "Ix_R", "Iy_R")
 
@@ -190,21 +190,21 @@ def resolve_method(params: DipolarRareParams, method: Optional[str]) -> Tuple[st
     A spin-3/2 rare spin (local dimension 4) has two paths only: N <= 10 bits always goes through the propagator (the
     stepped on-chip kernel cannot report its observables), N > 10 is always stepped (``_evolve_pauli``)."""
     n, steps = _size_of(params)
-    if params.is_spin_three_half:
+    if local_dim4(params):
         integrator, asked = split_method(method)
         if asked and n > engine.SMALL_MAX_QUBITS:
             raise ValueError(f"method 'propagator' with a spin-3/2 rare spin needs n_sea + 2 <= {engine.SMALL_MAX_QUBITS}")
         return integrator, n <= engine.SMALL_MAX_QUBITS
     norm_t = None
     m = method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)
-    if m == "auto" and engine.SMALL_MAX_QUBITS < n <= engine.HBM_PROPAGATOR_MAX_QUBITS and not params.is_spin_three_half:
+    if m == "auto" and engine.SMALL_MAX_QUBITS < n <= engine.HBM_PROPAGATOR_MAX_QUBITS:
         norm_t = compile_table(params).spectral_bound() * float(params.t_final)
     return split_method(method, n, steps, norm_t)
 
 
 def _size_of(params: DipolarRareParams) -> Tuple[int, int]:
     """(index bits, outputs): the spin-3/2 rare spin takes two bits (table.py)."""
-    return params.n_sea + (2 if params.is_spin_three_half else 1), params.steps
+    return params.n_sea + (2 if local_dim4(params) else 1), params.steps
 
 
 def _options_from(params: DipolarRareParams, method: Optional[str], tol_scale: Optional[float] = None
@@ -343,9 +343,9 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
     """Independent trajectories; those with N <= 10 share ONE kernel launch (one CTA each), 11 <= N <= 14 on a uniform
     grid may go through the HBM-resident propagator (``resolve_method``), the rest is stepped on the tiled path."""
     n = len(params_list)
-    special = [i for i, p in enumerate(params_list) if p.is_spin_three_half]
+    special = [i for i, p in enumerate(params_list) if local_dim4(p)]
     if special:   # local dimension 4: one call per trajectory (_evolve_pauli); the rest batches as usual
-        rest = [i for i in range(n) if not params_list[i].is_spin_three_half]
+        rest = [i for i in range(n) if not local_dim4(params_list[i])]
         results, stats_out = [None] * n, [None] * n
         for i in special:
             t, out, st = simulate_rare(params_list[i], device=device, method=method, tol_scale=tol_scale,

@@ -114,14 +114,39 @@ int qsb_propagate_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_
   if ((rc = sc.get(sizeof(ExpectTerm) * staged.size(), (void**)&d_terms))) return rc;
   if ((rc = sc.get(sizeof(double) * 8 * (size_t)nb * (size_t)n_out, (void**)&d_partials))) return rc;
   if ((rc = sc.get(sizeof(double) * QSB_NOBS * (size_t)n_out, (void**)&d_obs))) return rc;
+  // Time-split chain, exactly as in propagate_impl: ~128 segments of 2^seg_lb outputs (a function of n_out only), each
+  // its own CTA, seeded with (U^(2^seg_lb))^c psi_0 from seg_lb more squarings of a copy of U.
+  int seg_lb = 0, n_seg = 1;
+  int64_t seg_len = n_out;
+  if (n_out >= 256) {
+    seg_lb = 6;
+    while (((int64_t)1 << seg_lb) * 128 < n_out) ++seg_lb;
+    if (const char* e = getenv("QSB200_PROP_SEGMENT")) seg_lb = std::max(0, std::min(40, atoi(e)));  // 0: no split
+    if (seg_lb > 0 && ((int64_t)1 << seg_lb) < n_out) {
+      seg_len = (int64_t)1 << seg_lb;
+      n_seg = (int)((n_out + seg_len - 1) / seg_len);
+    } else {
+      seg_lb = 0;
+    }
+  }
+  cplx *d_v = nullptr, *d_seeds = nullptr;
+  int32_t* d_seg_sq = nullptr;
+  if (n_seg > 1) {
+    if ((rc = sc.get(u_bytes, (void**)&d_v))) return rc;
+    if ((rc = sc.get(sizeof(cplx) * dim * (size_t)n_seg, (void**)&d_seeds))) return rc;
+    if ((rc = sc.get(sizeof(int32_t), (void**)&d_seg_sq))) return rc;
+    if (!d_tmp && (rc = sc.get(u_bytes, (void**)&d_tmp))) return rc;
+  }
 
   SmallDesc desc;
   compile_small(table, psi0_index, opts, 1, &desc);
   const double tp[2] = {0.0, std::ldexp(dt, -s)};
+  const int32_t seg_sq = seg_lb;
   QSB_CUDA(cudaMemcpyAsync(d_desc, &desc, sizeof desc, cudaMemcpyHostToDevice, st));
   QSB_CUDA(cudaMemcpyAsync(d_t, tp, sizeof tp, cudaMemcpyHostToDevice, st));
   QSB_CUDA(cudaMemcpyAsync(d_terms, staged.data(), sizeof(ExpectTerm) * staged.size(), cudaMemcpyHostToDevice, st));
   if (s > 0) QSB_CUDA(cudaMemcpyAsync(d_sq, &s, sizeof s, cudaMemcpyHostToDevice, st));
+  if (n_seg > 1) QSB_CUDA(cudaMemcpyAsync(d_seg_sq, &seg_sq, sizeof seg_sq, cudaMemcpyHostToDevice, st));
   QSB_CUDA(cudaEventRecord(sc.e0, st));
   launch_small_columns(d_desc, 1, n, d_t, d_stats, d_u, st);  // U^(1 / 2^s), one CTA per column
   QSB_CUDA(cudaGetLastError());
@@ -129,7 +154,16 @@ int qsb_propagate_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_
     launch_small_square(d_u, d_tmp, d_sq, 1, n, st);
     QSB_CUDA(cudaGetLastError());
   }
-  rc = launch_small_propagate(d_desc, 1, n, d_u, n_out, nullptr, 0, st, nullptr, 1, n_out, d_states);  // psi_k = U psi_{k-1}, kept
+  if (n_seg > 1) {
+    QSB_CUDA(cudaMemcpyAsync(d_v, d_u, u_bytes, cudaMemcpyDeviceToDevice, st));
+    launch_small_square(d_v, d_tmp, d_seg_sq, 1, n, st);                                               // V = U^seg_len
+    QSB_CUDA(cudaGetLastError());
+    rc = launch_small_propagate(d_desc, 1, n, d_v, n_seg, nullptr, 0, st, nullptr, 1, n_seg, d_seeds);  // seeds
+    if (rc) return rc;
+    rc = launch_small_propagate(d_desc, 1, n, d_u, n_out, nullptr, 0, st, d_seeds, n_seg, seg_len, d_states);  // every psi_k, kept
+  } else {
+    rc = launch_small_propagate(d_desc, 1, n, d_u, n_out, nullptr, 0, st, nullptr, 1, n_out, d_states);  // psi_k = U psi_{k-1}, kept
+  }
   if (rc) return rc;
   if (obs_by_column) launch_expect(d_states, n_out, dim, d_terms, (int)staged.size(), column_begin, d_partials, d_obs, 1, n_out, st);
   else launch_expect(d_states, n_out, dim, d_terms, (int)staged.size(), column_begin, d_partials, d_obs, QSB_NOBS, 1, st);

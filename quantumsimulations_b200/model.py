@@ -49,7 +49,7 @@ class DipolarRareParams:
     drive_rare: bool = False
     init_x_sign: int = -1
     init_rare_level: int = 3          # never read by the reference either
-    is_spin_three_half: bool = True   # only False can run, here and in the reference
+    is_spin_three_half: bool = True   # J = 3/2 rare spin: runs here (table.py, two index bits); not in the reference
     is_center_rare: bool = True
     solver_atol: Optional[float] = None
     solver_rtol: Optional[float] = None

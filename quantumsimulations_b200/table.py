@@ -177,15 +177,19 @@ def spin32_observable_terms(n_sea: int, phi_rare: float) -> List[Tuple[int, int,
     return terms
 
 
+def local_dim4(params: DipolarRareParams) -> bool:
+    """True when the parameter record has a four-level site: ``is_spin_three_half`` AND a rare centre.  In the
+    sea-centre control (``is_center_rare=False``, the sweep's "shell_off" variant, SW:640-668) the centre is one more
+    sea spin - a spin 1/2 by definition (DE:488-489 embeds the 2 x 2 sea operators there) - so there is no rare spin for
+    the flag to describe and the record compiles exactly as with ``is_spin_three_half=False``.  (The reference's own
+    observables for that combination mix 4 x 4 operators into all-2 dims, DE:499-501 / DE:576-578: unrunnable under any
+    one-line repair.)"""
+    return bool(params.is_spin_three_half and params.is_center_rare)
+
+
 def _compile_spin32(params: DipolarRareParams) -> SpinTable:
     """``compile_table`` for the J = 3/2 rare spin: n_sea + 2 bits, rotated frame (module docstring)."""
-    if not params.is_center_rare:
-        # DE:486 gives the centre local dimension 4 exactly when it is NOT the rare spin, and DE:507 / DE:552-557 then
-        # embed 2 x 2 sea operators there: no reading of that combination is a spin model.
-        raise NotImplementedError(
-            "is_spin_three_half=True needs is_center_rare=True (the sea-centre control has no spin-3/2 site; "
-            "the reference's own dims for it are inconsistent, DE:486 vs DE:507)"
-        )
+    assert local_dim4(params)
     n_sea = params.n_sea
     n = n_sea + 2
     sa, sb = n_sea, n_sea + 1                      # sites of the two bits of the four-level site: a = bit 1, b = bit 0
@@ -227,7 +231,7 @@ def _compile_spin32(params: DipolarRareParams) -> SpinTable:
 
 def compile_table(params: DipolarRareParams) -> SpinTable:
     """Compile the reference's Hamiltonian/observable/initial-state recipe (DE:483-606) into a SpinTable."""
-    if params.is_spin_three_half:
+    if local_dim4(params):
         return _compile_spin32(params)
     n_shell = params.n_sea
     n = n_shell + 1

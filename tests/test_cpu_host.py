@@ -49,8 +49,9 @@ def test_error_behaviour_matches_reference():
         q.simulate_rare(q.DipolarRareParams(n_sea=6, is_spin_three_half=False, steps=1))
     with pytest.raises(ValueError, match="Bad time grid"):
         q.simulate_rare(q.DipolarRareParams(n_sea=6, is_spin_three_half=False, t_final=0.0))
-    with pytest.raises(NotImplementedError, match="is_center_rare"):
-        q.compile_table(q.DipolarRareParams(is_center_rare=False))   # spin-3/2 without a rare site: no spin model (DE:486 vs DE:507)
+    # spin-3/2 flag on the sea-centre control: there is no rare spin, the record compiles as spin 1/2 (table.local_dim4)
+    ctl = q.compile_table(q.DipolarRareParams(n_sea=4, is_center_rare=False))
+    assert ctl.n == 5 and ctl.pauli_terms is None and ctl.frame_phi is None
 
 
 def test_geometry_shapes_and_symmetry():
@@ -200,8 +201,8 @@ def test_replay_shim_batches_an_unchanged_script(tmp_path):
     assert float(open(os.path.join(out, "out.txt")).read()) == pytest.approx(1e-3 * 10)
 
 
-def _check_sweep_dir_against_golden(base, rel_slope=1e-7):
-    with open(os.path.join(GOLDEN, "sweep_small.json")) as f:
+def _check_sweep_dir_against_golden(base, rel_slope=1e-7, golden="sweep_small.json"):
+    with open(os.path.join(GOLDEN, golden)) as f:
         gold = json.load(f)
     with open(os.path.join(base, "summary.json")) as f:
         mine = json.load(f)
@@ -246,6 +247,30 @@ def test_unchanged_reference_sweep_script_runs_on_the_dropin(tmp_path):
     assert info["bound"] == {"simulate_rare": True, "params": True, "freqs": True, "model_module_is_dropin": True,
                              "qutip_imported": False}
     mine, gold = _check_sweep_dir_against_golden(info["base"])
+    for got, want in zip(mine["sweep_results"], gold["summary"]["sweep_results"]):
+        for k in ("contrast_rare_center", "contrast_sea_center"):
+            assert got[k] == pytest.approx(want[k], rel=1e-6, abs=1e-12), k
+
+
+def test_unchanged_reference_sweep_script_runs_with_a_spin_three_half_rare_spin(tmp_path):
+    """The same unmodified script with ``is_spin_three_half=True`` (SW:370, SW:651 hand the flag to every parameter
+    record): one batch of 39 through the drop-in, whose rare-centre variants compile to the two-bit four-level site
+    (table.py) and whose sea-centre control has no rare spin; summary and file set equal what the reference's own
+    driver wrote on top of its model with the dims repaired (tests/golden/sweep_small_spin32.json,
+    oracle/make_goldens_spin32.py)."""
+    import subprocess
+
+    from oracle import ref_loader
+
+    if not ref_loader.reference_available():
+        pytest.skip("reference checkout not present")
+    res = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "run_reference_sweep_on_dropin.py"), str(tmp_path), "oracle",
+                          "spin32"], capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
+    info = json.loads([ln for ln in res.stdout.splitlines() if ln.startswith("{")][-1])
+    assert info["calls"] == [39] and info["bound"]["simulate_rare"] and not info["bound"]["qutip_imported"]
+    mine, gold = _check_sweep_dir_against_golden(info["base"], golden="sweep_small_spin32.json")
+    assert mine["global_params"]["rare_spin_type"] == "3/2"
     for got, want in zip(mine["sweep_results"], gold["summary"]["sweep_results"]):
         for k in ("contrast_rare_center", "contrast_sea_center"):
             assert got[k] == pytest.approx(want[k], rel=1e-6, abs=1e-12), k

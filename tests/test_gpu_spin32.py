@@ -123,3 +123,82 @@ def test_lab_frame_h_apply_of_a_spin_three_half_operator():
     rel = float(np.max(np.abs(got - want)) / np.max(np.abs(want)))
     print(f"lab-frame H-apply rel err {rel:.2e}")
     assert rel < 1e-13
+
+
+@pytest.mark.parametrize("n", [5, 7, 8])
+def test_time_split_state_storing_chain(n, monkeypatch):
+    """>= 256 outputs: qsb_propagate_expect cuts the chain into segments seeded with powers of U^seg_len, like
+    qsb_propagate_batch.  Against that call (same segments: the states are the same numbers) and against its own
+    unsplit chain (QSB200_PROP_SEGMENT=0: one CTA walks all outputs)."""
+    from quantumsimulations_b200 import engine
+
+    table = random_table(n, 4300 + n)
+    opts = engine.SolverOptions(atol=1e-12, rtol=1e-11, method="taylor", order=20, nsteps=0)
+    n_out, dt = 1500, 0.01
+    want, _ = engine.propagate_batch([table], n_out, dt, [opts])
+    got, st = engine.propagate_expect(table, n_out, dt, opts, terms=standard_terms(table))
+    monkeypatch.setenv("QSB200_PROP_SEGMENT", "0")
+    flat, _ = engine.propagate_expect(table, n_out, dt, opts, terms=standard_terms(table))
+    d_split, d_flat = float(np.max(np.abs(got - want[0]))), float(np.max(np.abs(got - flat)))
+    print(f"n={n}: split strings vs split fused {d_split:.2e}, split vs unsplit {d_flat:.2e}, {st.device_ms:.2f} ms")
+    assert d_split < 1e-12 and d_flat < 1e-10
+
+
+def test_sweep_driver_with_a_spin_three_half_rare_spin(tmp_path):
+    """run_sweep_sea_detuning(is_spin_three_half=True) (SW:370, SW:651) at the function-default grid against the
+    metrics the reference's own unmodified driver produced on top of its model with the dims repaired
+    (tests/golden/sweep_small_spin32.json): 26 trajectories with the four-level rare site + 13 sea-centre controls."""
+    import json
+    import os
+
+    from conftest import GOLDEN
+    from quantumsimulations_b200.sweep import run_sweep_sea_detuning
+
+    with open(os.path.join(GOLDEN, "sweep_small_spin32.json")) as f:
+        gold = json.load(f)
+    gp = gold["summary"]["global_params"]
+    assert gp["rare_spin_type"] == "3/2"
+    base = run_sweep_sea_detuning(
+        f_Az=gp["f_Az_Hz"], f1A=gp["f1A_Hz"], target_sea_detuning=gp["target_sea_detuning"],
+        gamma_sea=gp["gamma_sea"], gamma_rare=gp["gamma_rare"], sea_detunings_Hz=gp["sea_detunings_Hz"],
+        n_sea=gp["n_sea"], t_final=gp["t_final_s"], steps=gp["steps"], phi_sea=gp["phi_sea_rad"],
+        phi_rare=gp["phi_rare_rad"], out_root=str(tmp_path), is_spin_three_half=True,
+        solver_atol=gp["solver_atol"], solver_rtol=gp["solver_rtol"], solver_nsteps=gp["solver_nsteps"],
+        solver_max_step=gp["solver_max_step"], coarse_window=gp["coarse_window"], timestamp="gpu", verbose=False)
+    with open(os.path.join(base, "summary.json")) as f:
+        mine = json.load(f)
+    assert mine["global_params"]["rare_spin_type"] == "3/2" and len(mine["sweep_results"]) == 13
+    worst = 0.0
+    for got, want in zip(mine["sweep_results"], gold["summary"]["sweep_results"]):
+        for k in want:
+            if k.startswith("I_z_slope"):
+                worst = max(worst, abs(got[k] - want[k]))
+                assert abs(got[k] - want[k]) < 2e-6, (k, got[k], want[k])       # traces agree to 1e-6
+            elif k.startswith("t_") or k.startswith("R_"):
+                assert got[k] == pytest.approx(want[k], rel=2e-3, abs=2e-4), k
+            elif k.startswith("contrast"):
+                ts = [want[x] for x in ("t_on_center", "t_off_center", "t_off_sea_center")]
+                if all(abs(abs(t) - 1.0) > 0.01 for t in ts):                   # discontinuous at |t| = 1 (SW:308-309)
+                    assert got[k] == pytest.approx(want[k], abs=2e-3), k
+            else:
+                assert got[k] == pytest.approx(want[k], rel=1e-9, abs=1e-12), k
+    print(f"spin-3/2 sweep: worst slope deviation {worst:.2e}")
+
+
+def test_full_size_spin_three_half_trajectory_vs_exact():
+    """The reference's full trajectory size (30 s, 20000 outputs, SW:1223-1250) with the J = 3/2 rare spin, n_sea = 6:
+    all six traces against exact diagonalisation (oracle X on the compiled table + Pauli strings, which the CPU suite
+    pins to the repaired reference) <= 1e-6 - the bar of the spin-1/2 full-size test."""
+    import dataclasses
+
+    import quantumsimulations_b200 as q
+    from bench import sweep_params
+    from conftest import exact_traces
+
+    p = dataclasses.replace(sweep_params(6, 50e3, t_final=30.0, steps=20000), is_spin_three_half=True)
+    t, out, st = q.simulate_rare(p, return_stats=True, raw_norm=True)
+    want = exact_traces(q.compile_table(p), t)
+    devs = {k: float(np.max(np.abs(out[k] - want[k]))) for k in KEYS}
+    drift = float(np.max(np.abs(out["raw_norm"] - 1.0)))
+    print(f"full-size spin-3/2 trajectory: {st.device_ms:.1f} ms on the device, max dev {max(devs.values()):.2e}, norm drift {drift:.1e}")
+    assert max(devs.values()) < 1e-6 and drift < 1e-6 and st.path == 4
