@@ -238,6 +238,26 @@ def zvode_worker(spec):
     print(json.dumps({"trajectories": len(jobs), "steps": float(sum(r[0] for r in res))}), flush=True)
 
 
+def c1_spin32_leg(device):
+    """The sweep's N = 7 point (SW:1201-1252) with the J = 3/2 rare spin the reference declares (DE:22-25, DE:377) and
+    cannot run: 8 index bits, rotated frame + Pauli-string observables."""
+    import dataclasses
+
+    from quantumsimulations_b200 import simulate_rare
+
+    p = dataclasses.replace(sweep_params(6, 50e3, t_final=30.0, steps=20000), is_spin_three_half=True)
+    simulate_rare(dataclasses.replace(p, t_final=3e-3, steps=300), device=device)          # warm-up
+    t0 = time.perf_counter()
+    _, obs, st = simulate_rare(p, device=device, return_stats=True, raw_norm=True)
+    wall = time.perf_counter() - t0
+    return {"workload": "C1 (i) with is_spin_three_half=True: n_sea=6 + a four-level rare site (8 index bits), delta=50 kHz, "
+                        "rare ON, t_final=30 s, 20000 outputs, atol 1e-10 / rtol 1e-9",
+            "method": "propagator columns + squarings as C1 (i), state-storing time-split chain, Pauli-string reduction "
+                      "(qsb_propagate_expect); not an ODE step rate",
+            "wall_s": wall, "kernel_ms": st.device_ms, "path": st.path, "column_h_applies": st.n_rhs,
+            "max_raw_norm_deviation": float(np.max(np.abs(obs["raw_norm"] - 1.0)))}
+
+
 def c1_leg(device, with_cpu):
     """BASELINE config 1: ONE trajectory at the reference's own sizes, through simulate_rare.
     (i) the sweep's N = 7 point (SW:1201-1252: 30 s, 20000 outputs); (ii) the dataclass-default N = 13 icosahedron
@@ -265,6 +285,10 @@ def c1_leg(device, with_cpu):
         "workload": "C1 (i): N=7, delta=50 kHz, rare ON, t_final=30 s, 20000 outputs, atol 1e-10 / rtol 1e-9 (SW:1201-1252)",
         "wall_s": w_auto, "kernel_ms": st.device_ms, "path": st.path, "column_h_applies": st.n_rhs,
         "method": "auto (propagator: not an ODE step rate)", "stepped_3ms_window": legs}
+    try:
+        out["n7_sweep_point_spin_three_half"] = c1_spin32_leg(device)
+    except Exception as e:  # noqa: BLE001  a side leg must not take the bench line down
+        out["n7_sweep_point_spin_three_half"] = {"error": repr(e)}
     p13 = DipolarRareParams(is_spin_three_half=False)
     simulate_rare(p13, device=device)                                                      # plan + dense buffers warm
     t0 = time.perf_counter()
