@@ -225,6 +225,13 @@ typedef struct {
 int qsb_propagate_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt, const qsb_solver_opts* opts,
                          int32_t max_squarings, const qsb_pauli_term* terms, int32_t n_terms, int32_t obs_by_column,
                          double* out_obs, qsb_stats* stats, int device);
+/* qsb_propagate_hbm with such observables, QSB_SMALL_MAX_QUBITS < n <= QSB_HBM_PROPAGATOR_MAX_QUBITS (9 <= n_sea <= 12 with a
+ * spin-3/2 rare spin; n_sea = 12 is the reference's dataclass default, dipolar_ensemble_with_rare.py:332-384, and its sweep
+ * function's default, sweep_sea_detuning.py:363): same columns, cuBLAS squarings and chain; the strings are reduced on
+ * the chain's state buffer after every matvec.  stats->path = 3.                                                    */
+int qsb_propagate_hbm_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt, const qsb_solver_opts* opts,
+                             int32_t max_squarings, const qsb_pauli_term* terms, int32_t n_terms, int32_t obs_by_column,
+                             double* out_obs, qsb_stats* stats, int device);
 /* The same observables on the current state of an open session (tiled path, unsharded plans), [QSB_NOBS] host:
  * qsb_session_advance to every output time + this call is the spin-3/2 trajectory for n > QSB_SMALL_MAX_QUBITS.    */
 int qsb_session_expect(qsb_plan* plan, const qsb_pauli_term* terms, int32_t n_terms, double* obs);

@@ -187,14 +187,24 @@ def split_method(method: Optional[str], n_qubits: Optional[int] = None, steps: O
 
 def resolve_method(params: DipolarRareParams, method: Optional[str]) -> Tuple[str, bool]:
     """``split_method`` for one parameter record (computes the ||H|| t_final bound only where "auto" needs it).
-    A spin-3/2 rare spin (local dimension 4) has two paths only: N <= 10 bits always goes through the propagator (the
-    stepped on-chip kernel cannot report its observables), N > 10 is always stepped (``_evolve_pauli``)."""
+    A spin-3/2 rare spin (local dimension 4): N <= 10 bits always goes through the propagator (the stepped on-chip
+    kernel cannot report its observables); 11 <= N <= 14 like the spin-1/2 tables (HBM-resident propagator when asked
+    for, or when "auto" finds stepping the expensive way); beyond that a stepping session (``_evolve_pauli``)."""
     n, steps = _size_of(params)
     if local_dim4(params):
         integrator, asked = split_method(method)
-        if asked and n > engine.SMALL_MAX_QUBITS:
-            raise ValueError(f"method 'propagator' with a spin-3/2 rare spin needs n_sea + 2 <= {engine.SMALL_MAX_QUBITS}")
-        return integrator, n <= engine.SMALL_MAX_QUBITS
+        if n <= engine.SMALL_MAX_QUBITS:
+            return integrator, True
+        if n > engine.HBM_PROPAGATOR_MAX_QUBITS:
+            if asked:
+                raise ValueError(f"method 'propagator' with a spin-3/2 rare spin needs n_sea + 2 <= {engine.HBM_PROPAGATOR_MAX_QUBITS}")
+            return integrator, False
+        if asked:
+            return integrator, True
+        if (method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)) != "auto":
+            return integrator, False
+        norm_t = compile_table(params).spectral_bound() * float(params.t_final)     # the rule of the spin-1/2 tables
+        return integrator, bool(norm_t > AUTO_HBM_NORM_T and steps >= 3)
     norm_t = None
     m = method or os.environ.get("QSB200_METHOD", DEFAULT_METHOD)
     if m == "auto" and engine.SMALL_MAX_QUBITS < n <= engine.HBM_PROPAGATOR_MAX_QUBITS:
@@ -274,7 +284,7 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
     if table.pauli_terms is not None:
         if checkpoint is not None:
             raise ValueError("checkpoint= is not available with is_spin_three_half=True")
-        obs, stats = _evolve_pauli(table, t, opts, device)
+        obs, stats = _evolve_pauli(table, t, opts, device, resolve_method(params, method)[1])
         out = _pack(obs, override, raw_norm, by_column=True)
         return (t, out, stats) if return_stats else (t, out)
     if resolve_method(params, method)[1]:
@@ -294,17 +304,18 @@ def simulate_rare(params: DipolarRareParams, *, device: int = 0, method: Optiona
     return t, out
 
 
-def _evolve_pauli(table: SpinTable, t: np.ndarray, opts: engine.SolverOptions, device: int):
+def _evolve_pauli(table: SpinTable, t: np.ndarray, opts: engine.SolverOptions, device: int, propagate: bool = False):
     """One trajectory of a local-dimension-4 table (spin-3/2 rare spin on two bits, DE:22-25 / DE:499-501): the time
     evolution runs through the spin-1/2 kernels in the rotated frame, the observables are the table's weighted Pauli
     strings.  N <= 10 bits: the propagator path with every state kept on the device (engine.propagate_expect; the
-    reference's grid is uniform, DE:626).  Larger: a stepping session on the tiled path, advanced to every output time
+    reference's grid is uniform, DE:626); ``propagate`` for 11 <= N <= 14: the same through the HBM-resident propagator.
+    Otherwise: a stepping session on the tiled path, advanced to every output time
     (``nsteps`` per output interval, like the stepped integrators) and read with ``Plan.session_expect``.
     Returns (obs [NOBS, n_out], Stats)."""
-    if table.n <= engine.SMALL_MAX_QUBITS:
+    if table.n <= engine.SMALL_MAX_QUBITS or propagate:
         dt = engine.uniform_step(t)
         if dt is None:
-            raise ValueError("the spin-3/2 on-chip path needs a uniform output grid (np.linspace, DE:626)")
+            raise ValueError("the spin-3/2 propagator paths need a uniform output grid (np.linspace, DE:626)")
         return engine.propagate_expect(table, len(t), dt, opts, device, by_column=True)
     obs = np.empty((engine.NOBS, len(t)), dtype=np.float64)
     with engine.Plan(table, device) as plan:

@@ -63,15 +63,23 @@ static int cublas_for(int device, cublasHandle_t* out) {
   return QSB_OK;
 }
 
-extern "C" int qsb_propagate_hbm(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt,
-                                 const qsb_solver_opts* opts, int32_t max_squarings, int32_t obs_by_column, double* out_obs,
-                                 qsb_stats* stats, int device) {
+static int stage_terms(const qsb_pauli_term* terms, int32_t n_terms, int n_qubits, std::vector<ExpectTerm>* out,
+                       int* column_begin);  // qsb_api_expect.inl
+
+// terms == nullptr: the six mask-based observables (qsb_propagate_hbm); else weighted Pauli strings reduced by
+// launch_expect on the same chain buffer (qsb_propagate_hbm_expect: a local-dimension-4 table, qsb_api_expect.inl).
+static int propagate_hbm_impl(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt,
+                              const qsb_solver_opts* opts, int32_t max_squarings, int32_t obs_by_column, double* out_obs,
+                              qsb_stats* stats, int device, const qsb_pauli_term* terms, int32_t n_terms) {
   if (!table || !opts || !out_obs || n_out < 1) return fail(QSB_ERR_BAD_ARG, "qsb_propagate_hbm: null argument or n_out < 1");
   int rc = check_table(table);
   if (rc) return rc;
   rc = check_opts(opts);
   if (rc) return rc;
   const int n = table->n_qubits;
+  std::vector<ExpectTerm> staged;
+  int column_begin[7] = {};
+  if (terms && (rc = stage_terms(terms, n_terms, n, &staged, column_begin))) return rc;
   if (n <= QSB_SMALL_MAX_QUBITS || n > QSB_HBM_PROPAGATOR_MAX_QUBITS)
     return fail(QSB_ERR_UNSUPPORTED, "qsb_propagate_hbm handles " + std::to_string(QSB_SMALL_MAX_QUBITS + 1) + " <= n_qubits <= " +
                                          std::to_string(QSB_HBM_PROPAGATOR_MAX_QUBITS) + " (smaller: qsb_propagate_batch)");
@@ -170,9 +178,36 @@ extern "C" int qsb_propagate_hbm(const qsb_table* table, uint64_t psi0_index, in
         return fail(QSB_ERR_CUDA, "cublasZgemv failed");
   }
   QSB_CUDA(cudaGetLastError());
+  // Pauli-string observables: the terms and the per-CTA partial sums live in one small allocation of their own
+  char* d_expect = nullptr;
+  struct ExpectFree { char*& p; cudaStream_t s; ~ExpectFree() { if (p) { cudaStreamSynchronize(s); cudaFree(p); } } } xfree{d_expect, bp->stream};
+  ExpectTerm* d_terms = nullptr;
+  double* d_partials = nullptr;
+  if (terms) {
+    const size_t tb = (sizeof(ExpectTerm) * staged.size() + 255) & ~size_t(255);
+    cudaError_t e = cudaMalloc((void**)&d_expect, tb + sizeof(double) * 8 * (size_t)expect_blocks(dim) * (size_t)n_seg);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      d_expect = nullptr;
+      return fail(QSB_ERR_OOM, std::string("qsb_propagate_hbm_expect: cudaMalloc failed: ") + cudaGetErrorString(e));
+    }
+    d_terms = (ExpectTerm*)d_expect;
+    d_partials = (double*)(d_expect + tb);
+    QSB_CUDA(cudaMemcpyAsync(d_terms, staged.data(), sizeof(ExpectTerm) * staged.size(), cudaMemcpyHostToDevice, bp->stream));
+  }
   for (int64_t k = 0; k < seg_len; ++k) {
-    launch_observe_columns((const cplx*)X0, n, n_seg, seg_len, k, n_out, table->sea_mask, table->rare_mask, d_obs,
-                           obs_by_column != 0, bp->stream);
+    if (terms) {  // column c of X0 is output c seg_len + k; the last segment may be shorter
+      const int64_t valid = k < n_out ? (n_out - k + seg_len - 1) / seg_len : 0;
+      if (valid > 0) {
+        if (obs_by_column) launch_expect((const cplx*)X0, valid, dim, d_terms, (int)staged.size(), column_begin, d_partials,
+                                         d_obs + k, seg_len, n_out, bp->stream);
+        else launch_expect((const cplx*)X0, valid, dim, d_terms, (int)staged.size(), column_begin, d_partials,
+                           d_obs + k * QSB_NOBS, seg_len * QSB_NOBS, 1, bp->stream);
+      }
+    } else {
+      launch_observe_columns((const cplx*)X0, n, n_seg, seg_len, k, n_out, table->sea_mask, table->rare_mask, d_obs,
+                             obs_by_column != 0, bp->stream);
+    }
     if (k + 1 < seg_len) {
       if ((rc = gemm(U, X0, X1, n_seg))) return rc;
       std::swap(X0, X1);
@@ -190,4 +225,17 @@ extern "C" int qsb_propagate_hbm(const qsb_table* table, uint64_t psi0_index, in
     stats->last_h = s->h; stats->device_ms = ms; stats->path = 3; stats->status = QSB_OK;
   }
   return QSB_OK;
+}
+
+extern "C" int qsb_propagate_hbm(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt,
+                                 const qsb_solver_opts* opts, int32_t max_squarings, int32_t obs_by_column, double* out_obs,
+                                 qsb_stats* stats, int device) {
+  return propagate_hbm_impl(table, psi0_index, n_out, dt, opts, max_squarings, obs_by_column, out_obs, stats, device, nullptr, 0);
+}
+
+extern "C" int qsb_propagate_hbm_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt,
+                                        const qsb_solver_opts* opts, int32_t max_squarings, const qsb_pauli_term* terms,
+                                        int32_t n_terms, int32_t obs_by_column, double* out_obs, qsb_stats* stats, int device) {
+  if (!terms) return fail(QSB_ERR_BAD_ARG, "qsb_propagate_hbm_expect: terms is null");
+  return propagate_hbm_impl(table, psi0_index, n_out, dt, opts, max_squarings, obs_by_column, out_obs, stats, device, terms, n_terms);
 }

@@ -70,7 +70,7 @@ EXPORTS = (
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_shard_set_stream_barrier", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather", "qsb_local_stream_barrier",
     "qsb_propagate_batch", "qsb_propagate_hbm", "qsb_release_caches", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
-    "qsb_propagate_expect", "qsb_session_expect",
+    "qsb_propagate_expect", "qsb_propagate_hbm_expect", "qsb_session_expect",
 )
 
 SHARD_BLOB_BYTES = 96
@@ -113,6 +113,7 @@ def load_library() -> C.CDLL:
     lib.qsb_debug_squarings.argtypes = [C.POINTER(_Table), C.c_double, C.POINTER(C.c_int32)]
     lib.qsb_propagate_expect.argtypes = [C.POINTER(_Table), C.c_uint64, C.c_int64, C.c_double, C.POINTER(_Opts), C.c_int32,
                                          C.POINTER(_PauliTerm), C.c_int32, C.c_int32, dp, C.POINTER(_Stats), C.c_int]
+    lib.qsb_propagate_hbm_expect.argtypes = lib.qsb_propagate_expect.argtypes
     lib.qsb_session_expect.argtypes = [vp, C.POINTER(_PauliTerm), C.c_int32, dp]
     lib.qsb_debug_propagate_shape.argtypes = [C.c_int32, C.POINTER(C.c_int32)]
     lib.qsb_apply_h.argtypes = [vp, dp, dp]
@@ -549,10 +550,11 @@ def _pauli_terms(terms):
 
 def propagate_expect(table: SpinTable, n_out: int, dt: float, opts: SolverOptions, device: int = 0,
                      max_squarings: Optional[int] = None, by_column: bool = False, terms=None):
-    """``propagate_batch`` for ONE trajectory whose six observables are weighted Pauli strings (``terms``, default
-    ``table.pauli_terms``: a local-dimension-4 table, n <= 10 bits) - qsb_propagate_expect: U built as usual, the chain
-    keeps every state on the device, one kernel reduces the strings.  Returns (obs [n_out, NOBS] or [NOBS, n_out] with
-    ``by_column``, Stats)."""
+    """``propagate_batch`` / ``propagate_hbm`` for ONE trajectory whose six observables are weighted Pauli strings
+    (``terms``, default ``table.pauli_terms``: a local-dimension-4 table).  n <= 10 bits - qsb_propagate_expect: U built
+    as usual, the chain keeps every state on the device, one kernel reduces the strings; 11 <= n <= 14 -
+    qsb_propagate_hbm_expect: U resident in HBM, the strings reduced on the chain's buffer after every matvec.
+    Returns (obs [n_out, NOBS] or [NOBS, n_out] with ``by_column``, Stats)."""
     lib = load_library()
     terms = table.pauli_terms if terms is None else terms
     if terms is None:
@@ -562,9 +564,9 @@ def propagate_expect(table: SpinTable, n_out: int, dt: float, opts: SolverOption
     copts = opts.to_c()
     st = _Stats()
     obs = np.empty((NOBS, int(n_out)) if by_column else (int(n_out), NOBS), dtype=np.float64)
-    _check(lib.qsb_propagate_expect(C.byref(holder.c), table.psi0_index, int(n_out), float(dt), C.byref(copts),
-                                    _max_squarings(max_squarings), cterms, len(cterms), 1 if by_column else 0, _dptr(obs),
-                                    C.byref(st), int(device)))
+    fn = lib.qsb_propagate_expect if table.n <= SMALL_MAX_QUBITS else lib.qsb_propagate_hbm_expect
+    _check(fn(C.byref(holder.c), table.psi0_index, int(n_out), float(dt), C.byref(copts), _max_squarings(max_squarings),
+              cterms, len(cterms), 1 if by_column else 0, _dptr(obs), C.byref(st), int(device)))
     return obs, Stats.from_c(st)
 
 

@@ -134,6 +134,13 @@ def test_live_repaired_reference_agrees(tmp_path):
     assert np.array_equal(np.abs(q.initial_state_rare(p)), np.abs(psi0))
 
 
+def lib_call_is_bad_arg(engine):
+    """qsb_session_expect without a plan and qsb_propagate_hbm_expect without terms: QSB_ERR_BAD_ARG (1)."""
+    lib = engine.load_library()
+    return lib.qsb_session_expect(None, None, 0, None) == 1 and \
+        lib.qsb_propagate_hbm_expect(None, 0, 1, 1.0, None, -1, None, 0, 0, None, None, 0) == 1
+
+
 def test_pauli_entry_points_validate_before_touching_a_device():
     import quantumsimulations_b200 as q
     from quantumsimulations_b200 import engine
@@ -148,13 +155,14 @@ def test_pauli_entry_points_validate_before_touching_a_device():
         engine.propagate_expect(tb, 5, 1e-3, o, terms=[])
     with pytest.raises(ValueError, match="dt must be"):
         engine.propagate_expect(tb, 5, 0.0, o)
-    big = q.compile_table(q.DipolarRareParams(n_sea=9))
-    with pytest.raises(engine.EngineError, match="n_qubits <= 10"):
+    big = q.compile_table(q.DipolarRareParams(n_sea=13))         # 15 bits: beyond the HBM-resident propagator too
+    with pytest.raises(engine.EngineError, match="n_qubits <= 14"):
         engine.propagate_expect(big, 5, 1e-3, o)
-    lib = engine.load_library()
-    assert lib.qsb_session_expect(None, None, 0, None) == 1      # QSB_ERR_BAD_ARG: no plan
+    assert lib_call_is_bad_arg(engine)
     with pytest.raises(ValueError, match="spin-3/2"):
-        q.api.resolve_method(q.DipolarRareParams(n_sea=9), "propagator")
+        q.api.resolve_method(q.DipolarRareParams(n_sea=13), "propagator")
+    assert q.api.resolve_method(q.DipolarRareParams(n_sea=9), "propagator") == ("taylor", True)   # HBM-resident propagator
+    assert q.api.resolve_method(q.DipolarRareParams(n_sea=9), "taylor") == ("taylor", False)
     assert q.api.resolve_method(q.DipolarRareParams(n_sea=8), "dp5") == ("dp5", True)
     assert q.api.resolve_method(q.DipolarRareParams(n_sea=9), None) == ("taylor", False)
     if engine.device_count() == 0:

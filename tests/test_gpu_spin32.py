@@ -202,3 +202,34 @@ def test_full_size_spin_three_half_trajectory_vs_exact():
     drift = float(np.max(np.abs(out["raw_norm"] - 1.0)))
     print(f"full-size spin-3/2 trajectory: {st.device_ms:.1f} ms on the device, max dev {max(devs.values()):.2e}, norm drift {drift:.1e}")
     assert max(devs.values()) < 1e-6 and drift < 1e-6 and st.path == 4
+
+
+@pytest.mark.parametrize("n_out", [40, 300])
+def test_hbm_propagator_string_observables_equal_the_fused_ones(n_out):
+    """qsb_propagate_hbm_expect against qsb_propagate_hbm on a random 11-bit spin-1/2 table (same U, same chain; the
+    strings reduced by launch_expect on the chain buffer instead of observe_columns_kernel), unsplit and time-split."""
+    from quantumsimulations_b200 import engine
+
+    table = random_table(11, 4411, dense_pairs=False)
+    opts = engine.SolverOptions(atol=1e-12, rtol=1e-11, method="taylor", order=20, nsteps=0)
+    want, st_w = engine.propagate_hbm(table, n_out, 0.02, opts)
+    got, st_g = engine.propagate_expect(table, n_out, 0.02, opts, terms=standard_terms(table))
+    by_col, _ = engine.propagate_expect(table, n_out, 0.02, opts, terms=standard_terms(table), by_column=True)
+    dev = float(np.max(np.abs(got - want)))
+    print(f"n_out={n_out}: HBM strings vs fused sums max dev {dev:.2e}; path {st_g.path}, {st_g.device_ms:.1f} ms")
+    assert dev < 1e-12 and st_g.path == 3 and st_g.n_rhs == st_w.n_rhs
+    assert np.array_equal(by_col, got.T)
+
+
+@pytest.mark.parametrize("name", ["s32_n9_tiled", "s32_n10_tiled"])
+def test_spin_three_half_through_the_hbm_propagator(golden_spin32, name):
+    """method="propagator" at 11 / 12 index bits: the HBM-resident propagator with the spin-3/2 strings, against the
+    repaired reference's traces (the stepped session of the same records is in the test above)."""
+    import quantumsimulations_b200 as q
+
+    meta, gold = golden_spin32
+    p = params_from_meta(meta[name])
+    _, out, st = q.simulate_rare(p, method="propagator", return_stats=True)
+    dev = max(float(np.max(np.abs(out[k] - gold[f"{name}/{k}"]))) for k in KEYS)
+    print(f"{name} via the HBM propagator: path {st.path}, max dev {dev:.2e}, {st.device_ms:.1f} ms")
+    assert dev < 1e-6 and st.path == 3
