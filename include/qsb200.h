@@ -225,6 +225,13 @@ typedef struct {
 int qsb_propagate_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt, const qsb_solver_opts* opts,
                          int32_t max_squarings, const qsb_pauli_term* terms, int32_t n_terms, int32_t obs_by_column,
                          double* out_obs, qsb_stats* stats, int device);
+/* The same for n_traj trajectories of equal n_qubits that SHARE the list of strings (a sweep: same n_sea and phi_R,
+ * sweep_sea_detuning.py:611-702) in one pass: arguments as qsb_propagate_batch, out_obs [n_traj][n_out][QSB_NOBS] or
+ * [n_traj][QSB_NOBS][n_out].  Trajectories are taken in chunks whose kept states stay below ~8 GiB.                 */
+int qsb_propagate_expect_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
+                               const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
+                               const qsb_pauli_term* terms, int32_t n_terms, int32_t obs_by_column, double* out_obs,
+                               qsb_stats* stats, int device);
 /* qsb_propagate_hbm with such observables, QSB_SMALL_MAX_QUBITS < n <= QSB_HBM_PROPAGATOR_MAX_QUBITS (9 <= n_sea <= 12 with a
  * spin-3/2 rare spin; n_sea = 12 is the reference's dataclass default, dipolar_ensemble_with_rare.py:332-384, and its sweep
  * function's default, sweep_sea_detuning.py:363): same columns, cuBLAS squarings and chain; the strings are reduced on

@@ -355,10 +355,27 @@ def simulate_rare_batch(params_list: Sequence[DipolarRareParams], *, device: int
     grid may go through the HBM-resident propagator (``resolve_method``), the rest is stepped on the tiled path."""
     n = len(params_list)
     special = [i for i, p in enumerate(params_list) if local_dim4(p)]
-    if special:   # local dimension 4: one call per trajectory (_evolve_pauli); the rest batches as usual
+    if special:   # local dimension 4 (_evolve_pauli); the rest batches as usual
         rest = [i for i in range(n) if not local_dim4(params_list[i])]
         results, stats_out = [None] * n, [None] * n
+        # on-chip sizes: the trajectories of a sweep share bits, grid length and Pauli strings -> ONE call per group
+        groups: Dict[Tuple, List[int]] = {}
+        single = []
         for i in special:
+            p = params_list[i]
+            if _size_of(p)[0] <= engine.SMALL_MAX_QUBITS:
+                groups.setdefault((p.n_sea, int(p.steps), float(p.phi_rare)), []).append(i)
+            else:
+                single.append(i)
+        for idxs in groups.values():
+            tabs = [compile_table(params_list[i]) for i in idxs]
+            om = [_options_from(params_list[i], method, tol_scale) for i in idxs]
+            grids = [_check_grid(params_list[i]) for i in idxs]
+            dts = [engine.uniform_step(g) for g in grids]
+            obs, sts = engine.propagate_expect_batch(tabs, len(grids[0]), dts, [o for o, _ in om], device, by_column=True)
+            for j, i in enumerate(idxs):
+                results[i], stats_out[i] = (grids[j], _pack(obs[j], om[j][1], raw_norm, by_column=True)), sts[j]
+        for i in single:
             t, out, st = simulate_rare(params_list[i], device=device, method=method, tol_scale=tol_scale,
                                        return_stats=True, raw_norm=raw_norm)
             results[i], stats_out[i] = (t, out), st

@@ -60,60 +60,42 @@ struct ExpectScratch {  // device buffers, events and the stream of one qsb_prop
 };
 }  // namespace
 
-extern "C" {
-
-int qsb_propagate_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt, const qsb_solver_opts* opts,
-                         int32_t max_squarings, const qsb_pauli_term* terms, int32_t n_terms, int32_t obs_by_column,
-                         double* out_obs, qsb_stats* stats, int device) {
-  if (!table || !opts || !out_obs || n_out < 1) return fail(QSB_ERR_BAD_ARG, "qsb_propagate_expect: null argument or n_out < 1");
-  int rc = check_table(table);
-  if (rc) return rc;
-  rc = check_opts(opts);
-  if (rc) return rc;
-  const int n = table->n_qubits;
-  if (n > QSB_SMALL_MAX_QUBITS)
-    return fail(QSB_ERR_UNSUPPORTED, "qsb_propagate_expect handles n_qubits <= " + std::to_string(QSB_SMALL_MAX_QUBITS) +
-                                         " (larger: a session with qsb_session_expect)");
-  if (psi0_index >> n) return fail(QSB_ERR_BAD_ARG, "psi0_index out of range");
-  if (!(dt > 0.0) || !std::isfinite(dt)) return fail(QSB_ERR_BAD_ARG, "dt must be finite and > 0");
+// Shared body of qsb_propagate_expect / qsb_propagate_expect_batch: n_traj trajectories of equal n_qubits that share one
+// list of Pauli strings (a sweep: same n_sea, same phi_R), chunked so that the kept states of one pass stay below ~8 GiB.
+static int propagate_expect_impl(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
+                                 const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
+                                 const qsb_pauli_term* terms, int32_t n_terms, int32_t obs_by_column, double* out_obs,
+                                 qsb_stats* stats, int device) {
+  if (n_traj < 1 || !tables || !psi0_index || !opts || !out_obs || !dt || n_out < 1)
+    return fail(QSB_ERR_BAD_ARG, "qsb_propagate_expect: null argument, n_traj < 1 or n_out < 1");
+  const int n = tables[0].n_qubits;
+  int rc;
+  for (int i = 0; i < n_traj; ++i) {
+    if ((rc = check_table(&tables[i]))) return rc;
+    if (tables[i].n_qubits > QSB_SMALL_MAX_QUBITS)
+      return fail(QSB_ERR_UNSUPPORTED, "qsb_propagate_expect handles n_qubits <= " + std::to_string(QSB_SMALL_MAX_QUBITS) +
+                                           " (11 .. 14: qsb_propagate_hbm_expect; any size: a session with qsb_session_expect)");
+    if (tables[i].n_qubits != n) return fail(QSB_ERR_BAD_ARG, "qsb_propagate_expect_batch needs the same n_qubits in every table");
+    if ((rc = check_opts(&opts[i]))) return rc;
+    if (psi0_index[i] >> n) return fail(QSB_ERR_BAD_ARG, "psi0_index out of range");
+    const double h = dt[dt_per_traj ? i : 0];
+    if (!(h > 0.0) || !std::isfinite(h)) return fail(QSB_ERR_BAD_ARG, "dt must be finite and > 0");
+  }
   std::vector<ExpectTerm> staged;
   int column_begin[7];
-  rc = stage_terms(terms, n_terms, n, &staged, column_begin);
-  if (rc) return rc;
+  if ((rc = stage_terms(terms, n_terms, n, &staged, column_begin))) return rc;
   const size_t dim = (size_t)1 << n;
   const int nb = expect_blocks(dim);
-  if ((double)n_out * (double)dim * sizeof(cplx) > 16.0 * 1073741824.0 || (double)n_out * nb > 2.0e9)
+  const double state_bytes = (double)n_out * (double)dim * sizeof(cplx);
+  if (state_bytes > 16.0 * 1073741824.0 || (double)n_out * nb > 2.0e9)
     return fail(QSB_ERR_UNSUPPORTED, "qsb_propagate_expect keeps every output state in device memory: n_out * 2^n * 16 bytes must stay below 16 GiB");
-  rc = pick_device(device);
-  if (rc) return rc;
-
-  std::vector<SmallStats> hs(dim);  // declared before `sc`: its destructor drains the stream that copies into it
-  ExpectScratch sc;
-  QSB_CUDA(cudaStreamCreateWithFlags(&sc.st, cudaStreamNonBlocking));
-  QSB_CUDA(cudaEventCreate(&sc.e0));
-  QSB_CUDA(cudaEventCreate(&sc.e1));
-  cudaStream_t st = sc.st;
+  if ((rc = pick_device(device))) return rc;
   const size_t u_bytes = sizeof(cplx) * dim * dim;
-  SmallDesc* d_desc = nullptr;
-  double *d_t = nullptr, *d_partials = nullptr, *d_obs = nullptr;
-  SmallStats* d_stats = nullptr;
-  cplx *d_u = nullptr, *d_tmp = nullptr, *d_states = nullptr;
-  int32_t* d_sq = nullptr;
-  ExpectTerm* d_terms = nullptr;
-  int32_t s = max_squarings == 0 ? 0 : auto_squarings(table, dt);
-  if (max_squarings > 0 && s > max_squarings) s = max_squarings;
-  if ((rc = sc.get(sizeof(SmallDesc), (void**)&d_desc))) return rc;
-  if ((rc = sc.get(sizeof(double) * 2, (void**)&d_t))) return rc;
-  if ((rc = sc.get(sizeof(SmallStats) * dim, (void**)&d_stats))) return rc;
-  if ((rc = sc.get(u_bytes, (void**)&d_u))) return rc;
-  if (s > 0) {
-    if ((rc = sc.get(u_bytes, (void**)&d_tmp))) return rc;
-    if ((rc = sc.get(sizeof(int32_t), (void**)&d_sq))) return rc;
-  }
-  if ((rc = sc.get(sizeof(cplx) * dim * (size_t)n_out, (void**)&d_states))) return rc;
-  if ((rc = sc.get(sizeof(ExpectTerm) * staged.size(), (void**)&d_terms))) return rc;
-  if ((rc = sc.get(sizeof(double) * 8 * (size_t)nb * (size_t)n_out, (void**)&d_partials))) return rc;
-  if ((rc = sc.get(sizeof(double) * QSB_NOBS * (size_t)n_out, (void**)&d_obs))) return rc;
+  // trajectories per pass: kept states within ~8 GiB (one trajectory may take up to 16), propagators within ~2 GiB
+  int chunk = (int)std::max(1.0, std::min((double)n_traj, 8.0 * 1073741824.0 / state_bytes));
+  chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)chunk, ((size_t)2 << 30) / u_bytes));
+  if (const char* e = getenv("QSB200_PROP_CHUNK")) chunk = std::max(1, std::min(chunk, atoi(e)));  // test knob
+
   // Time-split chain, exactly as in propagate_impl: ~128 segments of 2^seg_lb outputs (a function of n_out only), each
   // its own CTA, seeded with (U^(2^seg_lb))^c psi_0 from seg_lb more squarings of a copy of U.
   int seg_lb = 0, n_seg = 1;
@@ -129,63 +111,129 @@ int qsb_propagate_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_
       seg_lb = 0;
     }
   }
-  cplx *d_v = nullptr, *d_seeds = nullptr;
-  int32_t* d_seg_sq = nullptr;
-  if (n_seg > 1) {
-    if ((rc = sc.get(u_bytes, (void**)&d_v))) return rc;
-    if ((rc = sc.get(sizeof(cplx) * dim * (size_t)n_seg, (void**)&d_seeds))) return rc;
-    if ((rc = sc.get(sizeof(int32_t), (void**)&d_seg_sq))) return rc;
-    if (!d_tmp && (rc = sc.get(u_bytes, (void**)&d_tmp))) return rc;
+  std::vector<int32_t> n_sq(n_traj, 0);
+  bool any_sq = false;
+  for (int i = 0; i < n_traj; ++i) {
+    int s = max_squarings == 0 ? 0 : auto_squarings(&tables[i], dt[dt_per_traj ? i : 0]);
+    if (max_squarings > 0 && s > max_squarings) s = max_squarings;
+    n_sq[i] = s;
+    any_sq = any_sq || s > 0;
   }
 
-  SmallDesc desc;
-  compile_small(table, psi0_index, opts, 1, &desc);
-  const double tp[2] = {0.0, std::ldexp(dt, -s)};
-  const int32_t seg_sq = seg_lb;
-  QSB_CUDA(cudaMemcpyAsync(d_desc, &desc, sizeof desc, cudaMemcpyHostToDevice, st));
-  QSB_CUDA(cudaMemcpyAsync(d_t, tp, sizeof tp, cudaMemcpyHostToDevice, st));
-  QSB_CUDA(cudaMemcpyAsync(d_terms, staged.data(), sizeof(ExpectTerm) * staged.size(), cudaMemcpyHostToDevice, st));
-  if (s > 0) QSB_CUDA(cudaMemcpyAsync(d_sq, &s, sizeof s, cudaMemcpyHostToDevice, st));
-  if (n_seg > 1) QSB_CUDA(cudaMemcpyAsync(d_seg_sq, &seg_sq, sizeof seg_sq, cudaMemcpyHostToDevice, st));
-  QSB_CUDA(cudaEventRecord(sc.e0, st));
-  launch_small_columns(d_desc, 1, n, d_t, d_stats, d_u, st);  // U^(1 / 2^s), one CTA per column
-  QSB_CUDA(cudaGetLastError());
-  if (s > 0) {
-    launch_small_square(d_u, d_tmp, d_sq, 1, n, st);
-    QSB_CUDA(cudaGetLastError());
+  std::vector<SmallStats> hs((size_t)chunk * dim);  // declared before `sc`: its destructor drains the stream that copies into it
+  std::vector<SmallDesc> descs(chunk);
+  std::vector<double> tp(2 * (size_t)chunk);
+  std::vector<int32_t> seg_sq(chunk, seg_lb);
+  ExpectScratch sc;
+  QSB_CUDA(cudaStreamCreateWithFlags(&sc.st, cudaStreamNonBlocking));
+  QSB_CUDA(cudaEventCreate(&sc.e0));
+  QSB_CUDA(cudaEventCreate(&sc.e1));
+  cudaStream_t st = sc.st;
+  SmallDesc* d_desc = nullptr;
+  double *d_t = nullptr, *d_partials = nullptr, *d_obs = nullptr;
+  SmallStats* d_stats = nullptr;
+  cplx *d_u = nullptr, *d_tmp = nullptr, *d_states = nullptr, *d_v = nullptr, *d_seeds = nullptr;
+  int32_t *d_sq = nullptr, *d_seg_sq = nullptr;
+  ExpectTerm* d_terms = nullptr;
+  if ((rc = sc.get(sizeof(SmallDesc) * chunk, (void**)&d_desc))) return rc;
+  if ((rc = sc.get(sizeof(double) * 2 * chunk, (void**)&d_t))) return rc;
+  if ((rc = sc.get(sizeof(SmallStats) * dim * chunk, (void**)&d_stats))) return rc;
+  if ((rc = sc.get(u_bytes * chunk, (void**)&d_u))) return rc;
+  if (any_sq || n_seg > 1) {
+    if ((rc = sc.get(u_bytes * chunk, (void**)&d_tmp))) return rc;
+    if ((rc = sc.get(sizeof(int32_t) * chunk, (void**)&d_sq))) return rc;
   }
+  if ((rc = sc.get(sizeof(cplx) * dim * (size_t)n_out * chunk, (void**)&d_states))) return rc;
+  if ((rc = sc.get(sizeof(ExpectTerm) * staged.size(), (void**)&d_terms))) return rc;
+  if ((rc = sc.get(sizeof(double) * 8 * (size_t)nb * (size_t)n_out * chunk, (void**)&d_partials))) return rc;
+  if ((rc = sc.get(sizeof(double) * QSB_NOBS * (size_t)n_out * chunk, (void**)&d_obs))) return rc;
   if (n_seg > 1) {
-    QSB_CUDA(cudaMemcpyAsync(d_v, d_u, u_bytes, cudaMemcpyDeviceToDevice, st));
-    launch_small_square(d_v, d_tmp, d_seg_sq, 1, n, st);                                               // V = U^seg_len
+    if ((rc = sc.get(u_bytes * chunk, (void**)&d_v))) return rc;
+    if ((rc = sc.get(sizeof(cplx) * dim * (size_t)n_seg * chunk, (void**)&d_seeds))) return rc;
+    if ((rc = sc.get(sizeof(int32_t) * chunk, (void**)&d_seg_sq))) return rc;
+    QSB_CUDA(cudaMemcpyAsync(d_seg_sq, seg_sq.data(), sizeof(int32_t) * chunk, cudaMemcpyHostToDevice, st));
+  }
+  QSB_CUDA(cudaMemcpyAsync(d_terms, staged.data(), sizeof(ExpectTerm) * staged.size(), cudaMemcpyHostToDevice, st));
+
+  int worst = QSB_OK;
+  for (int base = 0; base < n_traj; base += chunk) {
+    const int m = std::min(chunk, n_traj - base);
+    for (int i = 0; i < m; ++i) {
+      compile_small(&tables[base + i], psi0_index[base + i], &opts[base + i], 1, &descs[i]);
+      tp[2 * i] = 0.0;
+      tp[2 * i + 1] = std::ldexp(dt[dt_per_traj ? base + i : 0], -n_sq[base + i]);
+    }
+    if (any_sq) QSB_CUDA(cudaMemcpyAsync(d_sq, n_sq.data() + base, sizeof(int32_t) * m, cudaMemcpyHostToDevice, st));
+    QSB_CUDA(cudaMemcpyAsync(d_desc, descs.data(), sizeof(SmallDesc) * m, cudaMemcpyHostToDevice, st));
+    QSB_CUDA(cudaMemcpyAsync(d_t, tp.data(), sizeof(double) * 2 * m, cudaMemcpyHostToDevice, st));
+    QSB_CUDA(cudaEventRecord(sc.e0, st));
+    launch_small_columns(d_desc, m, n, d_t, d_stats, d_u, st);  // U^(1 / 2^s), one CTA per column
     QSB_CUDA(cudaGetLastError());
-    rc = launch_small_propagate(d_desc, 1, n, d_v, n_seg, nullptr, 0, st, nullptr, 1, n_seg, d_seeds);  // seeds
+    if (any_sq) {
+      launch_small_square(d_u, d_tmp, d_sq, m, n, st);
+      QSB_CUDA(cudaGetLastError());
+    }
+    if (n_seg > 1) {
+      QSB_CUDA(cudaMemcpyAsync(d_v, d_u, u_bytes * m, cudaMemcpyDeviceToDevice, st));
+      launch_small_square(d_v, d_tmp, d_seg_sq, m, n, st);                                               // V = U^seg_len
+      QSB_CUDA(cudaGetLastError());
+      rc = launch_small_propagate(d_desc, m, n, d_v, n_seg, nullptr, 0, st, nullptr, 1, n_seg, d_seeds);  // seeds
+      if (rc) return rc;
+      rc = launch_small_propagate(d_desc, m, n, d_u, n_out, nullptr, 0, st, d_seeds, n_seg, seg_len, d_states);  // every psi_k, kept
+    } else {
+      rc = launch_small_propagate(d_desc, m, n, d_u, n_out, nullptr, 0, st, nullptr, 1, n_out, d_states);  // psi_k = U psi_{k-1}, kept
+    }
     if (rc) return rc;
-    rc = launch_small_propagate(d_desc, 1, n, d_u, n_out, nullptr, 0, st, d_seeds, n_seg, seg_len, d_states);  // every psi_k, kept
-  } else {
-    rc = launch_small_propagate(d_desc, 1, n, d_u, n_out, nullptr, 0, st, nullptr, 1, n_out, d_states);  // psi_k = U psi_{k-1}, kept
+    if (obs_by_column) {  // [traj][QSB_NOBS][n_out]: one reduction per trajectory
+      for (int i = 0; i < m; ++i)
+        launch_expect(d_states + (size_t)i * n_out * dim, n_out, dim, d_terms, (int)staged.size(), column_begin,
+                      d_partials + (size_t)i * n_out * nb * 8, d_obs + (size_t)i * n_out * QSB_NOBS, 1, n_out, st);
+    } else {              // [traj][n_out][QSB_NOBS] is one run of states
+      launch_expect(d_states, (int64_t)m * n_out, dim, d_terms, (int)staged.size(), column_begin, d_partials, d_obs, QSB_NOBS, 1, st);
+    }
+    QSB_CUDA(cudaGetLastError());
+    QSB_CUDA(cudaEventRecord(sc.e1, st));
+    QSB_CUDA(cudaMemcpyAsync(hs.data(), d_stats, sizeof(SmallStats) * dim * m, cudaMemcpyDeviceToHost, st));
+    QSB_CUDA(cudaMemcpyAsync(out_obs + (size_t)base * n_out * QSB_NOBS, d_obs, sizeof(double) * QSB_NOBS * (size_t)n_out * m,
+                             cudaMemcpyDeviceToHost, st));
+    QSB_CUDA(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, sc.e0, sc.e1);
+    for (int i = 0; i < m; ++i) {
+      qsb_stats acc = {0, 0, 0, 0.0, (double)ms, 4, QSB_OK};
+      for (size_t c = 0; c < dim; ++c) {
+        const SmallStats& s = hs[(size_t)i * dim + c];
+        acc.n_accepted += s.n_accepted; acc.n_rejected += s.n_rejected; acc.n_rhs += s.n_rhs;
+        acc.last_h = s.last_h;
+        if (s.status != QSB_OK && acc.status == QSB_OK) acc.status = s.status;
+      }
+      if (stats) stats[base + i] = acc;
+      if (acc.status != QSB_OK && worst == QSB_OK) {
+        worst = acc.status;
+        g_err = "propagator of trajectory " + std::to_string(base + i) + (acc.status == QSB_ERR_NSTEPS
+                    ? ": more than nsteps internal steps inside one output interval (excess work)"
+                    : ": step size underflow");
+      }
+    }
   }
-  if (rc) return rc;
-  if (obs_by_column) launch_expect(d_states, n_out, dim, d_terms, (int)staged.size(), column_begin, d_partials, d_obs, 1, n_out, st);
-  else launch_expect(d_states, n_out, dim, d_terms, (int)staged.size(), column_begin, d_partials, d_obs, QSB_NOBS, 1, st);
-  QSB_CUDA(cudaGetLastError());
-  QSB_CUDA(cudaEventRecord(sc.e1, st));
-  QSB_CUDA(cudaMemcpyAsync(hs.data(), d_stats, sizeof(SmallStats) * dim, cudaMemcpyDeviceToHost, st));
-  QSB_CUDA(cudaMemcpyAsync(out_obs, d_obs, sizeof(double) * QSB_NOBS * (size_t)n_out, cudaMemcpyDeviceToHost, st));
-  QSB_CUDA(cudaStreamSynchronize(st));
-  float ms = 0.f;
-  cudaEventElapsedTime(&ms, sc.e0, sc.e1);
-  qsb_stats acc = {0, 0, 0, 0.0, (double)ms, 4, QSB_OK};
-  for (size_t c = 0; c < dim; ++c) {
-    acc.n_accepted += hs[c].n_accepted; acc.n_rejected += hs[c].n_rejected; acc.n_rhs += hs[c].n_rhs;
-    acc.last_h = hs[c].last_h;
-    if (hs[c].status != QSB_OK && acc.status == QSB_OK) acc.status = hs[c].status;
-  }
-  if (stats) *stats = acc;
-  if (acc.status != QSB_OK)
-    return fail(acc.status, acc.status == QSB_ERR_NSTEPS
-                                ? "propagator column: more than nsteps internal steps inside one output interval (excess work)"
-                                : "propagator column: step size underflow");
-  return QSB_OK;
+  return worst;
+}
+
+extern "C" {
+
+int qsb_propagate_expect(const qsb_table* table, uint64_t psi0_index, int64_t n_out, double dt, const qsb_solver_opts* opts,
+                         int32_t max_squarings, const qsb_pauli_term* terms, int32_t n_terms, int32_t obs_by_column,
+                         double* out_obs, qsb_stats* stats, int device) {
+  return propagate_expect_impl(1, table, &psi0_index, n_out, &dt, 0, opts, max_squarings, terms, n_terms, obs_by_column, out_obs,
+                               stats, device);
+}
+
+int qsb_propagate_expect_batch(int32_t n_traj, const qsb_table* tables, const uint64_t* psi0_index, int64_t n_out,
+                               const double* dt, int32_t dt_per_traj, const qsb_solver_opts* opts, int32_t max_squarings,
+                               const qsb_pauli_term* terms, int32_t n_terms, int32_t obs_by_column, double* out_obs,
+                               qsb_stats* stats, int device) {
+  return propagate_expect_impl(n_traj, tables, psi0_index, n_out, dt, dt_per_traj, opts, max_squarings, terms, n_terms,
+                               obs_by_column, out_obs, stats, device);
 }
 
 int qsb_session_expect(qsb_plan* p, const qsb_pauli_term* terms, int32_t n_terms, double* obs) {

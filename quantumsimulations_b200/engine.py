@@ -70,7 +70,7 @@ EXPORTS = (
     "qsb_shard_plan_create", "qsb_shard_export", "qsb_shard_connect", "qsb_shard_allgather", "qsb_shard_set_stream_barrier", "qsb_plan_local_dim", "qsb_debug_layouts", "qsb_debug_fusion",
     "qsb_local_group_create", "qsb_local_group_destroy", "qsb_local_group_member", "qsb_local_allgather", "qsb_local_stream_barrier",
     "qsb_propagate_batch", "qsb_propagate_hbm", "qsb_release_caches", "qsb_build_propagator", "qsb_debug_propagate_shape", "qsb_debug_squarings",
-    "qsb_propagate_expect", "qsb_propagate_hbm_expect", "qsb_session_expect",
+    "qsb_propagate_expect", "qsb_propagate_expect_batch", "qsb_propagate_hbm_expect", "qsb_session_expect",
 )
 
 SHARD_BLOB_BYTES = 96
@@ -114,6 +114,9 @@ def load_library() -> C.CDLL:
     lib.qsb_propagate_expect.argtypes = [C.POINTER(_Table), C.c_uint64, C.c_int64, C.c_double, C.POINTER(_Opts), C.c_int32,
                                          C.POINTER(_PauliTerm), C.c_int32, C.c_int32, dp, C.POINTER(_Stats), C.c_int]
     lib.qsb_propagate_hbm_expect.argtypes = lib.qsb_propagate_expect.argtypes
+    lib.qsb_propagate_expect_batch.argtypes = [C.c_int32, C.POINTER(_Table), C.POINTER(C.c_uint64), C.c_int64, dp, C.c_int32,
+                                               C.POINTER(_Opts), C.c_int32, C.POINTER(_PauliTerm), C.c_int32, C.c_int32, dp,
+                                               C.POINTER(_Stats), C.c_int]
     lib.qsb_session_expect.argtypes = [vp, C.POINTER(_PauliTerm), C.c_int32, dp]
     lib.qsb_debug_propagate_shape.argtypes = [C.c_int32, C.POINTER(C.c_int32)]
     lib.qsb_apply_h.argtypes = [vp, dp, dp]
@@ -568,6 +571,36 @@ def propagate_expect(table: SpinTable, n_out: int, dt: float, opts: SolverOption
     _check(fn(C.byref(holder.c), table.psi0_index, int(n_out), float(dt), C.byref(copts), _max_squarings(max_squarings),
               cterms, len(cterms), 1 if by_column else 0, _dptr(obs), C.byref(st), int(device)))
     return obs, Stats.from_c(st)
+
+
+def propagate_expect_batch(tables: Sequence[SpinTable], n_out: int, dt, opts: Sequence[SolverOptions], device: int = 0,
+                           max_squarings: Optional[int] = None, by_column: bool = False, terms=None):
+    """``propagate_expect`` for many trajectories of equal n <= 10 that share one list of Pauli strings (``terms``,
+    default ``tables[0].pauli_terms``; a sweep's trajectories do) - qsb_propagate_expect_batch.  ``dt`` as in
+    ``propagate_batch``.  Returns (obs [n_traj, n_out, NOBS] or [n_traj, NOBS, n_out] with ``by_column``, [Stats])."""
+    lib = load_library()
+    n = len(tables)
+    if n == 0:
+        return np.empty((0, 0, NOBS)), []
+    terms = tables[0].pauli_terms if terms is None else terms
+    if terms is None:
+        raise ValueError("the tables carry no Pauli-string observables")
+    cterms = _pauli_terms(terms)
+    dts = np.ascontiguousarray(np.atleast_1d(dt), dtype=np.float64)
+    if dts.shape not in ((1,), (n,)):
+        raise ValueError("dt must be a scalar or one value per trajectory")
+    holders = [_TableHolder(t) for t in tables]
+    ctabs = (_Table * n)(*[h.c for h in holders])
+    psi0 = (C.c_uint64 * n)(*[t.psi0_index for t in tables])
+    copts = (_Opts * n)(*[o.to_c() for o in opts])
+    cstats = (_Stats * n)()
+    obs = np.empty((n, NOBS, int(n_out)) if by_column else (n, int(n_out), NOBS), dtype=np.float64)
+    code = lib.qsb_propagate_expect_batch(n, ctabs, psi0, int(n_out), _dptr(dts), 1 if (dts.shape == (n,) and n > 1) else 0,
+                                          copts, _max_squarings(max_squarings), cterms, len(cterms), 1 if by_column else 0,
+                                          _dptr(obs), cstats, int(device))
+    stats = [Stats.from_c(s) for s in cstats]
+    _check(code)
+    return obs, stats
 
 
 def build_propagator(table: SpinTable, dt: float, opts: SolverOptions, device: int = 0,

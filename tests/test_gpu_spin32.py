@@ -233,3 +233,27 @@ def test_spin_three_half_through_the_hbm_propagator(golden_spin32, name):
     dev = max(float(np.max(np.abs(out[k] - gold[f"{name}/{k}"]))) for k in KEYS)
     print(f"{name} via the HBM propagator: path {st.path}, max dev {dev:.2e}, {st.device_ms:.1f} ms")
     assert dev < 1e-6 and st.path == 3
+
+
+def test_batched_string_trajectories_equal_single_calls(monkeypatch):
+    """qsb_propagate_expect_batch (what a spin-3/2 sweep runs: one pass for all trajectories that share bits, grid length
+    and strings) against one qsb_propagate_expect call per trajectory: bitwise, also when the batch is cut into chunks."""
+    import dataclasses
+
+    import quantumsimulations_b200 as q
+    from bench import sweep_params
+    from quantumsimulations_b200 import api, engine
+
+    plist = [dataclasses.replace(sweep_params(4, d, variant=v, t_final=6e-3, steps=400), is_spin_three_half=True)
+             for d in (0.0, 40e3, 90e3) for v in ("center_on", "center_off")][:5]
+    tabs = [q.compile_table(p) for p in plist]
+    opts = [api._options_from(p, None)[0] for p in plist]
+    dts = [p.t_final / (p.steps - 1) * (1.0 + 0.01 * i) for i, p in enumerate(plist)]
+    single = np.stack([engine.propagate_expect(tb, 400, dt, o)[0] for tb, dt, o in zip(tabs, dts, opts)])
+    batch, stats = engine.propagate_expect_batch(tabs, 400, dts, opts)
+    by_col, _ = engine.propagate_expect_batch(tabs, 400, dts, opts, by_column=True)
+    monkeypatch.setenv("QSB200_PROP_CHUNK", "2")
+    chunked, _ = engine.propagate_expect_batch(tabs, 400, dts, opts)
+    print(f"batch of 5: max |batch - single| = {float(np.max(np.abs(batch - single))):.1e}, {stats[0].device_ms:.2f} ms")
+    assert np.array_equal(batch, single) and np.array_equal(chunked, single)
+    assert np.array_equal(by_col, np.swapaxes(single, 1, 2)) and [s.path for s in stats] == [4] * 5
