@@ -582,9 +582,14 @@ def propagate_expect_batch(tables: Sequence[SpinTable], n_out: int, dt, opts: Se
     n = len(tables)
     if n == 0:
         return np.empty((0, 0, NOBS)), []
-    terms = tables[0].pauli_terms if terms is None else terms
     if terms is None:
-        raise ValueError("the tables carry no Pauli-string observables")
+        terms = tables[0].pauli_terms
+        if terms is None:
+            raise ValueError("the tables carry no Pauli-string observables")
+        if any(t.pauli_terms != terms for t in tables[1:]):
+            raise ValueError("one call reduces ONE list of Pauli strings: group the tables by their pauli_terms")
+    if any(t.n != tables[0].n for t in tables[1:]):
+        raise ValueError("the tables of one call must have the same number of index bits")
     cterms = _pauli_terms(terms)
     dts = np.ascontiguousarray(np.atleast_1d(dt), dtype=np.float64)
     if dts.shape not in ((1,), (n,)):

@@ -165,6 +165,13 @@ def test_pauli_entry_points_validate_before_touching_a_device():
     assert q.api.resolve_method(q.DipolarRareParams(n_sea=9), "taylor") == ("taylor", False)
     assert q.api.resolve_method(q.DipolarRareParams(n_sea=8), "dp5") == ("dp5", True)
     assert q.api.resolve_method(q.DipolarRareParams(n_sea=9), None) == ("taylor", False)
+    other_phase = q.compile_table(q.DipolarRareParams(n_sea=3, phi_rare=0.5))
+    with pytest.raises(ValueError, match="ONE list of Pauli strings"):
+        engine.propagate_expect_batch([tb, other_phase], 5, 1e-3, [o, o])
+    with pytest.raises(ValueError, match="same number of index bits"):
+        engine.propagate_expect_batch([tb, q.compile_table(q.DipolarRareParams(n_sea=4))], 5, 1e-3, [o, o], terms=tb.pauli_terms)
     if engine.device_count() == 0:
         with pytest.raises(engine.EngineError, match="no CUDA device"):
             q.simulate_rare(q.DipolarRareParams(n_sea=3))
+        with pytest.raises(engine.EngineError, match="no CUDA device"):
+            q.simulate_rare_batch([q.DipolarRareParams(n_sea=3), q.DipolarRareParams(n_sea=3, drive_sea=True, B1_sea=1e-3)])
